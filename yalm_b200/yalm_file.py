@@ -1,0 +1,342 @@
+"""Reader / writer / random-init generator for `.yalm` checkpoints.
+
+The container is the safetensors layout the reference writes with
+`safetensors.torch.save_file` (reference convert.py:248) and parses in
+src/codec.cpp:116-175: `u64 LE header_len | JSON header | raw tensor bytes`,
+all `__metadata__` values strings (src/model.cpp:17-75).
+
+fp8 is net-new (the reference has no fp8 arithmetic).  Our
+superset: metadata `dtype: "fp8"`, weight tensors `F8_E4M3`, and for every
+such tensor `<name>` a companion `<name>.scale` F32 tensor holding one scale
+per output row (shape = weight shape minus its last axis):
+`w[.., i, j] = scale[.., i] * e4m3[.., i, j]`.
+
+Pure numpy (no torch) so the CPU tests stay light; `random_model(...,
+device="cuda")` optionally draws the big tensors with torch on a GPU for the
+full-size bench models.
+"""
+from __future__ import annotations
+
+import json
+import struct
+from dataclasses import dataclass, asdict, field
+
+import numpy as np
+
+_NP_OF = {"F32": np.float32, "F16": np.float16, "F8_E4M3": np.uint8, "F8_E5M2": np.uint8,
+          "U8": np.uint8, "I32": np.int32}
+
+
+@dataclass
+class Arch:
+    """Hyper-parameters = the reference's Config fields (src/model.h:41-68)."""
+    dim: int
+    hidden_dim: int
+    head_dim: int
+    n_layers: int
+    n_heads: int
+    n_kv_heads: int
+    vocab_size: int
+    max_seq_len: int = 4096
+    rope_theta: float = 10000.0
+    rotary_dim: int = 0            # 0 -> head_dim
+    norm_eps: float = 1e-5
+    act_type: str = "silu"
+    qkv_clip: float | None = None
+    n_experts: int = 0
+    n_experts_active: int = 0
+    tied: bool = False
+    name: str = "custom"
+
+    def __post_init__(self):
+        if self.rotary_dim == 0:
+            self.rotary_dim = self.head_dim
+
+
+# The five BASELINE.json configs (+ slim variants for CPU-sized parity runs).
+ARCHS = {
+    "llama-3.2-1b": Arch(2048, 8192, 64, 16, 32, 8, 128256, 131072, 500000.0, tied=True, name="llama-3.2-1b"),
+    "mistral-7b": Arch(4096, 14336, 128, 32, 32, 8, 32000, 32768, 1000000.0, name="mistral-7b"),
+    "mixtral-8x7b": Arch(4096, 14336, 128, 32, 32, 8, 32000, 32768, 1000000.0, n_experts=8,
+                         n_experts_active=2, name="mixtral-8x7b"),
+    "llama-3-70b": Arch(8192, 28672, 128, 80, 64, 8, 128256, 8192, 500000.0, name="llama-3-70b"),
+    # small shapes for tests (keep every divisibility property of the big ones)
+    "tiny": Arch(256, 512, 32, 2, 8, 2, 512, 64, 10000.0, name="tiny"),
+    "tiny-moe": Arch(256, 512, 32, 2, 8, 2, 512, 64, 10000.0, n_experts=4, n_experts_active=2,
+                     name="tiny-moe"),
+    "tiny-gelu-clip": Arch(256, 512, 32, 2, 8, 4, 512, 64, 10000.0, act_type="gelu", qkv_clip=1.5,
+                           rotary_dim=16, tied=True, name="tiny-gelu-clip"),
+}
+
+
+def slim(arch: Arch, n_layers: int, vocab_size: int | None = None) -> Arch:
+    d = asdict(arch)
+    d["n_layers"] = n_layers
+    if vocab_size:
+        d["vocab_size"] = vocab_size
+    d["name"] = f"{arch.name}-slim{n_layers}"
+    return Arch(**d)
+
+
+def metadata_of(arch: Arch, dtype: str) -> dict:
+    md = {
+        "arch": arch.name, "dtype": dtype,
+        "dim": arch.dim, "hidden_dim": arch.hidden_dim, "head_dim": arch.head_dim,
+        "n_layers": arch.n_layers, "n_heads": arch.n_heads, "n_kv_heads": arch.n_kv_heads,
+        "vocab_size": arch.vocab_size, "max_seq_len": arch.max_seq_len,
+        "bos_token_id": 1, "eos_token_id": 2,
+        "rope_theta": arch.rope_theta, "rotary_dim": arch.rotary_dim,
+        "norm_eps": arch.norm_eps, "norm_type": "rmsnorm", "act_type": arch.act_type,
+    }
+    if arch.qkv_clip is not None:
+        md["qkv_clip"] = arch.qkv_clip
+    if arch.n_experts:
+        md["n_experts"] = arch.n_experts
+        md["n_experts_active"] = arch.n_experts_active
+    return {k: str(v) for k, v in md.items()}
+
+
+def tensor_plan(arch: Arch):
+    """(name, shape, kind) for every tensor, kind in {"weight","norm","embed"}; names and shapes per
+    src/model.cpp:352-377 / convert.py:171-201."""
+    a = arch
+    q_dim, kv_dim = a.n_heads * a.head_dim, a.n_kv_heads * a.head_dim
+    plan = [("model.embed.weight", (a.vocab_size, a.dim), "embed")]
+    e = (a.n_experts,) if a.n_experts else ()
+    for l in range(a.n_layers):
+        p = f"model.layers.{l}."
+        plan += [
+            (p + "attn.norm.weight", (a.dim,), "norm"),
+            (p + "attn.wq.weight", (q_dim, a.dim), "weight"),
+            (p + "attn.wk.weight", (kv_dim, a.dim), "weight"),
+            (p + "attn.wv.weight", (kv_dim, a.dim), "weight"),
+            (p + "attn.wo.weight", (a.dim, q_dim), "weight"),
+            (p + "mlp.norm.weight", (a.dim,), "norm"),
+            (p + "mlp.w1.weight", e + (a.hidden_dim, a.dim), "weight"),
+            (p + "mlp.w2.weight", e + (a.dim, a.hidden_dim), "weight"),
+            (p + "mlp.w3.weight", e + (a.hidden_dim, a.dim), "weight"),
+        ]
+        if a.n_experts:
+            plan.append((p + "moegate.weight", (a.n_experts, a.dim), "weight"))
+    plan.append(("model.norm.weight", (a.dim,), "norm"))
+    if not a.tied:
+        plan.append(("model.output.weight", (a.vocab_size, a.dim), "weight"))
+    return plan
+
+
+# ----------------------------------------------------------------------------------------------
+# fp8 e4m3 (the "fn" flavour: no inf, max 448, 0x7f/0xff = NaN) <-> float32, in numpy.
+# ----------------------------------------------------------------------------------------------
+def e4m3_decode_table() -> np.ndarray:
+    c = np.arange(256, dtype=np.int32)
+    e, m = (c >> 3) & 15, c & 7
+    mag = np.where(e == 0, m * 2.0 ** -9, (1.0 + m / 8.0) * np.exp2((e - 7).astype(np.float64)))
+    mag = np.where((c & 0x7F) == 0x7F, np.nan, mag)
+    return np.where(c & 0x80, -mag, mag).astype(np.float32)
+
+
+def e4m3_to_f32(codes: np.ndarray) -> np.ndarray:
+    return e4m3_decode_table()[codes.astype(np.uint8)]
+
+
+def f32_to_e4m3(x: np.ndarray) -> np.ndarray:
+    """Round-to-nearest-even, saturating at +-448."""
+    x = np.asarray(x, dtype=np.float32)
+    sign = (np.signbit(x)).astype(np.uint8) << 7
+    a = np.minimum(np.abs(x).astype(np.float64), 448.0)
+    with np.errstate(divide="ignore"):
+        e = np.floor(np.log2(np.where(a > 0, a, 1.0))).astype(np.int32)
+    e = np.clip(e, -6, 8)
+    normal = a >= 2.0 ** -6
+    q_n = np.rint((a / np.exp2(e.astype(np.float64)) - 1.0) * 8.0).astype(np.int32)
+    carry = q_n == 8
+    e_n = np.where(carry, e + 1, e)
+    q_n = np.where(carry, 0, q_n)
+    code_n = ((e_n + 7) << 3) | q_n
+    code_s = np.rint(a / 2.0 ** -9).astype(np.int32)        # 0..8; 8 == smallest normal (0x08)
+    code = np.where(normal, code_n, code_s)
+    code = np.minimum(code, 0x7E)
+    return (code.astype(np.uint8) | sign).astype(np.uint8)
+
+
+def quantize_rows_e4m3(w: np.ndarray):
+    """Per-output-row scale so each row's max |w| maps to 448. Returns (codes u8, scale f32)."""
+    w = np.asarray(w, dtype=np.float32)
+    amax = np.max(np.abs(w), axis=-1)
+    scale = np.where(amax > 0, amax / 448.0, 1.0).astype(np.float32)
+    codes = f32_to_e4m3(w / scale[..., None])
+    return codes, scale
+
+
+# ----------------------------------------------------------------------------------------------
+# container I/O
+# ----------------------------------------------------------------------------------------------
+def _st_dtype(arr: np.ndarray, hint: str | None) -> str:
+    if hint:
+        return hint
+    return {np.dtype(np.float32): "F32", np.dtype(np.float16): "F16", np.dtype(np.uint8): "U8",
+            np.dtype(np.int32): "I32"}[arr.dtype]
+
+
+def build_image(tensors: dict, metadata: dict, dtype_hints: dict | None = None) -> bytearray:
+    """Serialise {name: ndarray} to one in-memory .yalm image (tensor data 64-byte aligned)."""
+    dtype_hints = dtype_hints or {}
+    header, off = {"__metadata__": metadata}, 0
+    order = list(tensors)
+    for name in order:
+        arr = tensors[name]
+        off = (off + 63) // 64 * 64
+        header[name] = {"dtype": _st_dtype(arr, dtype_hints.get(name)), "shape": list(arr.shape),
+                        "data_offsets": [off, off + arr.nbytes]}
+        off += arr.nbytes
+    hj = json.dumps(header, separators=(",", ":")).encode()
+    hj += b" " * ((-(8 + len(hj))) % 64)                     # data section starts 64-byte aligned
+    img = bytearray(8 + len(hj) + off)
+    img[:8] = struct.pack("<Q", len(hj))
+    img[8:8 + len(hj)] = hj
+    base = 8 + len(hj)
+    view = memoryview(img)
+    for name in order:
+        s, e = header[name]["data_offsets"]
+        view[base + s: base + e] = np.ascontiguousarray(tensors[name]).view(np.uint8).reshape(-1).data
+    return img
+
+
+def save(path: str, tensors: dict, metadata: dict, dtype_hints: dict | None = None) -> None:
+    with open(path, "wb") as f:
+        f.write(build_image(tensors, metadata, dtype_hints))
+
+
+def load(path_or_bytes):
+    """-> (metadata dict, {name: ndarray view}, {name: safetensors dtype string})."""
+    if isinstance(path_or_bytes, (bytes, bytearray, memoryview)):
+        buf = np.frombuffer(path_or_bytes, dtype=np.uint8)
+    else:
+        buf = np.memmap(path_or_bytes, dtype=np.uint8, mode="r")
+    (hlen,) = struct.unpack("<Q", bytes(buf[:8]))
+    header = json.loads(bytes(buf[8:8 + hlen]))
+    base = 8 + hlen
+    md = header.pop("__metadata__", {})
+    out, kinds = {}, {}
+    for name, info in header.items():
+        s, e = info["data_offsets"]
+        out[name] = buf[base + s: base + e].view(_NP_OF[info["dtype"]]).reshape(info["shape"])
+        kinds[name] = info["dtype"]
+    return md, out, kinds
+
+
+# ----------------------------------------------------------------------------------------------
+# seeded random-init models
+# ----------------------------------------------------------------------------------------------
+_ST_OF_DTYPE = {"fp32": "F32", "fp16": "F16", "fp8": "F8_E4M3"}
+
+
+def synthetic_tokens(vocab_size: int) -> np.ndarray:
+    """`tokenizer.tokens`: NUL-separated UTF-8 pieces (src/tokenizer.cpp:11-19), vocab_size unique ones."""
+    pieces = ["<unk>", "<s>", "</s>"] + [f" t{i}" for i in range(3, vocab_size)]
+    return np.frombuffer(("\0".join(pieces[:vocab_size]) + "\0").encode(), dtype=np.uint8).copy()
+
+
+def _std_of(name: str, shape, kind: str, lm_scale: float) -> float:
+    if kind == "embed":
+        return 1.0
+    if name == "model.output.weight":
+        return lm_scale / np.sqrt(shape[-1])
+    return 1.0 / np.sqrt(shape[-1])
+
+
+def random_tensors(arch: Arch, dtype: str = "fp16", seed: int = 0, lm_scale: float = 4.0,
+                   device: str = "cpu"):
+    """Yield (name, ndarray, safetensors-dtype) for a seeded random-init model of `arch`.
+
+    weights ~ N(0, 1/fan_in); embedding ~ N(0,1); norm weights 1 + 0.1 N(0,1); LM head scaled by
+    `lm_scale` so greedy argmax margins are decisive (hard parts).  Every tensor
+    has its own generator seeded from (seed, index) so layouts can be produced in any order.
+    device="cuda" draws the large tensors with torch on the GPU (bench-size models)."""
+    st = _ST_OF_DTYPE[dtype]
+    for idx, (name, shape, kind) in enumerate(tensor_plan(arch)):
+        if kind == "norm":
+            rng = np.random.default_rng([seed, idx])
+            yield name, (1.0 + 0.1 * rng.standard_normal(shape, dtype=np.float32)).astype(np.float32), "F32"
+            continue
+        std = _std_of(name, shape, kind, lm_scale)
+        n = int(np.prod(shape))
+        if device == "cuda" and n >= (1 << 20):
+            import torch
+            g = torch.Generator(device="cuda")
+            g.manual_seed(seed * 1000003 + idx)
+            w = torch.randn(shape, generator=g, device="cuda", dtype=torch.float32) * std
+            if dtype == "fp32":
+                yield name, w.cpu().numpy(), "F32"
+            elif dtype == "fp16":
+                yield name, w.to(torch.float16).cpu().numpy(), "F16"
+            else:
+                amax = w.abs().amax(dim=-1)
+                scale = torch.where(amax > 0, amax / 448.0, torch.ones_like(amax))
+                codes = (w / scale[..., None]).to(torch.float8_e4m3fn).view(torch.uint8)
+                yield name, codes.cpu().numpy(), "F8_E4M3"
+                yield name + ".scale", scale.cpu().numpy().astype(np.float32), "F32"
+            del w
+            continue
+        rng = np.random.default_rng([seed, idx])
+        w = rng.standard_normal(shape, dtype=np.float32) * np.float32(std)
+        if dtype == "fp32":
+            yield name, w, "F32"
+        elif dtype == "fp16":
+            yield name, w.astype(np.float16), "F16"
+        else:
+            codes, scale = quantize_rows_e4m3(w)
+            yield name, codes, "F8_E4M3"
+            yield name + ".scale", scale, "F32"
+    yield "tokenizer.tokens", synthetic_tokens(arch.vocab_size), "U8"
+
+
+def random_model(arch: Arch, dtype: str = "fp16", seed: int = 0, lm_scale: float = 4.0,
+                 device: str = "cpu") -> bytearray:
+    """One in-memory .yalm image of a seeded random-init model (small/medium models)."""
+    tensors, hints = {}, {}
+    for name, arr, st in random_tensors(arch, dtype, seed, lm_scale, device):
+        tensors[name], hints[name] = arr, st
+    return build_image(tensors, metadata_of(arch, dtype), hints)
+
+
+def write_random_model(path: str, arch: Arch, dtype: str = "fp16", seed: int = 0, lm_scale: float = 4.0,
+                       device: str = "cpu") -> None:
+    with open(path, "wb") as f:
+        f.write(random_model(arch, dtype, seed, lm_scale, device))
+
+
+def dequantized_fp32_image(image) -> bytearray:
+    """fp16/fp8 model image -> the same model as an fp32 `.yalm` (dtype "fp32", no scales).  This is
+    what the reference CPU fp32 path is run on to serve as the fp8 oracle."""
+    md, tensors, kinds = load(image)
+    out, hints = {}, {}
+    for name, arr in tensors.items():
+        if name.endswith(".scale"):
+            continue
+        k = kinds[name]
+        if k == "F8_E4M3":
+            out[name] = (e4m3_to_f32(arr) * tensors[name + ".scale"][..., None]).astype(np.float32)
+        elif k == "F16":
+            out[name] = arr.astype(np.float32)
+        else:
+            out[name] = np.array(arr)
+        hints[name] = "U8" if k == "U8" else "F32"
+    md = dict(md)
+    md["dtype"] = "fp32"
+    return build_image(out, md, hints)
+
+
+def weight_bytes_per_token(arch: Arch, dtype: str) -> int:
+    """Algorithmic weight bytes one decoded token must read (SURVEY.md section 8(d) formula)."""
+    ws = {"fp32": 4, "fp16": 2, "fp8": 1}[dtype]
+    a = arch
+    q_dim, kv_dim = a.n_heads * a.head_dim, a.n_kv_heads * a.head_dim
+    ffn = (a.n_experts * a.dim + a.n_experts_active * 3 * a.dim * a.hidden_dim) if a.n_experts \
+        else 3 * a.dim * a.hidden_dim
+    per_layer = 2 * q_dim * a.dim + 2 * kv_dim * a.dim + ffn
+    return ws * (a.n_layers * per_layer + a.vocab_size * a.dim) + 4 * (2 * a.n_layers + 1) * a.dim + ws * a.dim
+
+
+def kv_bytes_per_token(arch: Arch, kv_len: int) -> int:
+    return 2 * kv_len * arch.n_kv_heads * arch.head_dim * 2 * arch.n_layers
