@@ -1,0 +1,172 @@
+/* yalm_b200 — C ABI of the B200-native token-generation forward pass.
+ *
+ * This is the drop-in boundary for xiaguan/yalm's `-d cuda` path.  Three layers:
+ *
+ *  (1) the seven memory/stream helpers the reference already exports from src/infer.cu and declares
+ *      in src/model.h:33-39 — same names, same meaning;
+ *  (2) one entry point per fused device op (device pointers + sizes + stream, returns the
+ *      cudaError_t as int) — what replaces the kernel launches inside Block::_block_cuda
+ *      (src/infer.cu:699-888) and Model::_forward_cuda_build_graph (src/infer.cu:1041-1128);
+ *  (3) host-pointer test entry points with the semantics of the reference's "exposed for tests"
+ *      functions matmul_cuda / mha_cuda / ffn_cuda (src/model.h:353-384, src/infer.cu:890-1007),
+ *      and opaque-handle wrappers over Model / InferenceState (src/model.h:84-327) for bindings
+ *      that cannot consume C++ classes (ctypes, cgo, JNI).
+ *
+ * Error convention: layer (1) keeps the reference's (CUDA failure -> message on stderr + abort(),
+ * src/infer.cu:13-31).  Layers (2)/(3) return 0 on success, a cudaError_t or a negative YALM_E*
+ * code otherwise, and never fall back to a CPU path.
+ */
+#ifndef YALM_B200_H
+#define YALM_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* Weight element types; values are the reference's DType enum (src/codec.h:15-25). */
+#define YALM_F32 0
+#define YALM_F16 1
+#define YALM_F8E5M2 3 /* parsed, but no arithmetic exists for it: rejected */
+#define YALM_F8E4M3 4 /* net-new: e4m3 codes + one fp32 scale per output row */
+
+#define YALM_ACT_GELU 0 /* ActivationType, src/model.h:14-17 */
+#define YALM_ACT_SILU 1
+
+#define YALM_MODE_HYDRATE 0 /* InferenceMode, src/model.h:28-31 */
+#define YALM_MODE_LOGITS 1
+
+#define YALM_EINVAL (-1)  /* unsupported shape / dtype / null pointer */
+#define YALM_ENOGPU (-2)  /* no CUDA device: there is deliberately no CPU fallback */
+#define YALM_EFORMAT (-3) /* bad .yalm container */
+
+typedef void *yalm_stream_t; /* cudaStream_t */
+
+/* ---- (1) reference C ABI, src/model.h:33-39 / src/infer.cu:59-90 ------------------------------ */
+void *upload_cuda(void *host, size_t size);            /* cudaMalloc + H2D, returns device pointer */
+void *download_cuda_raw(void *device, size_t size);    /* C-clean form of download_cuda (the reference's takes a std::string) */
+void register_cuda_host(void *host, size_t size);
+void free_cuda(void *device);
+void unregister_cuda_host(void *host);
+void set_cuda_device(int device);
+void init_cuda_stream(yalm_stream_t *stream);
+
+/* ---- (2) fused device ops ---------------------------------------------------------------------
+ * Decode control block `ctl` (device, 8 ints): [0] token [1] pos [2] kv_sink [3] kv_pos [4] kv_len
+ * [5] step counter [6..7] reserved.  Keeping pos/kv_* in device memory is what lets one CUDA graph be
+ * replayed for every token with zero per-token node updates (the reference patches 129-161 kernel
+ * nodes per token, src/infer.cu:1146-1163).                                                        */
+#define YALM_CTL_INTS 8
+
+/* x = float(E[token,:]) (src/infer.cu:622-640) and derive the KV ring position from pos
+ * (src/infer.cu:1081-1083: kv_sink/kv_pos/kv_len with KV_SINKS = 2).  If host_token_pos != NULL it
+ * is a device-mapped pinned int[2] {token,pos} read at execution time; if NULL, ctl[0..1] are taken
+ * as already set on the device (by yalm_argmax_advance). */
+int yalm_embed(float *x, const void *table, const float *row_scale, int dim, int dtype, int *ctl,
+               const int *host_token_pos, int max_seq_len, yalm_stream_t s);
+
+/* rmsnorm -> q,k,v GEMVs -> clip -> RoPE(q,k) -> fp16 KV append at ctl.kv_pos -> sink re-rotation.
+ * Replaces rmsnorm + fused_qkv_matmul_clip + fused_rope_and_cache_update + rotate_sink_tokens
+ * (src/infer.cu:526-539, 291-336, 642-697).  Weights are (out,in) row-major, y = W x. */
+int yalm_qkv_rope_append(float *q_out, uint16_t *key_cache, uint16_t *value_cache, const float *x,
+                         const float *rms_weight, const void *wq, const void *wk, const void *wv,
+                         const float *sq, const float *sk, const float *sv, int dim, int n_heads, int n_kv_heads,
+                         int head_dim, int rotary_dim, float rope_theta, float norm_eps, float qkv_clip,
+                         int dtype, const int *ctl, yalm_stream_t s);
+
+/* Split-K flash-decode GQA attention over the fp16 KV ring: replaces attn_dot + attn_softmax +
+ * att_mix (src/infer.cu:338-524).  `workspace` holds the per-split partials; size from
+ * yalm_attn_workspace_bytes().  out is (n_heads*head_dim) fp32. */
+size_t yalm_attn_workspace_bytes(int n_heads, int n_kv_heads, int head_dim);
+int yalm_attn_decode(float *out, const uint16_t *key_cache, const uint16_t *value_cache, const float *q,
+                     void *workspace, int n_heads, int n_kv_heads, int head_dim, const int *ctl, yalm_stream_t s);
+
+/* out[i] = (residual ? residual[i] : 0) + sum_k aw[k] * (W[e_k] v_k)[i]   (wo and w2 + residual:
+ * fused_matmul_add_residuals, src/infer.cu:270-288; MoE mix: src/infer.cpp:377-383).
+ * Dense: n_active = 1, active_e = active_w = NULL.  MoE: expert e's matrix starts at
+ * w + e*d*n elements, its scales at scale + e*d, and v_k = v + k*n. */
+int yalm_gemv_residual(float *out, const float *residual, const float *v, const void *w, const float *scale, int n,
+                       int d, int dtype, int n_active, const int *active_e, const float *active_w,
+                       yalm_stream_t s);
+
+/* rmsnorm -> [router GEMV + top-k gate] -> hb[k,i] = act(W1[e_k] xb)[i] * (W3[e_k] xb)[i].
+ * Replaces rmsnorm + fused_ffn_w1_w3_glu_act (src/infer.cu:598-620) and, for MoE, the CPU-only
+ * router (src/infer.cpp:100-132, 347-349).  Dense: n_experts = 0, gate = NULL; hb is (hidden).
+ * MoE: hb is (n_active, hidden); active_e/active_w (device, n_active) receive the selection. */
+int yalm_ffn_glu(float *hb, const float *x, const float *rms_weight, const void *w1, const void *w3,
+                 const float *s1, const float *s3, const void *gate, const float *sgate, int dim, int hidden_dim,
+                 int act, float norm_eps, int dtype, int n_experts, int n_active, int *active_e,
+                 float *active_w, float *moe_logits, yalm_stream_t s);
+
+/* logits = Wcls rmsnorm(x)  (final rmsnorm + matmul_wide, src/infer.cu:1097-1126).  logits may be
+ * device memory or device-mapped host memory. */
+int yalm_lm_head(float *logits, const float *x, const float *rms_weight, const void *wcls, const float *scale,
+                 int dim, int vocab, float norm_eps, int dtype, yalm_stream_t s);
+
+/* Greedy on device with Sampler::sample_argmax's first-max rule (src/sampler.cpp:27-38): writes the
+ * arg-max to tokens_out[ctl.step], then ctl.token = argmax, ctl.pos += 1, ring position re-derived. */
+int yalm_argmax_advance(const float *logits, int vocab, int *ctl, int max_seq_len, int *tokens_out,
+                        yalm_stream_t s);
+
+/* Bare GEMV xout = W x (matmul<T>, src/infer.cu:234-248), device pointers. */
+int yalm_gemv(float *xout, const float *x, const void *w, const float *scale, int n, int d, int dtype,
+              yalm_stream_t s);
+
+/* ---- (3a) host-pointer test entry points (src/infer.cu:890-1007 semantics) ------------------- */
+int yalm_matmul_host(float *xout, const float *x, const void *w, const float *scale, int n, int d, int dtype);
+int yalm_mha_host(float *xout, float *att, const uint16_t *kb, const uint16_t *vb, const float *q, int head_dim,
+                  int kv_len, int max_seq_len, int n_heads, int n_kv_heads);
+int yalm_ffn_host(float *xout, const float *x, const void *w1, const void *w2, const void *w3, const float *s1,
+                  const float *s2, const float *s3, int hidden_dim, int dim, int act, int dtype);
+/* Same ops timed on the device: `iters` launches after `warmup`, returns mean microseconds per
+ * launch (CUDA events) in *usec.  This is what `./build/test -k <name>` prints. */
+int yalm_bench_op(const char *name, int iters, int warmup, double *usec, double *bytes);
+
+/* ---- (3b) opaque handles over Model / InferenceState ------------------------------------------ */
+typedef struct yalm_model yalm_model;
+typedef struct yalm_state yalm_state;
+
+/* `context` = the reference's -T (0: min(metadata max_seq_len, 4096), src/model.cpp:31-36). */
+int yalm_model_open_file(const char *path, int context, yalm_model **out);
+/* Image must stay valid until yalm_model_cuda() has returned. */
+int yalm_model_open_memory(const void *image, size_t size, int context, yalm_model **out);
+/* Tensor-parallel shard `tp_rank` of `tp_size` (1 = whole model) is uploaded to `device`. */
+int yalm_model_cuda(yalm_model *m, int device, int tp_rank, int tp_size);
+void yalm_model_close(yalm_model *m);
+/* out[16]: dim, hidden_dim, head_dim, n_layers, n_heads, n_kv_heads, vocab_size, max_seq_len,
+ * rotary_dim, n_experts, n_experts_active, weight dtype, act, tp_rank, tp_size, reserved */
+void yalm_model_config(const yalm_model *m, int *out);
+size_t yalm_model_device_bytes(const yalm_model *m);
+
+int yalm_state_new(yalm_model *m, yalm_state **out);
+void yalm_state_free(yalm_state *s);
+/* Model::forward (src/model.cpp:396-407). After a YALM_MODE_LOGITS call returns, yalm_logits() is valid. */
+int yalm_forward(yalm_model *m, yalm_state *s, int token, int pos, int mode);
+float *yalm_logits(yalm_state *s); /* host, vocab_size fp32 */
+/* n_gen greedy steps entirely on the device starting from (token,pos): per step forward + argmax;
+ * tokens_out (host, n_gen ints) gets the generated ids.  If logits_out != NULL (host, n_gen*vocab)
+ * each step's logits are copied back too (parity mode).  *device_ms (optional) = CUDA-event time. */
+int yalm_generate_greedy(yalm_model *m, yalm_state *s, int token, int pos, int n_gen, int *tokens_out,
+                         float *logits_out, float *device_ms);
+/* Debug/parity taps: copy a device activation or one layer's KV rows to the host.
+ * which: 0 x, 1 xb2(attn out), 2 hb, 3 q, 4 key_cache(layer), 5 value_cache(layer),
+ * 6 active_experts (int), 7 active_experts_weights */
+int yalm_state_read(yalm_model *m, yalm_state *s, int which, int layer, void *dst, size_t bytes);
+/* Number of kernel launches one forward pass issues in `mode` (for bench.py's gpu_launches). */
+int yalm_forward_launches(const yalm_model *m, int mode);
+
+/* Tensor-parallel plumbing (one process per GPU).  The 128-byte NCCL unique id is created by rank 0
+ * with yalm_tp_unique_id() and distributed by the caller (torch.distributed / MPI / files). */
+int yalm_tp_unique_id(void *id128);
+int yalm_tp_init(const void *id128, int rank, int world);
+void yalm_tp_finalize(void);
+
+const char *yalm_error_string(int code);
+const char *yalm_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* YALM_B200_H */
