@@ -61,11 +61,11 @@ void init_cuda_stream(yalm_stream_t *stream);
 #define YALM_CTL_INTS 8
 
 /* x = float(E[token,:]) (src/infer.cu:622-640) and derive the KV ring position from pos
- * (src/infer.cu:1081-1083: kv_sink/kv_pos/kv_len with KV_SINKS = 2).  If host_token_pos != NULL it
- * is a device-mapped pinned int[2] {token,pos} read at execution time; if NULL, ctl[0..1] are taken
- * as already set on the device (by yalm_argmax_advance). */
-int yalm_embed(float *x, const void *table, const float *row_scale, int dim, int dtype, int *ctl,
-               const int *host_token_pos, int max_seq_len, yalm_stream_t s);
+ * (src/infer.cu:1081-1083: kv_sink/kv_pos/kv_len with KV_SINKS = 2) into ctl.  token >= 0: token and
+ * pos are taken from the arguments (copied at launch, so back-to-back calls never race); token < 0:
+ * ctl[0..1] are taken as already set on the device (by yalm_argmax_advance). */
+int yalm_embed(float *x, const void *table, const float *row_scale, int dim, int dtype, int *ctl, int token,
+               int pos, int max_seq_len, yalm_stream_t s);
 
 /* rmsnorm -> q,k,v GEMVs -> clip -> RoPE(q,k) -> fp16 KV append at ctl.kv_pos -> sink re-rotation.
  * Replaces rmsnorm + fused_qkv_matmul_clip + fused_rope_and_cache_update + rotate_sink_tokens

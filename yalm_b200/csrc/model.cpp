@@ -1,0 +1,643 @@
+// Host side of the forward pass: configuration, scratch state, weight binding / sharding / upload,
+// op sequencing and CUDA-graph capture.  See yalm_api.h for how this maps onto the reference API.
+#include "yalm_api.h"
+
+#include "tp.h"
+
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cassert>
+#include <cfloat>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <functional>
+#include <iostream>
+
+extern "C" int yalm_attn_generic(float *out, float *att, const uint16_t *key_cache, const uint16_t *value_cache,
+                                 const float *q, int n_heads, int n_kv_heads, int head_dim, int max_seq_len,
+                                 int kv_len, const int *ctl, yalm_stream_t s);
+extern "C" int yalm_attn_is_fast_shape(int n_heads, int n_kv_heads, int head_dim);
+
+#define CUDA_CHECK(x)                                                                                         \
+	do {                                                                                                      \
+		cudaError_t err__ = (x);                                                                              \
+		if (err__ != cudaSuccess) {                                                                           \
+			fprintf(stderr, "CUDA error in %s at %s:%d: %s (%s=%d)\n", __FUNCTION__, __FILE__, __LINE__,       \
+			        cudaGetErrorString(err__), cudaGetErrorName(err__), (int)err__);                          \
+			abort();                                                                                          \
+		}                                                                                                     \
+	} while (0)
+
+// op-level failures on the hot path follow the reference convention too: report and abort
+#define OP_CHECK(x)                                                                                           \
+	do {                                                                                                      \
+		int rc__ = (x);                                                                                       \
+		if (rc__ != 0) {                                                                                      \
+			fprintf(stderr, "yalm_b200: %s failed at %s:%d: %s (%d)\n", #x, __FILE__, __LINE__,               \
+			        yalm_error_string(rc__), rc__);                                                           \
+			abort();                                                                                          \
+		}                                                                                                     \
+	} while (0)
+
+static inline size_t align_up(size_t v, size_t a) {
+	return (v + a - 1) / a * a;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Config
+// ------------------------------------------------------------------------------------------------
+void Config::from_yalm(YALMData &yalm, int context) {
+	const Metadata &md = yalm.metadata;
+	auto geti = [&](const char *k) { return std::stoi(md.at(k)); };
+	dim = geti("dim");
+	hidden_dim = geti("hidden_dim");
+	head_dim = geti("head_dim");
+	n_layers = geti("n_layers");
+	n_heads = geti("n_heads");
+	n_kv_heads = geti("n_kv_heads");
+	vocab_size = geti("vocab_size");
+	n_experts = md.contains("n_experts") ? geti("n_experts") : 0;
+	n_experts_active = md.contains("n_experts_active") ? geti("n_experts_active") : 0;
+	// Reference rule (src/model.cpp:31-36): clamp to 4096 unless a context is given, which replaces it.
+	max_seq_len = std::min(geti("max_seq_len"), 4096);
+	if (context) max_seq_len = context;
+	rope_theta = std::stof(md.at("rope_theta"));
+	rotary_dim = geti("rotary_dim");
+	norm_eps = std::stof(md.value("norm_eps", "1e-5"));
+	std::string act_str = md.value("act_type", "gelu");
+	if (act_str == "silu") act = ActivationType::SILU;
+	else {
+		if (act_str != "gelu") std::cerr << "unsupported act_type, defaulting to gelu" << std::endl;
+		act = ActivationType::GELU;
+	}
+	if (md.value("norm_type", "rmsnorm") != "rmsnorm")
+		std::cerr << "unsupported norm_type, defaulting to rmsnorm" << std::endl;
+	norm_type = LayerNormType::RMSNorm;
+	qkv_clip = md.contains("qkv_clip") ? std::stof(md.at("qkv_clip")) : FLT_MAX;
+	std::string dtype = md.at("dtype");
+	if (dtype == "fp32") weight_dtype = DType::F32;
+	else if (dtype == "fp16") weight_dtype = DType::F16;
+	else if (dtype == "fp8") {
+		// The reference maps "fp8" to F8E5M2 and then reinterprets the bytes as fp16;
+		// there is no arithmetic to reproduce.  We define fp8 = e4m3 + per-row scales and say which
+		// flavour the file holds from the tensor dtype itself.
+		const Tensor *t = yalm.find("model.layers.0.attn.wq.weight");
+		weight_dtype = (t && t->dtype == DType::F8E5M2) ? DType::F8E5M2 : DType::F8E4M3;
+	} else {
+		std::cerr << "FATAL: unsupported dtype: " << dtype << std::endl;
+		assert(false);
+		abort();
+	}
+}
+
+size_t Config::active_bytes(size_t pos) const {
+	const size_t ws = dtype_size(weight_dtype);
+	const size_t q_dim = (size_t)n_heads * head_dim, kv_dim = (size_t)n_kv_heads * head_dim;
+	size_t per_block = 2 * (size_t)dim * sizeof(float);
+	per_block += (2 * q_dim + 2 * kv_dim) * dim * ws;
+	if (n_experts > 0) per_block += ((size_t)n_experts * dim + (size_t)n_experts_active * 3 * dim * hidden_dim) * ws;
+	else per_block += (size_t)3 * dim * hidden_dim * ws;
+	const size_t kv_len = std::min<size_t>(max_seq_len, pos + 1);
+	per_block += 2 * kv_len * kv_dim * sizeof(f16_t);
+	return (size_t)dim * ws + (size_t)n_layers * per_block + (size_t)dim * sizeof(float) + (size_t)vocab_size * dim * ws;
+}
+
+// ------------------------------------------------------------------------------------------------
+// CudaGraph
+// ------------------------------------------------------------------------------------------------
+void CudaGraph::launch(cudaStream_t s) {
+	CUDA_CHECK(cudaGraphLaunch(instance, s));
+}
+void CudaGraph::destroy() {
+	if (instance) cudaGraphExecDestroy(instance);
+	if (graph) cudaGraphDestroy(graph);
+	instance = nullptr, graph = nullptr, is_created = false;
+}
+
+// ------------------------------------------------------------------------------------------------
+// InferenceState
+// ------------------------------------------------------------------------------------------------
+InferenceState::InferenceState(const std::shared_ptr<Config> config) : _config(config) {
+	assert(config);
+	const Config &c = *config;
+	// Host scratch, as the reference allocates it (src/model.cpp:267-284); replaced by device memory in cuda().
+	_x = new float[c.dim]();
+	_xb = new float[c.dim]();
+	_xb2 = new float[std::max(c.dim, c.n_heads * c.head_dim)]();
+	const int k_act = std::max(1, c.n_experts_active);
+	_hb = new float[(size_t)k_act * c.hidden_dim]();
+	_hb2 = new float[c.hidden_dim]();
+	_q = new float[c.n_heads * c.head_dim]();
+	_k = new float[c.n_kv_heads * c.head_dim]();
+	_v = new float[c.n_kv_heads * c.head_dim]();
+	_att = new float[(size_t)c.n_heads * c.max_seq_len]();
+	_logits = new float[c.vocab_size]();
+	// Unlike the reference (src/model.cpp:279-283, the dense-model null store of SURVEY.md P4) the
+	// expert buffers always exist.
+	_moe_weights = new float[std::max(1, c.n_experts)]();
+	_active_experts = new int[k_act]();
+	_active_experts_weights = new float[k_act]();
+}
+
+InferenceState::~InferenceState() {
+	_hydrate_graph.destroy();
+	_output_graph.destroy();
+	_greedy_graph.destroy();
+	if (_device == Device::CPU) {
+		delete[] _x;
+		delete[] _xb;
+		delete[] _xb2;
+		delete[] _hb;
+		delete[] _hb2;
+		delete[] _q;
+		delete[] _k;
+		delete[] _v;
+		delete[] _att;
+		delete[] _moe_weights;
+		delete[] _active_experts;
+		delete[] _active_experts_weights;
+		delete[] _logits;
+	} else {
+		cudaFree(_arena);
+		cudaFreeHost(_logits);
+		if (_stream) cudaStreamDestroy(_stream);
+	}
+}
+
+void InferenceState::cuda() {
+	if (_device != Device::CPU) return;
+	const Config &c = *_config;
+	delete[] _x;
+	delete[] _xb;
+	delete[] _xb2;
+	delete[] _hb;
+	delete[] _hb2;
+	delete[] _q;
+	delete[] _k;
+	delete[] _v;
+	delete[] _att;
+	delete[] _moe_weights;
+	delete[] _active_experts;
+	delete[] _active_experts_weights;
+	delete[] _logits;
+	_device = Device::CUDA;
+	init_cuda_stream(reinterpret_cast<yalm_stream_t *>(&_stream));
+
+	const int lh = c.local_heads(), lkv = c.local_kv_heads(), lhid = c.local_hidden();
+	const int k_act = std::max(1, c.n_experts_active);
+	const bool generic_attn = !yalm_attn_is_fast_shape(lh, lkv, c.head_dim);
+	_tokens_cap = 1 << 16;
+	struct Slot {
+		void **ptr;
+		size_t bytes;
+	};
+	Slot slots[] = {
+	    {(void **)&_x, sizeof(float) * c.dim},
+	    {(void **)&_xb, sizeof(float) * c.dim}, // TP: partial sums before the all-reduce
+	    {(void **)&_xb2, sizeof(float) * std::max(c.dim, lh * c.head_dim)},
+	    {(void **)&_hb, sizeof(float) * (size_t)k_act * lhid},
+	    {(void **)&_hb2, sizeof(float) * (size_t)lhid},
+	    {(void **)&_q, sizeof(float) * lh * c.head_dim},
+	    {(void **)&_k, sizeof(float) * lkv * c.head_dim},
+	    {(void **)&_v, sizeof(float) * lkv * c.head_dim},
+	    {(void **)&_att, generic_attn ? sizeof(float) * (size_t)lh * c.max_seq_len : 16},
+	    {(void **)&_moe_weights, sizeof(float) * std::max(1, c.n_experts)},
+	    {(void **)&_active_experts, sizeof(int) * k_act},
+	    {(void **)&_active_experts_weights, sizeof(float) * k_act},
+	    {(void **)&_logits_dev, sizeof(float) * c.vocab_size},
+	    {(void **)&_ctl, sizeof(int) * YALM_CTL_INTS},
+	    {(void **)&_attn_ws, std::max<size_t>(256, yalm_attn_workspace_bytes(lh, lkv, c.head_dim))},
+	    {(void **)&_tokens_dev, sizeof(int) * (size_t)_tokens_cap},
+	};
+	size_t total = 0;
+	for (auto &s : slots) total += align_up(s.bytes, 256);
+	CUDA_CHECK(cudaMalloc(&_arena, total));
+	CUDA_CHECK(cudaMemset(_arena, 0, total));
+	size_t off = 0;
+	for (auto &s : slots) {
+		*s.ptr = static_cast<char *>(_arena) + off;
+		off += align_up(s.bytes, 256);
+	}
+	CUDA_CHECK(cudaHostAlloc((void **)&_logits, sizeof(float) * c.vocab_size, cudaHostAllocDefault));
+	memset(_logits, 0, sizeof(float) * c.vocab_size);
+}
+
+// ------------------------------------------------------------------------------------------------
+// Block
+// ------------------------------------------------------------------------------------------------
+static void *check_tensor(const Tensor *tensor, DType dtype, std::array<int, 4> shape) {
+	if (tensor == nullptr) {
+		std::cerr << "FATAL: missing tensor" << std::endl;
+		abort();
+	}
+	if (tensor->dtype != dtype || tensor->shape != shape) {
+		std::cerr << "FATAL: tensor mismatch for " << tensor->name << std::endl;
+		fprintf(stderr, "expected: dtype=%s, shape=[%d,%d,%d,%d]\n", dtype_to_string(dtype).c_str(), shape[0], shape[1],
+		        shape[2], shape[3]);
+		fprintf(stderr, "got: dtype=%s, shape=[%d,%d,%d,%d]\n", dtype_to_string(tensor->dtype).c_str(),
+		        tensor->shape[0], tensor->shape[1], tensor->shape[2], tensor->shape[3]);
+		abort();
+	}
+	return tensor->data;
+}
+
+static const Tensor *get_tensor(const YALMData &yalm, const std::string &key) {
+	const Tensor *t = yalm.find(key);
+	if (!t) {
+		std::cerr << "FATAL: missing tensor: " << key << std::endl;
+		abort();
+	}
+	return t;
+}
+
+Block::Block(int layer_i, const std::shared_ptr<Config> config, const Tensor *rms_att_weight,
+             const Tensor *rms_ffn_weight, const Tensor *wq, const Tensor *wk, const Tensor *wv, const Tensor *wo,
+             const Tensor *w1, const Tensor *w2, const Tensor *w3, const Tensor *moegate)
+    : _layer_i(layer_i), _config(config) {
+	const Config &c = *config;
+	const DType dt = c.weight_dtype;
+	if (dt != DType::F32 && dt != DType::F16 && dt != DType::F8E4M3) {
+		std::cerr << "FATAL: unsupported weight dtype " << dtype_to_string(dt)
+		          << " (fp8 checkpoints must be F8_E4M3 + .scale tensors; the reference's unscaled F8_E5M2 has no "
+		             "arithmetic defined)"
+		          << std::endl;
+		abort();
+	}
+	const int q_dim = c.n_heads * c.head_dim, kv_dim = c.n_kv_heads * c.head_dim;
+	_rms_att_weight = static_cast<float *>(check_tensor(rms_att_weight, DType::F32, {c.dim, 0, 0, 0}));
+	_rms_ffn_weight = static_cast<float *>(check_tensor(rms_ffn_weight, DType::F32, {c.dim, 0, 0, 0}));
+	_wq = check_tensor(wq, dt, {q_dim, c.dim, 0, 0});
+	_wk = check_tensor(wk, dt, {kv_dim, c.dim, 0, 0});
+	_wv = check_tensor(wv, dt, {kv_dim, c.dim, 0, 0});
+	_wo = check_tensor(wo, dt, {c.dim, q_dim, 0, 0});
+	if (c.n_experts > 0) {
+		_moegate = check_tensor(moegate, dt, {c.n_experts, c.dim, 0, 0});
+		_w1 = check_tensor(w1, dt, {c.n_experts, c.hidden_dim, c.dim, 0});
+		_w2 = check_tensor(w2, dt, {c.n_experts, c.dim, c.hidden_dim, 0});
+		_w3 = check_tensor(w3, dt, {c.n_experts, c.hidden_dim, c.dim, 0});
+	} else {
+		_w1 = check_tensor(w1, dt, {c.hidden_dim, c.dim, 0, 0});
+		_w2 = check_tensor(w2, dt, {c.dim, c.hidden_dim, 0, 0});
+		_w3 = check_tensor(w3, dt, {c.hidden_dim, c.dim, 0, 0});
+	}
+	// The KV cache is created on the device in cuda(); there is no host copy (the reference allocates
+	// and zero-fills 2*max_seq_len*kv_dim halfs per layer on the host first, src/model.cpp:171-172).
+}
+
+void Block::set_scales(const Tensor *sq, const Tensor *sk, const Tensor *sv, const Tensor *so, const Tensor *s1,
+                       const Tensor *s2, const Tensor *s3, const Tensor *sgate) {
+	const Config &c = *_config;
+	const int q_dim = c.n_heads * c.head_dim, kv_dim = c.n_kv_heads * c.head_dim;
+	_sq = static_cast<float *>(check_tensor(sq, DType::F32, {q_dim, 0, 0, 0}));
+	_sk = static_cast<float *>(check_tensor(sk, DType::F32, {kv_dim, 0, 0, 0}));
+	_sv = static_cast<float *>(check_tensor(sv, DType::F32, {kv_dim, 0, 0, 0}));
+	_so = static_cast<float *>(check_tensor(so, DType::F32, {c.dim, 0, 0, 0}));
+	if (c.n_experts > 0) {
+		_s1 = static_cast<float *>(check_tensor(s1, DType::F32, {c.n_experts, c.hidden_dim, 0, 0}));
+		_s2 = static_cast<float *>(check_tensor(s2, DType::F32, {c.n_experts, c.dim, 0, 0}));
+		_s3 = static_cast<float *>(check_tensor(s3, DType::F32, {c.n_experts, c.hidden_dim, 0, 0}));
+		_sgate = static_cast<float *>(check_tensor(sgate, DType::F32, {c.n_experts, 0, 0, 0}));
+	} else {
+		_s1 = static_cast<float *>(check_tensor(s1, DType::F32, {c.hidden_dim, 0, 0, 0}));
+		_s2 = static_cast<float *>(check_tensor(s2, DType::F32, {c.dim, 0, 0, 0}));
+		_s3 = static_cast<float *>(check_tensor(s3, DType::F32, {c.hidden_dim, 0, 0, 0}));
+	}
+}
+
+Block::~Block() {
+	for (void *p : _owned) cudaFree(p);
+}
+
+// `height` pieces of `width` bytes, piece i read at host + i*spitch + offset -> one dense device buffer.
+static void *upload_strided(std::vector<void *> &owned, size_t &acct, const void *host, size_t spitch, size_t offset,
+                            size_t width, size_t height) {
+	if (!host) return nullptr;
+	void *dev = nullptr;
+	CUDA_CHECK(cudaMalloc(&dev, width * height));
+	if (width == spitch) CUDA_CHECK(cudaMemcpy(dev, static_cast<const char *>(host) + offset, width * height, cudaMemcpyHostToDevice));
+	else CUDA_CHECK(cudaMemcpy2D(dev, width, static_cast<const char *>(host) + offset, spitch, width, height, cudaMemcpyHostToDevice));
+	owned.push_back(dev);
+	acct += width * height;
+	return dev;
+}
+
+void Block::cuda() {
+	if (_device != Device::CPU) return;
+	_device = Device::CUDA;
+	const Config &c = *_config;
+	const size_t B = dtype_size(c.weight_dtype), T = c.tp_size, r = c.tp_rank;
+	const size_t q_dim = (size_t)c.n_heads * c.head_dim, kv_dim = (size_t)c.n_kv_heads * c.head_dim;
+	const size_t lq = q_dim / T, lkv = kv_dim / T, lhid = (size_t)c.hidden_dim / T, dim = c.dim;
+	const size_t E = std::max(1, c.n_experts);
+	auto up = [&](const void *h, size_t spitch, size_t off, size_t width, size_t height) {
+		return upload_strided(_owned, _device_bytes, h, spitch, off, width, height);
+	};
+	_rms_att_weight = (float *)up(_rms_att_weight, dim * 4, 0, dim * 4, 1);
+	_rms_ffn_weight = (float *)up(_rms_ffn_weight, dim * 4, 0, dim * 4, 1);
+	// column-parallel (rows of W): q/k/v by head, w1/w3 by hidden unit
+	_wq = up(_wq, lq * dim * B, r * lq * dim * B, lq * dim * B, 1);
+	_wk = up(_wk, lkv * dim * B, r * lkv * dim * B, lkv * dim * B, 1);
+	_wv = up(_wv, lkv * dim * B, r * lkv * dim * B, lkv * dim * B, 1);
+	_w1 = up(_w1, (size_t)c.hidden_dim * dim * B, r * lhid * dim * B, lhid * dim * B, E);
+	_w3 = up(_w3, (size_t)c.hidden_dim * dim * B, r * lhid * dim * B, lhid * dim * B, E);
+	// row-parallel (columns of W): wo over q_dim, w2 over hidden
+	_wo = up(_wo, q_dim * B, r * lq * B, lq * B, dim);
+	_w2 = up(_w2, (size_t)c.hidden_dim * B, r * lhid * B, lhid * B, E * dim);
+	if (c.n_experts > 0) _moegate = up(_moegate, E * dim * B, 0, E * dim * B, 1);
+	if (_sq) {
+		_sq = (float *)up(_sq, lq * 4, r * lq * 4, lq * 4, 1);
+		_sk = (float *)up(_sk, lkv * 4, r * lkv * 4, lkv * 4, 1);
+		_sv = (float *)up(_sv, lkv * 4, r * lkv * 4, lkv * 4, 1);
+		_so = (float *)up(_so, dim * 4, 0, dim * 4, 1);
+		_s1 = (float *)up(_s1, (size_t)c.hidden_dim * 4, r * lhid * 4, lhid * 4, E);
+		_s3 = (float *)up(_s3, (size_t)c.hidden_dim * 4, r * lhid * 4, lhid * 4, E);
+		_s2 = (float *)up(_s2, E * dim * 4, 0, E * dim * 4, 1);
+		if (_sgate) _sgate = (float *)up(_sgate, E * 4, 0, E * 4, 1);
+	}
+	const size_t kv_bytes = (size_t)c.max_seq_len * lkv * sizeof(f16_t);
+	CUDA_CHECK(cudaMalloc((void **)&_key_cache, kv_bytes));
+	CUDA_CHECK(cudaMalloc((void **)&_value_cache, kv_bytes));
+	CUDA_CHECK(cudaMemset(_key_cache, 0, kv_bytes));
+	CUDA_CHECK(cudaMemset(_value_cache, 0, kv_bytes));
+	_owned.push_back(_key_cache);
+	_owned.push_back(_value_cache);
+	_device_bytes += 2 * kv_bytes;
+}
+
+int Block::enqueue(InferenceState &s) const {
+	const Config &c = *_config;
+	const int dt = static_cast<int>(c.weight_dtype);
+	const int lh = c.local_heads(), lkv = c.local_kv_heads(), lhid = c.local_hidden();
+	yalm_stream_t st = s.stream();
+	const bool tp = c.tp_size > 1;
+	int rc;
+	rc = yalm_qkv_rope_append(s.q(), _key_cache, _value_cache, s.x(), _rms_att_weight, _wq, _wk, _wv, _sq, _sk, _sv,
+	                          c.dim, lh, lkv, c.head_dim, c.rotary_dim, c.rope_theta, c.norm_eps, c.qkv_clip, dt,
+	                          s.ctl(), st);
+	if (rc) return rc;
+	if (yalm_attn_is_fast_shape(lh, lkv, c.head_dim))
+		rc = yalm_attn_decode(s.xb2(), _key_cache, _value_cache, s.q(), s.attn_workspace(), lh, lkv, c.head_dim,
+		                      s.ctl(), st);
+	else
+		rc = yalm_attn_generic(s.xb2(), s.att(), _key_cache, _value_cache, s.q(), lh, lkv, c.head_dim, c.max_seq_len, 0,
+		                       s.ctl(), st);
+	if (rc) return rc;
+	// wo + residual.  Under TP every rank holds a column slice: rank 0 folds the residual into its partial
+	// and the all-reduce leaves the new x on every rank.
+	if (!tp) {
+		rc = yalm_gemv_residual(s.x(), s.x(), s.xb2(), _wo, _so, lh * c.head_dim, c.dim, dt, 1, nullptr, nullptr, st);
+		if (rc) return rc;
+	} else {
+		rc = yalm_gemv_residual(s.xb(), c.tp_rank == 0 ? s.x() : nullptr, s.xb2(), _wo, _so, lh * c.head_dim, c.dim, dt,
+		                        1, nullptr, nullptr, st);
+		if (rc) return rc;
+		rc = yalm::tp_allreduce_sum(s.xb(), s.x(), c.dim, s.stream());
+		if (rc) return rc;
+	}
+	const bool moe = c.n_experts > 0;
+	rc = yalm_ffn_glu(s.hb(), s.x(), _rms_ffn_weight, _w1, _w3, _s1, _s3, _moegate, _sgate, c.dim, lhid,
+	                  c.act == ActivationType::SILU ? YALM_ACT_SILU : YALM_ACT_GELU, c.norm_eps, dt, c.n_experts,
+	                  c.n_experts_active, s.active_experts(), s.active_experts_weights(), s.moe_weights(), st);
+	if (rc) return rc;
+	const int k_act = moe ? c.n_experts_active : 1;
+	const int *ae = moe ? s.active_experts() : nullptr;
+	const float *aw = moe ? s.active_experts_weights() : nullptr;
+	if (!tp) {
+		rc = yalm_gemv_residual(s.x(), s.x(), s.hb(), _w2, _s2, lhid, c.dim, dt, k_act, ae, aw, st);
+	} else {
+		rc = yalm_gemv_residual(s.xb(), c.tp_rank == 0 ? s.x() : nullptr, s.hb(), _w2, _s2, lhid, c.dim, dt, k_act, ae,
+		                        aw, st);
+		if (rc) return rc;
+		rc = yalm::tp_allreduce_sum(s.xb(), s.x(), c.dim, s.stream());
+	}
+	return rc;
+}
+
+void Block::block(InferenceState &s, int pos, int kv_sink, int kv_pos, int kv_len) const {
+	if (_device != Device::CUDA || s.device() != Device::CUDA) {
+		std::cerr << "FATAL: yalm_b200 has no CPU execution path; call .cuda() on the model and the state" << std::endl;
+		abort();
+	}
+	int h[YALM_CTL_INTS] = {0, pos, kv_sink, kv_pos, kv_len, 0, 0, 0};
+	CUDA_CHECK(cudaMemcpyAsync(s.ctl(), h, sizeof(h), cudaMemcpyHostToDevice, s.stream()));
+	CUDA_CHECK(cudaStreamSynchronize(s.stream())); // `h` is a stack buffer
+	OP_CHECK(enqueue(s));
+}
+
+// ------------------------------------------------------------------------------------------------
+// Model
+// ------------------------------------------------------------------------------------------------
+Model::Model(YALMData &yalm, int context) {
+	config = std::make_shared<Config>();
+	config->from_yalm(yalm, context);
+	const Config &c = *config;
+	std::cout << "loading model with dtype: " << dtype_to_string(c.weight_dtype) << std::endl;
+	const DType dt = c.weight_dtype;
+	const bool fp8 = dt == DType::F8E4M3;
+	token_embedding_table = check_tensor(get_tensor(yalm, "model.embed.weight"), dt, {c.vocab_size, c.dim, 0, 0});
+	if (fp8)
+		embed_scale = static_cast<float *>(
+		    check_tensor(get_tensor(yalm, "model.embed.weight.scale"), DType::F32, {c.vocab_size, 0, 0, 0}));
+	for (int i = 0; i < c.n_layers; ++i) {
+		const std::string p = "model.layers." + std::to_string(i) + ".";
+		auto T = [&](const char *n) { return get_tensor(yalm, p + n); };
+		auto blk = std::make_shared<Block>(i, config, T("attn.norm.weight"), T("mlp.norm.weight"), T("attn.wq.weight"),
+		                                   T("attn.wk.weight"), T("attn.wv.weight"), T("attn.wo.weight"),
+		                                   T("mlp.w1.weight"), T("mlp.w2.weight"), T("mlp.w3.weight"),
+		                                   c.n_experts > 0 ? T("moegate.weight") : nullptr);
+		if (fp8)
+			blk->set_scales(T("attn.wq.weight.scale"), T("attn.wk.weight.scale"), T("attn.wv.weight.scale"),
+			                T("attn.wo.weight.scale"), T("mlp.w1.weight.scale"), T("mlp.w2.weight.scale"),
+			                T("mlp.w3.weight.scale"), c.n_experts > 0 ? T("moegate.weight.scale") : nullptr);
+		blocks.emplace_back(blk);
+	}
+	rms_final_weight = static_cast<float *>(check_tensor(get_tensor(yalm, "model.norm.weight"), DType::F32, {c.dim, 0, 0, 0}));
+	_tied = yalm.tensors.count("model.output.weight") == 0; // src/model.cpp:371-377
+	if (_tied) {
+		wcls = token_embedding_table;
+		wcls_scale = embed_scale;
+	} else {
+		wcls = check_tensor(get_tensor(yalm, "model.output.weight"), dt, {c.vocab_size, c.dim, 0, 0});
+		if (fp8)
+			wcls_scale = static_cast<float *>(
+			    check_tensor(get_tensor(yalm, "model.output.weight.scale"), DType::F32, {c.vocab_size, 0, 0, 0}));
+	}
+}
+
+Model::~Model() {
+	for (void *p : _owned) cudaFree(p);
+}
+
+void Model::cuda() {
+	int count = 0;
+	if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0) {
+		std::cerr << "FATAL: no CUDA device; yalm_b200 has no CPU fallback" << std::endl;
+		abort();
+	}
+	int dev = 0;
+	cudaGetDevice(&dev);
+	cuda(dev, yalm::tp_rank(), yalm::tp_world());
+}
+
+void Model::cuda(int device, int tp_rank, int tp_size) {
+	if (_device != Device::CPU) return;
+	Config &c = *config;
+	if (tp_size < 1 || tp_rank < 0 || tp_rank >= tp_size || c.n_kv_heads % tp_size || c.n_heads % tp_size ||
+	    c.hidden_dim % tp_size || c.vocab_size % tp_size) {
+		std::cerr << "FATAL: model does not shard " << tp_size << " ways (kv heads " << c.n_kv_heads << ", hidden "
+		          << c.hidden_dim << ", vocab " << c.vocab_size << ")" << std::endl;
+		abort();
+	}
+	c.tp_rank = tp_rank, c.tp_size = tp_size;
+	_device = Device::CUDA;
+	set_cuda_device(device);
+	const size_t B = dtype_size(c.weight_dtype), dim = c.dim, V = c.vocab_size, lv = V / tp_size;
+	void *host_embed = token_embedding_table;
+	token_embedding_table = upload_strided(_owned, _device_bytes, host_embed, V * dim * B, 0, V * dim * B, 1);
+	if (embed_scale) embed_scale = (float *)upload_strided(_owned, _device_bytes, embed_scale, V * 4, 0, V * 4, 1);
+	for (auto &b : blocks) b->cuda();
+	for (auto &b : blocks) _device_bytes += b->device_bytes();
+	rms_final_weight = (float *)upload_strided(_owned, _device_bytes, rms_final_weight, dim * 4, 0, dim * 4, 1);
+	// LM head: vocabulary rows are split across ranks; tied heads alias the (replicated) embedding table.
+	if (_tied) {
+		wcls = static_cast<char *>(token_embedding_table) + (size_t)tp_rank * lv * dim * B;
+		wcls_scale = embed_scale ? embed_scale + (size_t)tp_rank * lv : nullptr;
+	} else {
+		wcls = upload_strided(_owned, _device_bytes, wcls, lv * dim * B, (size_t)tp_rank * lv * dim * B, lv * dim * B, 1);
+		if (wcls_scale)
+			wcls_scale = (float *)upload_strided(_owned, _device_bytes, wcls_scale, lv * 4, (size_t)tp_rank * lv * 4, lv * 4, 1);
+	}
+	CUDA_CHECK(cudaDeviceSynchronize());
+}
+
+int Model::launches_per_forward(InferenceMode mode) const {
+	// embed + 5 kernels per block (qkv+rope+append, flash-decode, wo+res, ffn-glu, w2+res) [+ lm head]
+	// (+ 2 NCCL all-reduce kernels per block and one all-gather under tensor parallelism)
+	const int per_block = 5 + (config->tp_size > 1 ? 2 : 0);
+	int n = 1 + per_block * config->n_layers;
+	if (mode == InferenceMode::OUTPUT_LOGITS) n += 1 + (config->tp_size > 1 ? 1 : 0);
+	return n;
+}
+
+// Enqueue (eagerly or into a capturing stream) everything after the embedding.
+int Model::enqueue_forward(InferenceState &s, InferenceMode mode, bool /*from_host*/, bool greedy_tail) {
+	const Config &c = *config;
+	const int dt = static_cast<int>(c.weight_dtype);
+	yalm_stream_t st = s.stream();
+	int rc;
+	if (greedy_tail) { // token/pos come from the device-side control block
+		rc = yalm_embed(s.x(), token_embedding_table, embed_scale, c.dim, dt, s.ctl(), -1, 0, c.max_seq_len, st);
+		if (rc) return rc;
+	}
+	for (auto &b : blocks) {
+		rc = b->enqueue(s);
+		if (rc) return rc;
+	}
+	if (mode == InferenceMode::HYDRATE_KV_CACHE) return 0;
+	const int lv = c.local_vocab();
+	rc = yalm_lm_head(s.logits_dev() + (size_t)c.tp_rank * lv, s.x(), rms_final_weight, wcls, wcls_scale, c.dim, lv,
+	                  c.norm_eps, dt, st);
+	if (rc) return rc;
+	if (c.tp_size > 1) {
+		rc = yalm::tp_allgather(s.logits_dev() + (size_t)c.tp_rank * lv, s.logits_dev(), lv, s.stream());
+		if (rc) return rc;
+	}
+	if (greedy_tail) return yalm_argmax_advance(s.logits_dev(), c.vocab_size, s.ctl(), c.max_seq_len, s.tokens_dev(), st);
+	return (int)cudaMemcpyAsync(s.logits(), s.logits_dev(), sizeof(float) * c.vocab_size, cudaMemcpyDeviceToHost,
+	                            s.stream());
+}
+
+static void capture_graph(CudaGraph &g, cudaStream_t st, const std::function<int()> &body);
+
+void Model::forward(InferenceState &s, int token, int pos, InferenceMode mode) {
+	if (s.device() != _device) {
+		std::cerr << "FATAL: inference state device mismatch" << std::endl;
+		abort();
+	}
+	if (_device != Device::CUDA) {
+		std::cerr << "FATAL: yalm_b200 has no CPU execution path; call model.cuda() and state.cuda() first" << std::endl;
+		abort();
+	}
+	const Config &c = *config;
+	if (token < 0 || token >= c.vocab_size || pos < 0) {
+		std::cerr << "FATAL: token/pos out of range" << std::endl;
+		abort();
+	}
+	s.set_mode(mode);
+	CudaGraph &g = s.graph();
+	// The embedding is an ordinary launch: token and pos travel as kernel arguments (copied at launch
+	// time), everything after it reads positions from the device control block and is one graph replay.
+	OP_CHECK(yalm_embed(s.x(), token_embedding_table, embed_scale, c.dim, static_cast<int>(c.weight_dtype), s.ctl(),
+	                    token, pos, c.max_seq_len, s.stream()));
+	if (!g.is_created) {
+		// First call in this mode: run eagerly (this also sizes every kernel's shared memory and
+		// occupancy), then capture the same sequence for all later calls.
+		OP_CHECK(enqueue_forward(s, mode, true, false));
+		CUDA_CHECK(cudaStreamSynchronize(s.stream()));
+		capture_graph(g, s.stream(), [&]() { return enqueue_forward(s, mode, true, false); });
+	} else {
+		g.launch(s.stream());
+	}
+	if (mode == InferenceMode::OUTPUT_LOGITS) CUDA_CHECK(cudaStreamSynchronize(s.stream()));
+	CUDA_CHECK(cudaGetLastError());
+}
+
+static void capture_graph(CudaGraph &g, cudaStream_t st, const std::function<int()> &body) {
+	CUDA_CHECK(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+	int rc = body();
+	cudaError_t end = cudaStreamEndCapture(st, &g.graph);
+	if (rc != 0 || end != cudaSuccess) {
+		fprintf(stderr, "yalm_b200: graph capture failed (%d, %s)\n", rc, cudaGetErrorString(end));
+		abort();
+	}
+	CUDA_CHECK(cudaGraphInstantiate(&g.instance, g.graph, 0));
+	g.is_created = true;
+}
+
+int Model::generate_greedy(InferenceState &s, int token, int pos, int n_gen, int *tokens_out, float *logits_out,
+                           float *device_ms) {
+	if (_device != Device::CUDA || s.device() != Device::CUDA) return YALM_ENOGPU;
+	const Config &c = *config;
+	if (n_gen < 1 || n_gen > s.tokens_capacity() || token < 0 || token >= c.vocab_size || pos < 0 || !tokens_out)
+		return YALM_EINVAL;
+	cudaStream_t st = s.stream();
+	// seed the device control block: token, pos, ring position, step = 0
+	const int kv_sink = pos >= c.max_seq_len ? KV_SINKS : 0;
+	int h[YALM_CTL_INTS] = {token, pos, kv_sink, kv_sink + (pos - kv_sink) % (c.max_seq_len - kv_sink),
+	                        pos >= c.max_seq_len ? c.max_seq_len : pos + 1, 0, 0, 0};
+	CUDA_CHECK(cudaMemcpyAsync(s.ctl(), h, sizeof(h), cudaMemcpyHostToDevice, st));
+	CUDA_CHECK(cudaStreamSynchronize(st));
+	CudaGraph &g = s.greedy_graph();
+	int done = 0;
+	if (!g.is_created) {
+		int rc = enqueue_forward(s, InferenceMode::OUTPUT_LOGITS, false, true);
+		if (rc) return rc;
+		if (logits_out)
+			CUDA_CHECK(cudaMemcpyAsync(logits_out, s.logits_dev(), sizeof(float) * c.vocab_size, cudaMemcpyDeviceToHost, st));
+		CUDA_CHECK(cudaStreamSynchronize(st));
+		capture_graph(g, st, [&]() { return enqueue_forward(s, InferenceMode::OUTPUT_LOGITS, false, true); });
+		done = 1;
+	}
+	cudaEvent_t e0, e1;
+	CUDA_CHECK(cudaEventCreate(&e0));
+	CUDA_CHECK(cudaEventCreate(&e1));
+	CUDA_CHECK(cudaEventRecord(e0, st));
+	for (int i = done; i < n_gen; ++i) {
+		g.launch(st);
+		if (logits_out)
+			CUDA_CHECK(cudaMemcpyAsync(logits_out + (size_t)i * c.vocab_size, s.logits_dev(),
+			                           sizeof(float) * c.vocab_size, cudaMemcpyDeviceToHost, st));
+	}
+	CUDA_CHECK(cudaEventRecord(e1, st));
+	CUDA_CHECK(cudaMemcpyAsync(tokens_out, s.tokens_dev(), sizeof(int) * n_gen, cudaMemcpyDeviceToHost, st));
+	CUDA_CHECK(cudaStreamSynchronize(st));
+	if (device_ms) {
+		CUDA_CHECK(cudaEventElapsedTime(device_ms, e0, e1));
+		if (n_gen > done) *device_ms = *device_ms * n_gen / (n_gen - done); // scale to n_gen steps when step 0 ran eagerly
+	}
+	cudaEventDestroy(e0);
+	cudaEventDestroy(e1);
+	return (int)cudaGetLastError();
+}

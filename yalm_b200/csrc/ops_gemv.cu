@@ -31,19 +31,16 @@ __device__ __forceinline__ void derive_ring(int *ctl, int pos, int max_seq_len) 
 
 template <int DT>
 __global__ void embed_kernel(float *__restrict__ x, const void *__restrict__ table, const float *__restrict__ row_scale,
-                             int dim, int *ctl, const int *host_tp, int max_seq_len) {
-	int token, pos;
-	if (host_tp) {
-		token = host_tp[0];
-		pos = host_tp[1];
-	} else {
+                             int dim, int *ctl, int token_arg, int pos_arg, int max_seq_len) {
+	int token = token_arg, pos = pos_arg;
+	if (token_arg < 0) {
 		token = ctl[CTL_TOKEN];
 		pos = ctl[CTL_POS];
 	}
 	const float sc = (DT == YALM_F8E4M3 && row_scale) ? row_scale[token] : 1.0f;
 	for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < dim; i += gridDim.x * blockDim.x)
 		x[i] = WTraits<DT>::to_float(table, (size_t)token * dim + i) * sc;
-	if (blockIdx.x == 0 && threadIdx.x == 0 && host_tp) {
+	if (blockIdx.x == 0 && threadIdx.x == 0 && token_arg >= 0) {
 		ctl[CTL_TOKEN] = token;
 		ctl[CTL_POS] = pos;
 		derive_ring(ctl, pos, max_seq_len);
@@ -375,11 +372,11 @@ static int launch_persistent(K kernel, const A &args, size_t smem, long tasks, c
 }
 
 extern "C" int yalm_embed(float *x, const void *table, const float *row_scale, int dim, int dtype, int *ctl,
-                          const int *host_token_pos, int max_seq_len, yalm_stream_t s) {
+                          int token, int pos, int max_seq_len, yalm_stream_t s) {
 	if (!x || !table || !ctl || dim <= 0 || max_seq_len <= KV_SINKS) return YALM_EINVAL;
 	cudaStream_t st = (cudaStream_t)s;
 	const int grid = std::max(1, std::min(8, (dim + 1023) / 1024));
-	YALM_DISPATCH_DT(dtype, (embed_kernel<DT><<<grid, 1024, 0, st>>>(x, table, row_scale, dim, ctl, host_token_pos,
+	YALM_DISPATCH_DT(dtype, (embed_kernel<DT><<<grid, 1024, 0, st>>>(x, table, row_scale, dim, ctl, token, pos,
 	                                                                  max_seq_len)));
 	return (int)cudaGetLastError();
 }

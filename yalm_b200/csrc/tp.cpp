@@ -1,0 +1,121 @@
+// Tensor-parallel plumbing: one process per GPU, NCCL over NVLink 5 / NVSwitch.
+// NCCL is bound at run time (dlopen of the libnccl.so.2 that torch bundles, or the system one) so that
+// the single-GPU build has no link-time dependency on it.  Only the five calls the decode path needs.
+#include "tp.h"
+
+#include <dlfcn.h>
+
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+
+namespace yalm {
+namespace {
+
+typedef struct ncclComm *ncclComm_t;
+struct ncclUniqueId_ {
+	char internal[128];
+};
+constexpr int kNcclFloat32 = 7, kNcclSum = 0; // nccl.h: ncclDataType_t / ncclRedOp_t
+
+struct Api {
+	void *lib = nullptr;
+	int (*GetUniqueId)(ncclUniqueId_ *) = nullptr;
+	int (*CommInitRank)(ncclComm_t *, int, ncclUniqueId_, int) = nullptr;
+	int (*AllReduce)(const void *, void *, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
+	int (*AllGather)(const void *, void *, size_t, int, ncclComm_t, cudaStream_t) = nullptr;
+	int (*CommDestroy)(ncclComm_t) = nullptr;
+	const char *(*GetErrorString)(int) = nullptr;
+};
+
+Api g_api;
+ncclComm_t g_comm = nullptr;
+int g_rank = 0, g_world = 1;
+
+bool load_api() {
+	if (g_api.lib) return true;
+	const char *env = getenv("YALM_NCCL_LIB");
+	const char *names[] = {env, "libnccl.so.2", "libnccl.so"};
+	for (const char *n : names) {
+		if (!n) continue;
+		g_api.lib = dlopen(n, RTLD_NOW | RTLD_GLOBAL);
+		if (g_api.lib) break;
+	}
+	if (!g_api.lib) {
+		fprintf(stderr, "yalm_b200: cannot load NCCL (%s); set YALM_NCCL_LIB\n", dlerror());
+		return false;
+	}
+#define YALM_SYM(field, name)                                                                                 \
+	*(void **)(&g_api.field) = dlsym(g_api.lib, name);                                                        \
+	if (!g_api.field) {                                                                                       \
+		fprintf(stderr, "yalm_b200: NCCL symbol %s missing\n", name);                                         \
+		return false;                                                                                         \
+	}
+	YALM_SYM(GetUniqueId, "ncclGetUniqueId")
+	YALM_SYM(CommInitRank, "ncclCommInitRank")
+	YALM_SYM(AllReduce, "ncclAllReduce")
+	YALM_SYM(AllGather, "ncclAllGather")
+	YALM_SYM(CommDestroy, "ncclCommDestroy")
+	YALM_SYM(GetErrorString, "ncclGetErrorString")
+#undef YALM_SYM
+	return true;
+}
+
+int check(int rc, const char *what) {
+	if (rc != 0) {
+		fprintf(stderr, "yalm_b200: %s failed: %s\n", what, g_api.GetErrorString ? g_api.GetErrorString(rc) : "?");
+		return -100 - rc;
+	}
+	return 0;
+}
+
+} // namespace
+
+int tp_rank() { return g_rank; }
+int tp_world() { return g_world; }
+bool tp_active() { return g_comm != nullptr && g_world > 1; }
+
+int tp_allreduce_sum(const float *send, float *recv, size_t count, cudaStream_t st) {
+	if (!tp_active()) return YALM_EINVAL;
+	return check(g_api.AllReduce(send, recv, count, kNcclFloat32, kNcclSum, g_comm, st), "ncclAllReduce");
+}
+
+int tp_allgather(const float *send, float *recv, size_t count_per_rank, cudaStream_t st) {
+	if (!tp_active()) return YALM_EINVAL;
+	return check(g_api.AllGather(send, recv, count_per_rank, kNcclFloat32, g_comm, st), "ncclAllGather");
+}
+
+} // namespace yalm
+
+using namespace yalm;
+
+extern "C" int yalm_tp_unique_id(void *id128) {
+	if (!id128 || !load_api()) return YALM_EINVAL;
+	ncclUniqueId_ id;
+	int rc = check(g_api.GetUniqueId(&id), "ncclGetUniqueId");
+	if (rc) return rc;
+	memcpy(id128, &id, sizeof(id));
+	return 0;
+}
+
+extern "C" int yalm_tp_init(const void *id128, int rank, int world) {
+	if (!id128 || rank < 0 || world < 1 || rank >= world) return YALM_EINVAL;
+	if (world == 1) {
+		g_rank = 0, g_world = 1;
+		return 0;
+	}
+	if (!load_api()) return YALM_EINVAL;
+	ncclUniqueId_ id;
+	memcpy(&id, id128, sizeof(id));
+	int rc = check(g_api.CommInitRank(&g_comm, world, id, rank), "ncclCommInitRank");
+	if (rc) return rc;
+	g_rank = rank, g_world = world;
+	return 0;
+}
+
+extern "C" void yalm_tp_finalize(void) {
+	if (g_comm) g_api.CommDestroy(g_comm);
+	g_comm = nullptr;
+	g_rank = 0, g_world = 1;
+}
