@@ -1,0 +1,42 @@
+# yalm_b200 build: one shared library (kernels + C ABI + C++ API), plus the reference-shaped CLIs.
+#   make            -> yalm_b200/libyalm_b200.so, build/main, build/test
+#   make lib        -> only the library
+NVCC  ?= nvcc
+HOSTCXX := /usr/bin/g++
+ARCH  := -gencode arch=compute_100a,code=sm_100a
+CSRC  := yalm_b200/csrc
+BUILD := build
+NVFLAGS := -std=c++17 -O3 -lineinfo $(ARCH) -ccbin $(HOSTCXX) -Xcompiler -fPIC,-Wall,-fopenmp -Iinclude
+LIB   := yalm_b200/libyalm_b200.so
+
+LIB_SRCS := $(CSRC)/ops_gemv.cu $(CSRC)/ops_attn.cu $(CSRC)/model.cpp $(CSRC)/codec.cpp $(CSRC)/capi.cpp \
+            $(CSRC)/mem.cpp $(CSRC)/tp.cpp
+LIB_OBJS := $(patsubst $(CSRC)/%,$(BUILD)/%.o,$(LIB_SRCS))
+HDRS := $(wildcard $(CSRC)/*.h $(CSRC)/*.cuh include/*.h)
+
+all: lib $(BUILD)/main $(BUILD)/test
+lib: $(LIB)
+
+$(BUILD)/%.cu.o: $(CSRC)/%.cu $(HDRS)
+	@mkdir -p $(BUILD)
+	$(NVCC) $(NVFLAGS) -c $< -o $@
+
+$(BUILD)/%.cpp.o: $(CSRC)/%.cpp $(HDRS)
+	@mkdir -p $(BUILD)
+	$(NVCC) $(NVFLAGS) -x cu -c $< -o $@
+
+$(LIB): $(LIB_OBJS)
+	$(NVCC) $(ARCH) -ccbin $(HOSTCXX) -shared -o $@ $^ -lcudart -ldl -Xcompiler -fopenmp
+
+$(BUILD)/main: $(CSRC)/main.cpp $(CSRC)/sampler.cpp $(CSRC)/tokenizer.cpp $(LIB) $(HDRS)
+	$(NVCC) $(NVFLAGS) -x cu $(CSRC)/main.cpp $(CSRC)/sampler.cpp $(CSRC)/tokenizer.cpp -o $@ \
+	    -Lyalm_b200 -lyalm_b200 -Xlinker -rpath,'$$ORIGIN/../yalm_b200'
+
+$(BUILD)/test: $(CSRC)/test.cpp $(LIB) $(HDRS)
+	$(NVCC) $(NVFLAGS) -x cu $(CSRC)/test.cpp -o $@ -Lyalm_b200 -lyalm_b200 \
+	    -Xlinker -rpath,'$$ORIGIN/../yalm_b200'
+
+clean:
+	rm -rf $(BUILD) $(LIB)
+
+.PHONY: all lib clean

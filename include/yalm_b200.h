@@ -94,7 +94,8 @@ int yalm_gemv_residual(float *out, const float *residual, const float *v, const 
 /* rmsnorm -> [router GEMV + top-k gate] -> hb[k,i] = act(W1[e_k] xb)[i] * (W3[e_k] xb)[i].
  * Replaces rmsnorm + fused_ffn_w1_w3_glu_act (src/infer.cu:598-620) and, for MoE, the CPU-only
  * router (src/infer.cpp:100-132, 347-349).  Dense: n_experts = 0, gate = NULL; hb is (hidden).
- * MoE: hb is (n_active, hidden); active_e/active_w (device, n_active) receive the selection. */
+ * MoE: hb is (n_active, hidden); active_e/active_w (device, n_active) receive the selection.
+ * rms_weight == NULL skips the norm (the reference's ffn_cuda test entry has none). */
 int yalm_ffn_glu(float *hb, const float *x, const float *rms_weight, const void *w1, const void *w3,
                  const float *s1, const float *s3, const void *gate, const float *sgate, int dim, int hidden_dim,
                  int act, float norm_eps, int dtype, int n_experts, int n_active, int *active_e,

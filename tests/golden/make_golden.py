@@ -1,0 +1,46 @@
+"""Generates tests/golden/*.npz by running the UNMODIFIED reference (oracle/_ref/libyalm_ref.so, built by
+oracle/Makefile from /root/reference) on seeded random-init tiny models.  Run in the build container
+(where /root/reference exists):   python tests/golden/make_golden.py
+
+Each fixture holds, for one (arch, dtype): the prompt, the reference's greedy tokens (its CPU backend,
+Model::forward + Sampler::sample_argmax, src/model.cpp:396-407, src/sampler.cpp:27-38) for N_GEN steps —
+long enough to run past max_seq_len=64 so the ring buffer and the two attention sinks are exercised —
+and the reference logits at a few of those steps.  The model itself is regenerated from
+(arch, dtype, seed) by yalm_b200.yalm_file.random_model, whose bytes are pinned by a sha256 in the fixture.
+Reference build flags (they affect the last bits): g++ 13.3 -O3 -ffast-math -fopenmp -mavx2
+-mf16c -mfma, 8 OpenMP threads.
+"""
+import hashlib
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, ROOT)
+from oracle import oracle as O  # noqa: E402
+from yalm_b200 import yalm_file as yf  # noqa: E402
+
+CASES = [(a, d) for a in ("tiny", "tiny-moe", "tiny-gelu-clip") for d in ("fp32", "fp16")]
+SEED, PROMPT, N_GEN = 14, [1, 17, 300, 42, 5], 72
+KEEP = [0, 1, 2, 30, 58, 59, 60, 61, 71]   # steps whose logits are stored (pos = len(prompt)-1+step)
+
+
+def main():
+    out_dir = os.path.dirname(os.path.abspath(__file__))
+    for arch, dt in CASES:
+        img = bytes(yf.random_model(yf.ARCHS[arch], dt, seed=SEED))
+        ref = O.RefModel(img)
+        toks, logits = ref.generate(PROMPT, N_GEN, keep_logits=True)
+        kv = [np.stack(ref.kv(l)) for l in range(ref.n_layers)]
+        ref.close()
+        np.savez_compressed(os.path.join(out_dir, f"{arch}-{dt}.npz"), prompt=np.array(PROMPT, np.int32),
+                            tokens=np.array(toks, np.int32), keep=np.array(KEEP, np.int32),
+                            logits=logits[KEEP].astype(np.float32), kv_layer0=kv[0],
+                            sha256=np.frombuffer(hashlib.sha256(img).digest(), np.uint8), seed=SEED)
+        print(arch, dt, toks[:8], "...", "margin(top1-top2) min over steps:",
+              float(np.min(np.sort(logits, axis=1)[:, -1] - np.sort(logits, axis=1)[:, -2])))
+
+
+if __name__ == "__main__":
+    main()

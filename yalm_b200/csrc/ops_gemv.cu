@@ -194,7 +194,8 @@ __global__ void __launch_bounds__(kThreads) ffn_glu_kernel(FfnArgs a) {
 	int *sel_e = reinterpret_cast<int *>(sel_w + kMaxExperts); // kMaxExperts
 	float *xs = smem + 36 + 3 * kMaxExperts;
 	constexpr int EP = WTraits<DT>::EP, B = WTraits<DT>::BYTES;
-	stage_x_rmsnorm<EP>(xs, a.x, a.rms_w, a.dim, a.eps, red);
+	if (a.rms_w) stage_x_rmsnorm<EP>(xs, a.x, a.rms_w, a.dim, a.eps, red);
+	else stage_x_plain<EP>(xs, a.x, a.dim); // test entry ffn_cuda: no norm in front
 	__syncthreads();
 	const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
 	const size_t row_bytes = (size_t)a.dim * B;
@@ -423,7 +424,7 @@ extern "C" int yalm_ffn_glu(float *hb, const float *x, const float *rms_weight, 
                             int hidden_dim, int act, float norm_eps, int dtype, int n_experts, int n_active,
                             int *active_e, float *active_w, float *moe_logits, yalm_stream_t s) {
 	const int ep = ep_of(dtype);
-	if (!ep || !hb || !x || !rms_weight || !w1 || !w3 || dim % ep || dim % 4 || hidden_dim <= 0) return YALM_EINVAL;
+	if (!ep || !hb || !x || !w1 || !w3 || dim % ep || dim % 4 || hidden_dim <= 0) return YALM_EINVAL;
 	if (n_experts < 0 || n_experts > kMaxExperts) return YALM_EINVAL;
 	if (n_experts > 0 && (!gate || !active_e || !active_w || n_active < 1 || n_active > n_experts)) return YALM_EINVAL;
 	FfnArgs a;
