@@ -155,6 +155,9 @@ int yalm_generate_greedy(yalm_model *m, yalm_state *s, int token, int pos, int n
  * which: 0 x, 1 xb2(attn out), 2 hb, 3 q, 4 key_cache(layer), 5 value_cache(layer),
  * 6 active_experts (int), 7 active_experts_weights */
 int yalm_state_read(yalm_model *m, yalm_state *s, int which, int layer, void *dst, size_t bytes);
+/* Mean duration (microseconds, CUDA events on the launching stream) of the dominant kernel — the fused
+ * rmsnorm + w1/w3 + GLU GEMV — over n_steps greedy decode steps x n_layers launches from (token,pos). */
+int yalm_profile_ffn(yalm_model *m, yalm_state *s, int token, int pos, int n_steps, double *mean_us);
 /* Number of kernel launches one forward pass issues in `mode` (for bench.py's gpu_launches). */
 int yalm_forward_launches(const yalm_model *m, int mode);
 

@@ -28,7 +28,7 @@ SYMBOLS = [
     "yalm_matmul_host", "yalm_mha_host", "yalm_ffn_host", "yalm_bench_op",
     "yalm_model_open_file", "yalm_model_open_memory", "yalm_model_cuda", "yalm_model_close", "yalm_model_config",
     "yalm_model_device_bytes", "yalm_state_new", "yalm_state_free", "yalm_forward", "yalm_logits",
-    "yalm_generate_greedy", "yalm_state_read", "yalm_forward_launches",
+    "yalm_generate_greedy", "yalm_state_read", "yalm_forward_launches", "yalm_profile_ffn",
     "yalm_tp_unique_id", "yalm_tp_init", "yalm_tp_finalize", "yalm_error_string", "yalm_version",
 ]
 
@@ -76,6 +76,7 @@ def lib():
     L.yalm_generate_greedy.argtypes = [vp, vp, i, i, i, vp, vp, C.POINTER(f)]
     L.yalm_state_read.argtypes = [vp, vp, i, i, vp, sz]
     L.yalm_forward_launches.argtypes = [vp, i]
+    L.yalm_profile_ffn.argtypes = [vp, vp, i, i, i, C.POINTER(C.c_double)]
     L.yalm_tp_unique_id.argtypes = [vp]
     L.yalm_tp_init.argtypes = [vp, i, i]
     L.yalm_tp_finalize.restype = None
@@ -207,6 +208,11 @@ class InferenceState:
                "generate_greedy")
         self.device_ms = ms.value
         return (toks.tolist(), lg) if keep_logits else toks.tolist()
+
+    def profile_ffn(self, token: int, pos: int, n_steps: int) -> float:
+        us = C.c_double()
+        _check(lib().yalm_profile_ffn(self.model.h, self.h, token, pos, n_steps, C.byref(us)), "profile_ffn")
+        return us.value
 
     def generate(self, prompt, n_gen: int, keep_logits: bool = False):
         """run_completion's loop (src/main.cpp:91-112) with host-side first-max argmax, via forward()."""

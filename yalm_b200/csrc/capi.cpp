@@ -363,3 +363,8 @@ extern "C" int yalm_forward_launches(const yalm_model *m, int mode) {
 	return m->model->launches_per_forward(mode == YALM_MODE_HYDRATE ? InferenceMode::HYDRATE_KV_CACHE
 	                                                                : InferenceMode::OUTPUT_LOGITS);
 }
+
+extern "C" int yalm_profile_ffn(yalm_model *m, yalm_state *s, int token, int pos, int n_steps, double *mean_us) {
+	if (!m || !s) return YALM_EINVAL;
+	return m->model->profile_ffn(*s->state, token, pos, n_steps, mean_us);
+}

@@ -145,6 +145,8 @@ InferenceState::~InferenceState() {
 	_hydrate_graph.destroy();
 	_output_graph.destroy();
 	_greedy_graph.destroy();
+	_profile_graph.destroy();
+	for (cudaEvent_t e : _ffn_events) cudaEventDestroy(e);
 	if (_device == Device::CPU) {
 		delete[] _x;
 		delete[] _xb;
@@ -164,6 +166,14 @@ InferenceState::~InferenceState() {
 		cudaFreeHost(_logits);
 		if (_stream) cudaStreamDestroy(_stream);
 	}
+}
+
+void InferenceState::enable_ffn_timing(bool on) {
+	if (on && _ffn_events.empty()) {
+		_ffn_events.resize(2 * (size_t)_config->n_layers);
+		for (auto &e : _ffn_events) CUDA_CHECK(cudaEventCreate(&e));
+	}
+	_ffn_timing = on;
 }
 
 void InferenceState::cuda() {
@@ -397,10 +407,12 @@ int Block::enqueue(InferenceState &s) const {
 		if (rc) return rc;
 	}
 	const bool moe = c.n_experts > 0;
+	if (s.ffn_timing()) CUDA_CHECK(cudaEventRecord(s.ffn_event(_layer_i, 0), s.stream()));
 	rc = yalm_ffn_glu(s.hb(), s.x(), _rms_ffn_weight, _w1, _w3, _s1, _s3, _moegate, _sgate, c.dim, lhid,
 	                  c.act == ActivationType::SILU ? YALM_ACT_SILU : YALM_ACT_GELU, c.norm_eps, dt, c.n_experts,
 	                  c.n_experts_active, s.active_experts(), s.active_experts_weights(), s.moe_weights(), st);
 	if (rc) return rc;
+	if (s.ffn_timing()) CUDA_CHECK(cudaEventRecord(s.ffn_event(_layer_i, 1), s.stream()));
 	const int k_act = moe ? c.n_experts_active : 1;
 	const int *ae = moe ? s.active_experts() : nullptr;
 	const float *aw = moe ? s.active_experts_weights() : nullptr;
@@ -640,4 +652,32 @@ int Model::generate_greedy(InferenceState &s, int token, int pos, int n_gen, int
 	cudaEventDestroy(e0);
 	cudaEventDestroy(e1);
 	return (int)cudaGetLastError();
+}
+
+int Model::profile_ffn(InferenceState &s, int token, int pos, int n_steps, double *mean_us) {
+	if (_device != Device::CUDA || s.device() != Device::CUDA) return YALM_ENOGPU;
+	const Config &c = *config;
+	if (n_steps < 1 || !mean_us || token < 0 || token >= c.vocab_size || pos < 0) return YALM_EINVAL;
+	cudaStream_t st = s.stream();
+	const int kv_sink = pos >= c.max_seq_len ? KV_SINKS : 0;
+	int h[YALM_CTL_INTS] = {token, pos, kv_sink, kv_sink + (pos - kv_sink) % (c.max_seq_len - kv_sink),
+	                        pos >= c.max_seq_len ? c.max_seq_len : pos + 1, 0, 0, 0};
+	CUDA_CHECK(cudaMemcpyAsync(s.ctl(), h, sizeof(h), cudaMemcpyHostToDevice, st));
+	CUDA_CHECK(cudaStreamSynchronize(st));
+	s.enable_ffn_timing(true);
+	CudaGraph &g = s.profile_graph();
+	if (!g.is_created) capture_graph(g, st, [&]() { return enqueue_forward(s, InferenceMode::OUTPUT_LOGITS, false, true); });
+	s.enable_ffn_timing(false);
+	double total = 0;
+	for (int i = 0; i < n_steps; ++i) {
+		g.launch(st);
+		CUDA_CHECK(cudaStreamSynchronize(st));
+		for (int l = 0; l < c.n_layers; ++l) {
+			float ms = 0.f;
+			CUDA_CHECK(cudaEventElapsedTime(&ms, s.ffn_event(l, 0), s.ffn_event(l, 1)));
+			total += ms;
+		}
+	}
+	*mean_us = 1000.0 * total / ((double)n_steps * c.n_layers);
+	return 0;
 }

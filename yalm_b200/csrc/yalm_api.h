@@ -105,13 +105,21 @@ struct InferenceState {
 	int tokens_capacity() const { return _tokens_cap; }
 	CudaGraph &greedy_graph() { return _greedy_graph; }
 	const Config &config() const { return *_config; }
+	// Optional kernel timing: when enabled, Block::enqueue brackets the w1/w3 GLU kernel (the dominant
+	// kernel: 54 % of a layer's weight bytes) with an event pair per layer.
+	void enable_ffn_timing(bool on);
+	bool ffn_timing() const { return _ffn_timing; }
+	cudaEvent_t ffn_event(int layer, int which) const { return _ffn_events[2 * layer + which]; }
+	CudaGraph &profile_graph() { return _profile_graph; }
 
 private:
 	std::shared_ptr<Config> _config;
 	Device _device = Device::CPU;
 	cudaStream_t _stream = nullptr;
 	InferenceMode _mode = InferenceMode::OUTPUT_LOGITS;
-	CudaGraph _hydrate_graph, _output_graph, _greedy_graph;
+	CudaGraph _hydrate_graph, _output_graph, _greedy_graph, _profile_graph;
+	bool _ffn_timing = false;
+	std::vector<cudaEvent_t> _ffn_events;
 
 	float *_x = nullptr, *_xb = nullptr, *_xb2 = nullptr, *_hb = nullptr, *_hb2 = nullptr;
 	float *_q = nullptr, *_k = nullptr, *_v = nullptr, *_att = nullptr;
@@ -199,6 +207,9 @@ struct Model {
 	// Returns 0 or an error code; see yalm_generate_greedy in include/yalm_b200.h.
 	int generate_greedy(InferenceState &s, int token, int pos, int n_gen, int *tokens_out, float *logits_out,
 	                    float *device_ms);
+	// n_steps greedy steps with an event pair around every layer's w1/w3 GLU kernel; returns the mean
+	// duration of that kernel in microseconds (CUDA events on the launching stream).
+	int profile_ffn(InferenceState &s, int token, int pos, int n_steps, double *mean_us);
 	size_t device_bytes() const { return _device_bytes; }
 	int launches_per_forward(InferenceMode mode) const;
 

@@ -340,3 +340,42 @@ def weight_bytes_per_token(arch: Arch, dtype: str) -> int:
 
 def kv_bytes_per_token(arch: Arch, kv_len: int) -> int:
     return 2 * kv_len * arch.n_kv_heads * arch.head_dim * 2 * arch.n_layers
+
+
+def random_model_streamed(arch: Arch, dtype: str = "fp16", seed: int = 0, lm_scale: float = 4.0,
+                          device: str = "cpu", pinned: bool = False) -> np.ndarray:
+    """Same model as random_model() (identical bytes), built straight into one preallocated uint8 array so
+    peak host memory is 1x the image (bench-size models: 14 GB Mistral-7B, 93 GB Mixtral)."""
+    st = _ST_OF_DTYPE[dtype]
+    esz = {"F32": 4, "F16": 2, "F8_E4M3": 1}[st]
+    entries = []          # (name, st dtype, shape, nbytes)
+    for name, shape, kind in tensor_plan(arch):
+        n = int(np.prod(shape))
+        if kind == "norm":
+            entries.append((name, "F32", shape, 4 * n))
+        else:
+            entries.append((name, st, shape, esz * n))
+            if dtype == "fp8":
+                entries.append((name + ".scale", "F32", shape[:-1], 4 * int(np.prod(shape[:-1]))))
+    tok = synthetic_tokens(arch.vocab_size)
+    entries.append(("tokenizer.tokens", "U8", tok.shape, tok.nbytes))
+    header, off = {"__metadata__": metadata_of(arch, dtype)}, 0
+    for name, sdt, shape, nb in entries:
+        off = (off + 63) // 64 * 64
+        header[name] = {"dtype": sdt, "shape": list(shape), "data_offsets": [off, off + nb]}
+        off += nb
+    hj = json.dumps(header, separators=(",", ":")).encode()
+    hj += b" " * ((-(8 + len(hj))) % 64)
+    total = 8 + len(hj) + off
+    if pinned:
+        import torch
+        img = torch.empty(total, dtype=torch.uint8, pin_memory=True).numpy()
+    else:
+        img = np.empty(total, np.uint8)
+    img[:8] = np.frombuffer(struct.pack("<Q", len(hj)), np.uint8)
+    img[8:8 + len(hj)] = np.frombuffer(hj, np.uint8)
+    base = 8 + len(hj)
+    for name, arr, _ in random_tensors(arch, dtype, seed, lm_scale, device):
+        s, e = header[name]["data_offsets"]
+        img[base + s: base + e] = np.ascontiguousarray(arr).view(np.uint8).reshape(-1)
+    return img
