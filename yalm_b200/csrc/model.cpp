@@ -407,12 +407,12 @@ int Block::enqueue(InferenceState &s) const {
 		if (rc) return rc;
 	}
 	const bool moe = c.n_experts > 0;
-	if (s.ffn_timing()) CUDA_CHECK(cudaEventRecord(s.ffn_event(_layer_i, 0), s.stream()));
+	if (s.ffn_timing()) CUDA_CHECK(cudaEventRecordWithFlags(s.ffn_event(_layer_i, 0), s.stream(), cudaEventRecordExternal));
 	rc = yalm_ffn_glu(s.hb(), s.x(), _rms_ffn_weight, _w1, _w3, _s1, _s3, _moegate, _sgate, c.dim, lhid,
 	                  c.act == ActivationType::SILU ? YALM_ACT_SILU : YALM_ACT_GELU, c.norm_eps, dt, c.n_experts,
 	                  c.n_experts_active, s.active_experts(), s.active_experts_weights(), s.moe_weights(), st);
 	if (rc) return rc;
-	if (s.ffn_timing()) CUDA_CHECK(cudaEventRecord(s.ffn_event(_layer_i, 1), s.stream()));
+	if (s.ffn_timing()) CUDA_CHECK(cudaEventRecordWithFlags(s.ffn_event(_layer_i, 1), s.stream(), cudaEventRecordExternal));
 	const int k_act = moe ? c.n_experts_active : 1;
 	const int *ae = moe ? s.active_experts() : nullptr;
 	const float *aw = moe ? s.active_experts_weights() : nullptr;
