@@ -245,7 +245,8 @@ def main():
     tok, pos = toks[-1], pos + K
     clk = clocks.stop() if rank == 0 else None
     # ---- dominant kernel, CUDA events around each launch (separate pass, does not perturb the numbers above) -----
-    ffn_us = state.profile_ffn(tok, pos - 1, min(K, 8))
+    mega = model.uses_megakernel()
+    ffn_us = 0.0 if mega else state.profile_ffn(tok, pos - 1, min(K, 8))
 
     if world > 1:
         t = torch.tensor([dev_ms, e2e_s, ffn_us], dtype=torch.float64, device="cuda")
@@ -256,14 +257,21 @@ def main():
         wsize = {"fp32": 4, "fp16": 2, "fp8": 1}[dtype]
         k_act = max(1, arch.n_experts_active)
         ffn_bytes = k_act * 2 * arch.hidden_dim * arch.dim * wsize / world + 4 * arch.dim * 2
-        achieved = ffn_bytes / (ffn_us * 1e-6) / 1e9
         wbytes = yf.weight_bytes_per_token(arch, dtype)
         kvbytes = yf.kv_bytes_per_token(arch, min(context, pos))
         tok_s = K / (dev_ms * 1e-3)
+        if mega:
+            # one persistent kernel per token IS the step: algorithmic bytes = weights + KV rows it reads
+            kname = "decode_mega_kernel (whole token: all GEMVs + flash-decode + LM head, TMA ring)"
+            ffn_bytes = wbytes + yf.kv_bytes_per_token(arch, min(context, pos - K // 2))
+            ffn_us = 1000.0 * dev_ms / K
+        else:
+            kname = "ffn_glu_kernel (rmsnorm + w1/w3 GEMV + GLU)"
+        achieved = ffn_bytes / (ffn_us * 1e-6) / 1e9
         line = dict(base, impl="ours", value=tok_s, ms_per_step=dev_ms / K, clocks=clk,
                     e2e={"value": K / e2e_s, "unit": "tok/s", "h2d_bytes_per_step": 8, "d2h_bytes_per_step": 4 * V},
-                    gpu_launches=(model.launches(api.MODE_LOGITS) + 1) * K,
-                    roofline={"bound": "hbm", "kernel": "ffn_glu_kernel (rmsnorm + w1/w3 GEMV + GLU)",
+                    gpu_launches=(model.launches(api.MODE_LOGITS) + (0 if mega else 1)) * K,
+                    roofline={"bound": "hbm", "kernel": kname,
                               "achieved": achieved, "peak": peak, "peak_source": peak_src, "unit": "GB/s",
                               "frac": achieved / peak, "traffic": None, "bytes_per_launch": ffn_bytes,
                               "launch_us": ffn_us},

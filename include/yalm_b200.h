@@ -67,21 +67,27 @@ void init_cuda_stream(yalm_stream_t *stream);
 int yalm_embed(float *x, const void *table, const float *row_scale, int dim, int dtype, int *ctl, int token,
                int pos, int max_seq_len, yalm_stream_t s);
 
+/* KV cache layout on the device: HEAD-MAJOR fp16 ring, (n_kv_heads, max_seq_len, head_dim) — one contiguous
+ * slab per KV head, so a run of rows of one head is one 1-D bulk (TMA) copy.  The reference keeps
+ * (max_seq_len, n_kv_heads, head_dim) (src/model.cpp:171-172); the host-pointer test entry yalm_mha_host and
+ * the yalm_state_read taps take / return the reference layout and convert. */
+
 /* rmsnorm -> q,k,v GEMVs -> clip -> RoPE(q,k) -> fp16 KV append at ctl.kv_pos -> sink re-rotation.
  * Replaces rmsnorm + fused_qkv_matmul_clip + fused_rope_and_cache_update + rotate_sink_tokens
  * (src/infer.cu:526-539, 291-336, 642-697).  Weights are (out,in) row-major, y = W x. */
 int yalm_qkv_rope_append(float *q_out, uint16_t *key_cache, uint16_t *value_cache, const float *x,
                          const float *rms_weight, const void *wq, const void *wk, const void *wv,
                          const float *sq, const float *sk, const float *sv, int dim, int n_heads, int n_kv_heads,
-                         int head_dim, int rotary_dim, float rope_theta, float norm_eps, float qkv_clip,
-                         int dtype, const int *ctl, yalm_stream_t s);
+                         int head_dim, int rotary_dim, int max_seq_len, float rope_theta, float norm_eps,
+                         float qkv_clip, int dtype, const int *ctl, yalm_stream_t s);
 
 /* Split-K flash-decode GQA attention over the fp16 KV ring: replaces attn_dot + attn_softmax +
  * att_mix (src/infer.cu:338-524).  `workspace` holds the per-split partials; size from
  * yalm_attn_workspace_bytes().  out is (n_heads*head_dim) fp32. */
 size_t yalm_attn_workspace_bytes(int n_heads, int n_kv_heads, int head_dim);
 int yalm_attn_decode(float *out, const uint16_t *key_cache, const uint16_t *value_cache, const float *q,
-                     void *workspace, int n_heads, int n_kv_heads, int head_dim, const int *ctl, yalm_stream_t s);
+                     void *workspace, int n_heads, int n_kv_heads, int head_dim, int max_seq_len, const int *ctl,
+                     yalm_stream_t s);
 
 /* out[i] = (residual ? residual[i] : 0) + sum_k aw[k] * (W[e_k] v_k)[i]   (wo and w2 + residual:
  * fused_matmul_add_residuals, src/infer.cu:270-288; MoE mix: src/infer.cpp:377-383).
@@ -160,6 +166,10 @@ int yalm_state_read(yalm_model *m, yalm_state *s, int which, int layer, void *ds
 int yalm_profile_ffn(yalm_model *m, yalm_state *s, int token, int pos, int n_steps, double *mean_us);
 /* Number of kernel launches one forward pass issues in `mode` (for bench.py's gpu_launches). */
 int yalm_forward_launches(const yalm_model *m, int mode);
+/* 1 when forward() is one persistent cooperative kernel per token (unsharded dense models; the weight and KV
+ * tiles of the whole pass stream through a shared-memory TMA ring), 0 when it is the per-op kernel graph
+ * (tensor-parallel shards, MoE, shapes the tile planner rejects, or YALM_B200_MEGA=0 in the environment). */
+int yalm_model_uses_megakernel(const yalm_model *m);
 
 /* Tensor-parallel plumbing (one process per GPU).  The 128-byte NCCL unique id is created by rank 0
  * with yalm_tp_unique_id() and distributed by the caller (torch.distributed / MPI / files). */

@@ -1,0 +1,121 @@
+"""-m gpu: the whole-token persistent kernel (decode_mega.cuh) — one cooperative launch per token with the
+weight / KV tiles streamed through a shared-memory TMA ring — against the oracle and against the per-op kernel
+path (YALM_B200_MEGA=0) on the same models: tile shapes with and without K splits, every compiled
+(head_dim, group) pair, sliding window + sinks, on-device greedy loop."""
+import os
+
+import numpy as np
+import pytest
+
+from conftest import LOGIT_TOL, golden_case
+from yalm_b200 import api
+from yalm_b200 import yalm_file as yf
+
+pytestmark = pytest.mark.gpu
+
+
+def run(img, prompt, n_gen, context=0, mega=True, device_loop=False):
+    old = os.environ.get("YALM_B200_MEGA")
+    os.environ["YALM_B200_MEGA"] = "1" if mega else "0"
+    try:
+        m = api.Model(img, context).cuda()
+    finally:
+        if old is None:
+            del os.environ["YALM_B200_MEGA"]
+        else:
+            os.environ["YALM_B200_MEGA"] = old
+    used = m.uses_megakernel()
+    s = api.InferenceState(m)
+    if device_loop:
+        for pos, tok in enumerate(prompt[:-1]):
+            s.forward(tok, pos, api.MODE_HYDRATE)
+        toks, lg = s.generate_greedy(prompt[-1], len(prompt) - 1, n_gen, keep_logits=True)
+    else:
+        toks, lg = s.generate(prompt, n_gen, keep_logits=True)
+    s.close()
+    m.close()
+    return toks, lg, used
+
+
+def test_path_selection():
+    _, img = golden_case("tiny-fp16")
+    assert run(img, [1, 2], 2)[2] is True
+    assert run(img, [1, 2], 2, mega=False)[2] is False
+    _, moe = golden_case("tiny-moe-fp16")
+    assert run(moe, [1, 2], 2)[2] is False          # MoE stays on the per-op path
+
+
+@pytest.mark.parametrize("name", ["tiny-fp32", "tiny-fp16", "tiny-gelu-clip-fp32", "tiny-gelu-clip-fp16"])
+def test_mega_matches_reference_golden_and_per_op_path(name):
+    fx, img = golden_case(name)
+    prompt, n = fx["prompt"].tolist(), len(fx["tokens"])
+    tm, lm, used = run(img, prompt, n)
+    assert used
+    assert np.abs(lm[fx["keep"]] - fx["logits"]).max() < LOGIT_TOL
+    assert tm == fx["tokens"].tolist()
+    to, lo, _ = run(img, prompt, n, mega=False)
+    assert np.abs(lm - lo).max() < 2e-3
+    assert tm == to
+    td, ld, _ = run(img, prompt, n, device_loop=True)      # on-device arg-max + control-block advance
+    assert td == tm
+    assert np.abs(ld - lm).max() < 1e-5
+
+
+CUSTOM = {
+    # K-split tiles: fp32 rows of hidden 9216 (36 KB) exceed one 32 KB ring stage
+    "ksplit-fp32": (yf.Arch(256, 9216, 32, 1, 8, 2, 512, 64, 10000.0, name="ksplit"), "fp32"),
+    # head_dim 64 / group 4 (Llama-3.2-1B geometry), ragged vocab tile count
+    "hd64-fp16": (yf.Arch(512, 1024, 64, 2, 8, 2, 1000, 256, 500000.0, name="hd64"), "fp16"),
+    # head_dim 128 / group 8 (70B geometry)
+    "hd128g8-fp16": (yf.Arch(1024, 1536, 128, 1, 8, 1, 512, 128, 500000.0, name="hd128g8"), "fp16"),
+    "hd128g4-fp8": (yf.Arch(1024, 2048, 128, 2, 8, 2, 512, 128, 1000000.0, name="hd128g4"), "fp8"),
+}
+
+
+@pytest.mark.parametrize("case", sorted(CUSTOM))
+def test_mega_shapes_vs_oracle(oracle, case):
+    arch, dt = CUSTOM[case]
+    img = bytes(yf.random_model(arch, dt, seed=3))
+    ref_img = bytes(yf.dequantized_fp32_image(img)) if dt == "fp8" else img
+    prompt = [1, 5, 9, 200, 77]
+    to, lo = oracle.OracleModel(ref_img).generate(prompt, 40, keep_logits=True)
+    tg, lg, used = run(img, prompt, 40)
+    assert used
+    assert np.abs(lg - lo).max() < LOGIT_TOL
+    assert tg == to
+
+
+def test_mega_sliding_window_and_sinks(oracle):
+    """-T 24 on a 2-layer model, 90 steps: the ring wraps 3 times, the two sink keys are re-rotated every step,
+    and the producer's prefetched KV tiles must not leak stale sink / current rows into the scores."""
+    arch = yf.Arch(256, 512, 32, 2, 8, 2, 512, 64, 10000.0, name="tiny-win")
+    img = bytes(yf.random_model(arch, "fp16", seed=21))
+    to, lo = oracle.OracleModel(img, context=24).generate([1, 2, 3], 90, keep_logits=True)
+    tg, lg, used = run(img, [1, 2, 3], 90, context=24)
+    assert used
+    assert np.abs(lg - lo).max() < LOGIT_TOL
+    assert tg == to
+
+
+def test_mega_long_context_many_tiles(oracle):
+    """kv_len up to 700 at head_dim 32 (256-row KV tiles, several per head) and units spread over all CTAs."""
+    arch = yf.Arch(256, 512, 32, 1, 8, 2, 512, 1024, 10000.0, name="tiny-long")
+    img = bytes(yf.random_model(arch, "fp16", seed=8))
+    prompt = [(i * 37 + 1) % 512 for i in range(690)]
+    to, lo = oracle.OracleModel(img).generate(prompt, 10, keep_logits=True)
+    tg, lg, used = run(img, prompt, 10)
+    assert used
+    assert np.abs(lg - lo).max() < LOGIT_TOL
+    assert tg == to
+
+
+def test_mega_deterministic():
+    fx, img = golden_case("tiny-fp16")
+    a = run(img, fx["prompt"].tolist(), 30)[1]
+    b = run(img, fx["prompt"].tolist(), 30)[1]
+    assert (a == b).all()
+
+
+def test_stream_probe_runs():
+    us, by = api.bench_op("stream", iters=3, warmup=0)
+    assert by / us / 1e3 > 1000.0        # GB/s: anything on a B200 streams faster than 1 TB/s

@@ -28,7 +28,8 @@ SYMBOLS = [
     "yalm_matmul_host", "yalm_mha_host", "yalm_ffn_host", "yalm_bench_op",
     "yalm_model_open_file", "yalm_model_open_memory", "yalm_model_cuda", "yalm_model_close", "yalm_model_config",
     "yalm_model_device_bytes", "yalm_state_new", "yalm_state_free", "yalm_forward", "yalm_logits",
-    "yalm_generate_greedy", "yalm_state_read", "yalm_forward_launches", "yalm_profile_ffn",
+    "yalm_generate_greedy", "yalm_state_read", "yalm_forward_launches", "yalm_model_uses_megakernel",
+    "yalm_profile_ffn",
     "yalm_tp_unique_id", "yalm_tp_init", "yalm_tp_finalize", "yalm_error_string", "yalm_version",
 ]
 
@@ -76,6 +77,7 @@ def lib():
     L.yalm_generate_greedy.argtypes = [vp, vp, i, i, i, vp, vp, C.POINTER(f)]
     L.yalm_state_read.argtypes = [vp, vp, i, i, vp, sz]
     L.yalm_forward_launches.argtypes = [vp, i]
+    L.yalm_model_uses_megakernel.argtypes = [vp]
     L.yalm_profile_ffn.argtypes = [vp, vp, i, i, i, C.POINTER(C.c_double)]
     L.yalm_tp_unique_id.argtypes = [vp]
     L.yalm_tp_init.argtypes = [vp, i, i]
@@ -167,6 +169,9 @@ class Model:
 
     def device_bytes(self) -> int:
         return lib().yalm_model_device_bytes(self.h)
+
+    def uses_megakernel(self) -> bool:
+        return bool(lib().yalm_model_uses_megakernel(self.h))
 
     def launches(self, mode=MODE_LOGITS) -> int:
         return lib().yalm_forward_launches(self.h, mode)

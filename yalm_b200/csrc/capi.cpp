@@ -14,6 +14,7 @@ extern "C" int yalm_attn_generic(float *out, float *att, const uint16_t *key_cac
                                  const float *q, int n_heads, int n_kv_heads, int head_dim, int max_seq_len,
                                  int kv_len, const int *ctl, yalm_stream_t s);
 extern "C" int yalm_attn_is_fast_shape(int n_heads, int n_kv_heads, int head_dim);
+extern "C" int yalm_stream_probe(size_t bytes, int iters, double *usec);
 
 namespace {
 
@@ -68,8 +69,16 @@ extern "C" int yalm_mha_host(float *xout, float *att, const uint16_t *kb, const 
 	if (!have_gpu()) return YALM_ENOGPU;
 	if (!xout || !kb || !vb || !q || kv_len < 1 || kv_len > max_seq_len || n_kv_heads < 1 || n_heads % n_kv_heads)
 		return YALM_EINVAL;
-	const size_t kv_bytes = sizeof(uint16_t) * (size_t)max_seq_len * n_kv_heads * head_dim;
-	DevBuf dk(kb, kv_bytes), dv(vb, kv_bytes), dq(q, sizeof(float) * n_heads * head_dim), dout, datt, dctl, dws;
+	const size_t kv_elems = (size_t)max_seq_len * n_kv_heads * head_dim, kv_bytes = sizeof(uint16_t) * kv_elems;
+	// reference layout (t, kv head, d) -> the device's head-major ring (kv head, t, d)
+	std::vector<uint16_t> kh(kv_elems), vh(kv_elems);
+	for (int t = 0; t < max_seq_len; ++t)
+		for (int h = 0; h < n_kv_heads; ++h) {
+			const size_t src = ((size_t)t * n_kv_heads + h) * head_dim, dst = ((size_t)h * max_seq_len + t) * head_dim;
+			memcpy(&kh[dst], kb + src, sizeof(uint16_t) * head_dim);
+			memcpy(&vh[dst], vb + src, sizeof(uint16_t) * head_dim);
+		}
+	DevBuf dk(kh.data(), kv_bytes), dv(vh.data(), kv_bytes), dq(q, sizeof(float) * n_heads * head_dim), dout, datt, dctl, dws;
 	RET_IF(dout.alloc(sizeof(float) * n_heads * head_dim));
 	int ctl[YALM_CTL_INTS] = {0, kv_len - 1, 0, kv_len - 1, kv_len, 0, 0, 0};
 	RET_IF(dctl.alloc(sizeof(ctl), ctl));
@@ -85,7 +94,7 @@ extern "C" int yalm_mha_host(float *xout, float *att, const uint16_t *kb, const 
 	if (fast) { // xout always comes from the production flash-decode kernel when the shape allows
 		RET_IF(dws.alloc(yalm_attn_workspace_bytes(n_heads, n_kv_heads, head_dim)));
 		RET_IF(yalm_attn_decode(dout.as<float>(), dk.as<uint16_t>(), dv.as<uint16_t>(), dq.as<float>(), dws.p, n_heads,
-		                        n_kv_heads, head_dim, dctl.as<int>(), nullptr));
+		                        n_kv_heads, head_dim, max_seq_len, dctl.as<int>(), nullptr));
 		RET_IF(cudaDeviceSynchronize());
 	}
 	return (int)cudaMemcpy(xout, dout.p, sizeof(float) * n_heads * head_dim, cudaMemcpyDeviceToHost);
@@ -153,6 +162,11 @@ extern "C" int yalm_bench_op(const char *name, int iters, int warmup, double *us
 	if (!have_gpu()) return YALM_ENOGPU;
 	if (!name || iters < 1 || !usec) return YALM_EINVAL;
 	const std::string k(name);
+	if (k == "stream") { // ceiling of the megakernel's TMA ring: pure streaming read of 4 GiB
+		const double b = 4.0 * (1u << 30);
+		if (bytes) *bytes = b;
+		return yalm_stream_probe((size_t)b, iters, usec);
+	}
 	const int head_dim = 128, n_heads = 32, dim = head_dim * n_heads, n_kv_heads = 8, kv_len = 4096;
 	int hidden = 14336;
 	cudaStream_t st;
@@ -204,7 +218,7 @@ extern "C" int yalm_bench_op(const char *name, int iters, int warmup, double *us
 		algo_bytes = 2.0 * kvb;
 		rc = timed([&] {
 			return yalm_attn_decode(out.as<float>(), kb.as<uint16_t>(), vb.as<uint16_t>(), q.as<float>(), ws.p, n_heads,
-			                        n_kv_heads, head_dim, ctl.as<int>(), st);
+			                        n_kv_heads, head_dim, kv_len, ctl.as<int>(), st);
 		});
 	} else if (k == "ffn") {
 		const size_t wb = 2 * (size_t)dim * hidden;
@@ -356,12 +370,31 @@ extern "C" int yalm_state_read(yalm_model *m, yalm_state *sh, int which, int lay
 	default: return YALM_EINVAL;
 	}
 	RET_IF(cudaStreamSynchronize(s.stream()));
+	if (which == 4 || which == 5) {
+		// device ring is head-major; the tap returns the reference layout (t, kv head, d)
+		const Config &c = *m->model->config;
+		const int H = c.local_kv_heads(), D = c.head_dim, T = c.max_seq_len;
+		const size_t n = (size_t)H * T * D;
+		if (bytes > n * sizeof(uint16_t) || bytes % (sizeof(uint16_t) * H * D)) return YALM_EINVAL;
+		std::vector<uint16_t> tmp(n);
+		RET_IF(cudaMemcpy(tmp.data(), src, n * sizeof(uint16_t), cudaMemcpyDeviceToHost));
+		const int rows = (int)(bytes / (sizeof(uint16_t) * H * D));
+		uint16_t *out = static_cast<uint16_t *>(dst);
+		for (int t = 0; t < rows; ++t)
+			for (int h = 0; h < H; ++h)
+				memcpy(out + ((size_t)t * H + h) * D, &tmp[((size_t)h * T + t) * D], sizeof(uint16_t) * D);
+		return 0;
+	}
 	return (int)cudaMemcpy(dst, src, bytes, cudaMemcpyDeviceToHost);
 }
 
 extern "C" int yalm_forward_launches(const yalm_model *m, int mode) {
 	return m->model->launches_per_forward(mode == YALM_MODE_HYDRATE ? InferenceMode::HYDRATE_KV_CACHE
 	                                                                : InferenceMode::OUTPUT_LOGITS);
+}
+
+extern "C" int yalm_model_uses_megakernel(const yalm_model *m) {
+	return m && m->model->uses_megakernel() ? 1 : 0;
 }
 
 extern "C" int yalm_profile_ffn(yalm_model *m, yalm_state *s, int token, int pos, int n_steps, double *mean_us) {

@@ -1,0 +1,167 @@
+// Host side of the whole-token persistent decode kernel (planning, launch) and the streaming probe.
+// The kernel itself is in decode_mega.cuh, instantiated per weight type in decode_mega_{f32,f16,f8}.cu.
+#include "decode_mega.cuh"
+#include "launch.h"
+
+#include <algorithm>
+
+namespace yalm {
+namespace mega {
+
+// Pure streaming probe: the same ring and bulk copies over a flat buffer, consumers only wait and release.
+// Its GB/s is the ceiling the megakernel can reach on this part (yalm_bench_op("stream")).
+__global__ void __launch_bounds__(kThreads, 1) stream_probe_kernel(const char *buf, size_t bytes, int stages, unsigned *sink) {
+	extern __shared__ __align__(128) unsigned char smem_raw[];
+	uint64_t *bars = reinterpret_cast<uint64_t *>(smem_raw + (size_t)stages * kStageBytes);
+	const uint32_t full0 = smem_u32(bars), empty0 = full0 + 8 * kMaxStages, st0 = smem_u32(smem_raw);
+	const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+	if (threadIdx.x == 0) {
+		for (int i = 0; i < stages; ++i) {
+			mbar_init(full0 + 8 * i, 1);
+			mbar_init(empty0 + 8 * i, kConsumerWarps);
+		}
+		asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+	}
+	__syncthreads();
+	const size_t ntiles = bytes / kStageBytes;
+	if (warp == kConsumerWarps) {
+		if (lane != 0) return;
+		const uint64_t pol = policy_evict_first();
+		uint32_t it = 0;
+		for (size_t t = blockIdx.x; t < ntiles; t += gridDim.x, ++it) {
+			const uint32_t s = it % stages, par = ((it / stages) & 1u) ^ 1u;
+			mbar_wait(empty0 + 8 * s, par);
+			mbar_expect_tx(full0 + 8 * s, kStageBytes);
+			bulk_g2s(st0 + s * kStageBytes, buf + t * kStageBytes, kStageBytes, full0 + 8 * s, pol);
+		}
+		return;
+	}
+	uint32_t it = 0;
+	unsigned acc = 0;
+	for (size_t t = blockIdx.x; t < ntiles; t += gridDim.x, ++it) {
+		const uint32_t s = it % stages, par = (it / stages) & 1u;
+		mbar_wait(full0 + 8 * s, par);
+		acc += *reinterpret_cast<const unsigned *>(smem_raw + (size_t)s * kStageBytes + threadIdx.x * 16);
+		__syncwarp();
+		if (lane == 0) mbar_arrive(empty0 + 8 * s);
+	}
+	if (acc == 0x12345678u) *sink = acc;
+}
+
+// ---- host side --------------------------------------------------------------------------------------------
+static inline int ep_of(int dtype) {
+	return dtype == YALM_F32 ? 4 : dtype == YALM_F16 ? 8 : dtype == YALM_F8E4M3 ? 16 : 0;
+}
+static inline int bytes_of(int dtype) {
+	return dtype == YALM_F32 ? 4 : dtype == YALM_F16 ? 2 : 1;
+}
+static inline int padded(int n, int ep) {
+	const int ch = 32 * ep;
+	return (n + ch - 1) / ch * ch;
+}
+
+size_t attn_ws_floats(int grid, int n_heads, int head_dim) {
+	return (size_t)grid * n_heads * (head_dim + 2);
+}
+
+const void *kernel_f32(int head_dim, int g);
+const void *kernel_f16(int head_dim, int g);
+const void *kernel_f8(int head_dim, int g);
+
+static const void *kernel_of(int dtype, int head_dim, int g) {
+	switch (dtype) {
+	case YALM_F32: return kernel_f32(head_dim, g);
+	case YALM_F16: return kernel_f16(head_dim, g);
+	case YALM_F8E4M3: return kernel_f8(head_dim, g);
+	}
+	return nullptr;
+}
+
+Plan plan(int dtype, int dim, int q_dim, int kv_dim, int head_dim, int hidden, int vocab, int n_heads, int n_kv_heads,
+          int n_experts, int n_active) {
+	Plan p;
+	const int ep = ep_of(dtype), B = bytes_of(dtype);
+	if (!ep || n_experts > 0) return p;
+	(void)n_active;
+	if (n_kv_heads <= 0 || n_heads % n_kv_heads) return p;
+	const int G = n_heads / n_kv_heads;
+	p.kernel = kernel_of(dtype, head_dim, G);
+	if (!p.kernel) return p;
+	if (dim % ep || q_dim % ep || hidden % ep || dim % 4 || q_dim % 4 || hidden % 4) return p;
+	Shape s;
+	if (!tile_shape(q_dim, kv_dim, dim, B, ep, false, true, &s)) return p;
+	if (!tile_shape(dim, 0, q_dim, B, ep, false, false, &s)) return p;
+	if (!tile_shape(hidden, 0, dim, B, ep, true, true, &s)) return p;
+	if (!tile_shape(dim, 0, hidden, B, ep, false, false, &s)) return p;
+	if (!tile_shape(vocab, 0, dim, B, ep, false, false, &s)) return p;
+	const DeviceInfo &di = device_info();
+	int coop = 0, dev = 0;
+	cudaGetDevice(&dev);
+	cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
+	if (!coop || di.sms < 1) return p;
+	p.grid = di.sms;
+	int vf = std::max(padded(dim, ep), std::max(padded(q_dim, ep), padded(hidden, ep)));
+	vf = std::max(vf, kConsumerWarps * G * (head_dim + 2));
+	vf = std::max(vf, p.grid * G + G + 32);
+	p.vec_floats = (vf + 31) / 32 * 32;
+	const size_t fixed = (size_t)p.vec_floats * 4 + (2 * kConsumerWarps * 4 + 16 + 16) * 4 + 2 * kMaxStages * 8;
+	const long room = (long)di.max_smem_optin - (long)fixed;
+	p.stages = (int)std::min<long>(kMaxStages, room / kStageBytes);
+	if (p.stages < 2) return p;
+	p.smem = (size_t)p.stages * kStageBytes + fixed;
+	p.dtype = dtype;
+	if (cudaFuncSetAttribute(p.kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem) != cudaSuccess) {
+		cudaGetLastError();
+		return p;
+	}
+	int occ = 0;
+	if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, p.kernel, kThreads, p.smem) != cudaSuccess || occ < 1) {
+		cudaGetLastError();
+		return p;
+	}
+	p.ok = true;
+	return p;
+}
+
+int launch(const Plan &p, const Args &a, cudaStream_t st) {
+	if (!p.ok) return YALM_EINVAL;
+	Args args = a;
+	args.stages = p.stages, args.vec_floats = p.vec_floats;
+	void *params[] = {&args};
+	return (int)cudaLaunchCooperativeKernel(p.kernel, dim3(p.grid), dim3(kThreads), params, p.smem, st);
+}
+
+} // namespace mega
+} // namespace yalm
+
+// Streaming ceiling of the ring (GB/s = bytes / usec / 1e3): `iters` timed launches over a `bytes` buffer.
+extern "C" int yalm_stream_probe(size_t bytes, int iters, double *usec) {
+	using namespace yalm;
+	using namespace yalm::mega;
+	if (!usec || iters < 1 || bytes < (size_t)kStageBytes) return YALM_EINVAL;
+	const DeviceInfo &di = device_info();
+	const int stages = (int)std::min<long>(kMaxStages, ((long)di.max_smem_optin - 256) / kStageBytes);
+	const size_t smem = (size_t)stages * kStageBytes + 2 * kMaxStages * 8;
+	YALM_TRY(cudaFuncSetAttribute(stream_probe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+	char *buf = nullptr;
+	unsigned *sink = nullptr;
+	YALM_TRY(cudaMalloc(&buf, bytes));
+	YALM_TRY(cudaMalloc(&sink, 4));
+	YALM_TRY(cudaMemset(buf, 1, bytes));
+	cudaEvent_t e0, e1;
+	cudaEventCreate(&e0);
+	cudaEventCreate(&e1);
+	for (int i = 0; i < 2; ++i) stream_probe_kernel<<<di.sms, kThreads, smem>>>(buf, bytes, stages, sink);
+	cudaEventRecord(e0);
+	for (int i = 0; i < iters; ++i) stream_probe_kernel<<<di.sms, kThreads, smem>>>(buf, bytes, stages, sink);
+	cudaEventRecord(e1);
+	cudaError_t err = cudaDeviceSynchronize();
+	float ms = 0.f;
+	cudaEventElapsedTime(&ms, e0, e1);
+	cudaEventDestroy(e0);
+	cudaEventDestroy(e1);
+	cudaFree(buf);
+	cudaFree(sink);
+	*usec = 1000.0 * ms / iters;
+	return (int)err;
+}

@@ -1,0 +1,10 @@
+// decode_mega_kernel instantiations for YALM_F16 weights (one translation unit per weight type: build time).
+#include "decode_mega.cuh"
+
+namespace yalm {
+namespace mega {
+const void *kernel_f16(int head_dim, int g) {
+	return kernel_for<YALM_F16>(head_dim, g);
+}
+} // namespace mega
+} // namespace yalm

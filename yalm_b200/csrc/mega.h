@@ -1,0 +1,73 @@
+// Whole-token persistent decode kernel ("megakernel"): one cooperative launch per token, one CTA per SM.
+// A producer warp streams every weight / KV tile of the forward pass through a shared-memory ring with
+// 1-D bulk async copies (TMA engine, mbarrier completion) in a fixed per-CTA order, running ahead of the
+// eight consumer warps by the depth of the ring, so the HBM pipe stays full across the ~160 phase
+// boundaries (grid barriers) of a 32-layer model instead of draining at every kernel launch.
+// Host-side planning and launch; the kernel is in decode_mega.cu.
+#pragma once
+
+#include <cuda_runtime_api.h>
+#include <stddef.h>
+#include <stdint.h>
+
+namespace yalm {
+namespace mega {
+
+constexpr int kStageBytes = 32768; // one ring stage = one weight tile or one K+V tile pair
+constexpr int kConsumerWarps = 8;
+constexpr int kThreads = (kConsumerWarps + 1) * 32; // + the producer warp
+constexpr int kMaxStages = 8;
+
+// Per-layer device pointers (weights are (out,in) row-major; KV cache is head-major, see yalm_b200.h).
+struct Layer {
+	const char *wq, *wk, *wv, *wo, *w1, *w2, *w3, *gate;
+	const float *rms_att, *rms_ffn;
+	const float *sq, *sk, *sv, *so, *s1, *s2, *s3, *sgate; // fp8 per-row scales (null otherwise)
+	uint16_t *kc, *vc;
+};
+
+enum Mode { kHydrate = 0, kLogits = 1, kGreedy = 2 };
+
+struct Args {
+	const Layer *layers;
+	int n_layers;
+	int dim, q_dim, kv_dim, head_dim, hidden, vocab, n_heads, n_kv_heads, rotary_dim, max_seq_len, act;
+	int n_experts, n_active;
+	float theta, eps, clip;
+	const char *embed;
+	const float *embed_scale, *rms_final;
+	const char *wcls;
+	const float *wcls_scale;
+	// activations (global, fp32)
+	float *x, *q, *att_out, *hb, *logits;
+	float *moe_logits, *active_w;
+	int *active_e;
+	// attention split partials: acc (n_kv, grid, G, HD), ml (n_kv, grid, G, 2)
+	float *ws_acc, *ws_ml;
+	unsigned *head_counters; // (n_kv) arrival counters, zero between uses
+	unsigned *sync;          // [0] grid-barrier counter, [1] exit counter; zero between launches
+	float *amax_val;         // (grid) per-CTA arg-max candidates
+	int *amax_idx;
+	int *ctl, *tokens_out;
+	int token, pos; // token >= 0: taken from here; < 0: from ctl (device greedy loop)
+	int mode;
+	int stages, vec_floats;
+};
+
+struct Plan {
+	bool ok = false;
+	int dtype = 0, grid = 0, stages = 0, vec_floats = 0;
+	size_t smem = 0;
+	const void *kernel = nullptr;
+};
+
+// Can this (unsharded, dense or MoE) model shape run on the megakernel on the current device?
+Plan plan(int dtype, int dim, int q_dim, int kv_dim, int head_dim, int hidden, int vocab, int n_heads,
+          int n_kv_heads, int n_experts, int n_active);
+// Bytes of the attention partial workspace (acc + ml) for `grid` CTAs.
+size_t attn_ws_floats(int grid, int n_heads, int head_dim);
+// One token.  Returns a cudaError_t.
+int launch(const Plan &p, const Args &a, cudaStream_t st);
+
+} // namespace mega
+} // namespace yalm

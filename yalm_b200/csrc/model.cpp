@@ -2,6 +2,7 @@
 // op sequencing and CUDA-graph capture.  See yalm_api.h for how this maps onto the reference API.
 #include "yalm_api.h"
 
+#include "mega.h"
 #include "tp.h"
 
 #include <cuda_runtime.h>
@@ -199,6 +200,9 @@ void InferenceState::cuda() {
 	const int k_act = std::max(1, c.n_experts_active);
 	const bool generic_attn = !yalm_attn_is_fast_shape(lh, lkv, c.head_dim);
 	_tokens_cap = 1 << 16;
+	int sms = 0, dev = 0;
+	CUDA_CHECK(cudaGetDevice(&dev));
+	CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
 	struct Slot {
 		void **ptr;
 		size_t bytes;
@@ -220,6 +224,12 @@ void InferenceState::cuda() {
 	    {(void **)&_ctl, sizeof(int) * YALM_CTL_INTS},
 	    {(void **)&_attn_ws, std::max<size_t>(256, yalm_attn_workspace_bytes(lh, lkv, c.head_dim))},
 	    {(void **)&_tokens_dev, sizeof(int) * (size_t)_tokens_cap},
+	    {(void **)&_mega_acc, sizeof(float) * (size_t)sms * lh * c.head_dim},
+	    {(void **)&_mega_ml, sizeof(float) * (size_t)sms * lh * 2},
+	    {(void **)&_mega_counters, sizeof(unsigned) * (size_t)std::max(1, lkv)},
+	    {(void **)&_mega_sync, 256},
+	    {(void **)&_mega_amax_val, sizeof(float) * (size_t)sms},
+	    {(void **)&_mega_amax_idx, sizeof(int) * (size_t)sms},
 	};
 	size_t total = 0;
 	for (auto &s : slots) total += align_up(s.bytes, 256);
@@ -384,12 +394,12 @@ int Block::enqueue(InferenceState &s) const {
 	const bool tp = c.tp_size > 1;
 	int rc;
 	rc = yalm_qkv_rope_append(s.q(), _key_cache, _value_cache, s.x(), _rms_att_weight, _wq, _wk, _wv, _sq, _sk, _sv,
-	                          c.dim, lh, lkv, c.head_dim, c.rotary_dim, c.rope_theta, c.norm_eps, c.qkv_clip, dt,
-	                          s.ctl(), st);
+	                          c.dim, lh, lkv, c.head_dim, c.rotary_dim, c.max_seq_len, c.rope_theta, c.norm_eps, c.qkv_clip,
+	                          dt, s.ctl(), st);
 	if (rc) return rc;
 	if (yalm_attn_is_fast_shape(lh, lkv, c.head_dim))
 		rc = yalm_attn_decode(s.xb2(), _key_cache, _value_cache, s.q(), s.attn_workspace(), lh, lkv, c.head_dim,
-		                      s.ctl(), st);
+		                      c.max_seq_len, s.ctl(), st);
 	else
 		rc = yalm_attn_generic(s.xb2(), s.att(), _key_cache, _value_cache, s.q(), lh, lkv, c.head_dim, c.max_seq_len, 0,
 		                       s.ctl(), st);
@@ -521,10 +531,66 @@ void Model::cuda(int device, int tp_rank, int tp_size) {
 		if (wcls_scale)
 			wcls_scale = (float *)upload_strided(_owned, _device_bytes, wcls_scale, lv * 4, (size_t)tp_rank * lv * 4, lv * 4, 1);
 	}
+	plan_mega();
 	CUDA_CHECK(cudaDeviceSynchronize());
 }
 
+// ---- megakernel path ---------------------------------------------------------------------------------------
+struct Model::MegaState {
+	yalm::mega::Plan plan;
+	yalm::mega::Layer *layers = nullptr; // device
+	~MegaState() { cudaFree(layers); }
+};
+
+void Model::plan_mega() {
+	const Config &c = *config;
+	const char *env = getenv("YALM_B200_MEGA");
+	if (env && env[0] == '0') return;
+	if (c.tp_size != 1) return;
+	auto ms = std::make_shared<MegaState>();
+	ms->plan = yalm::mega::plan(static_cast<int>(c.weight_dtype), c.dim, c.n_heads * c.head_dim, c.n_kv_heads * c.head_dim,
+	                            c.head_dim, c.hidden_dim, c.vocab_size, c.n_heads, c.n_kv_heads, c.n_experts,
+	                            c.n_experts_active);
+	if (!ms->plan.ok) return;
+	std::vector<yalm::mega::Layer> host(blocks.size());
+	for (size_t i = 0; i < blocks.size(); ++i) {
+		const Block &b = *blocks[i];
+		yalm::mega::Layer &L = host[i];
+		L.wq = (const char *)b._wq, L.wk = (const char *)b._wk, L.wv = (const char *)b._wv, L.wo = (const char *)b._wo;
+		L.w1 = (const char *)b._w1, L.w2 = (const char *)b._w2, L.w3 = (const char *)b._w3, L.gate = (const char *)b._moegate;
+		L.rms_att = b._rms_att_weight, L.rms_ffn = b._rms_ffn_weight;
+		L.sq = b._sq, L.sk = b._sk, L.sv = b._sv, L.so = b._so, L.s1 = b._s1, L.s2 = b._s2, L.s3 = b._s3, L.sgate = b._sgate;
+		L.kc = b._key_cache, L.vc = b._value_cache;
+	}
+	CUDA_CHECK(cudaMalloc((void **)&ms->layers, sizeof(yalm::mega::Layer) * host.size()));
+	CUDA_CHECK(cudaMemcpy(ms->layers, host.data(), sizeof(yalm::mega::Layer) * host.size(), cudaMemcpyHostToDevice));
+	_mega = ms;
+	_mega_ok = true;
+}
+
+int Model::launch_mega(InferenceState &s, int token, int pos, int mode) {
+	const Config &c = *config;
+	yalm::mega::Args a{};
+	a.layers = _mega->layers, a.n_layers = c.n_layers;
+	a.dim = c.dim, a.q_dim = c.n_heads * c.head_dim, a.kv_dim = c.n_kv_heads * c.head_dim, a.head_dim = c.head_dim;
+	a.hidden = c.hidden_dim, a.vocab = c.vocab_size, a.n_heads = c.n_heads, a.n_kv_heads = c.n_kv_heads;
+	a.rotary_dim = c.rotary_dim, a.max_seq_len = c.max_seq_len;
+	a.act = c.act == ActivationType::SILU ? YALM_ACT_SILU : YALM_ACT_GELU;
+	a.n_experts = c.n_experts, a.n_active = c.n_experts_active;
+	a.theta = c.rope_theta, a.eps = c.norm_eps, a.clip = c.qkv_clip;
+	a.embed = (const char *)token_embedding_table, a.embed_scale = embed_scale, a.rms_final = rms_final_weight;
+	a.wcls = (const char *)wcls, a.wcls_scale = wcls_scale;
+	a.x = s.x(), a.q = s.q(), a.att_out = s.xb2(), a.hb = s.hb(), a.logits = s.logits_dev();
+	a.moe_logits = s.moe_weights(), a.active_w = s.active_experts_weights(), a.active_e = s.active_experts();
+	a.ws_acc = s.mega_acc(), a.ws_ml = s.mega_ml(), a.head_counters = s.mega_counters(), a.sync = s.mega_sync();
+	a.amax_val = s.mega_amax_val(), a.amax_idx = s.mega_amax_idx();
+	a.ctl = s.ctl(), a.tokens_out = s.tokens_dev();
+	a.token = token, a.pos = pos, a.mode = mode;
+	return yalm::mega::launch(_mega->plan, a, s.stream());
+}
+
 int Model::launches_per_forward(InferenceMode mode) const {
+	if (_mega_ok) return 1;
 	// embed + 5 kernels per block (qkv+rope+append, flash-decode, wo+res, ffn-glu, w2+res) [+ lm head]
 	// (+ 2 NCCL all-reduce kernels per block and one all-gather under tensor parallelism)
 	const int per_block = 5 + (config->tp_size > 1 ? 2 : 0);
@@ -578,6 +644,18 @@ void Model::forward(InferenceState &s, int token, int pos, InferenceMode mode) {
 		abort();
 	}
 	s.set_mode(mode);
+	if (_mega_ok) {
+		// one persistent kernel per token; token / pos travel as kernel arguments
+		OP_CHECK(launch_mega(s, token, pos,
+		                     mode == InferenceMode::OUTPUT_LOGITS ? yalm::mega::kLogits : yalm::mega::kHydrate));
+		if (mode == InferenceMode::OUTPUT_LOGITS) {
+			CUDA_CHECK(cudaMemcpyAsync(s.logits(), s.logits_dev(), sizeof(float) * c.vocab_size, cudaMemcpyDeviceToHost,
+			                           s.stream()));
+			CUDA_CHECK(cudaStreamSynchronize(s.stream()));
+		}
+		CUDA_CHECK(cudaGetLastError());
+		return;
+	}
 	CudaGraph &g = s.graph();
 	// The embedding is an ordinary launch: token and pos travel as kernel arguments (copied at launch
 	// time), everything after it reads positions from the device control block and is one graph replay.
@@ -621,6 +699,26 @@ int Model::generate_greedy(InferenceState &s, int token, int pos, int n_gen, int
 	                        pos >= c.max_seq_len ? c.max_seq_len : pos + 1, 0, 0, 0};
 	CUDA_CHECK(cudaMemcpyAsync(s.ctl(), h, sizeof(h), cudaMemcpyHostToDevice, st));
 	CUDA_CHECK(cudaStreamSynchronize(st));
+	if (_mega_ok) {
+		cudaEvent_t e0, e1;
+		CUDA_CHECK(cudaEventCreate(&e0));
+		CUDA_CHECK(cudaEventCreate(&e1));
+		CUDA_CHECK(cudaEventRecord(e0, st));
+		for (int i = 0; i < n_gen; ++i) {
+			int rc = launch_mega(s, -1, 0, yalm::mega::kGreedy); // token / pos from the device control block
+			if (rc) return rc;
+			if (logits_out)
+				CUDA_CHECK(cudaMemcpyAsync(logits_out + (size_t)i * c.vocab_size, s.logits_dev(),
+				                           sizeof(float) * c.vocab_size, cudaMemcpyDeviceToHost, st));
+		}
+		CUDA_CHECK(cudaEventRecord(e1, st));
+		CUDA_CHECK(cudaMemcpyAsync(tokens_out, s.tokens_dev(), sizeof(int) * n_gen, cudaMemcpyDeviceToHost, st));
+		CUDA_CHECK(cudaStreamSynchronize(st));
+		if (device_ms) CUDA_CHECK(cudaEventElapsedTime(device_ms, e0, e1));
+		cudaEventDestroy(e0);
+		cudaEventDestroy(e1);
+		return (int)cudaGetLastError();
+	}
 	CudaGraph &g = s.greedy_graph();
 	int done = 0;
 	if (!g.is_created) {
@@ -658,6 +756,7 @@ int Model::profile_ffn(InferenceState &s, int token, int pos, int n_steps, doubl
 	if (_device != Device::CUDA || s.device() != Device::CUDA) return YALM_ENOGPU;
 	const Config &c = *config;
 	if (n_steps < 1 || !mean_us || token < 0 || token >= c.vocab_size || pos < 0) return YALM_EINVAL;
+	if (_mega_ok) return YALM_EINVAL; // no separate w1/w3 kernel on the megakernel path
 	cudaStream_t st = s.stream();
 	const int kv_sink = pos >= c.max_seq_len ? KV_SINKS : 0;
 	int h[YALM_CTL_INTS] = {token, pos, kv_sink, kv_sink + (pos - kv_sink) % (c.max_seq_len - kv_sink),

@@ -26,12 +26,12 @@ constexpr int kTile = 512; // rows per online-softmax tile
 
 struct AttnArgs {
 	float *out;            // (n_heads*head_dim)
-	const __half *kb, *vb; // (max_seq_len, n_kv_heads*head_dim)
+	const __half *kb, *vb; // head-major ring: (n_kv_heads, max_seq_len, head_dim)
 	const float *q;        // (n_heads*head_dim)
 	float *ws_acc;         // (n_kv_heads, S, G, HD) unnormalised partial outputs
 	float *ws_ml;          // (n_kv_heads, S, G, 2)  running max, running sum
 	unsigned *counters;    // (n_kv_heads) arrival counters, zero between launches
-	int n_kv_heads;
+	int n_kv_heads, max_seq_len;
 	const int *ctl;
 };
 
@@ -59,7 +59,7 @@ __global__ void __launch_bounds__(kAttnThreads) attn_decode_kernel(AttnArgs a) {
 
 	const int kvh = blockIdx.y, S = gridDim.x, split = blockIdx.x;
 	const int kv_len = a.ctl[CTL_KVLEN];
-	const int kv_dim = a.n_kv_heads * HD;
+	constexpr int kv_dim = HD; // row stride inside one head's slab
 	const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
 	const int sub = lane % L, rgrp = lane / L;
 
@@ -84,8 +84,8 @@ __global__ void __launch_bounds__(kAttnThreads) attn_decode_kernel(AttnArgs a) {
 #pragma unroll
 		for (int j = 0; j < 8; ++j) acc[g][j] = 0.f;
 	const float inv_div = sqrtf((float)HD);
-	const __half *kbase = a.kb + (size_t)kvh * HD + sub * 8;
-	const __half *vbase = a.vb + (size_t)kvh * HD + sub * 8;
+	const __half *kbase = a.kb + (size_t)kvh * a.max_seq_len * HD + sub * 8;
+	const __half *vbase = a.vb + (size_t)kvh * a.max_seq_len * HD + sub * 8;
 	__syncthreads();
 
 	for (int tile0 = t_begin; tile0 < t_end; tile0 += kTile) {
@@ -253,12 +253,12 @@ __global__ void __launch_bounds__(256) attn_generic_kernel(float *out, float *at
 	__shared__ float red[36];
 	const int h = blockIdx.x, kvh = h / (n_heads / n_kv_heads);
 	const int kv_len = ctl ? ctl[CTL_KVLEN] : kv_len_arg;
-	const int kv_dim = n_kv_heads * head_dim;
+	const __half *kh = kb + (size_t)kvh * max_seq_len * head_dim, *vh = vb + (size_t)kvh * max_seq_len * head_dim;
 	const float *qh = q + (size_t)h * head_dim;
 	float *atth = att + (size_t)h * max_seq_len;
 	float mx = -INFINITY;
 	for (int t = threadIdx.x; t < kv_len; t += blockDim.x) {
-		const __half *k = kb + (size_t)t * kv_dim + kvh * head_dim;
+		const __half *k = kh + (size_t)t * head_dim;
 		float s = 0.f;
 		for (int i = 0; i < head_dim; ++i) s += qh[i] * __half2float(k[i]);
 		s /= sqrtf((float)head_dim);
@@ -277,7 +277,7 @@ __global__ void __launch_bounds__(256) attn_generic_kernel(float *out, float *at
 	__syncthreads();
 	for (int i = threadIdx.x; i < head_dim; i += blockDim.x) {
 		float v = 0.f;
-		for (int t = 0; t < kv_len; ++t) v += atth[t] * __half2float(vb[(size_t)t * kv_dim + kvh * head_dim + i]);
+		for (int t = 0; t < kv_len; ++t) v += atth[t] * __half2float(vh[(size_t)t * head_dim + i]);
 		out[(size_t)h * head_dim + i] = v;
 	}
 }
@@ -317,10 +317,10 @@ extern "C" size_t yalm_attn_workspace_bytes(int n_heads, int n_kv_heads, int hea
 }
 
 extern "C" int yalm_attn_decode(float *out, const uint16_t *key_cache, const uint16_t *value_cache, const float *q,
-                                void *workspace, int n_heads, int n_kv_heads, int head_dim, const int *ctl,
-                                yalm_stream_t s) {
+                                void *workspace, int n_heads, int n_kv_heads, int head_dim, int max_seq_len,
+                                const int *ctl, yalm_stream_t s) {
 	if (!out || !key_cache || !value_cache || !q || !workspace || !ctl) return YALM_EINVAL;
-	if (n_heads <= 0 || n_kv_heads <= 0 || n_heads % n_kv_heads) return YALM_EINVAL;
+	if (n_heads <= 0 || n_kv_heads <= 0 || n_heads % n_kv_heads || max_seq_len <= 0) return YALM_EINVAL;
 	const int g = n_heads / n_kv_heads;
 	if (!attn_fast_shape(head_dim, g)) return YALM_EINVAL; // callers use yalm_attn_generic for odd shapes
 	const int S = attn_splits(n_kv_heads);
@@ -330,7 +330,7 @@ extern "C" int yalm_attn_decode(float *out, const uint16_t *key_cache, const uin
 	a.counters = (unsigned *)workspace;
 	a.ws_ml = (float *)((char *)workspace + 256);
 	a.ws_acc = a.ws_ml + (size_t)n_kv_heads * S * g * 2;
-	a.n_kv_heads = n_kv_heads, a.ctl = ctl;
+	a.n_kv_heads = n_kv_heads, a.max_seq_len = max_seq_len, a.ctl = ctl;
 	cudaStream_t st = (cudaStream_t)s;
 #define YALM_ATTN_CASE(HD, G)                                                                                 \
 	if (head_dim == HD && g == G) return launch_attn<HD, G>(a, S, st);

@@ -56,7 +56,7 @@ struct QkvArgs {
 	const float *x, *rms_w;
 	const char *wq, *wk, *wv;
 	const float *sq, *sk, *sv;
-	int dim, q_dim, kv_dim, head_dim, rotary_dim;
+	int dim, q_dim, kv_dim, head_dim, rotary_dim, max_seq_len;
 	float theta, eps, clip;
 	const int *ctl;
 };
@@ -95,7 +95,9 @@ __global__ void __launch_bounds__(kThreads) qkv_rope_append_kernel(QkvArgs a) {
 			if (which == 0) {
 				*reinterpret_cast<float2 *>(a.q_out + row) = make_float2(v0, v1);
 			} else {
-				__half *dst = (which == 1 ? a.kb : a.vb) + (size_t)kv_pos * a.kv_dim + row;
+				// head-major KV ring: (n_kv_heads, max_seq_len, head_dim)
+				__half *dst = (which == 1 ? a.kb : a.vb) + ((size_t)(row / a.head_dim) * a.max_seq_len + kv_pos) * a.head_dim +
+				              row % a.head_dim;
 				*reinterpret_cast<__half2 *>(dst) = __floats2half2_rn(v0, v1);
 			}
 		}
@@ -106,7 +108,8 @@ __global__ void __launch_bounds__(kThreads) qkv_rope_append_kernel(QkvArgs a) {
 		const int npairs = kv_sink * (a.kv_dim >> 1);
 		for (int p = threadIdx.x; p < npairs; p += blockDim.x) {
 			const int r = p / (a.kv_dim >> 1), i = (p % (a.kv_dim >> 1)) * 2;
-			__half2 *ptr = reinterpret_cast<__half2 *>(a.kb + (size_t)r * a.kv_dim + i);
+			__half2 *ptr = reinterpret_cast<__half2 *>(a.kb + ((size_t)(i / a.head_dim) * a.max_seq_len + r) * a.head_dim +
+			                                           i % a.head_dim);
 			float2 v = __half22float2(*ptr);
 			rope_pair(v.x, v.y, i % a.head_dim, 1, a.theta, a.rotary_dim);
 			*ptr = __floats2half2_rn(v.x, v.y);
@@ -385,19 +388,19 @@ extern "C" int yalm_embed(float *x, const void *table, const float *row_scale, i
 extern "C" int yalm_qkv_rope_append(float *q_out, uint16_t *key_cache, uint16_t *value_cache, const float *x,
                                     const float *rms_weight, const void *wq, const void *wk, const void *wv,
                                     const float *sq, const float *sk, const float *sv, int dim, int n_heads,
-                                    int n_kv_heads, int head_dim, int rotary_dim, float rope_theta, float norm_eps,
-                                    float qkv_clip, int dtype, const int *ctl, yalm_stream_t s) {
+                                    int n_kv_heads, int head_dim, int rotary_dim, int max_seq_len, float rope_theta,
+                                    float norm_eps, float qkv_clip, int dtype, const int *ctl, yalm_stream_t s) {
 	const int ep = ep_of(dtype);
 	if (!ep || !q_out || !key_cache || !value_cache || !x || !rms_weight || !wq || !wk || !wv || !ctl)
 		return YALM_EINVAL;
-	if (dim % ep || dim % 4 || head_dim % 2 || n_heads <= 0 || n_kv_heads <= 0) return YALM_EINVAL;
+	if (dim % ep || dim % 4 || head_dim % 2 || n_heads <= 0 || n_kv_heads <= 0 || max_seq_len <= 0) return YALM_EINVAL;
 	QkvArgs a;
 	a.q_out = q_out, a.kb = (__half *)key_cache, a.vb = (__half *)value_cache;
 	a.x = x, a.rms_w = rms_weight;
 	a.wq = (const char *)wq, a.wk = (const char *)wk, a.wv = (const char *)wv;
 	a.sq = sq, a.sk = sk, a.sv = sv;
 	a.dim = dim, a.q_dim = n_heads * head_dim, a.kv_dim = n_kv_heads * head_dim;
-	a.head_dim = head_dim, a.rotary_dim = rotary_dim, a.theta = rope_theta, a.eps = norm_eps, a.clip = qkv_clip;
+	a.head_dim = head_dim, a.rotary_dim = rotary_dim, a.max_seq_len = max_seq_len, a.theta = rope_theta, a.eps = norm_eps, a.clip = qkv_clip;
 	a.ctl = ctl;
 	const size_t smem = 36 * sizeof(float) + xs_bytes(dtype, dim);
 	const long tasks = (a.q_dim + 2 * a.kv_dim) / 2;

@@ -111,6 +111,14 @@ struct InferenceState {
 	bool ffn_timing() const { return _ffn_timing; }
 	cudaEvent_t ffn_event(int layer, int which) const { return _ffn_events[2 * layer + which]; }
 	CudaGraph &profile_graph() { return _profile_graph; }
+	// megakernel workspace (decode_mega.cu): attention partials, head arrival counters, grid-barrier words,
+	// per-CTA arg-max candidates
+	float *mega_acc() const { return _mega_acc; }
+	float *mega_ml() const { return _mega_ml; }
+	unsigned *mega_counters() const { return _mega_counters; }
+	unsigned *mega_sync() const { return _mega_sync; }
+	float *mega_amax_val() const { return _mega_amax_val; }
+	int *mega_amax_idx() const { return _mega_amax_idx; }
 
 private:
 	std::shared_ptr<Config> _config;
@@ -131,6 +139,9 @@ private:
 	void *_attn_ws = nullptr;
 	int *_tokens_dev = nullptr;
 	int _tokens_cap = 0;
+	float *_mega_acc = nullptr, *_mega_ml = nullptr, *_mega_amax_val = nullptr;
+	unsigned *_mega_counters = nullptr, *_mega_sync = nullptr;
+	int *_mega_amax_idx = nullptr;
 	void *_arena = nullptr; // one device allocation behind all of the above
 };
 
@@ -212,9 +223,18 @@ struct Model {
 	int profile_ffn(InferenceState &s, int token, int pos, int n_steps, double *mean_us);
 	size_t device_bytes() const { return _device_bytes; }
 	int launches_per_forward(InferenceMode mode) const;
+	// true when forward() runs as ONE persistent cooperative kernel per token (decode_mega.cu) instead of
+	// the per-op kernel graph: unsharded dense models whose shapes the tile planner accepts.  Set
+	// YALM_B200_MEGA=0 in the environment before cuda() to force the per-op path.
+	bool uses_megakernel() const { return _mega_ok; }
 
 private:
 	int enqueue_forward(InferenceState &s, InferenceMode mode, bool from_host, bool greedy_tail);
+	int launch_mega(InferenceState &s, int token, int pos, int mode);
+	void plan_mega();
+	bool _mega_ok = false;
+	struct MegaState;
+	std::shared_ptr<MegaState> _mega;
 	Device _device = Device::CPU;
 	bool _tied = false;
 	std::vector<void *> _owned;
