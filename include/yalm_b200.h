@@ -170,6 +170,11 @@ int yalm_forward_launches(const yalm_model *m, int mode);
  * tiles of the whole pass stream through a shared-memory TMA ring), 0 when it is the per-op kernel graph
  * (tensor-parallel shards, MoE, shapes the tile planner rejects, or YALM_B200_MEGA=0 in the environment). */
 int yalm_model_uses_megakernel(const yalm_model *m);
+/* One forward pass (logits mode) with the megakernel's phase profile on.  out receives grid * n_layers * 48
+ * clock64 values: per CTA, per layer, 6 phases (qkv, attention, wo, w1/w3, w2, lm head) x 8 slots
+ * ([0] phase entered [1] grid barrier passed [2] input vector staged [3] tiles + epilogue done
+ * [4] cycles spent waiting for ring stages to fill).  out == NULL: only *grid (CTAs) is returned. */
+int yalm_mega_profile(yalm_model *m, yalm_state *s, int token, int pos, long long *out, size_t count, int *grid);
 
 /* Tensor-parallel plumbing (one process per GPU).  The 128-byte NCCL unique id is created by rank 0
  * with yalm_tp_unique_id() and distributed by the caller (torch.distributed / MPI / files). */

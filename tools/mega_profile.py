@@ -1,0 +1,67 @@
+#!/usr/bin/env python
+"""Phase profile of the whole-token decode kernel (decode_mega.cuh): where a token's time goes per phase —
+grid-barrier wait, input staging, tile loop, and how much of the tile loop the consumers spent starved for
+ring stages (= HBM-bound) — from the kernel's own clock64 stamps.  Usage:
+    python tools/mega_profile.py [--workload mistral-7b-fp16-4k] [--layers N] [--pos P] [--out file]"""
+import argparse
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from yalm_b200 import api, yalm_file as yf  # noqa: E402
+import bench  # noqa: E402
+
+PH = ["qkv", "attn", "wo", "ffn(w1/w3)", "w2", "lm_head"]
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--workload", default="mistral-7b-fp16-4k")
+    ap.add_argument("--layers", type=int, default=0)
+    ap.add_argument("--pos", type=int, default=4000)
+    ap.add_argument("--mhz", type=float, default=1965.0)
+    ap.add_argument("--out", default="")
+    args = ap.parse_args()
+    arch_name, dtype, context, desc = bench.WORKLOADS[args.workload]
+    arch = yf.ARCHS[arch_name]
+    if args.layers:
+        arch = yf.slim(arch, args.layers)
+    img = yf.random_model_streamed(arch, dtype, seed=0, device="cuda")
+    m = api.Model(img, context).cuda()
+    del img
+    s = api.InferenceState(m)
+    assert m.uses_megakernel()
+    for i in range(3):
+        s.forward(1, args.pos + i)
+    p = s.mega_profile(1, args.pos + 3).astype(np.float64)          # (grid, L, 6, 8)
+    us = 1.0 / args.mhz
+    lines = []
+    t_begin = p[:, 0, 0, 0]
+    t_end = p[:, -1, 5, 3]
+    lines.append(f"{desc}; pos {args.pos}; grid {p.shape[0]} CTAs; {p.shape[1]} layers")
+    lines.append(f"kernel span per CTA (first stamp -> last): mean {np.mean(t_end - t_begin) * us:.1f} us")
+    lines.append(f"{'phase':12s} {'barrier':>9s} {'stage':>8s} {'tiles':>8s} {'starved':>8s}   (us per layer, mean over CTAs; max over CTAs in brackets)")
+    tot = np.zeros(4)
+    for ph in range(6):
+        q = p[:, :, ph, :] if ph < 5 else p[:, -1:, ph, :]
+        bar = (q[..., 1] - q[..., 0]) * us
+        stg = (q[..., 2] - q[..., 1]) * us
+        til = (q[..., 3] - q[..., 2]) * us
+        stv = q[..., 4] * us
+        nl = q.shape[1]
+        lines.append(f"{PH[ph]:12s} {bar.mean():9.2f} {stg.mean():8.2f} {til.mean():8.2f} {stv.mean():8.2f}   "
+                     f"[{bar.max(0).mean():.2f} {stg.max(0).mean():.2f} {til.max(0).mean():.2f} {stv.max(0).mean():.2f}] x{nl}")
+        tot += np.array([bar.mean() * nl, stg.mean() * nl, til.mean() * nl, stv.mean() * nl])
+    lines.append(f"{'token total':12s} {tot[0]:9.1f} {tot[1]:8.1f} {tot[2]:8.1f} {tot[3]:8.1f}   (us per token)")
+    txt = "\n".join(lines)
+    print(txt)
+    if args.out:
+        open(args.out, "w").write(txt + "\n")
+        np.save(os.path.splitext(args.out)[0] + ".npy", p.astype(np.int64))
+
+
+if __name__ == "__main__":
+    main()

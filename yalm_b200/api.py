@@ -28,7 +28,7 @@ SYMBOLS = [
     "yalm_matmul_host", "yalm_mha_host", "yalm_ffn_host", "yalm_bench_op",
     "yalm_model_open_file", "yalm_model_open_memory", "yalm_model_cuda", "yalm_model_close", "yalm_model_config",
     "yalm_model_device_bytes", "yalm_state_new", "yalm_state_free", "yalm_forward", "yalm_logits",
-    "yalm_generate_greedy", "yalm_state_read", "yalm_forward_launches", "yalm_model_uses_megakernel",
+    "yalm_generate_greedy", "yalm_state_read", "yalm_forward_launches", "yalm_model_uses_megakernel", "yalm_mega_profile",
     "yalm_profile_ffn",
     "yalm_tp_unique_id", "yalm_tp_init", "yalm_tp_finalize", "yalm_error_string", "yalm_version",
 ]
@@ -78,6 +78,7 @@ def lib():
     L.yalm_state_read.argtypes = [vp, vp, i, i, vp, sz]
     L.yalm_forward_launches.argtypes = [vp, i]
     L.yalm_model_uses_megakernel.argtypes = [vp]
+    L.yalm_mega_profile.argtypes = [vp, vp, i, i, vp, sz, C.POINTER(i)]
     L.yalm_profile_ffn.argtypes = [vp, vp, i, i, i, C.POINTER(C.c_double)]
     L.yalm_tp_unique_id.argtypes = [vp]
     L.yalm_tp_init.argtypes = [vp, i, i]
@@ -213,6 +214,14 @@ class InferenceState:
                "generate_greedy")
         self.device_ms = ms.value
         return (toks.tolist(), lg) if keep_logits else toks.tolist()
+
+    def mega_profile(self, token: int, pos: int) -> np.ndarray:
+        """(grid, n_layers, 6 phases, 8 slots) clock64 stamps of one forward pass on the megakernel."""
+        g = C.c_int()
+        _check(lib().yalm_mega_profile(self.model.h, self.h, token, pos, None, 0, C.byref(g)), "mega_profile")
+        out = np.zeros((g.value, self.model.n_layers, 6, 8), np.int64)
+        _check(lib().yalm_mega_profile(self.model.h, self.h, token, pos, _p(out), out.size, C.byref(g)), "mega_profile")
+        return out
 
     def profile_ffn(self, token: int, pos: int, n_steps: int) -> float:
         us = C.c_double()

@@ -397,6 +397,11 @@ extern "C" int yalm_model_uses_megakernel(const yalm_model *m) {
 	return m && m->model->uses_megakernel() ? 1 : 0;
 }
 
+extern "C" int yalm_mega_profile(yalm_model *m, yalm_state *s, int token, int pos, long long *out, size_t count, int *grid) {
+	if (!m || !s) return YALM_EINVAL;
+	return m->model->mega_profile(*s->state, token, pos, out, count, grid);
+}
+
 extern "C" int yalm_profile_ffn(yalm_model *m, yalm_state *s, int token, int pos, int n_steps, double *mean_us) {
 	if (!m || !s) return YALM_EINVAL;
 	return m->model->profile_ffn(*s->state, token, pos, n_steps, mean_us);

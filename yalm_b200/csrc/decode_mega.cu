@@ -4,6 +4,7 @@
 #include "launch.h"
 
 #include <algorithm>
+#include <cstdlib>
 
 namespace yalm {
 namespace mega {
@@ -104,7 +105,7 @@ Plan plan(int dtype, int dim, int q_dim, int kv_dim, int head_dim, int hidden, i
 	vf = std::max(vf, kConsumerWarps * G * (head_dim + 2));
 	vf = std::max(vf, p.grid * G + G + 32);
 	p.vec_floats = (vf + 31) / 32 * 32;
-	const size_t fixed = (size_t)p.vec_floats * 4 + (2 * kConsumerWarps * 4 + 16 + 16) * 4 + 2 * kMaxStages * 8;
+	const size_t fixed = (size_t)p.vec_floats * 4 + (2 * kEpiBatch * kConsumerWarps * 4 + 16 + 16) * 4 + 2 * kMaxStages * 8;
 	const long room = (long)di.max_smem_optin - (long)fixed;
 	p.stages = (int)std::min<long>(kMaxStages, room / kStageBytes);
 	if (p.stages < 2) return p;
@@ -127,6 +128,10 @@ int launch(const Plan &p, const Args &a, cudaStream_t st) {
 	if (!p.ok) return YALM_EINVAL;
 	Args args = a;
 	args.stages = p.stages, args.vec_floats = p.vec_floats;
+	static const int debug = getenv("YALM_MEGA_DEBUG") ? atoi(getenv("YALM_MEGA_DEBUG")) : 0;
+	static const int max_stages = getenv("YALM_MEGA_STAGES") ? atoi(getenv("YALM_MEGA_STAGES")) : 0;
+	args.debug = debug;
+	if (max_stages >= 2 && max_stages < args.stages) args.stages = max_stages;
 	void *params[] = {&args};
 	return (int)cudaLaunchCooperativeKernel(p.kernel, dim3(p.grid), dim3(kThreads), params, p.smem, st);
 }

@@ -24,15 +24,13 @@
 namespace yalm {
 namespace mega {
 
-constexpr unsigned long long kTimeoutNs = 4000000000ull; // a wait longer than this is a bug: trap, never hang
+// A wait longer than this many SM cycles (~4 s) is a bug: trap, never hang.  clock64, not %globaltimer: the
+// global timer read costs about a microsecond, which on the producer's empty-stage wait throttled the whole ring.
+constexpr long long kTimeoutCycles = 8000000000ll;
 constexpr int kCT = kConsumerWarps * 32;
+constexpr int kEpiBatch = 32; // row groups per epilogue batch (two batches of partials live in shared memory)
 
 // ---- PTX helpers -------------------------------------------------------------------------------------
-__device__ __forceinline__ unsigned long long gtime() {
-	unsigned long long t;
-	asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-	return t;
-}
 __device__ __forceinline__ uint32_t smem_u32(const void *p) {
 	return static_cast<uint32_t>(__cvta_generic_to_shared(p));
 }
@@ -55,13 +53,14 @@ __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
 }
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
 	if (mbar_try_wait(bar, parity)) return;
-	const unsigned long long t0 = gtime();
+	const long long t0 = clock64();
 	while (!mbar_try_wait(bar, parity))
-		if (gtime() - t0 > kTimeoutNs) __trap();
+		if (clock64() - t0 > kTimeoutCycles) __trap();
 }
 // 1-D bulk copy global -> shared, completion counted in bytes on `bar`; weights/KV are read once per
 // token, so they are tagged evict-first in L2 (activations and partials stay resident).
 __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void *src, uint32_t bytes, uint32_t bar, uint64_t policy) {
+	if (policy == 0) return; // debug: no copies
 	asm volatile(
 	    "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;" ::"r"(dst),
 	    "l"(src), "r"(bytes), "r"(bar), "l"(policy)
@@ -112,7 +111,15 @@ __host__ __device__ inline bool tile_shape(int rows, int rows_b, int K, int B, i
 	return false;
 }
 
+// Optional phase profile (Args.prof != null): per CTA, per (layer, phase) kProfSlots clock64 values written by
+// consumer thread 0: [0] phase entered (before the grid barrier) [1] barrier passed [2] input vector staged
+// [3] tiles + epilogue done; [4] cycles warp 0 spent waiting for full ring stages (starvation = HBM-bound).
+constexpr int kProfSlots = 8, kProfPhases = 6; // phases: qkv, attn, wo, ffn, w2, lm(+argmax) (last layer slot only)
+
 struct Ctx {
+	long long *prof; // this CTA's profile rows or null
+	long long wait_cycles;
+	int debug;
 	unsigned char *stages;
 	uint32_t stages_u32, full0, empty0;
 	float *vec, *part, *red;
@@ -133,7 +140,8 @@ struct Producer {
 		const uint32_t s = c.it % c.S, par = ((c.it / c.S) & 1u) ^ 1u;
 		mbar_wait(c.empty0 + 8 * s, par);
 		*bar = c.full0 + 8 * s;
-		mbar_expect_tx(*bar, bytes);
+		if (c.debug & 8) mbar_arrive(*bar);
+		else mbar_expect_tx(*bar, bytes);
 		++c.it;
 		return c.stages_u32 + s * kStageBytes;
 	}
@@ -209,18 +217,31 @@ __device__ __forceinline__ void grid_barrier(Ctx &c, unsigned *sync) {
 		__threadfence();
 		atomicAdd(sync, 1u);
 		if (ld_acquire(sync) < target) {
-			const unsigned long long t0 = gtime();
+			const long long t0 = clock64();
 			while (ld_acquire(sync) < target)
-				if (gtime() - t0 > kTimeoutNs) __trap();
+				if (clock64() - t0 > kTimeoutCycles) __trap();
 		}
 		__threadfence();
 	}
 	cbar();
 }
 
+__device__ __forceinline__ void stamp(Ctx &c, int layer, int phase, int k) {
+	if (c.prof && c.tid == 0) {
+		long long *row = c.prof + ((size_t)layer * kProfPhases + phase) * kProfSlots;
+		row[k] = clock64();
+		if (k == 3) row[4] = c.wait_cycles, c.wait_cycles = 0;
+	}
+}
+
 __device__ __forceinline__ const unsigned char *wait_full(Ctx &c, uint32_t *slot) {
 	const uint32_t s = c.it % c.S, par = (c.it / c.S) & 1u;
-	mbar_wait(c.full0 + 8 * s, par);
+	if (c.prof && c.tid == 0) {
+		const long long t0 = clock64();
+		mbar_wait(c.full0 + 8 * s, par);
+		c.wait_cycles += clock64() - t0;
+	} else
+		mbar_wait(c.full0 + 8 * s, par);
 	*slot = s;
 	++c.it;
 	return c.stages + (size_t)s * kStageBytes;
@@ -242,27 +263,61 @@ __device__ __forceinline__ float4 load_in4(const Args &a, const float *src, int 
 }
 
 template <int DT>
-__device__ void stage_vec(Ctx &c, const Args &a, const float *src, int n, const float *rms_w, int embed_token) {
+__device__ __forceinline__ void stage_vec(Ctx &c, const Args &a, const float *src, int n, const float *rms_w, int embed_token) {
 	constexpr int EP = WTraits<DT>::EP;
+	constexpr int NC = 8; // float4 per thread kept in registers between the two rmsnorm passes (n <= 8192)
 	if (rms_w) {
 		// reference formula and association order (src/infer.cpp:134-144): o = x * (1/sqrt(ss/n + eps)) * w
+		float4 cache[NC], wv[NC];
 		float ss = 0.f;
-		for (int e = c.tid * 4; e < n; e += kCT * 4) {
+#pragma unroll
+		for (int i = 0; i < NC; ++i) {
+			const int e = (c.tid + i * kCT) * 4;
+			if (e < n) {
+				cache[i] = load_in4<DT>(a, src, embed_token, e);
+				wv[i] = *reinterpret_cast<const float4 *>(rms_w + e);
+			}
+		}
+#pragma unroll
+		for (int i = 0; i < NC; ++i) {
+			const int e = (c.tid + i * kCT) * 4;
+			if (e < n) ss += cache[i].x * cache[i].x + cache[i].y * cache[i].y + cache[i].z * cache[i].z + cache[i].w * cache[i].w;
+		}
+		for (int e = (c.tid + NC * kCT) * 4; e < n; e += kCT * 4) {
 			const float4 v = load_in4<DT>(a, src, embed_token, e);
 			ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
 		}
 		ss = cons_sum(c, ss);
 		const float scale = 1.0f / sqrtf(ss / n + a.eps);
-		for (int e = c.tid * 4; e < n; e += kCT * 4) {
+		const bool seed_x = embed_token >= 0 && c.cta == 0; // layer 0: the residual stream starts as the embedding row
+#pragma unroll
+		for (int i = 0; i < NC; ++i) {
+			const int e = (c.tid + i * kCT) * 4;
+			if (e < n) {
+				const float4 v = cache[i], w = wv[i];
+				*reinterpret_cast<float4 *>(c.vec + xs_slot<EP>(e)) =
+				    make_float4(v.x * scale * w.x, v.y * scale * w.y, v.z * scale * w.z, v.w * scale * w.w);
+				if (seed_x) *reinterpret_cast<float4 *>(a.x + e) = v;
+			}
+		}
+		for (int e = (c.tid + NC * kCT) * 4; e < n; e += kCT * 4) {
 			const float4 v = load_in4<DT>(a, src, embed_token, e);
 			const float4 w = *reinterpret_cast<const float4 *>(rms_w + e);
 			*reinterpret_cast<float4 *>(c.vec + xs_slot<EP>(e)) =
 			    make_float4(v.x * scale * w.x, v.y * scale * w.y, v.z * scale * w.z, v.w * scale * w.w);
-			if (embed_token >= 0 && c.cta == 0) *reinterpret_cast<float4 *>(a.x + e) = v; // residual stream starts here
+			if (seed_x) *reinterpret_cast<float4 *>(a.x + e) = v;
 		}
 	} else {
-		for (int e = c.tid * 4; e < n; e += kCT * 4)
-			*reinterpret_cast<float4 *>(c.vec + xs_slot<EP>(e)) = load_in4<DT>(a, src, -1, e);
+		int e = c.tid * 4;
+		for (; e + 3 * kCT * 4 < n; e += 4 * kCT * 4) { // four independent L2 loads in flight per thread
+			float4 v[4];
+#pragma unroll
+			for (int i = 0; i < 4; ++i) v[i] = __ldcg(reinterpret_cast<const float4 *>(src + e + i * kCT * 4));
+#pragma unroll
+			for (int i = 0; i < 4; ++i) *reinterpret_cast<float4 *>(c.vec + xs_slot<EP>(e + i * kCT * 4)) = v[i];
+		}
+		for (; e < n; e += kCT * 4)
+			*reinterpret_cast<float4 *>(c.vec + xs_slot<EP>(e)) = __ldcg(reinterpret_cast<const float4 *>(src + e));
 	}
 	cbar();
 }
@@ -277,19 +332,18 @@ struct Epi {
 	int best_i;
 };
 
+// Epilogue of output item `t` of row group `g` (a row, a RoPE pair or a w1/w3 pair); `part` holds the eight
+// warps' partial sums of the group's rows: part[warp*4 + r].  Sum order over warps is fixed (deterministic).
 template <int DT>
-__device__ __forceinline__ void finalize(Ctx &c, const Args &a, Epi &ep, const Shape &sh, int g, int buf) {
-	const float *part = c.part + buf * kConsumerWarps * 4;
+__device__ __forceinline__ void finalize(Ctx &c, const Args &a, Epi &ep, const Shape &sh, int g, int t, const float *part) {
 	auto rowsum = [&](int r) {
 		float v = 0.f;
 #pragma unroll
 		for (int w = 0; w < kConsumerWarps; ++w) v += part[w * 4 + r];
 		return v;
 	};
-	const int t = c.tid;
 	switch (ep.kind) {
 	case kQKV: {
-		if (t >= sh.R / 2) return;
 		long row = (long)g * sh.R + 2 * t;
 		int which = 0;
 		const float *sc = ep.scale0;
@@ -311,7 +365,6 @@ __device__ __forceinline__ void finalize(Ctx &c, const Args &a, Epi &ep, const S
 	}
 	case kWO:
 	case kW2: {
-		if (t >= sh.R) return;
 		const long row = (long)g * sh.R + t;
 		float v = rowsum(t);
 		if (DT == YALM_F8E4M3 && ep.scale0) v *= ep.scale0[row];
@@ -320,7 +373,6 @@ __device__ __forceinline__ void finalize(Ctx &c, const Args &a, Epi &ep, const S
 	}
 	case kFFN: {
 		const int rh = sh.R / 2;
-		if (t >= rh) return;
 		const long row = (long)g * rh + t;
 		float gt = rowsum(t), up = rowsum(rh + t);
 		if (DT == YALM_F8E4M3 && ep.scale0) gt *= ep.scale0[row], up *= ep.scale1[row];
@@ -329,18 +381,21 @@ __device__ __forceinline__ void finalize(Ctx &c, const Args &a, Epi &ep, const S
 		return;
 	}
 	default: { // kLM
-		if (t >= sh.R) return;
 		const long row = (long)g * sh.R + t;
 		float v = rowsum(t);
 		if (DT == YALM_F8E4M3 && ep.scale0) v *= ep.scale0[row];
 		a.logits[row] = v;
-		if (v > ep.best_v) ep.best_v = v, ep.best_i = (int)row; // rows ascend: first maximum wins
+		if (v > ep.best_v) ep.best_v = v, ep.best_i = (int)row; // a thread's rows ascend: first maximum wins
 		return;
 	}
 	}
 }
 
 // All row groups of one GEMV phase owned by this CTA.  The input vector is already staged in c.vec.
+// The eight warps never wait for each other inside the tile loop: each adds its slice of every tile and parks
+// its per-row partial in shared memory; every kEpiBatch groups (and at the end) one barrier hands a whole batch
+// to all 256 threads for the cross-warp sum and the fused epilogue, so global-memory latency in the epilogue
+// (residual read, KV append) is paid once per batch, not once per tile.
 template <int DT, int R>
 __device__ __forceinline__ void gemv_consume(Ctx &c, const Args &a, Epi &ep) {
 	using T = WTraits<DT>;
@@ -349,8 +404,17 @@ __device__ __forceinline__ void gemv_consume(Ctx &c, const Args &a, Epi &ep) {
 	const int chunks = (sh.KT + CH - 1) / CH;
 	const int row_stride = sh.KT * T::BYTES;
 	const int lane = c.lane, warp = c.warp;
-	int buf = 0;
-	for (int g = (c.cta - c.rot + c.ncta) % c.ncta; g < sh.G; g += c.ncta) {
+	const int nfin = (ep.kind == kQKV || ep.kind == kFFN) ? sh.R / 2 : sh.R; // epilogue items per group
+	const int g_first = (c.cta - c.rot + c.ncta) % c.ncta;
+	auto flush = [&](int batch, int n_groups) { // epilogue of groups [batch*kEpiBatch, +n_groups) of this CTA
+		const float *pb = c.part + (batch & 1) * kEpiBatch * kConsumerWarps * 4;
+		for (int i = c.tid; i < n_groups * nfin; i += kCT) {
+			const int gl = i / nfin, t = i % nfin;
+			finalize<DT>(c, a, ep, sh, g_first + (batch * kEpiBatch + gl) * c.ncta, t, pb + gl * kConsumerWarps * 4);
+		}
+	};
+	int gi = 0; // local group index
+	for (int g = g_first; g < sh.G; g += c.ncta, ++gi) {
 		float acc[R];
 #pragma unroll
 		for (int r = 0; r < R; ++r) acc[r] = 0.f;
@@ -360,6 +424,7 @@ __device__ __forceinline__ void gemv_consume(Ctx &c, const Args &a, Epi &ep) {
 			const int cbase = kc * chunks;
 			// chunk (cbase + cc) belongs to warp (cbase + cc) % 8: balanced over the K splits
 			int cc = (warp - cbase % kConsumerWarps + kConsumerWarps) % kConsumerWarps;
+			if (c.debug & 1) cc = chunks;
 #pragma unroll 2
 			for (; cc < chunks; cc += kConsumerWarps) {
 				if (cc * CH + lane * EP < sh.KT) {
@@ -380,13 +445,17 @@ __device__ __forceinline__ void gemv_consume(Ctx &c, const Args &a, Epi &ep) {
 #pragma unroll
 		for (int r = 0; r < R; ++r) acc[r] = warp_sum(acc[r]);
 		if (lane == 0) {
+			float *dst = c.part + ((((gi / kEpiBatch) & 1) * kEpiBatch + gi % kEpiBatch) * kConsumerWarps + warp) * 4;
 #pragma unroll
-			for (int r = 0; r < R; ++r) c.part[(buf * kConsumerWarps + warp) * 4 + r] = acc[r];
+			for (int r = 0; r < R; ++r) dst[r] = acc[r];
 		}
-		cbar(); // also orders the previous group's finalize reads before part[buf^1] is rewritten next time
-		finalize<DT>(c, a, ep, sh, g, buf);
-		buf ^= 1;
+		if ((gi + 1) % kEpiBatch == 0) {
+			cbar(); // batch complete; also fences the flush two batches ago off the buffer half about to be refilled
+			flush(gi / kEpiBatch, kEpiBatch);
+		}
 	}
+	cbar();
+	if (gi % kEpiBatch) flush(gi / kEpiBatch, gi % kEpiBatch);
 	c.rot = (c.rot + sh.G) % c.ncta;
 }
 
@@ -455,7 +524,7 @@ __device__ __forceinline__ void attention_consume(Ctx &c, const Args &a, const L
 #pragma unroll
 		for (int st = 0; st < STEPS; ++st) {
 			const int row = st * (kConsumerWarps * RPS) + warp * RPS + rgrp, t = t0 + row;
-			const bool valid = row < n;
+			const bool valid = row < n && !(c.debug & 4);
 			// the row appended by this token and the re-rotated sink rows were written after the producer
 			// may have fetched the tile: read those from global memory (L2), everything else from the ring
 			const bool fresh = t == c.kv_pos || t < c.kv_sink;
@@ -497,7 +566,7 @@ __device__ __forceinline__ void attention_consume(Ctx &c, const Args &a, const L
 #pragma unroll
 		for (int st = 0; st < STEPS; ++st) {
 			const int row = st * (kConsumerWarps * RPS) + warp * RPS + rgrp, t = t0 + row;
-			if (row < n) {
+			if (row < n && !(c.debug & 4)) {
 				const bool fresh = t == c.kv_pos || t < c.kv_sink;
 				const uint4 vv = fresh ? __ldcg(reinterpret_cast<const uint4 *>(vg + (size_t)row * HD + sub * 8))
 				                       : *reinterpret_cast<const uint4 *>(vs + row * HD + sub * 8);
@@ -624,7 +693,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_c
 	c.stages_u32 = smem_u32(smem_raw);
 	c.vec = reinterpret_cast<float *>(smem_raw + (size_t)c.S * kStageBytes);
 	c.part = c.vec + a.vec_floats;
-	c.red = c.part + 2 * kConsumerWarps * 4;
+	c.red = c.part + 2 * kEpiBatch * kConsumerWarps * 4;
 	c.misc = reinterpret_cast<int *>(c.red + 16);
 	uint64_t *bars = reinterpret_cast<uint64_t *>(c.misc + 16);
 	c.full0 = smem_u32(bars);
@@ -632,6 +701,9 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_c
 	c.cta = blockIdx.x, c.ncta = gridDim.x;
 	c.tid = threadIdx.x, c.warp = threadIdx.x >> 5, c.lane = threadIdx.x & 31;
 	c.it = 0, c.rot = 0, c.bar_gen = 0;
+	c.prof = a.prof ? a.prof + (size_t)blockIdx.x * a.n_layers * kProfPhases * kProfSlots : nullptr;
+	c.wait_cycles = 0;
+	c.debug = a.debug;
 
 	c.token = a.token, c.pos = a.pos;
 	if (a.token < 0) c.token = a.ctl[CTL_TOKEN], c.pos = a.ctl[CTL_POS];
@@ -661,7 +733,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_c
 	if (c.warp == kConsumerWarps) {
 		// ================================ producer ================================
 		if (c.lane != 0) return;
-		Producer p{c, policy_evict_first()};
+		Producer p{c, (a.debug & 8) ? 0ull : policy_evict_first()};
 		for (int l = 0; l < a.n_layers; ++l) {
 			const Layer &L = a.layers[l];
 			p.gemv(kQKV, L.wq, L.wk, L.wv, a.q_dim, a.kv_dim, a.dim, B);
@@ -680,8 +752,11 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_c
 		const Layer &L = a.layers[l];
 		ep.L = &L;
 		// ---- rmsnorm -> q,k,v -> clip -> RoPE -> KV append (+ sink re-rotation) --------------------------
+		stamp(c, l, 0, 0);
 		if (l > 0) grid_barrier(c, a.sync);
+		stamp(c, l, 0, 1);
 		stage_vec<DT>(c, a, a.x, a.dim, L.rms_att, l == 0 ? c.token : -1);
+		stamp(c, l, 0, 2);
 		if (c.kv_sink > 0 && c.cta == c.ncta - 1) {
 			// rotate each sink key forward by one position, fp16 -> fp32 -> fp16 (src/infer.cpp:303-317)
 			const int hp = hd >> 1, npairs = c.kv_sink * a.n_kv_heads * hp;
@@ -695,38 +770,68 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_c
 		}
 		ep.kind = kQKV, ep.scale0 = L.sq, ep.scale1 = L.sk, ep.scale2 = L.sv, ep.rows0 = a.q_dim, ep.rows1 = a.kv_dim;
 		gemv_phase<DT>(c, a, ep);
+		stamp(c, l, 0, 3);
 		// ---- attention -----------------------------------------------------------------------------------
+		stamp(c, l, 1, 0);
 		grid_barrier(c, a.sync);
+		stamp(c, l, 1, 1);
+		stamp(c, l, 1, 2);
 		attention_consume<HD, G>(c, a, L);
+		stamp(c, l, 1, 3);
 		// ---- wo + residual -------------------------------------------------------------------------------
+		stamp(c, l, 2, 0);
 		grid_barrier(c, a.sync);
+		stamp(c, l, 2, 1);
 		stage_vec<DT>(c, a, a.att_out, a.q_dim, nullptr, -1);
+		stamp(c, l, 2, 2);
 		ep.kind = kWO, ep.scale0 = L.so;
 		gemv_phase<DT>(c, a, ep);
+		stamp(c, l, 2, 3);
 		// ---- rmsnorm -> w1/w3 -> GLU ---------------------------------------------------------------------
+		stamp(c, l, 3, 0);
 		grid_barrier(c, a.sync);
+		stamp(c, l, 3, 1);
 		stage_vec<DT>(c, a, a.x, a.dim, L.rms_ffn, -1);
+		stamp(c, l, 3, 2);
 		ep.kind = kFFN, ep.scale0 = L.s1, ep.scale1 = L.s3;
 		gemv_phase<DT>(c, a, ep);
+		stamp(c, l, 3, 3);
 		// ---- w2 + residual -------------------------------------------------------------------------------
+		stamp(c, l, 4, 0);
 		grid_barrier(c, a.sync);
+		stamp(c, l, 4, 1);
 		stage_vec<DT>(c, a, a.hb, a.hidden, nullptr, -1);
+		stamp(c, l, 4, 2);
 		ep.kind = kW2, ep.scale0 = L.s2;
 		gemv_phase<DT>(c, a, ep);
+		stamp(c, l, 4, 3);
 	}
 	if (a.mode != kHydrate) {
 		// ---- final rmsnorm -> LM head (+ greedy arg-max, first maximum wins: src/sampler.cpp:27-38) -----
+		stamp(c, a.n_layers - 1, 5, 0);
 		grid_barrier(c, a.sync);
+		stamp(c, a.n_layers - 1, 5, 1);
 		stage_vec<DT>(c, a, a.x, a.dim, a.rms_final, -1);
+		stamp(c, a.n_layers - 1, 5, 2);
 		ep.kind = kLM, ep.scale0 = a.wcls_scale, ep.best_v = -FLT_MAX, ep.best_i = 0x7fffffff;
 		gemv_phase<DT>(c, a, ep);
 		if (a.mode == kGreedy) {
-			if (c.tid < 4) c.red[c.tid] = ep.best_v, c.misc[4 + c.tid] = ep.best_i;
+			{
+				float bv = ep.best_v;
+				int bi = ep.best_i;
+#pragma unroll
+				for (int o = 16; o > 0; o >>= 1) {
+					const float ov = __shfl_xor_sync(kFull, bv, o);
+					const int oi = __shfl_xor_sync(kFull, bi, o);
+					if (ov > bv || (ov == bv && oi < bi)) bv = ov, bi = oi;
+				}
+				if (c.lane == 0) c.red[c.warp] = bv, c.misc[4 + c.warp] = bi;
+			}
 			cbar();
 			if (c.tid == 0) {
 				float bv = c.red[0];
 				int bi = c.misc[4];
-				for (int t = 1; t < 4; ++t)
+				for (int t = 1; t < kConsumerWarps; ++t)
 					if (c.red[t] > bv || (c.red[t] == bv && c.misc[4 + t] < bi)) bv = c.red[t], bi = c.misc[4 + t];
 				a.amax_val[c.cta] = bv, a.amax_idx[c.cta] = bi;
 			}
@@ -759,6 +864,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_c
 			}
 		}
 	}
+	if (a.mode != kHydrate) stamp(c, a.n_layers - 1, 5, 3);
 	// ---- leave the barrier words zeroed for the next launch ------------------------------------------
 	cbar();
 	if (c.tid == 0) {

@@ -17,6 +17,7 @@ constexpr int kStageBytes = 32768; // one ring stage = one weight tile or one K+
 constexpr int kConsumerWarps = 8;
 constexpr int kThreads = (kConsumerWarps + 1) * 32; // + the producer warp
 constexpr int kMaxStages = 8;
+constexpr int kProfileSlots = 6 * 8; // per (CTA, layer): phases x slots, see decode_mega.cuh
 
 // Per-layer device pointers (weights are (out,in) row-major; KV cache is head-major, see yalm_b200.h).
 struct Layer {
@@ -52,6 +53,8 @@ struct Args {
 	int token, pos; // token >= 0: taken from here; < 0: from ctl (device greedy loop)
 	int mode;
 	int stages, vec_floats;
+	int debug;       // timing experiments only (YALM_MEGA_DEBUG): 1 skip GEMV math, 4 skip attention math, 8 no copies
+	long long *prof; // optional phase profile, (grid, n_layers, 6 phases, 8 slots) clock64 values; null = off
 };
 
 struct Plan {

@@ -568,9 +568,27 @@ void Model::plan_mega() {
 	_mega_ok = true;
 }
 
-int Model::launch_mega(InferenceState &s, int token, int pos, int mode) {
+int Model::mega_profile(InferenceState &s, int token, int pos, long long *out, size_t count, int *grid) {
+	if (!_mega_ok) return YALM_EINVAL;
+	const Config &c = *config;
+	const size_t need = (size_t)_mega->plan.grid * c.n_layers * yalm::mega::kProfileSlots;
+	if (grid) *grid = _mega->plan.grid;
+	if (!out) return 0;
+	if (count < need) return YALM_EINVAL;
+	long long *dev = nullptr;
+	CUDA_CHECK(cudaMalloc((void **)&dev, need * sizeof(long long)));
+	CUDA_CHECK(cudaMemset(dev, 0, need * sizeof(long long)));
+	int rc = launch_mega(s, token, pos, yalm::mega::kLogits, dev);
+	if (rc == 0) rc = (int)cudaStreamSynchronize(s.stream());
+	if (rc == 0) rc = (int)cudaMemcpy(out, dev, need * sizeof(long long), cudaMemcpyDeviceToHost);
+	cudaFree(dev);
+	return rc;
+}
+
+int Model::launch_mega(InferenceState &s, int token, int pos, int mode, long long *prof) {
 	const Config &c = *config;
 	yalm::mega::Args a{};
+	a.prof = prof;
 	a.layers = _mega->layers, a.n_layers = c.n_layers;
 	a.dim = c.dim, a.q_dim = c.n_heads * c.head_dim, a.kv_dim = c.n_kv_heads * c.head_dim, a.head_dim = c.head_dim;
 	a.hidden = c.hidden_dim, a.vocab = c.vocab_size, a.n_heads = c.n_heads, a.n_kv_heads = c.n_kv_heads;

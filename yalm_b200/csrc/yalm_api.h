@@ -227,10 +227,13 @@ struct Model {
 	// the per-op kernel graph: unsharded dense models whose shapes the tile planner accepts.  Set
 	// YALM_B200_MEGA=0 in the environment before cuda() to force the per-op path.
 	bool uses_megakernel() const { return _mega_ok; }
+	// One forward pass with the kernel's phase profile on: clock64 stamps per (CTA, layer, phase, slot), see
+	// decode_mega.cuh.  out == null: only *grid is returned.
+	int mega_profile(InferenceState &s, int token, int pos, long long *out, size_t count, int *grid);
 
 private:
 	int enqueue_forward(InferenceState &s, InferenceMode mode, bool from_host, bool greedy_tail);
-	int launch_mega(InferenceState &s, int token, int pos, int mode);
+	int launch_mega(InferenceState &s, int token, int pos, int mode, long long *prof = nullptr);
 	void plan_mega();
 	bool _mega_ok = false;
 	struct MegaState;
