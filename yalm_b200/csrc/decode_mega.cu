@@ -5,13 +5,15 @@
 
 #include <algorithm>
 #include <cstdlib>
+#include <cstring>
 
 namespace yalm {
 namespace mega {
 
 // Pure streaming probe: the same ring and bulk copies over a flat buffer, consumers only wait and release.
 // Its GB/s is the ceiling the megakernel can reach on this part (yalm_bench_op("stream")).
-__global__ void __launch_bounds__(kThreads, 1) stream_probe_kernel(const char *buf, size_t bytes, int stages, unsigned *sink) {
+__global__ void __launch_bounds__(kThreads, 1) stream_probe_kernel(const char *buf, size_t bytes, int stages, unsigned *sink,
+                                                                      int copy_bytes) {
 	extern __shared__ __align__(128) unsigned char smem_raw[];
 	uint64_t *bars = reinterpret_cast<uint64_t *>(smem_raw + (size_t)stages * kStageBytes);
 	const uint32_t full0 = smem_u32(bars), empty0 = full0 + 8 * kMaxStages, st0 = smem_u32(smem_raw);
@@ -25,15 +27,16 @@ __global__ void __launch_bounds__(kThreads, 1) stream_probe_kernel(const char *b
 	}
 	__syncthreads();
 	const size_t ntiles = bytes / kStageBytes;
-	if (warp == kConsumerWarps) {
-		if (lane != 0) return;
+	if (warp >= kConsumerWarps) {
+		if (lane != 0 || warp > kConsumerWarps) return;
 		const uint64_t pol = policy_evict_first();
 		uint32_t it = 0;
 		for (size_t t = blockIdx.x; t < ntiles; t += gridDim.x, ++it) {
 			const uint32_t s = it % stages, par = ((it / stages) & 1u) ^ 1u;
 			mbar_wait(empty0 + 8 * s, par);
 			mbar_expect_tx(full0 + 8 * s, kStageBytes);
-			bulk_g2s(st0 + s * kStageBytes, buf + t * kStageBytes, kStageBytes, full0 + 8 * s, pol);
+			for (int o = 0; o < kStageBytes; o += copy_bytes) // one stage as kStageBytes / copy_bytes bulk copies
+				bulk_g2s(st0 + s * kStageBytes + o, buf + t * kStageBytes + o, copy_bytes, full0 + 8 * s, pol);
 		}
 		return;
 	}
@@ -89,12 +92,15 @@ Plan plan(int dtype, int dim, int q_dim, int kv_dim, int head_dim, int hidden, i
 	p.kernel = kernel_of(dtype, head_dim, G);
 	if (!p.kernel) return p;
 	if (dim % ep || q_dim % ep || hidden % ep || dim % 4 || q_dim % 4 || hidden % 4) return p;
-	Shape s;
-	if (!tile_shape(q_dim, kv_dim, dim, B, ep, false, true, &s)) return p;
-	if (!tile_shape(dim, 0, q_dim, B, ep, false, false, &s)) return p;
-	if (!tile_shape(hidden, 0, dim, B, ep, true, true, &s)) return p;
-	if (!tile_shape(dim, 0, hidden, B, ep, false, false, &s)) return p;
-	if (!tile_shape(vocab, 0, dim, B, ep, false, false, &s)) return p;
+	Shape s[kNumKinds];
+	if (!tile_shape(q_dim, kv_dim, dim, B, ep, false, true, &s[kQKV])) return p;
+	if (!tile_shape(dim, 0, q_dim, B, ep, false, false, &s[kWO])) return p;
+	if (!tile_shape(hidden, 0, dim, B, ep, true, true, &s[kFFN])) return p;
+	if (!tile_shape(dim, 0, hidden, B, ep, false, false, &s[kW2])) return p;
+	if (!tile_shape(vocab, 0, dim, B, ep, false, false, &s[kLM])) return p;
+	s[kQKV].G = (q_dim + 2 * kv_dim) / s[kQKV].R, s[kWO].G = dim / s[kWO].R, s[kFFN].G = hidden / (s[kFFN].R / 2);
+	s[kW2].G = dim / s[kW2].R, s[kLM].G = vocab / s[kLM].R;
+	for (int k = 0; k < kNumKinds; ++k) p.shape[k][0] = s[k].R, p.shape[k][1] = s[k].KT, p.shape[k][2] = s[k].nk, p.shape[k][3] = s[k].G;
 	const DeviceInfo &di = device_info();
 	int coop = 0, dev = 0;
 	cudaGetDevice(&dev);
@@ -102,10 +108,11 @@ Plan plan(int dtype, int dim, int q_dim, int kv_dim, int head_dim, int hidden, i
 	if (!coop || di.sms < 1) return p;
 	p.grid = di.sms;
 	int vf = std::max(padded(dim, ep), std::max(padded(q_dim, ep), padded(hidden, ep)));
-	vf = std::max(vf, kConsumerWarps * G * (head_dim + 2));
-	vf = std::max(vf, p.grid * G + G + 32);
+	if (n_kv_heads > p.grid) return p; // a CTA's attention units must span at most kHeadSlots KV heads
+	vf = std::max(vf, kHeadSlots * kConsumerWarps * G * (head_dim + 2) + p.grid * G + G + 32);
 	p.vec_floats = (vf + 31) / 32 * 32;
-	const size_t fixed = (size_t)p.vec_floats * 4 + (2 * kEpiBatch * kConsumerWarps * 4 + 16 + 16) * 4 + 2 * kMaxStages * 8;
+	// vec | rope table (64 float2) | red (16) | misc (16) | release counters (32) | mbarriers
+	const size_t fixed = (size_t)p.vec_floats * 4 + 64 * 8 + (16 + 16 + 32) * 4 + 2 * kMaxStages * 8;
 	const long room = (long)di.max_smem_optin - (long)fixed;
 	p.stages = (int)std::min<long>(kMaxStages, room / kStageBytes);
 	if (p.stages < 2) return p;
@@ -128,6 +135,7 @@ int launch(const Plan &p, const Args &a, cudaStream_t st) {
 	if (!p.ok) return YALM_EINVAL;
 	Args args = a;
 	args.stages = p.stages, args.vec_floats = p.vec_floats;
+	memcpy(args.shape, p.shape, sizeof(args.shape));
 	static const int debug = getenv("YALM_MEGA_DEBUG") ? atoi(getenv("YALM_MEGA_DEBUG")) : 0;
 	static const int max_stages = getenv("YALM_MEGA_STAGES") ? atoi(getenv("YALM_MEGA_STAGES")) : 0;
 	args.debug = debug;
@@ -144,6 +152,8 @@ extern "C" int yalm_stream_probe(size_t bytes, int iters, double *usec) {
 	using namespace yalm;
 	using namespace yalm::mega;
 	if (!usec || iters < 1 || bytes < (size_t)kStageBytes) return YALM_EINVAL;
+	int copy_bytes = getenv("YALM_PROBE_COPY") ? atoi(getenv("YALM_PROBE_COPY")) : kStageBytes;
+	if (copy_bytes < 16 || copy_bytes > kStageBytes || kStageBytes % copy_bytes) copy_bytes = kStageBytes;
 	const DeviceInfo &di = device_info();
 	const int stages = (int)std::min<long>(kMaxStages, ((long)di.max_smem_optin - 256) / kStageBytes);
 	const size_t smem = (size_t)stages * kStageBytes + 2 * kMaxStages * 8;
@@ -156,9 +166,9 @@ extern "C" int yalm_stream_probe(size_t bytes, int iters, double *usec) {
 	cudaEvent_t e0, e1;
 	cudaEventCreate(&e0);
 	cudaEventCreate(&e1);
-	for (int i = 0; i < 2; ++i) stream_probe_kernel<<<di.sms, kThreads, smem>>>(buf, bytes, stages, sink);
+	for (int i = 0; i < 2; ++i) stream_probe_kernel<<<di.sms, kThreads, smem>>>(buf, bytes, stages, sink, copy_bytes);
 	cudaEventRecord(e0);
-	for (int i = 0; i < iters; ++i) stream_probe_kernel<<<di.sms, kThreads, smem>>>(buf, bytes, stages, sink);
+	for (int i = 0; i < iters; ++i) stream_probe_kernel<<<di.sms, kThreads, smem>>>(buf, bytes, stages, sink, copy_bytes);
 	cudaEventRecord(e1);
 	cudaError_t err = cudaDeviceSynchronize();
 	float ms = 0.f;

@@ -1,19 +1,27 @@
 // Whole-token persistent decode kernel for sm_100a (see mega.h for the idea).
 //
 // Roles inside a CTA (one CTA per SM, cooperative launch so grid barriers are safe):
-//   warp 8      producer: walks this CTA's tile list for the WHOLE forward pass and issues
+//   warp 8      producer (all 32 lanes, one tile per lane and batch): walks this CTA's tile list for the WHOLE forward pass and issues
 //               cp.async.bulk (1-D TMA) copies global -> shared ring, completion on mbarriers.  It never
 //               waits for activations, only for free ring stages, so weight tiles of phase p+1 are in
 //               flight while the consumers are still finishing (or barrier-waiting for) phase p.
-//   warps 0-7   consumers: per phase  grid barrier -> stage the input vector (rmsnorm fused) into
-//               shared memory -> for every tile: wait(full) -> fp32 dot products straight out of shared
-//               memory -> release(empty) -> cross-warp reduce -> fused epilogue (clip + RoPE + KV append /
-//               residual add / GLU / logits + arg-max).
+//   warps 0-7   consumers.  Per phase: grid barrier -> stage the input vector (rmsnorm fused) into shared
+//               memory -> tile loop.  In the tile loop every warp OWNS whole row groups (all K-split tiles
+//               of a group land on the same warp), so there is no intra-CTA synchronisation at all between
+//               two grid barriers: wait(full) -> fp32 dot products straight out of shared memory ->
+//               release(empty) -> shuffle reduce -> the warp's own lanes run the fused epilogue (clip +
+//               RoPE + KV append / residual add / GLU / logits + arg-max).  Eight tiles are in progress per
+//               SM at any time, which is what hides the per-tile latency chain (mbarrier wait, LDS, shuffles).
 // Phases per layer: QKV | attention (split-K flash-decode over the head-major KV ring) | wo+residual |
 // w1/w3+GLU | w2+residual; then final norm + LM head (+ greedy arg-max and control-block advance).
 // Replaces, for one token, everything Model::_forward_cuda_build_graph launches (src/infer.cu:1041-1128,
 // 699-888): ~323 kernel nodes -> 1 launch.  Arithmetic (fp32 accumulate, formulas, clip/rope/softmax
 // definitions) follows the CPU reference exactly as the per-op kernels do (gemv.cuh, ops_attn.cu).
+//
+// Code size matters here: the per-layer instruction footprint has to stay inside the SM's instruction cache
+// (every phase body runs once per layer), so every phase body has exactly ONE call site (the phase loops below).
+// They are force-inlined all the same: a __noinline__ callee taking Ctx& forces the whole context struct into
+// local memory, and with the shared-memory carve-out at its maximum every such access is an L2 round trip.
 #pragma once
 
 #include "gemv.cuh"
@@ -24,11 +32,10 @@
 namespace yalm {
 namespace mega {
 
-// A wait longer than this many SM cycles (~4 s) is a bug: trap, never hang.  clock64, not %globaltimer: the
-// global timer read costs about a microsecond, which on the producer's empty-stage wait throttled the whole ring.
+// A wait longer than this many SM cycles (~4 s) is a bug: trap, never hang.
 constexpr long long kTimeoutCycles = 8000000000ll;
 constexpr int kCT = kConsumerWarps * 32;
-constexpr int kEpiBatch = 32; // row groups per epilogue batch (two batches of partials live in shared memory)
+constexpr int kHeadSlots = 2; // a CTA's attention units span at most two KV heads (n_kv_heads <= grid)
 
 // ---- PTX helpers -------------------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void *p) {
@@ -71,6 +78,21 @@ __device__ __forceinline__ uint64_t policy_evict_first() {
 	asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
 	return p;
 }
+// Per-stage release counters (shared memory): rel[s] = number of times stage s has been consumed and handed
+// back.  Tile idx (round r = idx / S of stage s = idx % S) may be issued once rel[s] >= r, and a consumer only
+// starts its parity wait on full[s] once rel[s] >= r, i.e. once every earlier round of the stage has completed —
+// an mbarrier parity wait alone cannot tell round r from round r-2, and here neither the producers (several
+// warps) nor the consumers (each warp owns different tiles) walk a stage's rounds in program order.
+// (Plain volatile accesses: ld.acquire / st.release on shared memory made ptxas emit CCTL.IVALL, an L1 invalidate,
+// per tile; the ordering that matters is carried by the mbarrier operations that follow the counter accesses.)
+__device__ __forceinline__ int ld_rel(const int *p) {
+	int v;
+	asm volatile("ld.volatile.shared.s32 %0, [%1];" : "=r"(v) : "r"(smem_u32(p)) : "memory");
+	return v;
+}
+__device__ __forceinline__ void st_rel(int *p, int v) {
+	asm volatile("st.volatile.shared.s32 [%0], %1;" ::"r"(smem_u32(p)), "r"(v) : "memory");
+}
 __device__ __forceinline__ void cbar() { // consumer warps only
 	asm volatile("bar.sync 1, %0;" ::"n"(kCT) : "memory");
 }
@@ -78,6 +100,56 @@ __device__ __forceinline__ unsigned ld_acquire(const unsigned *p) {
 	unsigned v;
 	asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
 	return v;
+}
+
+__device__ __forceinline__ uint4 lds128(uint32_t addr) {
+	uint4 v;
+	asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
+	return v;
+}
+__device__ __forceinline__ float4 lds128f(uint32_t addr) {
+	float4 v;
+	asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+	return v;
+}
+// Packed fp32 FMA (sm_100 FFMA2): (a.x*b.x + c.x, a.y*b.y + c.y), each lane IEEE round-to-nearest like fmaf.
+__device__ __forceinline__ float2 ffma2(float2 a, float2 b, float2 c) {
+	unsigned long long d;
+	asm("fma.rn.f32x2 %0, %1, %2, %3;"
+	    : "=l"(d)
+	    : "l"(*reinterpret_cast<unsigned long long *>(&a)), "l"(*reinterpret_cast<unsigned long long *>(&b)),
+	      "l"(*reinterpret_cast<unsigned long long *>(&c)));
+	return *reinterpret_cast<float2 *>(&d);
+}
+// acc += the EP weights of one 16-byte load times their x values, as EP/2 packed FMAs: acc.x collects the even
+// elements, acc.y the odd ones (summed at the end of the row).  fp32 accumulate like the reference.
+template <int DT>
+__device__ __forceinline__ float2 fma16x2(uint4 w, const float4 *xv, float2 acc);
+template <>
+__device__ __forceinline__ float2 fma16x2<YALM_F32>(uint4 w, const float4 *xv, float2 acc) {
+	acc = ffma2(make_float2(__uint_as_float(w.x), __uint_as_float(w.y)), make_float2(xv[0].x, xv[0].y), acc);
+	acc = ffma2(make_float2(__uint_as_float(w.z), __uint_as_float(w.w)), make_float2(xv[0].z, xv[0].w), acc);
+	return acc;
+}
+template <>
+__device__ __forceinline__ float2 fma16x2<YALM_F16>(uint4 w, const float4 *xv, float2 acc) {
+	using T = WTraits<YALM_F16>;
+	acc = ffma2(T::h2(w.x), make_float2(xv[0].x, xv[0].y), acc);
+	acc = ffma2(T::h2(w.y), make_float2(xv[0].z, xv[0].w), acc);
+	acc = ffma2(T::h2(w.z), make_float2(xv[1].x, xv[1].y), acc);
+	acc = ffma2(T::h2(w.w), make_float2(xv[1].z, xv[1].w), acc);
+	return acc;
+}
+template <>
+__device__ __forceinline__ float2 fma16x2<YALM_F8E4M3>(uint4 w, const float4 *xv, float2 acc) {
+	using T = WTraits<YALM_F8E4M3>;
+	const uint32_t ww[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+	for (int i = 0; i < 4; ++i) {
+		acc = ffma2(T::e2((uint16_t)(ww[i] & 0xffffu)), make_float2(xv[i].x, xv[i].y), acc);
+		acc = ffma2(T::e2((uint16_t)(ww[i] >> 16)), make_float2(xv[i].z, xv[i].w), acc);
+	}
+	return acc;
 }
 
 // ---- tile shapes ------------------------------------------------------------------------------------------
@@ -104,6 +176,9 @@ __host__ __device__ inline bool tile_shape(int rows, int rows_b, int K, int B, i
 			const int KT = K / nk;
 			if (nk > 1 && KT % CH) continue;
 			if ((long)R * KT * B > kStageBytes) continue;
+			// K-split tiles are one bulk copy per row: below 4 KB per copy the single issuing thread, not
+			// HBM, limits the ring (measured: 2 KB copies stream at 65 %), so prefer fewer rows per tile
+			if (nk > 1 && KT * B < 4096 && R > (pair ? 2 : 1)) break;
 			s->R = R, s->KT = KT, s->nk = nk;
 			return true;
 		}
@@ -121,28 +196,75 @@ struct Ctx {
 	long long wait_cycles;
 	int debug;
 	unsigned char *stages;
-	uint32_t stages_u32, full0, empty0;
-	float *vec, *part, *red;
+	uint32_t stages_u32, vec_u32, full0, empty0;
+	float *vec, *red;
+	float2 *rope; // (head_dim/2) cos/sin of pos * freq_j, the reference's fp32 formula
 	int *misc;
+	int *rel; // per-stage release counters
 	int cta, ncta, warp, lane, tid, S;
-	uint32_t it; // tiles produced / consumed so far by this role
+	uint32_t s_magic; // ceil(2^32 / S): idx / S == __umulhi(idx, s_magic) for every ring index of a launch
+	uint32_t it; // ring index of the next tile of this role (same sequence for the producer and every consumer warp)
 	int rot;     // CTA rotation of the current GEMV phase
 	unsigned bar_gen;
 	int token, pos, kv_sink, kv_pos, kv_len;
 	Shape shape[kNumKinds];
 };
 
+// (round, stage) of ring tile idx without an integer division
+__device__ __forceinline__ void ring_pos(const Ctx &c, uint32_t idx, uint32_t *s, int *r) {
+	const uint32_t q = __umulhi(idx, c.s_magic);
+	*r = (int)q;
+	*s = idx - q * (uint32_t)c.S;
+}
+
+__device__ __forceinline__ void stamp(Ctx &c, int layer, int phase, int k) {
+	if (c.prof && c.tid == 0) {
+		long long *row = c.prof + ((size_t)layer * kProfPhases + phase) * kProfSlots;
+		row[k] = clock64();
+		if (k == 3) row[4] = c.wait_cycles, c.wait_cycles = 0;
+	}
+}
+
+// This CTA's share of a phase's G row groups: groups g_first, g_first + ncta, ... (NL of them).
+__device__ __forceinline__ void my_groups(const Ctx &c, int G, int *g_first, int *NL) {
+	*g_first = (c.cta - c.rot + c.ncta) % c.ncta;
+	*NL = *g_first < G ? (G - *g_first + c.ncta - 1) / c.ncta : 0;
+}
+
 // ---- producer ---------------------------------------------------------------------------------------------
+// Ring order inside a GEMV phase: this CTA's groups in blocks of 8; inside a block the K-split index is the
+// slow axis and the group the fast one, so the 8 consumer warps (one group each) all have a tile in flight.
+//
+// One warp, all 32 lanes: a single thread needs ~1.5k cycles of dependent integer work per tile (measured: the
+// ring starved), so the tile list is walked a batch at a time with lane l issuing tile (batch start + l).  A
+// batch never exceeds the number of stages, so no lane waits on a stage another lane of the same batch fills.
 struct Producer {
 	Ctx &c;
 	uint64_t policy;
-	__device__ __forceinline__ uint32_t acquire(uint32_t bytes, uint32_t *bar) {
-		const uint32_t s = c.it % c.S, par = ((c.it / c.S) & 1u) ^ 1u;
-		mbar_wait(c.empty0 + 8 * s, par);
+	int batch; // min(stages, 32)
+
+	// Stage of ring tile idx is free (every earlier round consumed): expect `bytes` on its full barrier.
+	__device__ __forceinline__ uint32_t acquire(uint32_t idx, uint32_t bytes, uint32_t *bar) {
+		uint32_t s;
+		int r;
+		ring_pos(c, idx, &s, &r);
+		if (r > 0) {
+			// blocking wait on the stage's empty mbarrier (the hardware parks the thread: no issue slots burnt);
+			// the release counter first rules out the one case a parity wait gets wrong (two rounds behind)
+			if (ld_rel(c.rel + s) < r - 1) {
+				const long long t0 = clock64();
+				while (ld_rel(c.rel + s) < r - 1) {
+					__nanosleep(64);
+					if (clock64() - t0 > kTimeoutCycles) __trap();
+				}
+			}
+			mbar_wait(c.empty0 + 8 * s, (uint32_t)(r - 1) & 1u);
+		}
+		// the consumer's generic-proxy reads of the stage are ordered before the async-proxy refill
+		asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
 		*bar = c.full0 + 8 * s;
 		if (c.debug & 8) mbar_arrive(*bar);
 		else mbar_expect_tx(*bar, bytes);
-		++c.it;
 		return c.stages_u32 + s * kStageBytes;
 	}
 	// rows [row0, row0+nrows) x columns [kc*KT, (kc+1)*KT) of a (rows, K) matrix -> dst, tile rows packed
@@ -157,13 +279,29 @@ struct Producer {
 				bulk_g2s(dst + r * tb, m + (row0 + r) * row_bytes + (size_t)kc * tb, tb, bar, policy);
 		}
 	}
-	__device__ void gemv(int kind, const char *m0, const char *m1, const char *m2, int rows0, int rows1, int K, int B) {
+	__device__ __forceinline__ void gemv(int kind, const char *m0, const char *m1, const char *m2, int rows0, int rows1, int K,
+	                                  int B) {
 		const Shape sh = c.shape[kind];
 		const uint32_t tile_bytes = (uint32_t)sh.R * sh.KT * B;
-		for (int g = (c.cta - c.rot + c.ncta) % c.ncta; g < sh.G; g += c.ncta) {
-			for (int kc = 0; kc < sh.nk; ++kc) {
+		int g_first, NL;
+		my_groups(c, sh.G, &g_first, &NL);
+		const int ntiles = NL * sh.nk;
+		const int full_groups = NL / kConsumerWarps * kConsumerWarps, full_tiles = full_groups * sh.nk;
+		const int nb_last = NL - full_groups;
+		for (int t0 = 0; t0 < ntiles; t0 += batch) {
+			const int i = t0 + c.lane;
+			if (c.lane < batch && i < ntiles) {
+				int gl, kc;
+				if (i < full_tiles) {
+					const int r = i % (kConsumerWarps * sh.nk);
+					gl = i / (kConsumerWarps * sh.nk) * kConsumerWarps + r % kConsumerWarps, kc = r / kConsumerWarps;
+				} else {
+					const int r = i - full_tiles;
+					gl = full_groups + r % nb_last, kc = r / nb_last;
+				}
+				const int g = g_first + gl * c.ncta;
 				uint32_t bar;
-				const uint32_t dst = acquire(tile_bytes, &bar);
+				const uint32_t dst = acquire(c.it + (uint32_t)i, tile_bytes, &bar);
 				if (kind == kFFN) {
 					const int rh = sh.R / 2;
 					rows_copy(dst, bar, m0, (long)g * rh, rh, K, sh.KT, kc, sh.nk, B);
@@ -178,22 +316,30 @@ struct Producer {
 					rows_copy(dst, bar, m, row, sh.R, K, sh.KT, kc, sh.nk, B);
 				}
 			}
+			__syncwarp();
 		}
+		c.it += (uint32_t)ntiles;
 		c.rot = (c.rot + sh.G) % c.ncta;
 	}
-	__device__ void attention(const Layer &L, int HD, int n_kv, int max_seq) {
+	__device__ __forceinline__ void attention(const Layer &L, int HD, int n_kv, int max_seq) {
 		const int C = kStageBytes / (4 * HD);
 		const int nch = (c.kv_len + C - 1) / C, U = n_kv * nch;
 		const int u0 = (int)((long long)c.cta * U / c.ncta), u1 = (int)((long long)(c.cta + 1) * U / c.ncta);
-		for (int u = u0; u < u1; ++u) {
-			const int kvh = u / nch, t0 = (u % nch) * C, n = min(C, c.kv_len - t0);
-			const uint32_t bytes = (uint32_t)n * HD * 2;
-			uint32_t bar;
-			const uint32_t dst = acquire(2 * bytes, &bar);
-			const size_t off = ((size_t)kvh * max_seq + t0) * HD;
-			bulk_g2s(dst, L.kc + off, bytes, bar, policy);
-			bulk_g2s(dst + kStageBytes / 2, L.vc + off, bytes, bar, policy);
+		const int ntiles = u1 - u0;
+		for (int t0 = 0; t0 < ntiles; t0 += batch) {
+			const int i = t0 + c.lane;
+			if (c.lane < batch && i < ntiles) {
+				const int u = u0 + i, kvh = u / nch, r0 = (u % nch) * C, n = min(C, c.kv_len - r0);
+				const uint32_t bytes = (uint32_t)n * HD * 2;
+				uint32_t bar;
+				const uint32_t dst = acquire(c.it + (uint32_t)i, 2 * bytes, &bar);
+				const size_t off = ((size_t)kvh * max_seq + r0) * HD;
+				bulk_g2s(dst, L.kc + off, bytes, bar, policy);
+				bulk_g2s(dst + kStageBytes / 2, L.vc + off, bytes, bar, policy);
+			}
+			__syncwarp();
 		}
+		c.it += (uint32_t)ntiles;
 	}
 };
 
@@ -226,33 +372,44 @@ __device__ __forceinline__ void grid_barrier(Ctx &c, unsigned *sync) {
 	cbar();
 }
 
-__device__ __forceinline__ void stamp(Ctx &c, int layer, int phase, int k) {
-	if (c.prof && c.tid == 0) {
-		long long *row = c.prof + ((size_t)layer * kProfPhases + phase) * kProfSlots;
-		row[k] = clock64();
-		if (k == 3) row[4] = c.wait_cycles, c.wait_cycles = 0;
+// Wait until ring tile `idx` has landed; returns its shared-memory address.
+__device__ __forceinline__ const unsigned char *wait_tile(Ctx &c, uint32_t idx, uint32_t *slot) {
+	uint32_t s;
+	int r;
+	ring_pos(c, idx, &s, &r);
+	const uint32_t par = (uint32_t)r & 1u;
+	if (ld_rel(c.rel + s) < r) { // an earlier round of this stage is still in use (rare)
+		const long long t0 = clock64();
+		while (ld_rel(c.rel + s) < r)
+			if (clock64() - t0 > kTimeoutCycles) __trap();
 	}
-}
-
-__device__ __forceinline__ const unsigned char *wait_full(Ctx &c, uint32_t *slot) {
-	const uint32_t s = c.it % c.S, par = (c.it / c.S) & 1u;
 	if (c.prof && c.tid == 0) {
 		const long long t0 = clock64();
 		mbar_wait(c.full0 + 8 * s, par);
 		c.wait_cycles += clock64() - t0;
-	} else
+	} else {
 		mbar_wait(c.full0 + 8 * s, par);
-	*slot = s;
-	++c.it;
+	}
+	*slot = idx;
 	return c.stages + (size_t)s * kStageBytes;
 }
-__device__ __forceinline__ void release(Ctx &c, uint32_t slot) {
+__device__ __forceinline__ uint32_t tile_u32(const Ctx &c, const unsigned char *tile) {
+	return c.stages_u32 + (uint32_t)(tile - c.stages);
+}
+// Hand the stage of ring tile `idx` back to the producers.
+__device__ __forceinline__ void release(Ctx &c, uint32_t idx) {
 	__syncwarp();
-	if (c.lane == 0) mbar_arrive(c.empty0 + 8 * slot);
+	if (c.lane == 0) {
+		uint32_t s;
+		int r;
+		ring_pos(c, idx, &s, &r);
+		st_rel(c.rel + s, r + 1);
+		mbar_arrive(c.empty0 + 8 * s); // release semantics: orders the warp's reads of the stage and the counter store
+	}
 }
 
-// Input vector -> permuted shared layout (xs_slot).  src_kind 0: fp32 vector in global memory (read through L2,
-// it was written by other CTAs in this launch); 1: embedding row `token` of the weight-typed table (layer 0).
+// Input vector -> permuted shared layout (xs_slot).  embed_token < 0: fp32 vector in global memory (read through
+// L2: other CTAs wrote it during this launch); >= 0: that row of the weight-typed embedding table (layer 0).
 template <int DT>
 __device__ __forceinline__ float4 load_in4(const Args &a, const float *src, int embed_token, int e) {
 	if (embed_token < 0) return __ldcg(reinterpret_cast<const float4 *>(src + e));
@@ -265,7 +422,7 @@ __device__ __forceinline__ float4 load_in4(const Args &a, const float *src, int 
 template <int DT>
 __device__ __forceinline__ void stage_vec(Ctx &c, const Args &a, const float *src, int n, const float *rms_w, int embed_token) {
 	constexpr int EP = WTraits<DT>::EP;
-	constexpr int NC = 8; // float4 per thread kept in registers between the two rmsnorm passes (n <= 8192)
+	constexpr int NC = 4; // float4 per thread kept in registers between the two rmsnorm passes (n <= 4096)
 	if (rms_w) {
 		// reference formula and association order (src/infer.cpp:134-144): o = x * (1/sqrt(ss/n + eps)) * w
 		float4 cache[NC], wv[NC];
@@ -273,16 +430,15 @@ __device__ __forceinline__ void stage_vec(Ctx &c, const Args &a, const float *sr
 #pragma unroll
 		for (int i = 0; i < NC; ++i) {
 			const int e = (c.tid + i * kCT) * 4;
+			cache[i] = make_float4(0.f, 0.f, 0.f, 0.f), wv[i] = cache[i];
 			if (e < n) {
 				cache[i] = load_in4<DT>(a, src, embed_token, e);
 				wv[i] = *reinterpret_cast<const float4 *>(rms_w + e);
 			}
 		}
 #pragma unroll
-		for (int i = 0; i < NC; ++i) {
-			const int e = (c.tid + i * kCT) * 4;
-			if (e < n) ss += cache[i].x * cache[i].x + cache[i].y * cache[i].y + cache[i].z * cache[i].z + cache[i].w * cache[i].w;
-		}
+		for (int i = 0; i < NC; ++i)
+			ss += cache[i].x * cache[i].x + cache[i].y * cache[i].y + cache[i].z * cache[i].z + cache[i].w * cache[i].w;
 		for (int e = (c.tid + NC * kCT) * 4; e < n; e += kCT * 4) {
 			const float4 v = load_in4<DT>(a, src, embed_token, e);
 			ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
@@ -328,134 +484,134 @@ struct Epi {
 	const Layer *L;
 	const float *scale0, *scale1, *scale2; // fp8 row scales per matrix
 	int rows0, rows1;                      // QKV boundaries
-	float best_v;                          // LM head: running arg-max of this thread's rows
+	float best_v;                          // LM head: running arg-max of this lane's rows
 	int best_i;
 };
 
-// Epilogue of output item `t` of row group `g` (a row, a RoPE pair or a w1/w3 pair); `part` holds the eight
-// warps' partial sums of the group's rows: part[warp*4 + r].  Sum order over warps is fixed (deterministic).
-template <int DT>
-__device__ __forceinline__ void finalize(Ctx &c, const Args &a, Epi &ep, const Shape &sh, int g, int t, const float *part) {
-	auto rowsum = [&](int r) {
-		float v = 0.f;
-#pragma unroll
-		for (int w = 0; w < kConsumerWarps; ++w) v += part[w * 4 + r];
-		return v;
-	};
-	switch (ep.kind) {
-	case kQKV: {
-		long row = (long)g * sh.R + 2 * t;
-		int which = 0;
-		const float *sc = ep.scale0;
-		if (row >= ep.rows0 + ep.rows1) which = 2, row -= ep.rows0 + ep.rows1, sc = ep.scale2;
-		else if (row >= ep.rows0) which = 1, row -= ep.rows0, sc = ep.scale1;
-		float v0 = rowsum(2 * t), v1 = rowsum(2 * t + 1);
-		if (DT == YALM_F8E4M3 && sc) v0 *= sc[row], v1 *= sc[row + 1];
-		v0 = clipf(v0, a.clip), v1 = clipf(v1, a.clip);
-		const int hd = a.head_dim, j = (int)(row % hd);
-		if (which < 2) rope_pair(v0, v1, j, c.pos, a.theta, a.rotary_dim);
-		if (which == 0) {
-			*reinterpret_cast<float2 *>(a.q + row) = make_float2(v0, v1);
-		} else {
-			__half *cache = reinterpret_cast<__half *>(which == 1 ? ep.L->kc : ep.L->vc);
-			__half *dst = cache + ((size_t)(row / hd) * a.max_seq_len + c.kv_pos) * hd + j;
-			*reinterpret_cast<__half2 *>(dst) = __floats2half2_rn(v0, v1);
-		}
-		return;
-	}
-	case kWO:
-	case kW2: {
-		const long row = (long)g * sh.R + t;
-		float v = rowsum(t);
-		if (DT == YALM_F8E4M3 && ep.scale0) v *= ep.scale0[row];
-		a.x[row] = __ldcg(a.x + row) + v; // x += W v (src/infer.cpp:335-337, 381-383)
-		return;
-	}
-	case kFFN: {
-		const int rh = sh.R / 2;
-		const long row = (long)g * rh + t;
-		float gt = rowsum(t), up = rowsum(rh + t);
-		if (DT == YALM_F8E4M3 && ep.scale0) gt *= ep.scale0[row], up *= ep.scale1[row];
-		gt = a.act == YALM_ACT_GELU ? act_gelu(gt) : act_silu(gt);
-		a.hb[row] = gt * up;
-		return;
-	}
-	default: { // kLM
-		const long row = (long)g * sh.R + t;
-		float v = rowsum(t);
-		if (DT == YALM_F8E4M3 && ep.scale0) v *= ep.scale0[row];
-		a.logits[row] = v;
-		if (v > ep.best_v) ep.best_v = v, ep.best_i = (int)row; // a thread's rows ascend: first maximum wins
-		return;
-	}
-	}
-}
-
-// All row groups of one GEMV phase owned by this CTA.  The input vector is already staged in c.vec.
-// The eight warps never wait for each other inside the tile loop: each adds its slice of every tile and parks
-// its per-row partial in shared memory; every kEpiBatch groups (and at the end) one barrier hands a whole batch
-// to all 256 threads for the cross-warp sum and the fused epilogue, so global-memory latency in the epilogue
-// (residual read, KV append) is paid once per batch, not once per tile.
+// All row groups of one GEMV phase owned by this CTA; the input vector is already staged in c.vec.
+// Warp w owns groups w, w+8, ... of the CTA's list: it adds up all K-split tiles of the group, shuffle-reduces,
+// and its first lanes run the epilogue.  Nothing here synchronises with the other warps.
 template <int DT, int R>
 __device__ __forceinline__ void gemv_consume(Ctx &c, const Args &a, Epi &ep) {
 	using T = WTraits<DT>;
 	constexpr int EP = T::EP, CH = 32 * EP, Q = EP / 4;
 	const Shape sh = c.shape[ep.kind];
-	const int chunks = (sh.KT + CH - 1) / CH;
+	const int kind = ep.kind;
+	const int chunks = (sh.KT + CH - 1) / CH, nfull = sh.KT / CH;
 	const int row_stride = sh.KT * T::BYTES;
 	const int lane = c.lane, warp = c.warp;
-	const int nfin = (ep.kind == kQKV || ep.kind == kFFN) ? sh.R / 2 : sh.R; // epilogue items per group
-	const int g_first = (c.cta - c.rot + c.ncta) % c.ncta;
-	auto flush = [&](int batch, int n_groups) { // epilogue of groups [batch*kEpiBatch, +n_groups) of this CTA
-		const float *pb = c.part + (batch & 1) * kEpiBatch * kConsumerWarps * 4;
-		for (int i = c.tid; i < n_groups * nfin; i += kCT) {
-			const int gl = i / nfin, t = i % nfin;
-			finalize<DT>(c, a, ep, sh, g_first + (batch * kEpiBatch + gl) * c.ncta, t, pb + gl * kConsumerWarps * 4);
-		}
-	};
-	int gi = 0; // local group index
-	for (int g = g_first; g < sh.G; g += c.ncta, ++gi) {
-		float acc[R];
+	int g_first, NL;
+	my_groups(c, sh.G, &g_first, &NL);
+	const uint32_t base = c.it;
+	for (int b8 = 0; b8 < NL; b8 += kConsumerWarps) {
+		const int nb = min(kConsumerWarps, NL - b8);
+		if (warp >= nb) break;
+		const int g = g_first + (b8 + warp) * c.ncta;
+		// residual operand of the wo / w2 epilogue: issue the L2 read now, it is consumed after the tiles
+		float resid = 0.f;
+		if ((kind == kWO || kind == kW2) && lane < R) resid = __ldcg(a.x + (long)g * R + lane);
+		float2 acc2[R];
 #pragma unroll
-		for (int r = 0; r < R; ++r) acc[r] = 0.f;
+		for (int r = 0; r < R; ++r) acc2[r] = make_float2(0.f, 0.f);
 		for (int kc = 0; kc < sh.nk; ++kc) {
 			uint32_t slot;
-			const unsigned char *tile = wait_full(c, &slot);
-			const int cbase = kc * chunks;
-			// chunk (cbase + cc) belongs to warp (cbase + cc) % 8: balanced over the K splits
-			int cc = (warp - cbase % kConsumerWarps + kConsumerWarps) % kConsumerWarps;
-			if (c.debug & 1) cc = chunks;
-#pragma unroll 2
-			for (; cc < chunks; cc += kConsumerWarps) {
-				if (cc * CH + lane * EP < sh.KT) {
-					uint4 w[R];
+			const unsigned char *tile = wait_tile(c, base + (uint32_t)(b8 * sh.nk + kc * nb + warp), &slot);
+			if (!(c.debug & 1)) {
+				// shared-space addresses: this lane's 16 bytes of chunk 0 of row 0, and its x quarter 0
+				uint32_t wa = tile_u32(c, tile) + lane * 16;
+				uint32_t xa = c.vec_u32 + (uint32_t)(kc * chunks * CH) * 4 + lane * 16;
+				int cc = 0;
+				for (; cc + 2 <= nfull; cc += 2, wa += 1024, xa += 2 * CH * 4) { // all loads of two chunks, then the math
+					uint4 w[2][R];
+					float4 xv[2][Q];
 #pragma unroll
-					for (int r = 0; r < R; ++r)
-						w[r] = *reinterpret_cast<const uint4 *>(tile + r * row_stride + cc * 512 + lane * 16);
-					float4 xv[Q];
+					for (int u = 0; u < 2; ++u)
 #pragma unroll
-					for (int q = 0; q < Q; ++q)
-						xv[q] = *reinterpret_cast<const float4 *>(c.vec + (size_t)(cbase + cc) * CH + q * 128 + lane * 4);
+						for (int r = 0; r < R; ++r) w[u][r] = lds128(wa + r * row_stride + u * 512);
 #pragma unroll
-					for (int r = 0; r < R; ++r) acc[r] = T::fma16(w[r], xv, acc[r]);
+					for (int u = 0; u < 2; ++u)
+#pragma unroll
+						for (int q = 0; q < Q; ++q) xv[u][q] = lds128f(xa + (u * CH + q * 128) * 4);
+#pragma unroll
+					for (int u = 0; u < 2; ++u)
+#pragma unroll
+						for (int r = 0; r < R; ++r) acc2[r] = fma16x2<DT>(w[u][r], xv[u], acc2[r]);
+				}
+				for (; cc < chunks; ++cc, wa += 512, xa += CH * 4) { // odd full chunk and / or the ragged last one
+					if (cc * CH + lane * EP < sh.KT) {
+						uint4 w[R];
+						float4 xv[Q];
+#pragma unroll
+						for (int r = 0; r < R; ++r) w[r] = lds128(wa + r * row_stride);
+#pragma unroll
+						for (int q = 0; q < Q; ++q) xv[q] = lds128f(xa + q * 128 * 4);
+#pragma unroll
+						for (int r = 0; r < R; ++r) acc2[r] = fma16x2<DT>(w[r], xv, acc2[r]);
+					}
 				}
 			}
 			release(c, slot);
 		}
+		float acc[R];
 #pragma unroll
-		for (int r = 0; r < R; ++r) acc[r] = warp_sum(acc[r]);
-		if (lane == 0) {
-			float *dst = c.part + ((((gi / kEpiBatch) & 1) * kEpiBatch + gi % kEpiBatch) * kConsumerWarps + warp) * 4;
+		for (int r = 0; r < R; ++r) acc[r] = warp_sum(acc2[r].x + acc2[r].y);
+		// ---- epilogue: lane t handles output item t of the group -----------------------------------------
+		const int t = lane;
+		if (kind == kQKV) {
+			if (t < R / 2) {
+				float v0 = acc[0], v1 = acc[R > 1 ? 1 : 0];
 #pragma unroll
-			for (int r = 0; r < R; ++r) dst[r] = acc[r];
-		}
-		if ((gi + 1) % kEpiBatch == 0) {
-			cbar(); // batch complete; also fences the flush two batches ago off the buffer half about to be refilled
-			flush(gi / kEpiBatch, kEpiBatch);
+				for (int r = 2; r + 1 < R; r += 2)
+					if (t == r / 2) v0 = acc[r], v1 = acc[r + 1];
+				long row = (long)g * R + 2 * t;
+				int which = 0;
+				const float *sc = ep.scale0;
+				if (row >= ep.rows0 + ep.rows1) which = 2, row -= ep.rows0 + ep.rows1, sc = ep.scale2;
+				else if (row >= ep.rows0) which = 1, row -= ep.rows0, sc = ep.scale1;
+				if (DT == YALM_F8E4M3 && sc) v0 *= sc[row], v1 *= sc[row + 1];
+				v0 = clipf(v0, a.clip), v1 = clipf(v1, a.clip);
+				const int hd = a.head_dim, j = (int)(row % hd);
+				if (which < 2) { // interleaved-pair RoPE (src/infer.cpp:200-213), cos/sin from the per-token table
+					const float2 cs = c.rope[j >> 1];
+					const float r0 = v0 * cs.x - v1 * cs.y, r1 = v0 * cs.y + v1 * cs.x;
+					v0 = r0, v1 = r1;
+				}
+				if (which == 0) {
+					*reinterpret_cast<float2 *>(a.q + row) = make_float2(v0, v1);
+				} else {
+					__half *cache = reinterpret_cast<__half *>(which == 1 ? ep.L->kc : ep.L->vc);
+					__half *dst = cache + ((size_t)(row / hd) * a.max_seq_len + c.kv_pos) * hd + j;
+					*reinterpret_cast<__half2 *>(dst) = __floats2half2_rn(v0, v1);
+				}
+			}
+		} else if (kind == kFFN) {
+			constexpr int RH = R > 1 ? R / 2 : 1;
+			if (t < RH) {
+				float gt = acc[0], up = acc[RH < R ? RH : 0];
+#pragma unroll
+				for (int r = 1; r < RH; ++r)
+					if (t == r) gt = acc[r], up = acc[RH + r < R ? RH + r : 0];
+				const long row = (long)g * RH + t;
+				if (DT == YALM_F8E4M3 && ep.scale0) gt *= ep.scale0[row], up *= ep.scale1[row];
+				gt = a.act == YALM_ACT_GELU ? act_gelu(gt) : act_silu(gt);
+				a.hb[row] = gt * up;
+			}
+		} else if (t < R) {
+			float v = acc[0];
+#pragma unroll
+			for (int r = 1; r < R; ++r)
+				if (t == r) v = acc[r];
+			const long row = (long)g * R + t;
+			if (DT == YALM_F8E4M3 && ep.scale0) v *= ep.scale0[row];
+			if (kind == kLM) {
+				a.logits[row] = v;
+				if (v > ep.best_v) ep.best_v = v, ep.best_i = (int)row; // a lane's rows ascend: first maximum wins
+			} else {
+				a.x[row] = resid + v; // x += W v (src/infer.cpp:335-337, 381-383)
+			}
 		}
 	}
-	cbar();
-	if (gi % kEpiBatch) flush(gi / kEpiBatch, gi % kEpiBatch);
+	c.it = base + (uint32_t)(NL * sh.nk);
 	c.rot = (c.rot + sh.G) % c.ncta;
 }
 
@@ -482,25 +638,61 @@ __device__ __forceinline__ bool unit_overlap(int b, int ncta, int U, int X, int 
 }
 
 // Split-K flash-decode over this CTA's (kv head, row chunk) units; arithmetic as src/infer.cpp:216-248.
-// Each warp keeps its own online-softmax state over the rows it sees; warps, then CTAs, are merged with the
-// usual (max, sum, acc) rescaling in a fixed order, so results are run-to-run identical.
+// Warp w owns units w, w+8, ... of the CTA's contiguous unit range and keeps its own online-softmax state
+// (max, sum, acc) for all G query heads of the unit's KV head; a warp that moves on to the next KV head parks
+// its state in shared memory.  Warps, then CTAs, are merged with the usual rescaling in a fixed order, so
+// results are run-to-run identical.  The last CTA to publish a head's partial combines them (arrival counter).
 template <int HD, int G>
 __device__ __forceinline__ void attention_consume(Ctx &c, const Args &a, const Layer &L) {
-	constexpr int LPR = HD / 8, RPS = 32 / LPR;
-	constexpr int C = kStageBytes / (4 * HD);
-	constexpr int STEPS = C / (kConsumerWarps * RPS);
-	constexpr int WS = HD + 2; // per (warp, head) record in shared memory: acc[HD], m, l
-	static_assert(STEPS >= 1, "stage too small for this head_dim");
+	constexpr int LPR = HD / 8, RPS = 32 / LPR; // lanes per row, rows per warp step
+	constexpr int C = kStageBytes / (4 * HD);   // rows per tile
+	constexpr int STEPS = 4;                    // row steps per online-softmax update
+	constexpr int PASSES = C / (STEPS * RPS);
+	constexpr int WS = HD + 2; // per (slot, warp, head) record in shared memory: acc[HD], m, l
+	static_assert(PASSES >= 1 && PASSES * STEPS * RPS == C, "stage size / head_dim mismatch");
 	const int lane = c.lane, warp = c.warp, ncta = c.ncta;
 	const int sub = lane % LPR, rgrp = lane / LPR;
 	const int nch = (c.kv_len + C - 1) / C, U = a.n_kv_heads * nch;
 	const int u0 = (int)((long long)c.cta * U / ncta), u1 = (int)((long long)(c.cta + 1) * U / ncta);
+	const int NU = u1 - u0;
+	const uint32_t base = c.it;
+	c.it = base + (uint32_t)NU;
+	if (NU == 0) return;
+	const int kv_first = u0 / nch, kv_last = (u1 - 1) / nch;
 	const float div = sqrtf((float)HD);
+	float *wsm = c.vec; // [kHeadSlots][warps][G][WS]
+	// every record starts empty (m = -inf, l = 0): warps that never touch a head contribute nothing
+	if (lane < kHeadSlots * G) { // each warp initialises its own records, so a __syncwarp orders it against park()
+		float *rec = wsm + (((lane / G) * kConsumerWarps + warp) * G + lane % G) * WS;
+		rec[HD] = -INFINITY, rec[HD + 1] = 0.f;
+	}
+
 	float qr[G][8], acc[G][8], m[G], l[G];
 	int cur = -1;
-	for (int u = u0; u < u1; ++u) {
-		const int kvh = u / nch, t0 = (u % nch) * C, n = min(C, c.kv_len - t0);
+	auto park = [&](int kvh) { // merge the warp's row groups and store its state for head kvh
+#pragma unroll
+		for (int o = LPR; o < 32; o <<= 1)
+#pragma unroll
+			for (int g = 0; g < G; ++g) {
+				l[g] += __shfl_xor_sync(kFull, l[g], o);
+#pragma unroll
+				for (int j = 0; j < 8; ++j) acc[g][j] += __shfl_xor_sync(kFull, acc[g][j], o);
+			}
+		if (rgrp == 0) {
+#pragma unroll
+			for (int g = 0; g < G; ++g) {
+				float *rec = wsm + (((kvh - kv_first) * kConsumerWarps + warp) * G + g) * WS;
+#pragma unroll
+				for (int j = 0; j < 8; ++j) rec[sub * 8 + j] = acc[g][j];
+				if (sub == 0) rec[HD] = m[g], rec[HD + 1] = l[g];
+			}
+		}
+	};
+	__syncwarp();
+	for (int i = warp; i < NU; i += kConsumerWarps) {
+		const int u = u0 + i, kvh = u / nch, t0 = (u % nch) * C, n = min(C, c.kv_len - t0);
 		if (kvh != cur) {
+			if (cur >= 0) park(cur);
 			cur = kvh;
 #pragma unroll
 			for (int g = 0; g < G; ++g) {
@@ -514,107 +706,98 @@ __device__ __forceinline__ void attention_consume(Ctx &c, const Args &a, const L
 			}
 		}
 		uint32_t slot;
-		const unsigned char *tile = wait_full(c, &slot);
+		const unsigned char *tile = wait_tile(c, base + (uint32_t)i, &slot);
 		const __half *ks = reinterpret_cast<const __half *>(tile);
 		const __half *vs = reinterpret_cast<const __half *>(tile + kStageBytes / 2);
 		const size_t goff = ((size_t)kvh * a.max_seq_len + t0) * HD;
 		const __half *kg = reinterpret_cast<const __half *>(L.kc) + goff;
 		const __half *vg = reinterpret_cast<const __half *>(L.vc) + goff;
-		float s[STEPS][G];
-#pragma unroll
-		for (int st = 0; st < STEPS; ++st) {
-			const int row = st * (kConsumerWarps * RPS) + warp * RPS + rgrp, t = t0 + row;
-			const bool valid = row < n && !(c.debug & 4);
-			// the row appended by this token and the re-rotated sink rows were written after the producer
-			// may have fetched the tile: read those from global memory (L2), everything else from the ring
-			const bool fresh = t == c.kv_pos || t < c.kv_sink;
-			uint4 kv = make_uint4(0, 0, 0, 0);
-			if (valid) kv = fresh ? __ldcg(reinterpret_cast<const uint4 *>(kg + (size_t)row * HD + sub * 8))
-			                      : *reinterpret_cast<const uint4 *>(ks + row * HD + sub * 8);
-			float kf[8];
-			unpack8(kv, kf);
-#pragma unroll
-			for (int g = 0; g < G; ++g) {
-				float d = 0.f;
-#pragma unroll
-				for (int j = 0; j < 8; ++j) d = fmaf(qr[g][j], kf[j], d);
-#pragma unroll
-				for (int o = LPR / 2; o > 0; o >>= 1) d += __shfl_xor_sync(kFull, d, o);
-				s[st][g] = valid ? d / div : -INFINITY;
-			}
-		}
-#pragma unroll
-		for (int g = 0; g < G; ++g) {
-			float mt = s[0][g];
-#pragma unroll
-			for (int st = 1; st < STEPS; ++st) mt = fmaxf(mt, s[st][g]);
-#pragma unroll
-			for (int o = LPR; o < 32; o <<= 1) mt = fmaxf(mt, __shfl_xor_sync(kFull, mt, o));
-			const float m_new = fmaxf(m[g], mt);
-			const float corr = m_new == -INFINITY ? 1.f : expf(m[g] - m_new);
-			m[g] = m_new;
-			l[g] *= corr;
-#pragma unroll
-			for (int j = 0; j < 8; ++j) acc[g][j] *= corr;
+		for (int pass = 0; pass < PASSES; ++pass) {
+			const int row0 = pass * (STEPS * RPS);
+			if (row0 >= n) break;
+			float s[STEPS][G];
 #pragma unroll
 			for (int st = 0; st < STEPS; ++st) {
-				const float p = s[st][g] == -INFINITY ? 0.f : expf(s[st][g] - m_new);
-				s[st][g] = p;
-				l[g] += p;
-			}
-		}
-#pragma unroll
-		for (int st = 0; st < STEPS; ++st) {
-			const int row = st * (kConsumerWarps * RPS) + warp * RPS + rgrp, t = t0 + row;
-			if (row < n && !(c.debug & 4)) {
+				const int row = row0 + st * RPS + rgrp, t = t0 + row;
+				const bool valid = row < n && !(c.debug & 4);
+				// the row appended by this token and the re-rotated sink rows were written after the producer
+				// may have fetched the tile: read those from global memory (L2), everything else from the ring
 				const bool fresh = t == c.kv_pos || t < c.kv_sink;
-				const uint4 vv = fresh ? __ldcg(reinterpret_cast<const uint4 *>(vg + (size_t)row * HD + sub * 8))
-				                       : *reinterpret_cast<const uint4 *>(vs + row * HD + sub * 8);
-				float vf[8];
-				unpack8(vv, vf);
+				uint4 kv = make_uint4(0, 0, 0, 0);
+				if (valid) kv = fresh ? __ldcg(reinterpret_cast<const uint4 *>(kg + (size_t)row * HD + sub * 8))
+				                      : *reinterpret_cast<const uint4 *>(ks + row * HD + sub * 8);
+				float kf[8];
+				unpack8(kv, kf);
 #pragma unroll
-				for (int g = 0; g < G; ++g)
+				for (int g = 0; g < G; ++g) {
+					float d = 0.f;
 #pragma unroll
-					for (int j = 0; j < 8; ++j) acc[g][j] = fmaf(s[st][g], vf[j], acc[g][j]);
+					for (int j = 0; j < 8; ++j) d = fmaf(qr[g][j], kf[j], d);
+#pragma unroll
+					for (int o = LPR / 2; o > 0; o >>= 1) d += __shfl_xor_sync(kFull, d, o);
+					s[st][g] = valid ? d / div : -INFINITY;
+				}
+			}
+#pragma unroll
+			for (int g = 0; g < G; ++g) {
+				float mt = s[0][g];
+#pragma unroll
+				for (int st = 1; st < STEPS; ++st) mt = fmaxf(mt, s[st][g]);
+#pragma unroll
+				for (int o = LPR; o < 32; o <<= 1) mt = fmaxf(mt, __shfl_xor_sync(kFull, mt, o));
+				const float m_new = fmaxf(m[g], mt);
+				const float corr = m_new == -INFINITY ? 1.f : expf(m[g] - m_new);
+				m[g] = m_new;
+				l[g] *= corr;
+#pragma unroll
+				for (int j = 0; j < 8; ++j) acc[g][j] *= corr;
+#pragma unroll
+				for (int st = 0; st < STEPS; ++st) {
+					const float p = s[st][g] == -INFINITY ? 0.f : expf(s[st][g] - m_new);
+					s[st][g] = p;
+					l[g] += p;
+				}
+			}
+#pragma unroll
+			for (int st = 0; st < STEPS; ++st) {
+				const int row = row0 + st * RPS + rgrp, t = t0 + row;
+				if (row < n && !(c.debug & 4)) {
+					const bool fresh = t == c.kv_pos || t < c.kv_sink;
+					const uint4 vv = fresh ? __ldcg(reinterpret_cast<const uint4 *>(vg + (size_t)row * HD + sub * 8))
+					                       : *reinterpret_cast<const uint4 *>(vs + row * HD + sub * 8);
+					float vf[8];
+					unpack8(vv, vf);
+#pragma unroll
+					for (int g = 0; g < G; ++g)
+#pragma unroll
+						for (int j = 0; j < 8; ++j) acc[g][j] = fmaf(s[st][g], vf[j], acc[g][j]);
+				}
 			}
 		}
 		release(c, slot);
-		if (u + 1 < u1 && (u + 1) / nch == kvh) continue;
+	}
+	if (cur >= 0) park(cur);
+	cbar();
 
-		// ---- this CTA is done with head kvh: merge row groups, warps, then publish the partial ----------
-#pragma unroll
-		for (int o = LPR; o < 32; o <<= 1)
-#pragma unroll
-			for (int g = 0; g < G; ++g) {
-				l[g] += __shfl_xor_sync(kFull, l[g], o);
-#pragma unroll
-				for (int j = 0; j < 8; ++j) acc[g][j] += __shfl_xor_sync(kFull, acc[g][j], o);
-			}
-		float *wsm = c.vec;
-		if (rgrp == 0) {
-#pragma unroll
-			for (int g = 0; g < G; ++g) {
-				float *rec = wsm + (warp * G + g) * WS;
-#pragma unroll
-				for (int j = 0; j < 8; ++j) rec[sub * 8 + j] = acc[g][j];
-				if (sub == 0) rec[HD] = m[g], rec[HD + 1] = l[g];
-			}
-		}
-		cbar();
+	// ---- per KV head of this CTA: merge the warps, publish the partial, last CTA combines ---------------
+	for (int kvh = kv_first; kvh <= kv_last; ++kvh) {
+		const float *hs = wsm + (size_t)(kvh - kv_first) * kConsumerWarps * G * WS;
 		float *pa = a.ws_acc + ((size_t)kvh * ncta + c.cta) * G * HD;
 		float *pml = a.ws_ml + ((size_t)kvh * ncta + c.cta) * G * 2;
 		for (int i = c.tid; i < G * HD; i += kCT) {
 			const int g = i / HD, d = i % HD;
 			float M = -INFINITY;
 #pragma unroll
-			for (int w = 0; w < kConsumerWarps; ++w) M = fmaxf(M, wsm[(w * G + g) * WS + HD]);
+			for (int w = 0; w < kConsumerWarps; ++w) M = fmaxf(M, hs[(w * G + g) * WS + HD]);
 			float v = 0.f, ls = 0.f;
 #pragma unroll
 			for (int w = 0; w < kConsumerWarps; ++w) {
-				const float *rec = wsm + (w * G + g) * WS;
-				const float e = rec[HD] == -INFINITY ? 0.f : expf(rec[HD] - M);
-				v = fmaf(e, rec[d], v);
-				ls = fmaf(e, rec[HD + 1], ls);
+				const float *rec = hs + (w * G + g) * WS;
+				if (rec[HD] != -INFINITY) { // empty records hold no data
+					const float e = expf(rec[HD] - M);
+					v = fmaf(e, rec[d], v);
+					ls = fmaf(e, rec[HD + 1], ls);
+				}
 			}
 			pa[i] = v;
 			if (d == 0) pml[g * 2] = M, pml[g * 2 + 1] = ls;
@@ -633,44 +816,51 @@ __device__ __forceinline__ void attention_consume(Ctx &c, const Args &a, const L
 			}
 		}
 		cbar();
-		if (c.misc[0]) {
-			// last CTA of this head: combine every CTA's partial in CTA order
-			__threadfence();
-			const int b_lo = max(0, (int)((long long)X * ncta / U) - 1);
-			const int b_hi = min(ncta - 1, (int)(((long long)Y * ncta + U - 1) / U));
-			float *wts = c.vec; // [ncta][G] merge weights (-1: CTA has no partial), then Lsum[G]
-			for (int g = warp; g < G; g += kConsumerWarps) {
-				float M = -INFINITY;
-				for (int b = b_lo + lane; b <= b_hi; b += 32)
-					if (unit_overlap(b, ncta, U, X, Y)) M = fmaxf(M, __ldcg(a.ws_ml + (((size_t)kvh * ncta + b) * G + g) * 2));
-				M = warp_max(M);
-				float ls = 0.f;
-				for (int b = b_lo + lane; b <= b_hi; b += 32) {
-					float w = -1.f;
-					if (unit_overlap(b, ncta, U, X, Y)) {
-						const float *ml = a.ws_ml + (((size_t)kvh * ncta + b) * G + g) * 2;
-						const float mb = __ldcg(ml);
-						w = mb == -INFINITY ? 0.f : expf(mb - M);
-						ls += w * __ldcg(ml + 1);
-					}
-					wts[b * G + g] = w;
+		if (!c.misc[0]) continue; // CTA-uniform
+		// last CTA of this head: combine every CTA's partial in CTA order
+		__threadfence();
+		const int b_lo = max(0, (int)((long long)X * ncta / U) - 1);
+		const int b_hi = min(ncta - 1, (int)(((long long)Y * ncta + U - 1) / U));
+		float *wts = wsm + kHeadSlots * kConsumerWarps * G * WS; // [ncta][G] merge weights (-1: no partial), Lsum[G]
+		for (int g = warp; g < G; g += kConsumerWarps) {
+			float M = -INFINITY;
+			for (int b = b_lo + lane; b <= b_hi; b += 32)
+				if (unit_overlap(b, ncta, U, X, Y)) M = fmaxf(M, __ldcg(a.ws_ml + (((size_t)kvh * ncta + b) * G + g) * 2));
+			M = warp_max(M);
+			float ls = 0.f;
+			for (int b = b_lo + lane; b <= b_hi; b += 32) {
+				float w = -1.f;
+				if (unit_overlap(b, ncta, U, X, Y)) {
+					const float *ml = a.ws_ml + (((size_t)kvh * ncta + b) * G + g) * 2;
+					const float mb = __ldcg(ml);
+					w = mb == -INFINITY ? 0.f : expf(mb - M);
+					ls += w * __ldcg(ml + 1);
 				}
-				ls = warp_sum(ls);
-				if (lane == 0) wts[ncta * G + g] = ls;
+				wts[b * G + g] = w;
 			}
-			cbar();
-			for (int i = c.tid; i < G * HD; i += kCT) {
-				const int g = i / HD;
-				float v = 0.f;
-				for (int b = b_lo; b <= b_hi; ++b) {
-					const float w = wts[b * G + g];
-					if (w > 0.f) v = fmaf(w, __ldcg(a.ws_acc + ((size_t)kvh * ncta + b) * G * HD + i), v);
-				}
-				a.att_out[(size_t)kvh * G * HD + i] = v / wts[ncta * G + g];
-			}
-			if (c.tid == 0) a.head_counters[kvh] = 0;
+			ls = warp_sum(ls);
+			if (lane == 0) wts[ncta * G + g] = ls;
 		}
-		cbar(); // c.vec is reused by the next head / phase
+		cbar();
+		for (int i = c.tid; i < G * HD; i += kCT) {
+			const int g = i / HD;
+			const float *src = a.ws_acc + (size_t)kvh * ncta * G * HD + i;
+			float v = 0.f;
+			for (int b = b_lo; b <= b_hi; b += 8) { // eight independent L2 reads in flight, summed in CTA order
+				float pv[8], pw[8];
+#pragma unroll
+				for (int k = 0; k < 8; ++k) {
+					pw[k] = b + k <= b_hi ? wts[(b + k) * G + g] : -1.f;
+					pv[k] = pw[k] > 0.f ? __ldcg(src + (size_t)(b + k) * G * HD) : 0.f;
+				}
+#pragma unroll
+				for (int k = 0; k < 8; ++k)
+					if (pw[k] > 0.f) v = fmaf(pw[k], pv[k], v);
+			}
+			a.att_out[(size_t)kvh * G * HD + i] = v / wts[ncta * G + g];
+		}
+		if (c.tid == 0) a.head_counters[kvh] = 0;
+		cbar(); // wts is reused by the next head
 	}
 }
 
@@ -686,16 +876,19 @@ template <int DT, int HD, int G>
 __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_constant__ Args a) {
 	extern __shared__ __align__(128) unsigned char smem_raw[];
 	using T = WTraits<DT>;
-	constexpr int B = T::BYTES, EP = T::EP;
+	constexpr int B = T::BYTES;
 	Ctx c;
 	c.S = a.stages;
+	c.s_magic = (uint32_t)((0x100000000ull + (unsigned)a.stages - 1) / (unsigned)a.stages);
 	c.stages = smem_raw;
 	c.stages_u32 = smem_u32(smem_raw);
 	c.vec = reinterpret_cast<float *>(smem_raw + (size_t)c.S * kStageBytes);
-	c.part = c.vec + a.vec_floats;
-	c.red = c.part + 2 * kEpiBatch * kConsumerWarps * 4;
+	c.vec_u32 = c.stages_u32 + (uint32_t)c.S * kStageBytes;
+	c.rope = reinterpret_cast<float2 *>(c.vec + a.vec_floats);
+	c.red = reinterpret_cast<float *>(c.rope + 64);
 	c.misc = reinterpret_cast<int *>(c.red + 16);
-	uint64_t *bars = reinterpret_cast<uint64_t *>(c.misc + 16);
+	c.rel = c.misc + 16;
+	uint64_t *bars = reinterpret_cast<uint64_t *>(c.rel + 32);
 	c.full0 = smem_u32(bars);
 	c.empty0 = c.full0 + 8 * kMaxStages;
 	c.cta = blockIdx.x, c.ncta = gridDim.x;
@@ -709,162 +902,140 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_c
 	if (a.token < 0) c.token = a.ctl[CTL_TOKEN], c.pos = a.ctl[CTL_POS];
 	derive_ring(c.pos, a.max_seq_len, &c.kv_sink, &c.kv_pos, &c.kv_len);
 
-	constexpr int hd = HD;
-	tile_shape(a.q_dim, a.kv_dim, a.dim, B, EP, false, true, &c.shape[kQKV]);
-	c.shape[kQKV].G = (a.q_dim + 2 * a.kv_dim) / c.shape[kQKV].R;
-	tile_shape(a.dim, 0, a.q_dim, B, EP, false, false, &c.shape[kWO]);
-	c.shape[kWO].G = a.dim / c.shape[kWO].R;
-	tile_shape(a.hidden, 0, a.dim, B, EP, true, true, &c.shape[kFFN]);
-	c.shape[kFFN].G = a.hidden / (c.shape[kFFN].R / 2);
-	tile_shape(a.dim, 0, a.hidden, B, EP, false, false, &c.shape[kW2]);
-	c.shape[kW2].G = a.dim / c.shape[kW2].R;
-	tile_shape(a.vocab, 0, a.dim, B, EP, false, false, &c.shape[kLM]);
-	c.shape[kLM].G = a.vocab / c.shape[kLM].R;
+#pragma unroll
+	for (int k = 0; k < kNumKinds; ++k) // tile shapes are planned on the host (tile_shape)
+		c.shape[k].R = a.shape[k][0], c.shape[k].KT = a.shape[k][1], c.shape[k].nk = a.shape[k][2], c.shape[k].G = a.shape[k][3];
 
 	if (threadIdx.x == 0) {
 		for (int i = 0; i < c.S; ++i) {
 			mbar_init(c.full0 + 8 * i, 1);
-			mbar_init(c.empty0 + 8 * i, kConsumerWarps);
+			mbar_init(c.empty0 + 8 * i, 1);
+			c.rel[i] = 0;
 		}
 		asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
 	}
+	// RoPE table of this token: cos/sin(pos * theta^(-j/rotary_dim)) with the reference's fp32 formula
+	// (src/infer.cpp:200-213; accurate powf/cosf/sinf: pos * freq reaches 3e4 rad at 32k context)
+	if (threadIdx.x < HD / 2) {
+		const int j = 2 * threadIdx.x;
+		const float freq = j >= a.rotary_dim ? 0.f : 1.0f / powf(a.theta, (float)j / (float)a.rotary_dim);
+		const float val = c.pos * freq;
+		c.rope[threadIdx.x] = make_float2(cosf(val), sinf(val));
+	}
 	__syncthreads();
 
-	if (c.warp == kConsumerWarps) {
-		// ================================ producer ================================
-		if (c.lane != 0) return;
-		Producer p{c, (a.debug & 8) ? 0ull : policy_evict_first()};
-		for (int l = 0; l < a.n_layers; ++l) {
+	if (c.warp >= kConsumerWarps) {
+		// ================================ producers ================================
+		Producer p{c, (a.debug & 8) ? 0ull : policy_evict_first(), min(c.S, 32)};
+		const int n_phases = a.n_layers * 5 + (a.mode != kHydrate ? 1 : 0);
+		for (int ph = 0; ph < n_phases; ++ph) { // one call site per producer function (code size)
+			const int l = min(ph / 5, a.n_layers - 1), k = ph < a.n_layers * 5 ? ph % 5 : 5;
 			const Layer &L = a.layers[l];
-			p.gemv(kQKV, L.wq, L.wk, L.wv, a.q_dim, a.kv_dim, a.dim, B);
-			p.attention(L, hd, a.n_kv_heads, a.max_seq_len);
-			p.gemv(kWO, L.wo, nullptr, nullptr, a.dim, 0, a.q_dim, B);
-			p.gemv(kFFN, L.w1, L.w3, nullptr, a.hidden, 0, a.dim, B);
-			p.gemv(kW2, L.w2, nullptr, nullptr, a.dim, 0, a.hidden, B);
+			if (k == 1) {
+				p.attention(L, HD, a.n_kv_heads, a.max_seq_len);
+				continue;
+			}
+			int kind = kQKV, rows0 = a.q_dim, rows1 = a.kv_dim, K = a.dim;
+			const char *m0 = L.wq, *m1 = L.wk, *m2 = L.wv;
+			switch (k) {
+			case 2: kind = kWO, m0 = L.wo, rows0 = a.dim, K = a.q_dim; break;
+			case 3: kind = kFFN, m0 = L.w1, m1 = L.w3, rows0 = a.hidden; break;
+			case 4: kind = kW2, m0 = L.w2, rows0 = a.dim, K = a.hidden; break;
+			case 5: kind = kLM, m0 = a.wcls, rows0 = a.vocab; break;
+			default: break;
+			}
+			p.gemv(kind, m0, m1, m2, rows0, rows1, K, B);
 		}
-		if (a.mode != kHydrate) p.gemv(kLM, a.wcls, nullptr, nullptr, a.vocab, 0, a.dim, B);
 		return;
 	}
 
 	// ================================ consumers ================================
 	Epi ep;
-	for (int l = 0; l < a.n_layers; ++l) {
+	ep.best_v = -FLT_MAX, ep.best_i = 0x7fffffff;
+	const int n_phases = a.n_layers * 5 + (a.mode != kHydrate ? 1 : 0);
+	for (int ph = 0; ph < n_phases; ++ph) { // one loop body = one call site per phase function
+		const int l = min(ph / 5, a.n_layers - 1), k = ph < a.n_layers * 5 ? ph % 5 : 5;
 		const Layer &L = a.layers[l];
 		ep.L = &L;
-		// ---- rmsnorm -> q,k,v -> clip -> RoPE -> KV append (+ sink re-rotation) --------------------------
-		stamp(c, l, 0, 0);
-		if (l > 0) grid_barrier(c, a.sync);
-		stamp(c, l, 0, 1);
-		stage_vec<DT>(c, a, a.x, a.dim, L.rms_att, l == 0 ? c.token : -1);
-		stamp(c, l, 0, 2);
-		if (c.kv_sink > 0 && c.cta == c.ncta - 1) {
+		stamp(c, l, k, 0);
+		if (ph > 0) grid_barrier(c, a.sync);
+		stamp(c, l, k, 1);
+		if (k == 1) { // attention: q comes from registers, nothing to stage
+			stamp(c, l, k, 2);
+			attention_consume<HD, G>(c, a, L);
+			stamp(c, l, k, 3);
+			continue;
+		}
+		const float *src = a.x, *rms = nullptr;
+		int n = a.dim;
+		switch (k) {
+		case 0: rms = L.rms_att, ep.kind = kQKV, ep.scale0 = L.sq, ep.scale1 = L.sk, ep.scale2 = L.sv, ep.rows0 = a.q_dim, ep.rows1 = a.kv_dim; break;
+		case 2: src = a.att_out, n = a.q_dim, ep.kind = kWO, ep.scale0 = L.so; break;
+		case 3: rms = L.rms_ffn, ep.kind = kFFN, ep.scale0 = L.s1, ep.scale1 = L.s3; break;
+		case 4: src = a.hb, n = a.hidden, ep.kind = kW2, ep.scale0 = L.s2; break;
+		default: rms = a.rms_final, ep.kind = kLM, ep.scale0 = a.wcls_scale; break;
+		}
+		stage_vec<DT>(c, a, src, n, rms, ph == 0 ? c.token : -1);
+		stamp(c, l, k, 2);
+		if (k == 0 && c.kv_sink > 0 && c.cta == c.ncta - 1) {
 			// rotate each sink key forward by one position, fp16 -> fp32 -> fp16 (src/infer.cpp:303-317)
-			const int hp = hd >> 1, npairs = c.kv_sink * a.n_kv_heads * hp;
+			const int hp = HD >> 1, npairs = c.kv_sink * a.n_kv_heads * hp;
 			for (int p = c.tid; p < npairs; p += kCT) {
 				const int r = p / (a.n_kv_heads * hp), h = (p / hp) % a.n_kv_heads, i = (p % hp) * 2;
-				__half2 *ptr = reinterpret_cast<__half2 *>(reinterpret_cast<__half *>(L.kc) + ((size_t)h * a.max_seq_len + r) * hd + i);
+				__half2 *ptr = reinterpret_cast<__half2 *>(reinterpret_cast<__half *>(L.kc) + ((size_t)h * a.max_seq_len + r) * HD + i);
 				float2 v = __half22float2(*ptr);
 				rope_pair(v.x, v.y, i, 1, a.theta, a.rotary_dim);
 				*ptr = __floats2half2_rn(v.x, v.y);
 			}
 		}
-		ep.kind = kQKV, ep.scale0 = L.sq, ep.scale1 = L.sk, ep.scale2 = L.sv, ep.rows0 = a.q_dim, ep.rows1 = a.kv_dim;
 		gemv_phase<DT>(c, a, ep);
-		stamp(c, l, 0, 3);
-		// ---- attention -----------------------------------------------------------------------------------
-		stamp(c, l, 1, 0);
-		grid_barrier(c, a.sync);
-		stamp(c, l, 1, 1);
-		stamp(c, l, 1, 2);
-		attention_consume<HD, G>(c, a, L);
-		stamp(c, l, 1, 3);
-		// ---- wo + residual -------------------------------------------------------------------------------
-		stamp(c, l, 2, 0);
-		grid_barrier(c, a.sync);
-		stamp(c, l, 2, 1);
-		stage_vec<DT>(c, a, a.att_out, a.q_dim, nullptr, -1);
-		stamp(c, l, 2, 2);
-		ep.kind = kWO, ep.scale0 = L.so;
-		gemv_phase<DT>(c, a, ep);
-		stamp(c, l, 2, 3);
-		// ---- rmsnorm -> w1/w3 -> GLU ---------------------------------------------------------------------
-		stamp(c, l, 3, 0);
-		grid_barrier(c, a.sync);
-		stamp(c, l, 3, 1);
-		stage_vec<DT>(c, a, a.x, a.dim, L.rms_ffn, -1);
-		stamp(c, l, 3, 2);
-		ep.kind = kFFN, ep.scale0 = L.s1, ep.scale1 = L.s3;
-		gemv_phase<DT>(c, a, ep);
-		stamp(c, l, 3, 3);
-		// ---- w2 + residual -------------------------------------------------------------------------------
-		stamp(c, l, 4, 0);
-		grid_barrier(c, a.sync);
-		stamp(c, l, 4, 1);
-		stage_vec<DT>(c, a, a.hb, a.hidden, nullptr, -1);
-		stamp(c, l, 4, 2);
-		ep.kind = kW2, ep.scale0 = L.s2;
-		gemv_phase<DT>(c, a, ep);
-		stamp(c, l, 4, 3);
+		stamp(c, l, k, 3);
 	}
-	if (a.mode != kHydrate) {
-		// ---- final rmsnorm -> LM head (+ greedy arg-max, first maximum wins: src/sampler.cpp:27-38) -----
-		stamp(c, a.n_layers - 1, 5, 0);
+	if (a.mode == kGreedy) {
+		// greedy arg-max, first maximum wins (src/sampler.cpp:27-38): lanes -> warps -> CTA -> grid
+		float bv = ep.best_v;
+		int bi = ep.best_i;
+#pragma unroll
+		for (int o = 16; o > 0; o >>= 1) {
+			const float ov = __shfl_xor_sync(kFull, bv, o);
+			const int oi = __shfl_xor_sync(kFull, bi, o);
+			if (ov > bv || (ov == bv && oi < bi)) bv = ov, bi = oi;
+		}
+		if (c.lane == 0) c.red[c.warp] = bv, c.misc[4 + c.warp] = bi;
+		cbar();
+		if (c.tid == 0) {
+			bv = c.red[0], bi = c.misc[4];
+			for (int t = 1; t < kConsumerWarps; ++t)
+				if (c.red[t] > bv || (c.red[t] == bv && c.misc[4 + t] < bi)) bv = c.red[t], bi = c.misc[4 + t];
+			a.amax_val[c.cta] = bv, a.amax_idx[c.cta] = bi;
+		}
 		grid_barrier(c, a.sync);
-		stamp(c, a.n_layers - 1, 5, 1);
-		stage_vec<DT>(c, a, a.x, a.dim, a.rms_final, -1);
-		stamp(c, a.n_layers - 1, 5, 2);
-		ep.kind = kLM, ep.scale0 = a.wcls_scale, ep.best_v = -FLT_MAX, ep.best_i = 0x7fffffff;
-		gemv_phase<DT>(c, a, ep);
-		if (a.mode == kGreedy) {
-			{
-				float bv = ep.best_v;
-				int bi = ep.best_i;
-#pragma unroll
-				for (int o = 16; o > 0; o >>= 1) {
-					const float ov = __shfl_xor_sync(kFull, bv, o);
-					const int oi = __shfl_xor_sync(kFull, bi, o);
-					if (ov > bv || (ov == bv && oi < bi)) bv = ov, bi = oi;
-				}
-				if (c.lane == 0) c.red[c.warp] = bv, c.misc[4 + c.warp] = bi;
+		if (c.cta == 0 && c.warp == 0) {
+			bv = -FLT_MAX, bi = 0x7fffffff;
+			for (int b = c.lane; b < c.ncta; b += 32) {
+				const float v = __ldcg(a.amax_val + b);
+				const int i = __ldcg(a.amax_idx + b);
+				if (v > bv || (v == bv && i < bi)) bv = v, bi = i;
 			}
-			cbar();
-			if (c.tid == 0) {
-				float bv = c.red[0];
-				int bi = c.misc[4];
-				for (int t = 1; t < kConsumerWarps; ++t)
-					if (c.red[t] > bv || (c.red[t] == bv && c.misc[4 + t] < bi)) bv = c.red[t], bi = c.misc[4 + t];
-				a.amax_val[c.cta] = bv, a.amax_idx[c.cta] = bi;
-			}
-			grid_barrier(c, a.sync);
-			if (c.cta == 0 && c.warp == 0) {
-				float bv = -FLT_MAX;
-				int bi = 0x7fffffff;
-				for (int b = c.lane; b < c.ncta; b += 32) {
-					const float v = __ldcg(a.amax_val + b);
-					const int i = __ldcg(a.amax_idx + b);
-					if (v > bv || (v == bv && i < bi)) bv = v, bi = i;
-				}
 #pragma unroll
-				for (int o = 16; o > 0; o >>= 1) {
-					const float ov = __shfl_xor_sync(kFull, bv, o);
-					const int oi = __shfl_xor_sync(kFull, bi, o);
-					if (ov > bv || (ov == bv && oi < bi)) bv = ov, bi = oi;
-				}
-				if (c.lane == 0) {
-					if (bi == 0x7fffffff) bi = 0;
-					const int step = a.ctl[CTL_STEP];
-					if (a.tokens_out) a.tokens_out[step] = bi;
-					a.ctl[CTL_STEP] = step + 1;
-					a.ctl[CTL_TOKEN] = bi;
-					a.ctl[CTL_POS] = c.pos + 1;
-					int ks, kp, kl;
-					derive_ring(c.pos + 1, a.max_seq_len, &ks, &kp, &kl);
-					a.ctl[CTL_SINK] = ks, a.ctl[CTL_KVPOS] = kp, a.ctl[CTL_KVLEN] = kl;
-				}
+			for (int o = 16; o > 0; o >>= 1) {
+				const float ov = __shfl_xor_sync(kFull, bv, o);
+				const int oi = __shfl_xor_sync(kFull, bi, o);
+				if (ov > bv || (ov == bv && oi < bi)) bv = ov, bi = oi;
+			}
+			if (c.lane == 0) {
+				if (bi == 0x7fffffff) bi = 0;
+				const int step = a.ctl[CTL_STEP];
+				if (a.tokens_out) a.tokens_out[step] = bi;
+				a.ctl[CTL_STEP] = step + 1;
+				a.ctl[CTL_TOKEN] = bi;
+				a.ctl[CTL_POS] = c.pos + 1;
+				int ks, kp, kl;
+				derive_ring(c.pos + 1, a.max_seq_len, &ks, &kp, &kl);
+				a.ctl[CTL_SINK] = ks, a.ctl[CTL_KVPOS] = kp, a.ctl[CTL_KVLEN] = kl;
 			}
 		}
 	}
-	if (a.mode != kHydrate) stamp(c, a.n_layers - 1, 5, 3);
 	// ---- leave the barrier words zeroed for the next launch ------------------------------------------
 	cbar();
 	if (c.tid == 0) {

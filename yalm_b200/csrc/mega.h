@@ -13,10 +13,11 @@
 namespace yalm {
 namespace mega {
 
-constexpr int kStageBytes = 32768; // one ring stage = one weight tile or one K+V tile pair
+constexpr int kStageBytes = 8192;  // one ring stage = one weight tile or one K+V tile pair
 constexpr int kConsumerWarps = 8;
-constexpr int kThreads = (kConsumerWarps + 1) * 32; // + the producer warp
-constexpr int kMaxStages = 8;
+constexpr int kProducerWarps = 1; // all 32 lanes issue: lane l takes tile l of each batch of min(stages, 32) tiles
+constexpr int kThreads = (kConsumerWarps + kProducerWarps) * 32;
+constexpr int kMaxStages = 24;
 constexpr int kProfileSlots = 6 * 8; // per (CTA, layer): phases x slots, see decode_mega.cuh
 
 // Per-layer device pointers (weights are (out,in) row-major; KV cache is head-major, see yalm_b200.h).
@@ -53,6 +54,7 @@ struct Args {
 	int token, pos; // token >= 0: taken from here; < 0: from ctl (device greedy loop)
 	int mode;
 	int stages, vec_floats;
+	int shape[5][4]; // per GEMV kind (qkv, wo, w1/w3, w2, lm head): rows per tile, columns per tile, K splits, row groups
 	int debug;       // timing experiments only (YALM_MEGA_DEBUG): 1 skip GEMV math, 4 skip attention math, 8 no copies
 	long long *prof; // optional phase profile, (grid, n_layers, 6 phases, 8 slots) clock64 values; null = off
 };
@@ -62,6 +64,7 @@ struct Plan {
 	int dtype = 0, grid = 0, stages = 0, vec_floats = 0;
 	size_t smem = 0;
 	const void *kernel = nullptr;
+	int shape[5][4] = {};
 };
 
 // Can this (unsharded, dense or MoE) model shape run on the megakernel on the current device?
