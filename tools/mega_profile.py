@@ -55,6 +55,13 @@ def main():
         lines.append(f"{PH[ph]:12s} {bar.mean():9.2f} {stg.mean():8.2f} {til.mean():8.2f} {stv.mean():8.2f}   "
                      f"[{bar.max(0).mean():.2f} {stg.max(0).mean():.2f} {til.max(0).mean():.2f} {stv.max(0).mean():.2f}] x{nl}")
         tot += np.array([bar.mean() * nl, stg.mean() * nl, til.mean() * nl, stv.mean() * nl])
+    q = p[:, :, 1, :]
+    ok = q[..., 5] > 0
+    un = np.where(ok, (q[..., 5] - q[..., 2]) * us, np.nan)
+    mp = np.where(ok, (q[..., 6] - q[..., 5]) * us, np.nan)
+    cb = np.where(ok, (q[..., 3] - q[..., 6]) * us, np.nan)
+    lines.append(f"attn detail: units {np.nanmean(un):.2f} [{np.nanmax(un, 0).mean():.2f}]  merge+publish {np.nanmean(mp):.2f} "
+                 f"[{np.nanmax(mp, 0).mean():.2f}]  combine(last CTA) {np.nanmean(cb):.2f} [{np.nanmax(cb, 0).mean():.2f}]")
     lines.append(f"{'token total':12s} {tot[0]:9.1f} {tot[1]:8.1f} {tot[2]:8.1f} {tot[3]:8.1f}   (us per token)")
     txt = "\n".join(lines)
     print(txt)

@@ -109,7 +109,9 @@ Plan plan(int dtype, int dim, int q_dim, int kv_dim, int head_dim, int hidden, i
 	p.grid = di.sms;
 	int vf = std::max(padded(dim, ep), std::max(padded(q_dim, ep), padded(hidden, ep)));
 	if (n_kv_heads > p.grid) return p; // a CTA's attention units must span at most kHeadSlots KV heads
-	vf = std::max(vf, kHeadSlots * kConsumerWarps * G * (head_dim + 2) + p.grid * G + G + 32);
+	// attention: warp records, combine weights, per-warp probability scratch (C rows x G + G)
+	vf = std::max(vf, kHeadSlots * kConsumerWarps * G * (head_dim + 2) + p.grid * G + G +
+	                      kConsumerWarps * (kStageBytes / (4 * head_dim) * G + G) + 32);
 	p.vec_floats = (vf + 31) / 32 * 32;
 	// vec | rope table (64 float2) | red (16) | misc (16) | release counters (32) | mbarriers
 	const size_t fixed = (size_t)p.vec_floats * 4 + 64 * 8 + (16 + 16 + 32) * 4 + 2 * kMaxStages * 8;
@@ -139,6 +141,8 @@ int launch(const Plan &p, const Args &a, cudaStream_t st) {
 	static const int debug = getenv("YALM_MEGA_DEBUG") ? atoi(getenv("YALM_MEGA_DEBUG")) : 0;
 	static const int max_stages = getenv("YALM_MEGA_STAGES") ? atoi(getenv("YALM_MEGA_STAGES")) : 0;
 	args.debug = debug;
+	static const int ahead = getenv("YALM_MEGA_L2_AHEAD") ? atoi(getenv("YALM_MEGA_L2_AHEAD")) : 0;
+	args.l2_ahead = ahead;
 	if (max_stages >= 2 && max_stages < args.stages) args.stages = max_stages;
 	void *params[] = {&args};
 	return (int)cudaLaunchCooperativeKernel(p.kernel, dim3(p.grid), dim3(kThreads), params, p.smem, st);

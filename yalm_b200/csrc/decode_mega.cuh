@@ -73,6 +73,10 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void *src, uint32_t
 	    "l"(src), "r"(bytes), "r"(bar), "l"(policy)
 	    : "memory");
 }
+// Fire-and-forget L2 prefetch of a global range (no completion tracking, never blocks the issuing thread).
+__device__ __forceinline__ void bulk_prefetch_l2(const void *src, uint32_t bytes) {
+	asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src), "r"(bytes) : "memory");
+}
 __device__ __forceinline__ uint64_t policy_evict_first() {
 	uint64_t p;
 	asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
@@ -192,7 +196,8 @@ __host__ __device__ inline bool tile_shape(int rows, int rows_b, int K, int B, i
 constexpr int kProfSlots = 8, kProfPhases = 6; // phases: qkv, attn, wo, ffn, w2, lm(+argmax) (last layer slot only)
 
 struct Ctx {
-	long long *prof; // this CTA's profile rows or null
+	long long *prof;  // this CTA's profile rows or null
+	long long *trace; // event trace (CTA 0 only) or null
 	long long wait_cycles;
 	int debug;
 	unsigned char *stages;
@@ -207,8 +212,28 @@ struct Ctx {
 	int rot;     // CTA rotation of the current GEMV phase
 	unsigned bar_gen;
 	int token, pos, kv_sink, kv_pos, kv_len;
-	Shape shape[kNumKinds];
 };
+
+// Tile shape of a GEMV kind: planned on the host (tile_shape), read from the kernel-parameter constant bank
+// (a dynamically indexed array inside Ctx would push the context into local memory).
+__device__ __forceinline__ Shape shape_of(const Args &a, int kind) {
+	Shape s;
+	s.R = a.shape[kind][0], s.KT = a.shape[kind][1], s.nk = a.shape[kind][2], s.G = a.shape[kind][3];
+	return s;
+}
+
+// Optional event trace of CTA 0 (Args.trace != null): trace[0] = event count, then (tag, clock64) pairs.
+// tag = type << 56 | warp << 48 | ring index.  Types: 1 producer issued, 2 consumer wait begin, 3 wait end, 4 release,
+// 5 phase stamp (index = layer * 64 + phase * 8 + slot).
+__device__ __forceinline__ void trace(const Ctx &c, int type, uint32_t idx) {
+	if (c.trace) {
+		const unsigned long long k = atomicAdd(reinterpret_cast<unsigned long long *>(c.trace), 1ull);
+		if (k < (unsigned long long)kTraceEvents) {
+			c.trace[1 + 2 * k] = ((long long)type << 56) | ((long long)c.warp << 48) | (long long)idx;
+			c.trace[2 + 2 * k] = clock64();
+		}
+	}
+}
 
 // (round, stage) of ring tile idx without an integer division
 __device__ __forceinline__ void ring_pos(const Ctx &c, uint32_t idx, uint32_t *s, int *r) {
@@ -223,6 +248,7 @@ __device__ __forceinline__ void stamp(Ctx &c, int layer, int phase, int k) {
 		row[k] = clock64();
 		if (k == 3) row[4] = c.wait_cycles, c.wait_cycles = 0;
 	}
+	if (c.tid == 0) trace(c, 5, (uint32_t)(layer * 64 + phase * 8 + k));
 }
 
 // This CTA's share of a phase's G row groups: groups g_first, g_first + ncta, ... (NL of them).
@@ -242,6 +268,7 @@ struct Producer {
 	Ctx &c;
 	uint64_t policy;
 	int batch; // min(stages, 32)
+	int ahead; // L2 look-ahead distance in tiles (0: off)
 
 	// Stage of ring tile idx is free (every earlier round consumed): expect `bytes` on its full barrier.
 	__device__ __forceinline__ uint32_t acquire(uint32_t idx, uint32_t bytes, uint32_t *bar) {
@@ -265,6 +292,7 @@ struct Producer {
 		*bar = c.full0 + 8 * s;
 		if (c.debug & 8) mbar_arrive(*bar);
 		else mbar_expect_tx(*bar, bytes);
+		trace(c, 1, idx);
 		return c.stages_u32 + s * kStageBytes;
 	}
 	// rows [row0, row0+nrows) x columns [kc*KT, (kc+1)*KT) of a (rows, K) matrix -> dst, tile rows packed
@@ -272,49 +300,63 @@ struct Producer {
 	                                          int kc, int nk, int B) {
 		const size_t row_bytes = (size_t)K * B;
 		if (nk == 1) {
-			bulk_g2s(dst, m + row0 * row_bytes, (uint32_t)(nrows * row_bytes), bar, policy);
+			if (bar) bulk_g2s(dst, m + row0 * row_bytes, (uint32_t)(nrows * row_bytes), bar, policy);
+			else bulk_prefetch_l2(m + row0 * row_bytes, (uint32_t)(nrows * row_bytes));
 		} else {
 			const uint32_t tb = (uint32_t)KT * B;
-			for (int r = 0; r < nrows; ++r)
-				bulk_g2s(dst + r * tb, m + (row0 + r) * row_bytes + (size_t)kc * tb, tb, bar, policy);
+			for (int r = 0; r < nrows; ++r) {
+				const char *src = m + (row0 + r) * row_bytes + (size_t)kc * tb;
+				if (bar) bulk_g2s(dst + r * tb, src, tb, bar, policy);
+				else bulk_prefetch_l2(src, tb);
+			}
 		}
 	}
-	__device__ __forceinline__ void gemv(int kind, const char *m0, const char *m1, const char *m2, int rows0, int rows1, int K,
-	                                  int B) {
-		const Shape sh = c.shape[kind];
+	__device__ __forceinline__ void gemv(const Args &a, int kind, const char *m0, const char *m1, const char *m2, int rows0,
+	                                     int rows1, int K, int B) {
+		const Shape sh = shape_of(a, kind);
 		const uint32_t tile_bytes = (uint32_t)sh.R * sh.KT * B;
 		int g_first, NL;
 		my_groups(c, sh.G, &g_first, &NL);
 		const int ntiles = NL * sh.nk;
 		const int full_groups = NL / kConsumerWarps * kConsumerWarps, full_tiles = full_groups * sh.nk;
 		const int nb_last = NL - full_groups;
+		// tile i of this phase: load into the ring (ring = true: waits for its stage) or just pull it into L2
+		auto tile = [&](int i, bool ring) {
+			int gl, kc;
+			if (i < full_tiles) {
+				const int r = i % (kConsumerWarps * sh.nk);
+				gl = i / (kConsumerWarps * sh.nk) * kConsumerWarps + r % kConsumerWarps, kc = r / kConsumerWarps;
+			} else {
+				const int r = i - full_tiles;
+				gl = full_groups + r % nb_last, kc = r / nb_last;
+			}
+			const int g = g_first + gl * c.ncta;
+			uint32_t bar = 0, dst = 0;
+			if (ring) dst = acquire(c.it + (uint32_t)i, tile_bytes, &bar);
+			if (kind == kFFN) {
+				const int rh = sh.R / 2;
+				rows_copy(dst, bar, m0, (long)g * rh, rh, K, sh.KT, kc, sh.nk, B);
+				rows_copy(dst + rh * sh.KT * B, bar, m1, (long)g * rh, rh, K, sh.KT, kc, sh.nk, B);
+			} else {
+				long row = (long)g * sh.R;
+				const char *m = m0;
+				if (kind == kQKV) {
+					if (row >= rows0 + rows1) row -= rows0 + rows1, m = m2;
+					else if (row >= rows0) row -= rows0, m = m1;
+				}
+				rows_copy(dst, bar, m, row, sh.R, K, sh.KT, kc, sh.nk, B);
+			}
+		};
+		// L2 look-ahead: the first `ahead` tiles now, then tile i + ahead with every tile i.  HBM keeps streaming
+		// into L2 while the consumers sit in a barrier / staging / attention-merge latency chain with the ring
+		// full, and the ring then refills from L2 instead of DRAM.
+		if (ahead > 0)
+			for (int i = c.lane; i < min(ahead, ntiles); i += 32) tile(i, false);
 		for (int t0 = 0; t0 < ntiles; t0 += batch) {
 			const int i = t0 + c.lane;
 			if (c.lane < batch && i < ntiles) {
-				int gl, kc;
-				if (i < full_tiles) {
-					const int r = i % (kConsumerWarps * sh.nk);
-					gl = i / (kConsumerWarps * sh.nk) * kConsumerWarps + r % kConsumerWarps, kc = r / kConsumerWarps;
-				} else {
-					const int r = i - full_tiles;
-					gl = full_groups + r % nb_last, kc = r / nb_last;
-				}
-				const int g = g_first + gl * c.ncta;
-				uint32_t bar;
-				const uint32_t dst = acquire(c.it + (uint32_t)i, tile_bytes, &bar);
-				if (kind == kFFN) {
-					const int rh = sh.R / 2;
-					rows_copy(dst, bar, m0, (long)g * rh, rh, K, sh.KT, kc, sh.nk, B);
-					rows_copy(dst + rh * sh.KT * B, bar, m1, (long)g * rh, rh, K, sh.KT, kc, sh.nk, B);
-				} else {
-					long row = (long)g * sh.R;
-					const char *m = m0;
-					if (kind == kQKV) {
-						if (row >= rows0 + rows1) row -= rows0 + rows1, m = m2;
-						else if (row >= rows0) row -= rows0, m = m1;
-					}
-					rows_copy(dst, bar, m, row, sh.R, K, sh.KT, kc, sh.nk, B);
-				}
+				tile(i, true);
+				if (ahead > 0 && i + ahead < ntiles) tile(i + ahead, false);
 			}
 			__syncwarp();
 		}
@@ -326,16 +368,27 @@ struct Producer {
 		const int nch = (c.kv_len + C - 1) / C, U = n_kv * nch;
 		const int u0 = (int)((long long)c.cta * U / c.ncta), u1 = (int)((long long)(c.cta + 1) * U / c.ncta);
 		const int ntiles = u1 - u0;
+		auto tile = [&](int i, bool ring) {
+			const int u = u0 + i, kvh = u / nch, r0 = (u % nch) * C, n = min(C, c.kv_len - r0);
+			const uint32_t bytes = (uint32_t)n * HD * 2;
+			const size_t off = ((size_t)kvh * max_seq + r0) * HD;
+			if (ring) {
+				uint32_t bar;
+				const uint32_t dst = acquire(c.it + (uint32_t)i, 2 * bytes, &bar);
+				bulk_g2s(dst, L.kc + off, bytes, bar, policy);
+				bulk_g2s(dst + kStageBytes / 2, L.vc + off, bytes, bar, policy);
+			} else {
+				bulk_prefetch_l2(L.kc + off, bytes);
+				bulk_prefetch_l2(L.vc + off, bytes);
+			}
+		};
+		if (ahead > 0)
+			for (int i = c.lane; i < min(ahead, ntiles); i += 32) tile(i, false);
 		for (int t0 = 0; t0 < ntiles; t0 += batch) {
 			const int i = t0 + c.lane;
 			if (c.lane < batch && i < ntiles) {
-				const int u = u0 + i, kvh = u / nch, r0 = (u % nch) * C, n = min(C, c.kv_len - r0);
-				const uint32_t bytes = (uint32_t)n * HD * 2;
-				uint32_t bar;
-				const uint32_t dst = acquire(c.it + (uint32_t)i, 2 * bytes, &bar);
-				const size_t off = ((size_t)kvh * max_seq + r0) * HD;
-				bulk_g2s(dst, L.kc + off, bytes, bar, policy);
-				bulk_g2s(dst + kStageBytes / 2, L.vc + off, bytes, bar, policy);
+				tile(i, true);
+				if (ahead > 0 && i + ahead < ntiles) tile(i + ahead, false);
 			}
 			__syncwarp();
 		}
@@ -357,17 +410,20 @@ __device__ __forceinline__ float cons_sum(Ctx &c, float v) {
 
 __device__ __forceinline__ void grid_barrier(Ctx &c, unsigned *sync) {
 	++c.bar_gen;
-	cbar();
+	cbar(); // every consumer thread's writes of this phase happen-before thread 0's release below
 	if (c.tid == 0) {
 		const unsigned target = c.bar_gen * (unsigned)c.ncta;
-		__threadfence();
-		atomicAdd(sync, 1u);
-		if (ld_acquire(sync) < target) {
+		asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(sync) : "memory");
+		unsigned v;
+		asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(sync) : "memory");
+		if (v < target) {
 			const long long t0 = clock64();
-			while (ld_acquire(sync) < target)
+			do {
+				asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(sync) : "memory");
 				if (clock64() - t0 > kTimeoutCycles) __trap();
+			} while (v < target);
 		}
-		__threadfence();
+		asm volatile("fence.acq_rel.gpu;" ::: "memory");
 	}
 	cbar();
 }
@@ -378,6 +434,7 @@ __device__ __forceinline__ const unsigned char *wait_tile(Ctx &c, uint32_t idx, 
 	int r;
 	ring_pos(c, idx, &s, &r);
 	const uint32_t par = (uint32_t)r & 1u;
+	if (c.lane == 0) trace(c, 2, idx);
 	if (ld_rel(c.rel + s) < r) { // an earlier round of this stage is still in use (rare)
 		const long long t0 = clock64();
 		while (ld_rel(c.rel + s) < r)
@@ -390,6 +447,7 @@ __device__ __forceinline__ const unsigned char *wait_tile(Ctx &c, uint32_t idx, 
 	} else {
 		mbar_wait(c.full0 + 8 * s, par);
 	}
+	if (c.lane == 0) trace(c, 3, idx);
 	*slot = idx;
 	return c.stages + (size_t)s * kStageBytes;
 }
@@ -404,7 +462,8 @@ __device__ __forceinline__ void release(Ctx &c, uint32_t idx) {
 		int r;
 		ring_pos(c, idx, &s, &r);
 		st_rel(c.rel + s, r + 1);
-		mbar_arrive(c.empty0 + 8 * s); // release semantics: orders the warp's reads of the stage and the counter store
+		mbar_arrive(c.empty0 + 8 * s);
+		trace(c, 4, idx); // release semantics: orders the warp's reads of the stage and the counter store
 	}
 }
 
@@ -495,7 +554,7 @@ template <int DT, int R>
 __device__ __forceinline__ void gemv_consume(Ctx &c, const Args &a, Epi &ep) {
 	using T = WTraits<DT>;
 	constexpr int EP = T::EP, CH = 32 * EP, Q = EP / 4;
-	const Shape sh = c.shape[ep.kind];
+	const Shape sh = shape_of(a, ep.kind);
 	const int kind = ep.kind;
 	const int chunks = (sh.KT + CH - 1) / CH, nfull = sh.KT / CH;
 	const int row_stride = sh.KT * T::BYTES;
@@ -617,7 +676,7 @@ __device__ __forceinline__ void gemv_consume(Ctx &c, const Args &a, Epi &ep) {
 
 template <int DT>
 __device__ __forceinline__ void gemv_phase(Ctx &c, const Args &a, Epi &ep) {
-	const int R = c.shape[ep.kind].R;
+	const int R = a.shape[ep.kind][0];
 	if (R == 4) gemv_consume<DT, 4>(c, a, ep);
 	else if (R == 2) gemv_consume<DT, 2>(c, a, ep);
 	else gemv_consume<DT, 1>(c, a, ep);
@@ -637,21 +696,34 @@ __device__ __forceinline__ bool unit_overlap(int b, int ncta, int U, int X, int 
 	return max(b0, X) < min(b1, Y);
 }
 
-// Split-K flash-decode over this CTA's (kv head, row chunk) units; arithmetic as src/infer.cpp:216-248.
-// Warp w owns units w, w+8, ... of the CTA's contiguous unit range and keeps its own online-softmax state
-// (max, sum, acc) for all G query heads of the unit's KV head; a warp that moves on to the next KV head parks
-// its state in shared memory.  Warps, then CTAs, are merged with the usual rescaling in a fixed order, so
-// results are run-to-run identical.  The last CTA to publish a head's partial combines them (arrival counter).
+// Split-K flash-decode over this CTA's (kv head, row chunk) units; arithmetic as src/infer.cpp:216-248 (fp32 dot over
+// fp16 K, / sqrt(head_dim) folded into q, exp(s - max) / sum, fp32 mix over fp16 V).
+// Warp w owns units w, w+W, ... of the CTA's contiguous unit range.  Per unit (one ring tile: C rows of K and of V):
+//   A. partial dots: every lane holds 8 dims of every row of its row group for all G heads -> 8*G partial sums;
+//   B. transposing butterfly over the LPR lanes of a row: each exchange halves the number of values a lane
+//      carries, so 8*G values cost ~2 shuffles each instead of log2(LPR) — afterwards a lane owns the complete
+//      scores of NF rows of ONE head (head = high bits of its lane index);
+//   C. online softmax on the owned scores only (one head per lane: 1 max / 1 sum / NF+1 exps per lane);
+//      probabilities and the rescale factors go through a per-warp scratch in shared memory;
+//   D. acc[g][8 dims] += p[row][g] * V[row][dims] with the lane's 8 dims of each row of its row group.
+// A warp that moves on to the next KV head parks its state in shared memory.  Warps, then CTAs, are merged with
+// the usual (max, sum, acc) rescaling in a fixed order, so results are run-to-run identical.  The last CTA to
+// publish a head's partial combines them (arrival counter).
 template <int HD, int G>
-__device__ __forceinline__ void attention_consume(Ctx &c, const Args &a, const Layer &L) {
-	constexpr int LPR = HD / 8, RPS = 32 / LPR; // lanes per row, rows per warp step
+__device__ __forceinline__ void attention_consume(Ctx &c, const Args &a, const Layer &L, int layer) {
+	constexpr int W = kConsumerWarps;
+	constexpr int LPR = HD / 8, RPS = 32 / LPR; // lanes per row, rows per warp step (= row groups)
 	constexpr int C = kStageBytes / (4 * HD);   // rows per tile
-	constexpr int STEPS = 4;                    // row steps per online-softmax update
-	constexpr int PASSES = C / (STEPS * RPS);
-	constexpr int WS = HD + 2; // per (slot, warp, head) record in shared memory: acc[HD], m, l
-	static_assert(PASSES >= 1 && PASSES * STEPS * RPS == C, "stage size / head_dim mismatch");
+	constexpr int ST = C / RPS;                 // row steps per tile
+	constexpr int V = ST * G;                   // partial sums per lane before the butterfly
+	constexpr int NF = V / LPR;                 // complete scores per lane after it
+	constexpr int SB = ST / NF;                 // lanes of a row that share a head (each owns NF of the ST rows)
+	constexpr int WS = HD + 2;                  // per (slot, warp, head) record in shared memory: acc[HD], m, l
+	constexpr int PS = C * G + G;               // per-warp scratch: p[C][G], corr[G]
+	static_assert(ST == 8 && V % LPR == 0 && NF >= 1 && NF <= ST && SB * G == LPR, "unsupported head_dim / group combination");
 	const int lane = c.lane, warp = c.warp, ncta = c.ncta;
 	const int sub = lane % LPR, rgrp = lane / LPR;
+	const int my_g = sub / SB, my_st0 = (sub % SB) * NF; // this lane owns scores of head my_g, row steps my_st0 .. +NF
 	const int nch = (c.kv_len + C - 1) / C, U = a.n_kv_heads * nch;
 	const int u0 = (int)((long long)c.cta * U / ncta), u1 = (int)((long long)(c.cta + 1) * U / ncta);
 	const int NU = u1 - u0;
@@ -660,36 +732,45 @@ __device__ __forceinline__ void attention_consume(Ctx &c, const Args &a, const L
 	if (NU == 0) return;
 	const int kv_first = u0 / nch, kv_last = (u1 - 1) / nch;
 	const float div = sqrtf((float)HD);
-	float *wsm = c.vec; // [kHeadSlots][warps][G][WS]
-	// every record starts empty (m = -inf, l = 0): warps that never touch a head contribute nothing
+	float *wsm = c.vec;                                            // [kHeadSlots][W][G][WS]
+	float *wts = wsm + kHeadSlots * W * G * WS;                    // combine: [ncta][G] weights, Lsum[G]
+	float *ps = wts + ncta * G + G + (size_t)warp * PS;            // this warp's p / corr scratch
 	if (lane < kHeadSlots * G) { // each warp initialises its own records, so a __syncwarp orders it against park()
-		float *rec = wsm + (((lane / G) * kConsumerWarps + warp) * G + lane % G) * WS;
+		float *rec = wsm + (((lane / G) * W + warp) * G + lane % G) * WS;
 		rec[HD] = -INFINITY, rec[HD + 1] = 0.f;
 	}
-
-	float qr[G][8], acc[G][8], m[G], l[G];
+	float2 qr[G][4], acc[G][4]; // q / sqrt(HD) and the output accumulators: this lane's 8 dims as 4 pairs
+	float m = -INFINITY, l = 0.f; // running max / partial sum of head my_g (max identical in all lanes of the head)
 	int cur = -1;
-	auto park = [&](int kvh) { // merge the warp's row groups and store its state for head kvh
+	auto park = [&](int kvh) { // merge the warp's row groups and lanes, store its state for head kvh
 #pragma unroll
-		for (int o = LPR; o < 32; o <<= 1)
+		for (int o = LPR; o < 32; o <<= 1) {
+			l += __shfl_xor_sync(kFull, l, o);
 #pragma unroll
-			for (int g = 0; g < G; ++g) {
-				l[g] += __shfl_xor_sync(kFull, l[g], o);
+			for (int g = 0; g < G; ++g)
 #pragma unroll
-				for (int j = 0; j < 8; ++j) acc[g][j] += __shfl_xor_sync(kFull, acc[g][j], o);
-			}
+				for (int j = 0; j < 4; ++j) {
+					acc[g][j].x += __shfl_xor_sync(kFull, acc[g][j].x, o);
+					acc[g][j].y += __shfl_xor_sync(kFull, acc[g][j].y, o);
+				}
+		}
+#pragma unroll
+		for (int o = 1; o < SB; o <<= 1) l += __shfl_xor_sync(kFull, l, o);
 		if (rgrp == 0) {
 #pragma unroll
 			for (int g = 0; g < G; ++g) {
-				float *rec = wsm + (((kvh - kv_first) * kConsumerWarps + warp) * G + g) * WS;
+				float *rec = wsm + (((kvh - kv_first) * W + warp) * G + g) * WS;
 #pragma unroll
-				for (int j = 0; j < 8; ++j) rec[sub * 8 + j] = acc[g][j];
-				if (sub == 0) rec[HD] = m[g], rec[HD + 1] = l[g];
+				for (int j = 0; j < 4; ++j) rec[sub * 8 + 2 * j] = acc[g][j].x, rec[sub * 8 + 2 * j + 1] = acc[g][j].y;
+			}
+			if (sub % SB == 0) {
+				float *rec = wsm + (((kvh - kv_first) * W + warp) * G + my_g) * WS;
+				rec[HD] = m, rec[HD + 1] = l;
 			}
 		}
 	};
 	__syncwarp();
-	for (int i = warp; i < NU; i += kConsumerWarps) {
+	for (int i = warp; i < NU; i += W) {
 		const int u = u0 + i, kvh = u / nch, t0 = (u % nch) * C, n = min(C, c.kv_len - t0);
 		if (kvh != cur) {
 			if (cur >= 0) park(cur);
@@ -698,79 +779,109 @@ __device__ __forceinline__ void attention_consume(Ctx &c, const Args &a, const L
 			for (int g = 0; g < G; ++g) {
 				const float *qp = a.q + (size_t)(kvh * G + g) * HD + sub * 8;
 				const float4 lo = __ldcg(reinterpret_cast<const float4 *>(qp)), hi = __ldcg(reinterpret_cast<const float4 *>(qp + 4));
-				qr[g][0] = lo.x, qr[g][1] = lo.y, qr[g][2] = lo.z, qr[g][3] = lo.w;
-				qr[g][4] = hi.x, qr[g][5] = hi.y, qr[g][6] = hi.z, qr[g][7] = hi.w;
-				m[g] = -INFINITY, l[g] = 0.f;
+				qr[g][0] = make_float2(lo.x / div, lo.y / div), qr[g][1] = make_float2(lo.z / div, lo.w / div);
+				qr[g][2] = make_float2(hi.x / div, hi.y / div), qr[g][3] = make_float2(hi.z / div, hi.w / div);
 #pragma unroll
-				for (int j = 0; j < 8; ++j) acc[g][j] = 0.f;
+				for (int j = 0; j < 4; ++j) acc[g][j] = make_float2(0.f, 0.f);
 			}
+			m = -INFINITY, l = 0.f;
 		}
 		uint32_t slot;
 		const unsigned char *tile = wait_tile(c, base + (uint32_t)i, &slot);
-		const __half *ks = reinterpret_cast<const __half *>(tile);
-		const __half *vs = reinterpret_cast<const __half *>(tile + kStageBytes / 2);
+		const uint32_t ks = tile_u32(c, tile) + lane * 16, vs = ks + kStageBytes / 2; // row (st, rgrp) at + st * 512
 		const size_t goff = ((size_t)kvh * a.max_seq_len + t0) * HD;
 		const __half *kg = reinterpret_cast<const __half *>(L.kc) + goff;
 		const __half *vg = reinterpret_cast<const __half *>(L.vc) + goff;
-		for (int pass = 0; pass < PASSES; ++pass) {
-			const int row0 = pass * (STEPS * RPS);
-			if (row0 >= n) break;
-			float s[STEPS][G];
+		// the row appended by this token and the re-rotated sink rows were written after the producer may have
+		// fetched the tile: those come from global memory (L2), everything else from the ring
+		const bool has_fresh = (c.kv_pos >= t0 && c.kv_pos < t0 + n) || t0 < c.kv_sink;
+		// ---- A: partial dots, value index = g * ST + st ---------------------------------------------------------
+		float d[V];
 #pragma unroll
-			for (int st = 0; st < STEPS; ++st) {
-				const int row = row0 + st * RPS + rgrp, t = t0 + row;
-				const bool valid = row < n && !(c.debug & 4);
-				// the row appended by this token and the re-rotated sink rows were written after the producer
-				// may have fetched the tile: read those from global memory (L2), everything else from the ring
-				const bool fresh = t == c.kv_pos || t < c.kv_sink;
-				uint4 kv = make_uint4(0, 0, 0, 0);
-				if (valid) kv = fresh ? __ldcg(reinterpret_cast<const uint4 *>(kg + (size_t)row * HD + sub * 8))
-				                      : *reinterpret_cast<const uint4 *>(ks + row * HD + sub * 8);
-				float kf[8];
-				unpack8(kv, kf);
-#pragma unroll
-				for (int g = 0; g < G; ++g) {
-					float d = 0.f;
-#pragma unroll
-					for (int j = 0; j < 8; ++j) d = fmaf(qr[g][j], kf[j], d);
-#pragma unroll
-					for (int o = LPR / 2; o > 0; o >>= 1) d += __shfl_xor_sync(kFull, d, o);
-					s[st][g] = valid ? d / div : -INFINITY;
-				}
-			}
+		for (int st = 0; st < ST; ++st) {
+			const int row = st * RPS + rgrp, t = t0 + row;
+			uint4 kv = lds128(ks + st * 512);
+			if (has_fresh && row < n && (t == c.kv_pos || t < c.kv_sink))
+				kv = __ldcg(reinterpret_cast<const uint4 *>(kg + (size_t)row * HD + sub * 8));
+			const float2 k0 = WTraits<YALM_F16>::h2(kv.x), k1 = WTraits<YALM_F16>::h2(kv.y), k2 = WTraits<YALM_F16>::h2(kv.z),
+			             k3 = WTraits<YALM_F16>::h2(kv.w);
 #pragma unroll
 			for (int g = 0; g < G; ++g) {
-				float mt = s[0][g];
-#pragma unroll
-				for (int st = 1; st < STEPS; ++st) mt = fmaxf(mt, s[st][g]);
-#pragma unroll
-				for (int o = LPR; o < 32; o <<= 1) mt = fmaxf(mt, __shfl_xor_sync(kFull, mt, o));
-				const float m_new = fmaxf(m[g], mt);
-				const float corr = m_new == -INFINITY ? 1.f : expf(m[g] - m_new);
-				m[g] = m_new;
-				l[g] *= corr;
-#pragma unroll
-				for (int j = 0; j < 8; ++j) acc[g][j] *= corr;
-#pragma unroll
-				for (int st = 0; st < STEPS; ++st) {
-					const float p = s[st][g] == -INFINITY ? 0.f : expf(s[st][g] - m_new);
-					s[st][g] = p;
-					l[g] += p;
-				}
+				float2 s2 = ffma2(qr[g][0], k0, make_float2(0.f, 0.f));
+				s2 = ffma2(qr[g][1], k1, s2);
+				s2 = ffma2(qr[g][2], k2, s2);
+				s2 = ffma2(qr[g][3], k3, s2);
+				d[g * ST + st] = s2.x + s2.y;
 			}
+		}
+		// ---- B: transposing butterfly over the LPR lanes of a row ----------------------------------------------
+		{
+			int nv = V;
 #pragma unroll
-			for (int st = 0; st < STEPS; ++st) {
-				const int row = row0 + st * RPS + rgrp, t = t0 + row;
-				if (row < n && !(c.debug & 4)) {
-					const bool fresh = t == c.kv_pos || t < c.kv_sink;
-					const uint4 vv = fresh ? __ldcg(reinterpret_cast<const uint4 *>(vg + (size_t)row * HD + sub * 8))
-					                       : *reinterpret_cast<const uint4 *>(vs + row * HD + sub * 8);
-					float vf[8];
-					unpack8(vv, vf);
+			for (int o = LPR / 2; o > 0; o >>= 1) {
+				const bool up = (sub & o) != 0;
+				const int half = nv / 2;
 #pragma unroll
-					for (int g = 0; g < G; ++g)
+				for (int i2 = 0; i2 < V / 2; ++i2) {
+					if (i2 < half) {
+						const float send = up ? d[i2] : d[i2 + half];
+						const float keep = up ? d[i2 + half] : d[i2];
+						d[i2] = keep + __shfl_xor_sync(kFull, send, o);
+					}
+				}
+				nv = half;
+			}
+		}
+		// d[0..NF) = complete scores of head my_g, row steps my_st0 + i   (value index = g*ST + st, see above)
+		// ---- C: online softmax for head my_g over the tile's rows ------------------------------------------------
+		float mt = -INFINITY;
 #pragma unroll
-						for (int j = 0; j < 8; ++j) acc[g][j] = fmaf(s[st][g], vf[j], acc[g][j]);
+		for (int i2 = 0; i2 < NF; ++i2) {
+			const int row = (my_st0 + i2) * RPS + rgrp;
+			if (row >= n || (c.debug & 4)) d[i2] = -INFINITY;
+			mt = fmaxf(mt, d[i2]);
+		}
+#pragma unroll
+		for (int o = 1; o < SB; o <<= 1) mt = fmaxf(mt, __shfl_xor_sync(kFull, mt, o));
+#pragma unroll
+		for (int o = LPR; o < 32; o <<= 1) mt = fmaxf(mt, __shfl_xor_sync(kFull, mt, o));
+		const float m_new = fmaxf(m, mt); // finite: every tile has at least one valid row
+		const float corr = m == -INFINITY ? 0.f : __expf(m - m_new);
+		m = m_new;
+		l *= corr;
+		__syncwarp(); // the previous unit's scratch reads are done
+#pragma unroll
+		for (int i2 = 0; i2 < NF; ++i2) {
+			const float p = d[i2] == -INFINITY ? 0.f : __expf(d[i2] - m_new);
+			l += p;
+			ps[((my_st0 + i2) * RPS + rgrp) * G + my_g] = p;
+		}
+		if (rgrp == 0 && sub % SB == 0) ps[C * G + my_g] = corr;
+		__syncwarp();
+		// ---- D: rescale, then acc[g] += p[row][g] * V[row] --------------------------------------------------------
+#pragma unroll
+		for (int g = 0; g < G; ++g) {
+			const float cg = ps[C * G + g];
+#pragma unroll
+			for (int j = 0; j < 4; ++j) acc[g][j].x *= cg, acc[g][j].y *= cg;
+		}
+#pragma unroll
+		for (int st = 0; st < ST; ++st) {
+			const int row = st * RPS + rgrp, t = t0 + row;
+			if (row < n) {
+				uint4 vv = lds128(vs + st * 512);
+				if (has_fresh && (t == c.kv_pos || t < c.kv_sink))
+					vv = __ldcg(reinterpret_cast<const uint4 *>(vg + (size_t)row * HD + sub * 8));
+				const float2 v0 = WTraits<YALM_F16>::h2(vv.x), v1 = WTraits<YALM_F16>::h2(vv.y), v2 = WTraits<YALM_F16>::h2(vv.z),
+				             v3 = WTraits<YALM_F16>::h2(vv.w);
+#pragma unroll
+				for (int g = 0; g < G; ++g) {
+					const float p = ps[row * G + g];
+					const float2 pp = make_float2(p, p);
+					acc[g][0] = ffma2(pp, v0, acc[g][0]);
+					acc[g][1] = ffma2(pp, v1, acc[g][1]);
+					acc[g][2] = ffma2(pp, v2, acc[g][2]);
+					acc[g][3] = ffma2(pp, v3, acc[g][3]);
 				}
 			}
 		}
@@ -778,6 +889,7 @@ __device__ __forceinline__ void attention_consume(Ctx &c, const Args &a, const L
 	}
 	if (cur >= 0) park(cur);
 	cbar();
+	stamp(c, layer, 1, 5);
 
 	// ---- per KV head of this CTA: merge the warps, publish the partial, last CTA combines ---------------
 	for (int kvh = kv_first; kvh <= kv_last; ++kvh) {
@@ -802,8 +914,7 @@ __device__ __forceinline__ void attention_consume(Ctx &c, const Args &a, const L
 			pa[i] = v;
 			if (d == 0) pml[g * 2] = M, pml[g * 2 + 1] = ls;
 		}
-		__threadfence();
-		cbar();
+		cbar(); // the partial's stores happen-before lane 0's release below
 		const int X = kvh * nch, Y = X + nch;
 		if (warp == 0) {
 			int cnt = 0;
@@ -811,17 +922,17 @@ __device__ __forceinline__ void attention_consume(Ctx &c, const Args &a, const L
 #pragma unroll
 			for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(kFull, cnt, o);
 			if (lane == 0) {
-				const unsigned prev = atomicAdd(&a.head_counters[kvh], 1u);
+				unsigned prev;
+				asm volatile("atom.acq_rel.gpu.global.add.u32 %0, [%1], 1;" : "=r"(prev) : "l"(a.head_counters + kvh) : "memory");
 				c.misc[0] = prev + 1 == (unsigned)cnt;
 			}
 		}
 		cbar();
+		stamp(c, layer, 1, 6);
 		if (!c.misc[0]) continue; // CTA-uniform
 		// last CTA of this head: combine every CTA's partial in CTA order
-		__threadfence();
 		const int b_lo = max(0, (int)((long long)X * ncta / U) - 1);
 		const int b_hi = min(ncta - 1, (int)(((long long)Y * ncta + U - 1) / U));
-		float *wts = wsm + kHeadSlots * kConsumerWarps * G * WS; // [ncta][G] merge weights (-1: no partial), Lsum[G]
 		for (int g = warp; g < G; g += kConsumerWarps) {
 			float M = -INFINITY;
 			for (int b = b_lo + lane; b <= b_hi; b += 32)
@@ -897,14 +1008,11 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_c
 	c.prof = a.prof ? a.prof + (size_t)blockIdx.x * a.n_layers * kProfPhases * kProfSlots : nullptr;
 	c.wait_cycles = 0;
 	c.debug = a.debug;
+	c.trace = blockIdx.x == 0 ? a.trace : nullptr;
 
 	c.token = a.token, c.pos = a.pos;
 	if (a.token < 0) c.token = a.ctl[CTL_TOKEN], c.pos = a.ctl[CTL_POS];
 	derive_ring(c.pos, a.max_seq_len, &c.kv_sink, &c.kv_pos, &c.kv_len);
-
-#pragma unroll
-	for (int k = 0; k < kNumKinds; ++k) // tile shapes are planned on the host (tile_shape)
-		c.shape[k].R = a.shape[k][0], c.shape[k].KT = a.shape[k][1], c.shape[k].nk = a.shape[k][2], c.shape[k].G = a.shape[k][3];
 
 	if (threadIdx.x == 0) {
 		for (int i = 0; i < c.S; ++i) {
@@ -926,7 +1034,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_c
 
 	if (c.warp >= kConsumerWarps) {
 		// ================================ producers ================================
-		Producer p{c, (a.debug & 8) ? 0ull : policy_evict_first(), min(c.S, 32)};
+		Producer p{c, (a.debug & 8) ? 0ull : policy_evict_first(), min(c.S, 32), (a.debug & 8) ? 0 : a.l2_ahead};
 		const int n_phases = a.n_layers * 5 + (a.mode != kHydrate ? 1 : 0);
 		for (int ph = 0; ph < n_phases; ++ph) { // one call site per producer function (code size)
 			const int l = min(ph / 5, a.n_layers - 1), k = ph < a.n_layers * 5 ? ph % 5 : 5;
@@ -944,7 +1052,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_c
 			case 5: kind = kLM, m0 = a.wcls, rows0 = a.vocab; break;
 			default: break;
 			}
-			p.gemv(kind, m0, m1, m2, rows0, rows1, K, B);
+			p.gemv(a, kind, m0, m1, m2, rows0, rows1, K, B);
 		}
 		return;
 	}
@@ -962,7 +1070,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_c
 		stamp(c, l, k, 1);
 		if (k == 1) { // attention: q comes from registers, nothing to stage
 			stamp(c, l, k, 2);
-			attention_consume<HD, G>(c, a, L);
+			attention_consume<HD, G>(c, a, L, l);
 			stamp(c, l, k, 3);
 			continue;
 		}

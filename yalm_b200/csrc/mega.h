@@ -14,10 +14,11 @@ namespace yalm {
 namespace mega {
 
 constexpr int kStageBytes = 8192;  // one ring stage = one weight tile or one K+V tile pair
-constexpr int kConsumerWarps = 8;
+constexpr int kConsumerWarps = 11;
 constexpr int kProducerWarps = 1; // all 32 lanes issue: lane l takes tile l of each batch of min(stages, 32) tiles
 constexpr int kThreads = (kConsumerWarps + kProducerWarps) * 32;
 constexpr int kMaxStages = 24;
+constexpr int kTraceEvents = 1 << 16;
 constexpr int kProfileSlots = 6 * 8; // per (CTA, layer): phases x slots, see decode_mega.cuh
 
 // Per-layer device pointers (weights are (out,in) row-major; KV cache is head-major, see yalm_b200.h).
@@ -55,7 +56,9 @@ struct Args {
 	int mode;
 	int stages, vec_floats;
 	int shape[5][4]; // per GEMV kind (qkv, wo, w1/w3, w2, lm head): rows per tile, columns per tile, K splits, row groups
+	int l2_ahead;    // L2 look-ahead of the producer in tiles per CTA (0: off)
 	int debug;       // timing experiments only (YALM_MEGA_DEBUG): 1 skip GEMV math, 4 skip attention math, 8 no copies
+	long long *trace; // optional event trace of CTA 0: [0] count, then kTraceEvents (tag, clock) pairs; null = off
 	long long *prof; // optional phase profile, (grid, n_layers, 6 phases, 8 slots) clock64 values; null = off
 };
 

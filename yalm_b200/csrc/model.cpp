@@ -578,9 +578,28 @@ int Model::mega_profile(InferenceState &s, int token, int pos, long long *out, s
 	long long *dev = nullptr;
 	CUDA_CHECK(cudaMalloc((void **)&dev, need * sizeof(long long)));
 	CUDA_CHECK(cudaMemset(dev, 0, need * sizeof(long long)));
+	// YALM_MEGA_TRACE=<file>: also dump CTA 0's event trace (decode_mega.cuh: trace()) as raw int64
+	const char *tf = getenv("YALM_MEGA_TRACE");
+	long long *tdev = nullptr;
+	const size_t tn = 1 + 2 * (size_t)yalm::mega::kTraceEvents;
+	if (tf) {
+		CUDA_CHECK(cudaMalloc((void **)&tdev, tn * sizeof(long long)));
+		CUDA_CHECK(cudaMemset(tdev, 0, tn * sizeof(long long)));
+	}
+	_mega_trace = tdev;
 	int rc = launch_mega(s, token, pos, yalm::mega::kLogits, dev);
+	_mega_trace = nullptr;
 	if (rc == 0) rc = (int)cudaStreamSynchronize(s.stream());
 	if (rc == 0) rc = (int)cudaMemcpy(out, dev, need * sizeof(long long), cudaMemcpyDeviceToHost);
+	if (rc == 0 && tdev) {
+		std::vector<long long> h(tn);
+		rc = (int)cudaMemcpy(h.data(), tdev, tn * sizeof(long long), cudaMemcpyDeviceToHost);
+		if (FILE *f = fopen(tf, "wb")) {
+			fwrite(h.data(), sizeof(long long), tn, f);
+			fclose(f);
+		}
+	}
+	cudaFree(tdev);
 	cudaFree(dev);
 	return rc;
 }
@@ -589,6 +608,7 @@ int Model::launch_mega(InferenceState &s, int token, int pos, int mode, long lon
 	const Config &c = *config;
 	yalm::mega::Args a{};
 	a.prof = prof;
+	a.trace = _mega_trace;
 	a.layers = _mega->layers, a.n_layers = c.n_layers;
 	a.dim = c.dim, a.q_dim = c.n_heads * c.head_dim, a.kv_dim = c.n_kv_heads * c.head_dim, a.head_dim = c.head_dim;
 	a.hidden = c.hidden_dim, a.vocab = c.vocab_size, a.n_heads = c.n_heads, a.n_kv_heads = c.n_kv_heads;

@@ -236,6 +236,7 @@ private:
 	int launch_mega(InferenceState &s, int token, int pos, int mode, long long *prof = nullptr);
 	void plan_mega();
 	bool _mega_ok = false;
+	long long *_mega_trace = nullptr; // debug: event trace buffer for the next launch
 	struct MegaState;
 	std::shared_ptr<MegaState> _mega;
 	Device _device = Device::CPU;
