@@ -1,6 +1,6 @@
 # yalm_b200 build: one shared library (kernels + C ABI + C++ API), plus the reference-shaped CLIs.
-#   make            -> yalm_b200/libyalm_b200.so, build/main, build/test
-#   make lib        -> only the library
+#   make            -> yalm_b200/libyalm_b200.so
+#   make cli        -> build/main, build/test
 NVCC  ?= nvcc
 HOSTCXX := /usr/bin/g++
 ARCH  := -gencode arch=compute_100a,code=sm_100a
@@ -14,7 +14,8 @@ LIB_SRCS := $(CSRC)/ops_gemv.cu $(CSRC)/ops_attn.cu $(CSRC)/decode_mega.cu $(CSR
 LIB_OBJS := $(patsubst $(CSRC)/%,$(BUILD)/%.o,$(LIB_SRCS))
 HDRS := $(wildcard $(CSRC)/*.h $(CSRC)/*.cuh include/*.h)
 
-all: lib $(BUILD)/main $(BUILD)/test
+all: lib
+cli: $(BUILD)/main $(BUILD)/test
 lib: $(LIB)
 
 $(BUILD)/%.cu.o: $(CSRC)/%.cu $(HDRS)
@@ -39,4 +40,4 @@ $(BUILD)/test: $(CSRC)/test.cpp $(LIB) $(HDRS)
 clean:
 	rm -rf $(BUILD) $(LIB)
 
-.PHONY: all lib clean
+.PHONY: all lib cli clean

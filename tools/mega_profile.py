@@ -59,9 +59,10 @@ def main():
     ok = q[..., 5] > 0
     un = np.where(ok, (q[..., 5] - q[..., 2]) * us, np.nan)
     mp = np.where(ok, (q[..., 6] - q[..., 5]) * us, np.nan)
+    mg = np.where(ok & (q[..., 7] > 0), (q[..., 7] - q[..., 5]) * us, np.nan)
     cb = np.where(ok, (q[..., 3] - q[..., 6]) * us, np.nan)
     lines.append(f"attn detail: units {np.nanmean(un):.2f} [{np.nanmax(un, 0).mean():.2f}]  merge+publish {np.nanmean(mp):.2f} "
-                 f"[{np.nanmax(mp, 0).mean():.2f}]  combine(last CTA) {np.nanmean(cb):.2f} [{np.nanmax(cb, 0).mean():.2f}]")
+                 f"[{np.nanmax(mp, 0).mean():.2f}] (merge {np.nanmean(mg):.2f} [{np.nanmax(mg, 0).mean():.2f}])  combine(last CTA) {np.nanmean(cb):.2f} [{np.nanmax(cb, 0).mean():.2f}]")
     lines.append(f"{'token total':12s} {tot[0]:9.1f} {tot[1]:8.1f} {tot[2]:8.1f} {tot[3]:8.1f}   (us per token)")
     txt = "\n".join(lines)
     print(txt)

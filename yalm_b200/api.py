@@ -12,7 +12,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libyalm_b200.so")
+LIB_PATH = os.environ.get("YALM_B200_LIB") or os.path.join(_HERE, "libyalm_b200.so")  # override: A/B builds
 
 F32, F16, F8E4M3 = 0, 1, 4
 ACT_GELU, ACT_SILU = 0, 1

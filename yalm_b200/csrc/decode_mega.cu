@@ -82,7 +82,7 @@ static const void *kernel_of(int dtype, int head_dim, int g) {
 }
 
 Plan plan(int dtype, int dim, int q_dim, int kv_dim, int head_dim, int hidden, int vocab, int n_heads, int n_kv_heads,
-          int n_experts, int n_active) {
+          int n_experts, int n_active, int max_seq_len) {
 	Plan p;
 	const int ep = ep_of(dtype), B = bytes_of(dtype);
 	if (!ep || n_experts > 0) return p;
@@ -109,12 +109,15 @@ Plan plan(int dtype, int dim, int q_dim, int kv_dim, int head_dim, int hidden, i
 	p.grid = di.sms;
 	int vf = std::max(padded(dim, ep), std::max(padded(q_dim, ep), padded(hidden, ep)));
 	if (n_kv_heads > p.grid) return p; // a CTA's attention units must span at most kHeadSlots KV heads
+	// the attention unit split runs in 32-bit arithmetic: (units) x (grid + 1) must stay below 2^31
+	const long long units = (long long)n_kv_heads * (max_seq_len / (kStageBytes / (4 * head_dim)) + 1);
+	if (head_dim <= 0 || units * (p.grid + 1) >= (1ll << 31)) return p;
 	// attention: warp records, combine weights, per-warp probability scratch (C rows x G + G)
 	vf = std::max(vf, kHeadSlots * kConsumerWarps * G * (head_dim + 2) + p.grid * G + G +
 	                      kConsumerWarps * (kStageBytes / (4 * head_dim) * G + G) + 32);
 	p.vec_floats = (vf + 31) / 32 * 32;
-	// vec | rope table (64 float2) | red (16) | misc (16) | release counters (32) | mbarriers
-	const size_t fixed = (size_t)p.vec_floats * 4 + 64 * 8 + (16 + 16 + 32) * 4 + 2 * kMaxStages * 8;
+	// header (rope table, scratch, release counters, mbarriers) | ring | vec
+	const size_t fixed = (size_t)p.vec_floats * 4 + kSmemHeader;
 	const long room = (long)di.max_smem_optin - (long)fixed;
 	p.stages = (int)std::min<long>(kMaxStages, room / kStageBytes);
 	if (p.stages < 2) return p;

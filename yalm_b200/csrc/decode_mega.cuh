@@ -195,17 +195,32 @@ __host__ __device__ inline bool tile_shape(int rows, int rows_b, int K, int B, i
 // [3] tiles + epilogue done; [4] cycles warp 0 spent waiting for full ring stages (starvation = HBM-bound).
 constexpr int kProfSlots = 8, kProfPhases = 6; // phases: qkv, attn, wo, ffn, w2, lm(+argmax) (last layer slot only)
 
+// Shared-memory layout: the small arrays sit at fixed offsets in front of the ring, so their addresses are
+// compile-time constants instead of live registers:
+//   rope table (64 float2) | red (16) | misc (32) | release counters (32) | full mbarriers | empty mbarriers | ring | vec
+constexpr int kOffRope = 0, kOffRed = 512, kOffMisc = 576, kOffRel = 704, kOffFull = 832, kOffEmpty = kOffFull + 8 * kMaxStages;
+constexpr int kOffStages = (kOffEmpty + 8 * kMaxStages + 127) / 128 * 128;
+static_assert(kOffStages == kSmemHeader, "mega.h: kSmemHeader must match the kernel's shared-memory header");
+__device__ __forceinline__ unsigned char *sm_base() {
+	extern __shared__ __align__(128) unsigned char smem_raw[];
+	return smem_raw;
+}
+__device__ __forceinline__ float2 *sm_rope() { return reinterpret_cast<float2 *>(sm_base() + kOffRope); } // cos/sin of pos * freq_j
+__device__ __forceinline__ float *sm_red() { return reinterpret_cast<float *>(sm_base() + kOffRed); }
+__device__ __forceinline__ int *sm_misc() { return reinterpret_cast<int *>(sm_base() + kOffMisc); }
+__device__ __forceinline__ int *sm_rel() { return reinterpret_cast<int *>(sm_base() + kOffRel); } // per-stage release counters
+__device__ __forceinline__ uint32_t sm_full0() { return smem_u32(sm_base() + kOffFull); }
+__device__ __forceinline__ uint32_t sm_empty0() { return smem_u32(sm_base() + kOffEmpty); }
+__device__ __forceinline__ unsigned char *sm_stages() { return sm_base() + kOffStages; }
+__device__ __forceinline__ uint32_t sm_stages_u32() { return smem_u32(sm_base() + kOffStages); }
+
 struct Ctx {
 	long long *prof;  // this CTA's profile rows or null
 	long long *trace; // event trace (CTA 0 only) or null
 	long long wait_cycles;
 	int debug;
-	unsigned char *stages;
-	uint32_t stages_u32, vec_u32, full0, empty0;
-	float *vec, *red;
-	float2 *rope; // (head_dim/2) cos/sin of pos * freq_j, the reference's fp32 formula
-	int *misc;
-	int *rel; // per-stage release counters
+	uint32_t vec_u32;
+	float *vec;
 	int cta, ncta, warp, lane, tid, S;
 	uint32_t s_magic; // ceil(2^32 / S): idx / S == __umulhi(idx, s_magic) for every ring index of a launch
 	uint32_t it; // ring index of the next tile of this role (same sequence for the producer and every consumer warp)
@@ -246,7 +261,7 @@ __device__ __forceinline__ void stamp(Ctx &c, int layer, int phase, int k) {
 	if (c.prof && c.tid == 0) {
 		long long *row = c.prof + ((size_t)layer * kProfPhases + phase) * kProfSlots;
 		row[k] = clock64();
-		if (k == 3) row[4] = c.wait_cycles, c.wait_cycles = 0;
+		if (k == 3 && phase != 1) row[4] = c.wait_cycles, c.wait_cycles = 0; // attention: slot 4 = combine probe
 	}
 	if (c.tid == 0) trace(c, 5, (uint32_t)(layer * 64 + phase * 8 + k));
 }
@@ -278,22 +293,22 @@ struct Producer {
 		if (r > 0) {
 			// blocking wait on the stage's empty mbarrier (the hardware parks the thread: no issue slots burnt);
 			// the release counter first rules out the one case a parity wait gets wrong (two rounds behind)
-			if (ld_rel(c.rel + s) < r - 1) {
+			if (ld_rel(sm_rel() + s) < r - 1) {
 				const long long t0 = clock64();
-				while (ld_rel(c.rel + s) < r - 1) {
+				while (ld_rel(sm_rel() + s) < r - 1) {
 					__nanosleep(64);
 					if (clock64() - t0 > kTimeoutCycles) __trap();
 				}
 			}
-			mbar_wait(c.empty0 + 8 * s, (uint32_t)(r - 1) & 1u);
+			mbar_wait(sm_empty0() + 8 * s, (uint32_t)(r - 1) & 1u);
 		}
 		// the consumer's generic-proxy reads of the stage are ordered before the async-proxy refill
 		asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-		*bar = c.full0 + 8 * s;
+		*bar = sm_full0() + 8 * s;
 		if (c.debug & 8) mbar_arrive(*bar);
 		else mbar_expect_tx(*bar, bytes);
 		trace(c, 1, idx);
-		return c.stages_u32 + s * kStageBytes;
+		return sm_stages_u32() + s * kStageBytes;
 	}
 	// rows [row0, row0+nrows) x columns [kc*KT, (kc+1)*KT) of a (rows, K) matrix -> dst, tile rows packed
 	__device__ __forceinline__ void rows_copy(uint32_t dst, uint32_t bar, const char *m, long row0, int nrows, int K, int KT,
@@ -400,11 +415,11 @@ struct Producer {
 __device__ __forceinline__ float cons_sum(Ctx &c, float v) {
 	v = warp_sum(v);
 	cbar();
-	if (c.lane == 0) c.red[c.warp] = v;
+	if (c.lane == 0) sm_red()[c.warp] = v;
 	cbar();
 	float t = 0.f;
 #pragma unroll
-	for (int w = 0; w < kConsumerWarps; ++w) t += c.red[w];
+	for (int w = 0; w < kConsumerWarps; ++w) t += sm_red()[w];
 	return t;
 }
 
@@ -435,24 +450,24 @@ __device__ __forceinline__ const unsigned char *wait_tile(Ctx &c, uint32_t idx, 
 	ring_pos(c, idx, &s, &r);
 	const uint32_t par = (uint32_t)r & 1u;
 	if (c.lane == 0) trace(c, 2, idx);
-	if (ld_rel(c.rel + s) < r) { // an earlier round of this stage is still in use (rare)
+	if (ld_rel(sm_rel() + s) < r) { // an earlier round of this stage is still in use (rare)
 		const long long t0 = clock64();
-		while (ld_rel(c.rel + s) < r)
+		while (ld_rel(sm_rel() + s) < r)
 			if (clock64() - t0 > kTimeoutCycles) __trap();
 	}
 	if (c.prof && c.tid == 0) {
 		const long long t0 = clock64();
-		mbar_wait(c.full0 + 8 * s, par);
+		mbar_wait(sm_full0() + 8 * s, par);
 		c.wait_cycles += clock64() - t0;
 	} else {
-		mbar_wait(c.full0 + 8 * s, par);
+		mbar_wait(sm_full0() + 8 * s, par);
 	}
 	if (c.lane == 0) trace(c, 3, idx);
 	*slot = idx;
-	return c.stages + (size_t)s * kStageBytes;
+	return sm_stages() + (size_t)s * kStageBytes;
 }
 __device__ __forceinline__ uint32_t tile_u32(const Ctx &c, const unsigned char *tile) {
-	return c.stages_u32 + (uint32_t)(tile - c.stages);
+	return sm_stages_u32() + (uint32_t)(tile - sm_stages());
 }
 // Hand the stage of ring tile `idx` back to the producers.
 __device__ __forceinline__ void release(Ctx &c, uint32_t idx) {
@@ -461,8 +476,8 @@ __device__ __forceinline__ void release(Ctx &c, uint32_t idx) {
 		uint32_t s;
 		int r;
 		ring_pos(c, idx, &s, &r);
-		st_rel(c.rel + s, r + 1);
-		mbar_arrive(c.empty0 + 8 * s);
+		st_rel(sm_rel() + s, r + 1);
+		mbar_arrive(sm_empty0() + 8 * s);
 		trace(c, 4, idx); // release semantics: orders the warp's reads of the stage and the counter store
 	}
 }
@@ -631,7 +646,7 @@ __device__ __forceinline__ void gemv_consume(Ctx &c, const Args &a, Epi &ep) {
 				v0 = clipf(v0, a.clip), v1 = clipf(v1, a.clip);
 				const int hd = a.head_dim, j = (int)(row % hd);
 				if (which < 2) { // interleaved-pair RoPE (src/infer.cpp:200-213), cos/sin from the per-token table
-					const float2 cs = c.rope[j >> 1];
+					const float2 cs = sm_rope()[j >> 1];
 					const float r0 = v0 * cs.x - v1 * cs.y, r1 = v0 * cs.y + v1 * cs.x;
 					v0 = r0, v1 = r1;
 				}
@@ -692,8 +707,79 @@ __device__ __forceinline__ void unpack8(uint4 v, float (&f)[8]) {
 }
 
 __device__ __forceinline__ bool unit_overlap(int b, int ncta, int U, int X, int Y) {
-	const int b0 = (int)((long long)b * U / ncta), b1 = (int)((long long)(b + 1) * U / ncta);
+	const int b0 = (int)((unsigned)b * U / ncta), b1 = (int)((unsigned)(b + 1) * U / ncta);
 	return max(b0, X) < min(b1, Y);
+}
+
+// Last CTA of a KV head: combine the participating CTAs' partials (acc, max, sum) in CTA order into att_out.
+// Runs on 1 CTA per head and layer, so it is kept out of line: its registers do not weigh on the main loops.
+template <int HD, int G>
+__device__ __forceinline__ void combine_head(const float *ws_acc, const float *ws_ml, float *att_out, float *wts, float *scratch,
+                                          int kvh, int ncta, int nch, int U, int b_lo, int b_hi, long long *probe) {
+	constexpr int W = kConsumerWarps;
+	constexpr int kInFlight = 16;  // independent L2 reads per thread and output
+	const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+	const int X = kvh * nch, Y = X + nch;
+	for (int g = warp; g < G; g += W) {
+		const float2 *mlp = reinterpret_cast<const float2 *>(ws_ml) + (size_t)kvh * ncta * G + g;
+		// the first 32 CTAs of the range stay in registers: one L2 round trip in the common case
+		const int b0 = b_lo + lane;
+		const bool p0 = b0 <= b_hi && unit_overlap(b0, ncta, U, X, Y);
+		float2 ml0 = make_float2(-INFINITY, 0.f);
+		if (p0) ml0 = __ldcg(mlp + (size_t)b0 * G);
+		float M = ml0.x;
+		for (int b = b0 + 32; b <= b_hi; b += 32)
+			if (unit_overlap(b, ncta, U, X, Y)) M = fmaxf(M, __ldcg(mlp + (size_t)b * G).x);
+		M = warp_max(M);
+		float ls = 0.f;
+		if (b0 <= b_hi) {
+			const float w = !p0 ? -1.f : ml0.x == -INFINITY ? 0.f : expf(ml0.x - M);
+			if (p0) ls = w * ml0.y;
+			wts[b0 * G + g] = w;
+		}
+		for (int b = b0 + 32; b <= b_hi; b += 32) {
+			float w = -1.f;
+			if (unit_overlap(b, ncta, U, X, Y)) {
+				const float2 ml = __ldcg(mlp + (size_t)b * G);
+				w = ml.x == -INFINITY ? 0.f : expf(ml.x - M);
+				ls += w * ml.y;
+			}
+			wts[b * G + g] = w;
+		}
+		ls = warp_sum(ls);
+		if (lane == 0) wts[ncta * G + g] = ls;
+	}
+	cbar();
+	if (probe && tid == 0) probe[0] = clock64();
+	// two outputs per thread, kInFlight independent L2 reads each, summed in CTA order.  Branch-free: CTAs of the
+	// range that hold no unit of this head (weight -1) are read at b_lo's address and weighted 0.
+	for (int i0 = tid; i0 < G * HD; i0 += 2 * kCT) {
+		const bool two = i0 + kCT < G * HD;
+		const int i1 = two ? i0 + kCT : i0;
+		const int g0 = i0 / HD, g1 = i1 / HD;
+		const float *src = ws_acc + (size_t)kvh * ncta * G * HD;
+		float v0 = 0.f, v1 = 0.f;
+		for (int b = b_lo; b <= b_hi; b += kInFlight) {
+			float p0[kInFlight], p1[kInFlight];
+#pragma unroll
+			for (int k = 0; k < kInFlight; ++k) {
+				const int bk = min(b + k, b_hi);
+				const int ba = wts[bk * G + g0] < 0.f ? b_lo : bk, bb = wts[bk * G + g1] < 0.f ? b_lo : bk;
+				p0[k] = __ldcg(src + (size_t)ba * G * HD + i0);
+				p1[k] = __ldcg(src + (size_t)bb * G * HD + i1);
+			}
+#pragma unroll
+			for (int k = 0; k < kInFlight; ++k) {
+				const int bk = min(b + k, b_hi);
+				const bool in = b + k <= b_hi;
+				const float w0 = in ? fmaxf(wts[bk * G + g0], 0.f) : 0.f, w1 = in ? fmaxf(wts[bk * G + g1], 0.f) : 0.f;
+				v0 = fmaf(w0, p0[k], v0);
+				v1 = fmaf(w1, p1[k], v1);
+			}
+		}
+		att_out[(size_t)kvh * G * HD + i0] = v0 / wts[ncta * G + g0];
+		if (two) att_out[(size_t)kvh * G * HD + i1] = v1 / wts[ncta * G + g1];
+	}
 }
 
 // Split-K flash-decode over this CTA's (kv head, row chunk) units; arithmetic as src/infer.cpp:216-248 (fp32 dot over
@@ -725,7 +811,7 @@ __device__ __forceinline__ void attention_consume(Ctx &c, const Args &a, const L
 	const int sub = lane % LPR, rgrp = lane / LPR;
 	const int my_g = sub / SB, my_st0 = (sub % SB) * NF; // this lane owns scores of head my_g, row steps my_st0 .. +NF
 	const int nch = (c.kv_len + C - 1) / C, U = a.n_kv_heads * nch;
-	const int u0 = (int)((long long)c.cta * U / ncta), u1 = (int)((long long)(c.cta + 1) * U / ncta);
+	const int u0 = (int)((unsigned)c.cta * U / ncta), u1 = (int)((unsigned)(c.cta + 1) * U / ncta);
 	const int NU = u1 - u0;
 	const uint32_t base = c.it;
 	c.it = base + (uint32_t)NU;
@@ -891,87 +977,71 @@ __device__ __forceinline__ void attention_consume(Ctx &c, const Args &a, const L
 	cbar();
 	stamp(c, layer, 1, 5);
 
-	// ---- per KV head of this CTA: merge the warps, publish the partial, last CTA combines ---------------
-	for (int kvh = kv_first; kvh <= kv_last; ++kvh) {
-		const float *hs = wsm + (size_t)(kvh - kv_first) * kConsumerWarps * G * WS;
-		float *pa = a.ws_acc + ((size_t)kvh * ncta + c.cta) * G * HD;
-		float *pml = a.ws_ml + ((size_t)kvh * ncta + c.cta) * G * 2;
-		for (int i = c.tid; i < G * HD; i += kCT) {
-			const int g = i / HD, d = i % HD;
-			float M = -INFINITY;
-#pragma unroll
-			for (int w = 0; w < kConsumerWarps; ++w) M = fmaxf(M, hs[(w * G + g) * WS + HD]);
-			float v = 0.f, ls = 0.f;
-#pragma unroll
-			for (int w = 0; w < kConsumerWarps; ++w) {
-				const float *rec = hs + (w * G + g) * WS;
-				if (rec[HD] != -INFINITY) { // empty records hold no data
-					const float e = expf(rec[HD] - M);
-					v = fmaf(e, rec[d], v);
-					ls = fmaf(e, rec[HD + 1], ls);
-				}
-			}
-			pa[i] = v;
-			if (d == 0) pml[g * 2] = M, pml[g * 2 + 1] = ls;
-		}
-		cbar(); // the partial's stores happen-before lane 0's release below
-		const int X = kvh * nch, Y = X + nch;
-		if (warp == 0) {
+	// ---- merge the warps per KV head, publish the partials, the last CTA of a head combines ---------------
+	// (participants of head h: the CTAs owning units [h*nch, (h+1)*nch); owner(u) = ceil((u+1)*ncta/U) - 1;
+	//  32-bit arithmetic: the host plan guarantees U * ncta < 2^31)
+	const int nh = kv_last - kv_first + 1; // <= kHeadSlots
+	float *ew = wts;                        // [nh][W][G] merge weights (wts is not in use before the combine)
+	if (warp == W - 1) { // misc[4h .. 4h+3]: participants, first and last participating CTA, last-arriver flag
+
+		for (int h = 0; h < nh; ++h) {
+			const int X = (kv_first + h) * nch, Y = X + nch;
+			const int lo = (int)(((unsigned)(X + 1) * ncta + U - 1) / U) - 1, hi = (int)(((unsigned)Y * ncta + U - 1) / U) - 1;
 			int cnt = 0;
-			for (int b = lane; b < ncta; b += 32) cnt += unit_overlap(b, ncta, U, X, Y) ? 1 : 0;
+			for (int b = lo + lane; b <= hi; b += 32) cnt += unit_overlap(b, ncta, U, X, Y) ? 1 : 0;
 #pragma unroll
 			for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(kFull, cnt, o);
-			if (lane == 0) {
-				unsigned prev;
-				asm volatile("atom.acq_rel.gpu.global.add.u32 %0, [%1], 1;" : "=r"(prev) : "l"(a.head_counters + kvh) : "memory");
-				c.misc[0] = prev + 1 == (unsigned)cnt;
-			}
+			if (lane == 0) sm_misc()[4 * h] = cnt, sm_misc()[4 * h + 1] = lo, sm_misc()[4 * h + 2] = hi;
 		}
-		cbar();
-		stamp(c, layer, 1, 6);
-		if (!c.misc[0]) continue; // CTA-uniform
-		// last CTA of this head: combine every CTA's partial in CTA order
-		const int b_lo = max(0, (int)((long long)X * ncta / U) - 1);
-		const int b_hi = min(ncta - 1, (int)(((long long)Y * ncta + U - 1) / U));
-		for (int g = warp; g < G; g += kConsumerWarps) {
-			float M = -INFINITY;
-			for (int b = b_lo + lane; b <= b_hi; b += 32)
-				if (unit_overlap(b, ncta, U, X, Y)) M = fmaxf(M, __ldcg(a.ws_ml + (((size_t)kvh * ncta + b) * G + g) * 2));
-			M = warp_max(M);
+	}
+	if (c.tid < nh * W * G) { // weights of the W warp records of (head slot, g), computed once
+		const int h = c.tid / (W * G), w = (c.tid / G) % W, g = c.tid % G;
+		const float *hs = wsm + (size_t)h * W * G * WS;
+		float M = -INFINITY;
+#pragma unroll
+		for (int w2 = 0; w2 < W; ++w2) M = fmaxf(M, hs[(w2 * G + g) * WS + HD]);
+		const float mw = hs[(w * G + g) * WS + HD];
+		ew[c.tid] = mw == -INFINITY ? 0.f : expf(mw - M); // M is finite: every participating CTA has a non-empty unit
+		if (w == 0) {
 			float ls = 0.f;
-			for (int b = b_lo + lane; b <= b_hi; b += 32) {
-				float w = -1.f;
-				if (unit_overlap(b, ncta, U, X, Y)) {
-					const float *ml = a.ws_ml + (((size_t)kvh * ncta + b) * G + g) * 2;
-					const float mb = __ldcg(ml);
-					w = mb == -INFINITY ? 0.f : expf(mb - M);
-					ls += w * __ldcg(ml + 1);
-				}
-				wts[b * G + g] = w;
-			}
-			ls = warp_sum(ls);
-			if (lane == 0) wts[ncta * G + g] = ls;
-		}
-		cbar();
-		for (int i = c.tid; i < G * HD; i += kCT) {
-			const int g = i / HD;
-			const float *src = a.ws_acc + (size_t)kvh * ncta * G * HD + i;
-			float v = 0.f;
-			for (int b = b_lo; b <= b_hi; b += 8) { // eight independent L2 reads in flight, summed in CTA order
-				float pv[8], pw[8];
 #pragma unroll
-				for (int k = 0; k < 8; ++k) {
-					pw[k] = b + k <= b_hi ? wts[(b + k) * G + g] : -1.f;
-					pv[k] = pw[k] > 0.f ? __ldcg(src + (size_t)(b + k) * G * HD) : 0.f;
-				}
-#pragma unroll
-				for (int k = 0; k < 8; ++k)
-					if (pw[k] > 0.f) v = fmaf(pw[k], pv[k], v);
+			for (int w2 = 0; w2 < W; ++w2) {
+				const float m2 = hs[(w2 * G + g) * WS + HD];
+				if (m2 != -INFINITY) ls = fmaf(expf(m2 - M), hs[(w2 * G + g) * WS + HD + 1], ls);
 			}
-			a.att_out[(size_t)kvh * G * HD + i] = v / wts[ncta * G + g];
+			float *pml = a.ws_ml + (((size_t)(kv_first + h) * ncta + c.cta) * G + g) * 2;
+			pml[0] = M, pml[1] = ls;
 		}
-		if (c.tid == 0) a.head_counters[kvh] = 0;
-		cbar(); // wts is reused by the next head
+	}
+	cbar();
+	for (int i = c.tid; i < nh * G * (HD / 2); i += kCT) { // two dims per thread
+		const int h = i / (G * (HD / 2)), g = (i / (HD / 2)) % G, d = (i % (HD / 2)) * 2;
+		const float *hs = wsm + (size_t)h * W * G * WS;
+		float2 v = make_float2(0.f, 0.f);
+#pragma unroll
+		for (int w = 0; w < W; ++w) {
+			const float e = ew[(h * W + w) * G + g];
+			const float2 r = *reinterpret_cast<const float2 *>(hs + (w * G + g) * WS + d);
+			if (e != 0.f) v.x = fmaf(e, r.x, v.x), v.y = fmaf(e, r.y, v.y); // empty records hold no data
+		}
+		*reinterpret_cast<float2 *>(a.ws_acc + (((size_t)(kv_first + h) * ncta + c.cta) * G + g) * HD + d) = v;
+	}
+	stamp(c, layer, 1, 7);
+	cbar(); // the partials' stores happen-before the releases below
+	if (warp == W - 1 && lane < nh) { // both heads' arrivals in flight together
+		unsigned prev;
+		asm volatile("atom.acq_rel.gpu.global.add.u32 %0, [%1], 1;" : "=r"(prev) : "l"(a.head_counters + kv_first + lane) : "memory");
+		const bool last = prev + 1 == (unsigned)sm_misc()[4 * lane];
+		sm_misc()[4 * lane + 3] = last ? 1 : 0;
+		if (last) a.head_counters[kv_first + lane] = 0; // every participant has arrived: ready for the next layer
+	}
+	cbar();
+	stamp(c, layer, 1, 6);
+	for (int h = 0; h < nh; ++h) {
+		if (!sm_misc()[4 * h + 3]) continue; // CTA-uniform
+		combine_head<HD, G>(a.ws_acc, a.ws_ml, a.att_out, wts, wsm, kv_first + h, ncta, nch, U, sm_misc()[4 * h + 1], sm_misc()[4 * h + 2],
+		                    c.prof ? c.prof + ((size_t)layer * kProfPhases + 1) * kProfSlots + 4 : nullptr);
+		if (h + 1 < nh) cbar(); // wts / part are reused by the next head
 	}
 }
 
@@ -985,23 +1055,13 @@ __device__ __forceinline__ void derive_ring(int pos, int max_seq_len, int *kv_si
 // ---- the kernel -----------------------------------------------------------------------------------------
 template <int DT, int HD, int G>
 __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_constant__ Args a) {
-	extern __shared__ __align__(128) unsigned char smem_raw[];
 	using T = WTraits<DT>;
 	constexpr int B = T::BYTES;
 	Ctx c;
 	c.S = a.stages;
 	c.s_magic = (uint32_t)((0x100000000ull + (unsigned)a.stages - 1) / (unsigned)a.stages);
-	c.stages = smem_raw;
-	c.stages_u32 = smem_u32(smem_raw);
-	c.vec = reinterpret_cast<float *>(smem_raw + (size_t)c.S * kStageBytes);
-	c.vec_u32 = c.stages_u32 + (uint32_t)c.S * kStageBytes;
-	c.rope = reinterpret_cast<float2 *>(c.vec + a.vec_floats);
-	c.red = reinterpret_cast<float *>(c.rope + 64);
-	c.misc = reinterpret_cast<int *>(c.red + 16);
-	c.rel = c.misc + 16;
-	uint64_t *bars = reinterpret_cast<uint64_t *>(c.rel + 32);
-	c.full0 = smem_u32(bars);
-	c.empty0 = c.full0 + 8 * kMaxStages;
+	c.vec = reinterpret_cast<float *>(sm_stages() + (size_t)c.S * kStageBytes);
+	c.vec_u32 = sm_stages_u32() + (uint32_t)c.S * kStageBytes;
 	c.cta = blockIdx.x, c.ncta = gridDim.x;
 	c.tid = threadIdx.x, c.warp = threadIdx.x >> 5, c.lane = threadIdx.x & 31;
 	c.it = 0, c.rot = 0, c.bar_gen = 0;
@@ -1016,9 +1076,9 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_c
 
 	if (threadIdx.x == 0) {
 		for (int i = 0; i < c.S; ++i) {
-			mbar_init(c.full0 + 8 * i, 1);
-			mbar_init(c.empty0 + 8 * i, 1);
-			c.rel[i] = 0;
+			mbar_init(sm_full0() + 8 * i, 1);
+			mbar_init(sm_empty0() + 8 * i, 1);
+			sm_rel()[i] = 0;
 		}
 		asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
 	}
@@ -1028,7 +1088,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_c
 		const int j = 2 * threadIdx.x;
 		const float freq = j >= a.rotary_dim ? 0.f : 1.0f / powf(a.theta, (float)j / (float)a.rotary_dim);
 		const float val = c.pos * freq;
-		c.rope[threadIdx.x] = make_float2(cosf(val), sinf(val));
+		sm_rope()[threadIdx.x] = make_float2(cosf(val), sinf(val));
 	}
 	__syncthreads();
 
@@ -1109,12 +1169,12 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_c
 			const int oi = __shfl_xor_sync(kFull, bi, o);
 			if (ov > bv || (ov == bv && oi < bi)) bv = ov, bi = oi;
 		}
-		if (c.lane == 0) c.red[c.warp] = bv, c.misc[4 + c.warp] = bi;
+		if (c.lane == 0) sm_red()[c.warp] = bv, sm_misc()[4 + c.warp] = bi;
 		cbar();
 		if (c.tid == 0) {
-			bv = c.red[0], bi = c.misc[4];
+			bv = sm_red()[0], bi = sm_misc()[4];
 			for (int t = 1; t < kConsumerWarps; ++t)
-				if (c.red[t] > bv || (c.red[t] == bv && c.misc[4 + t] < bi)) bv = c.red[t], bi = c.misc[4 + t];
+				if (sm_red()[t] > bv || (sm_red()[t] == bv && sm_misc()[4 + t] < bi)) bv = sm_red()[t], bi = sm_misc()[4 + t];
 			a.amax_val[c.cta] = bv, a.amax_idx[c.cta] = bi;
 		}
 		grid_barrier(c, a.sync);

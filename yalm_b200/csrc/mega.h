@@ -18,6 +18,7 @@ constexpr int kConsumerWarps = 11;
 constexpr int kProducerWarps = 1; // all 32 lanes issue: lane l takes tile l of each batch of min(stages, 32) tiles
 constexpr int kThreads = (kConsumerWarps + kProducerWarps) * 32;
 constexpr int kMaxStages = 24;
+constexpr int kSmemHeader = 1280; // rope table, reduction scratch, release counters, mbarriers in front of the ring
 constexpr int kTraceEvents = 1 << 16;
 constexpr int kProfileSlots = 6 * 8; // per (CTA, layer): phases x slots, see decode_mega.cuh
 
@@ -72,7 +73,7 @@ struct Plan {
 
 // Can this (unsharded, dense or MoE) model shape run on the megakernel on the current device?
 Plan plan(int dtype, int dim, int q_dim, int kv_dim, int head_dim, int hidden, int vocab, int n_heads,
-          int n_kv_heads, int n_experts, int n_active);
+          int n_kv_heads, int n_experts, int n_active, int max_seq_len);
 // Bytes of the attention partial workspace (acc + ml) for `grid` CTAs.
 size_t attn_ws_floats(int grid, int n_heads, int head_dim);
 // One token.  Returns a cudaError_t.

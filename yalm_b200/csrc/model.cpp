@@ -550,7 +550,7 @@ void Model::plan_mega() {
 	auto ms = std::make_shared<MegaState>();
 	ms->plan = yalm::mega::plan(static_cast<int>(c.weight_dtype), c.dim, c.n_heads * c.head_dim, c.n_kv_heads * c.head_dim,
 	                            c.head_dim, c.hidden_dim, c.vocab_size, c.n_heads, c.n_kv_heads, c.n_experts,
-	                            c.n_experts_active);
+	                            c.n_experts_active, c.max_seq_len);
 	if (!ms->plan.ok) return;
 	std::vector<yalm::mega::Layer> host(blocks.size());
 	for (size_t i = 0; i < blocks.size(); ++i) {
