@@ -273,17 +273,82 @@ __device__ __forceinline__ void my_groups(const Ctx &c, int G, int *g_first, int
 }
 
 // ---- producer ---------------------------------------------------------------------------------------------
-// Ring order inside a GEMV phase: this CTA's groups in blocks of 8; inside a block the K-split index is the
-// slow axis and the group the fast one, so the 8 consumer warps (one group each) all have a tile in flight.
+// Ring order inside a GEMV phase: this CTA's groups in blocks of kConsumerWarps; inside a block the K-split index
+// is the slow axis and the group the fast one, so every consumer warp (one group each) has a tile in flight.
 //
 // One warp, all 32 lanes: a single thread needs ~1.5k cycles of dependent integer work per tile (measured: the
 // ring starved), so the tile list is walked a batch at a time with lane l issuing tile (batch start + l).  A
 // batch never exceeds the number of stages, so no lane waits on a stage another lane of the same batch fills.
+//
+// L2 look-ahead: with ring tile i of a phase the producer also issues an L2 prefetch for the tile `ahead`
+// positions further down the CTA's tile sequence — crossing into the next phase — so HBM keeps streaming into L2
+// while the consumers sit in a barrier / staging / attention-merge latency chain with the ring full, and the ring
+// then refills from L2 at a multiple of the DRAM rate.  Invariant: on entry to a phase its first
+// min(ahead, ntiles) tiles have been prefetched by the phase before it.
+constexpr int kAttn = -1, kNone = -2;
+struct PhaseDesc {
+	int kind; // kQKV .. kLM, kAttn, or kNone (past the last phase)
+	int ntiles;
+	int nunits;          // look-ahead units: row groups (all K splits of R rows) or attention tiles
+	uint32_t unit_bytes; // bytes of one unit
+	uint32_t tile_bytes;
+	// GEMV phases
+	const char *m0, *m1, *m2;
+	int rows0, rows1, K;
+	Shape sh;
+	int g_first, full_groups, full_tiles, nb_last;
+	// attention
+	const uint16_t *kc, *vc;
+	int nch, u0;
+	int rot_next; // CTA rotation after this phase
+};
+
 struct Producer {
 	Ctx &c;
 	uint64_t policy;
 	int batch; // min(stages, 32)
 	int ahead; // L2 look-ahead distance in tiles (0: off)
+
+	__device__ __forceinline__ PhaseDesc describe(const Args &a, int ph, int rot, int HD, int B) {
+		PhaseDesc d;
+		d.kind = kNone, d.ntiles = 0, d.nunits = 0, d.unit_bytes = kStageBytes, d.rot_next = rot, d.tile_bytes = 0;
+		d.m0 = d.m1 = d.m2 = nullptr, d.rows0 = d.rows1 = d.K = 0, d.g_first = d.full_groups = d.full_tiles = d.nb_last = 0;
+		d.kc = d.vc = nullptr, d.nch = 1, d.u0 = 0;
+		d.sh.R = d.sh.KT = d.sh.nk = d.sh.G = 1;
+		const int n_phases = a.n_layers * 5 + (a.mode != kHydrate ? 1 : 0);
+		if (ph >= n_phases) return d;
+		const int l = min(ph / 5, a.n_layers - 1), k = ph < a.n_layers * 5 ? ph % 5 : 5;
+		const Layer &L = a.layers[l];
+		if (k == 1) {
+			const int C = kStageBytes / (4 * HD);
+			d.kind = kAttn;
+			d.nch = (c.kv_len + C - 1) / C;
+			const int U = a.n_kv_heads * d.nch;
+			d.u0 = (int)((unsigned)c.cta * U / c.ncta);
+			d.ntiles = (int)((unsigned)(c.cta + 1) * U / c.ncta) - d.u0;
+			d.nunits = d.ntiles;
+			d.kc = L.kc, d.vc = L.vc;
+			return d;
+		}
+		d.kind = kQKV, d.m0 = L.wq, d.m1 = L.wk, d.m2 = L.wv, d.rows0 = a.q_dim, d.rows1 = a.kv_dim, d.K = a.dim;
+		switch (k) {
+		case 2: d.kind = kWO, d.m0 = L.wo, d.rows0 = a.dim, d.K = a.q_dim; break;
+		case 3: d.kind = kFFN, d.m0 = L.w1, d.m1 = L.w3, d.rows0 = a.hidden; break;
+		case 4: d.kind = kW2, d.m0 = L.w2, d.rows0 = a.dim, d.K = a.hidden; break;
+		case 5: d.kind = kLM, d.m0 = a.wcls, d.rows0 = a.vocab; break;
+		default: break;
+		}
+		d.sh = shape_of(a, d.kind);
+		d.tile_bytes = (uint32_t)d.sh.R * d.sh.KT * B;
+		d.g_first = (c.cta - rot + c.ncta) % c.ncta;
+		const int NL = d.g_first < d.sh.G ? (d.sh.G - d.g_first + c.ncta - 1) / c.ncta : 0;
+		d.ntiles = NL * d.sh.nk;
+		d.nunits = NL, d.unit_bytes = d.tile_bytes * d.sh.nk;
+		d.full_groups = NL / kConsumerWarps * kConsumerWarps, d.full_tiles = d.full_groups * d.sh.nk;
+		d.nb_last = NL - d.full_groups;
+		d.rot_next = (rot + d.sh.G) % c.ncta;
+		return d;
+	}
 
 	// Stage of ring tile idx is free (every earlier round consumed): expect `bytes` on its full barrier.
 	__device__ __forceinline__ uint32_t acquire(uint32_t idx, uint32_t bytes, uint32_t *bar) {
@@ -311,6 +376,7 @@ struct Producer {
 		return sm_stages_u32() + s * kStageBytes;
 	}
 	// rows [row0, row0+nrows) x columns [kc*KT, (kc+1)*KT) of a (rows, K) matrix -> dst, tile rows packed
+	// (bar == 0: pull the same bytes into L2 instead)
 	__device__ __forceinline__ void rows_copy(uint32_t dst, uint32_t bar, const char *m, long row0, int nrows, int K, int KT,
 	                                          int kc, int nk, int B) {
 		const size_t row_bytes = (size_t)K * B;
@@ -326,88 +392,102 @@ struct Producer {
 			}
 		}
 	}
-	__device__ __forceinline__ void gemv(const Args &a, int kind, const char *m0, const char *m1, const char *m2, int rows0,
-	                                     int rows1, int K, int B) {
-		const Shape sh = shape_of(a, kind);
-		const uint32_t tile_bytes = (uint32_t)sh.R * sh.KT * B;
-		int g_first, NL;
-		my_groups(c, sh.G, &g_first, &NL);
-		const int ntiles = NL * sh.nk;
-		const int full_groups = NL / kConsumerWarps * kConsumerWarps, full_tiles = full_groups * sh.nk;
-		const int nb_last = NL - full_groups;
-		// tile i of this phase: load into the ring (ring = true: waits for its stage) or just pull it into L2
-		auto tile = [&](int i, bool ring) {
-			int gl, kc;
-			if (i < full_tiles) {
-				const int r = i % (kConsumerWarps * sh.nk);
-				gl = i / (kConsumerWarps * sh.nk) * kConsumerWarps + r % kConsumerWarps, kc = r / kConsumerWarps;
-			} else {
-				const int r = i - full_tiles;
-				gl = full_groups + r % nb_last, kc = r / nb_last;
-			}
-			const int g = g_first + gl * c.ncta;
-			uint32_t bar = 0, dst = 0;
-			if (ring) dst = acquire(c.it + (uint32_t)i, tile_bytes, &bar);
-			if (kind == kFFN) {
-				const int rh = sh.R / 2;
-				rows_copy(dst, bar, m0, (long)g * rh, rh, K, sh.KT, kc, sh.nk, B);
-				rows_copy(dst + rh * sh.KT * B, bar, m1, (long)g * rh, rh, K, sh.KT, kc, sh.nk, B);
-			} else {
-				long row = (long)g * sh.R;
-				const char *m = m0;
-				if (kind == kQKV) {
-					if (row >= rows0 + rows1) row -= rows0 + rows1, m = m2;
-					else if (row >= rows0) row -= rows0, m = m1;
-				}
-				rows_copy(dst, bar, m, row, sh.R, K, sh.KT, kc, sh.nk, B);
-			}
-		};
-		// L2 look-ahead: the first `ahead` tiles now, then tile i + ahead with every tile i.  HBM keeps streaming
-		// into L2 while the consumers sit in a barrier / staging / attention-merge latency chain with the ring
-		// full, and the ring then refills from L2 instead of DRAM.
-		if (ahead > 0)
-			for (int i = c.lane; i < min(ahead, ntiles); i += 32) tile(i, false);
-		for (int t0 = 0; t0 < ntiles; t0 += batch) {
-			const int i = t0 + c.lane;
-			if (c.lane < batch && i < ntiles) {
-				tile(i, true);
-				if (ahead > 0 && i + ahead < ntiles) tile(i + ahead, false);
-			}
-			__syncwarp();
-		}
-		c.it += (uint32_t)ntiles;
-		c.rot = (c.rot + sh.G) % c.ncta;
-	}
-	__device__ __forceinline__ void attention(const Layer &L, int HD, int n_kv, int max_seq) {
-		const int C = kStageBytes / (4 * HD);
-		const int nch = (c.kv_len + C - 1) / C, U = n_kv * nch;
-		const int u0 = (int)((long long)c.cta * U / c.ncta), u1 = (int)((long long)(c.cta + 1) * U / c.ncta);
-		const int ntiles = u1 - u0;
-		auto tile = [&](int i, bool ring) {
-			const int u = u0 + i, kvh = u / nch, r0 = (u % nch) * C, n = min(C, c.kv_len - r0);
+	// Tile i of phase d -> ring index ring_idx (waits for its stage).  Returns the tile's look-ahead unit, or -1 if
+	// the tile is not the first of its unit.
+	__device__ __forceinline__ int tile(const PhaseDesc &d, int i, uint32_t ring_idx, int HD, int max_seq, int B) {
+		if (d.kind == kAttn) {
+			const int u = d.u0 + i, kvh = u / d.nch, r0 = (u % d.nch) * (kStageBytes / (4 * HD));
+			const int n = min(kStageBytes / (4 * HD), c.kv_len - r0);
 			const uint32_t bytes = (uint32_t)n * HD * 2;
 			const size_t off = ((size_t)kvh * max_seq + r0) * HD;
-			if (ring) {
-				uint32_t bar;
-				const uint32_t dst = acquire(c.it + (uint32_t)i, 2 * bytes, &bar);
-				bulk_g2s(dst, L.kc + off, bytes, bar, policy);
-				bulk_g2s(dst + kStageBytes / 2, L.vc + off, bytes, bar, policy);
-			} else {
-				bulk_prefetch_l2(L.kc + off, bytes);
-				bulk_prefetch_l2(L.vc + off, bytes);
-			}
-		};
-		if (ahead > 0)
-			for (int i = c.lane; i < min(ahead, ntiles); i += 32) tile(i, false);
-		for (int t0 = 0; t0 < ntiles; t0 += batch) {
-			const int i = t0 + c.lane;
-			if (c.lane < batch && i < ntiles) {
-				tile(i, true);
-				if (ahead > 0 && i + ahead < ntiles) tile(i + ahead, false);
-			}
-			__syncwarp();
+			uint32_t bar;
+			const uint32_t dst = acquire(ring_idx, 2 * bytes, &bar);
+			bulk_g2s(dst, d.kc + off, bytes, bar, policy);
+			bulk_g2s(dst + kStageBytes / 2, d.vc + off, bytes, bar, policy);
+			return i;
 		}
-		c.it += (uint32_t)ntiles;
+		int gl, kc;
+		if (i < d.full_tiles) {
+			const int r = i % (kConsumerWarps * d.sh.nk);
+			gl = i / (kConsumerWarps * d.sh.nk) * kConsumerWarps + r % kConsumerWarps, kc = r / kConsumerWarps;
+		} else {
+			const int r = i - d.full_tiles;
+			gl = d.full_groups + r % d.nb_last, kc = r / d.nb_last;
+		}
+		const int g = d.g_first + gl * c.ncta;
+		uint32_t bar;
+		const uint32_t dst = acquire(ring_idx, d.tile_bytes, &bar);
+		if (d.kind == kFFN) {
+			const int rh = d.sh.R / 2;
+			rows_copy(dst, bar, d.m0, (long)g * rh, rh, d.K, d.sh.KT, kc, d.sh.nk, B);
+			rows_copy(dst + rh * d.sh.KT * B, bar, d.m1, (long)g * rh, rh, d.K, d.sh.KT, kc, d.sh.nk, B);
+		} else {
+			long row = (long)g * d.sh.R;
+			const char *m = d.m0;
+			if (d.kind == kQKV) {
+				if (row >= d.rows0 + d.rows1) row -= d.rows0 + d.rows1, m = d.m2;
+				else if (row >= d.rows0) row -= d.rows0, m = d.m1;
+			}
+			rows_copy(dst, bar, m, row, d.sh.R, d.K, d.sh.KT, kc, d.sh.nk, B);
+		}
+		return kc == 0 ? gl : -1;
+	}
+	// Pull look-ahead unit `unit` of phase d into L2: whole rows, one or two large requests (the copy engine is
+	// bound by requests, not bytes, at the ring's 2 KB row pieces).
+	__device__ __forceinline__ void prefetch_unit(const PhaseDesc &d, int unit, int HD, int max_seq, int B) {
+		if (d.kind == kAttn) {
+			const int u = d.u0 + unit, kvh = u / d.nch, r0 = (u % d.nch) * (kStageBytes / (4 * HD));
+			const uint32_t bytes = (uint32_t)min(kStageBytes / (4 * HD), c.kv_len - r0) * HD * 2;
+			const size_t off = ((size_t)kvh * max_seq + r0) * HD;
+			bulk_prefetch_l2(d.kc + off, bytes);
+			bulk_prefetch_l2(d.vc + off, bytes);
+			return;
+		}
+		const int g = d.g_first + unit * c.ncta;
+		const size_t row_bytes = (size_t)d.K * B;
+		if (d.kind == kFFN) {
+			const int rh = d.sh.R / 2;
+			bulk_prefetch_l2(d.m0 + (size_t)g * rh * row_bytes, (uint32_t)(rh * row_bytes));
+			bulk_prefetch_l2(d.m1 + (size_t)g * rh * row_bytes, (uint32_t)(rh * row_bytes));
+		} else {
+			long row = (long)g * d.sh.R;
+			const char *m = d.m0;
+			if (d.kind == kQKV) {
+				if (row >= d.rows0 + d.rows1) row -= d.rows0 + d.rows1, m = d.m2;
+				else if (row >= d.rows0) row -= d.rows0, m = d.m1;
+			}
+			bulk_prefetch_l2(m + row * row_bytes, (uint32_t)(d.sh.R * row_bytes));
+		}
+	}
+	// Every phase of the token, in order (phase -1 is empty: it only fetches the prefix of phase 0).
+	// `ahead` is in ring stages (kStageBytes); per phase it becomes a whole number of look-ahead units.
+	__device__ __forceinline__ void run(const Args &a, int HD, int B) {
+		const int n_phases = a.n_layers * 5 + (a.mode != kHydrate ? 1 : 0);
+		const uint32_t ahead_bytes = (uint32_t)ahead * kStageBytes;
+		PhaseDesc cur = describe(a, n_phases, 0, HD, B); // kNone
+		for (int ph = -1; ph < n_phases; ++ph) {
+			const PhaseDesc nxt = describe(a, ph + 1, cur.rot_next, HD, B);
+			const int n = cur.ntiles, nu = cur.nunits;
+			const int dist = (int)max(1u, ahead_bytes / cur.unit_bytes);                         // look-ahead of this phase, in its units
+			const int npre = ahead > 0 ? min((int)max(1u, ahead_bytes / nxt.unit_bytes), nxt.nunits) : 0; // prefix of the next phase fetched here
+			const int m = nu > 0 ? min(nu, dist) : 32; // the last m units of this phase share the next phase's prefix
+			// a phase without tiles still walks one batch so that its lanes fetch the next prefix
+			const int n_eff = n > 0 ? n : 32, nb = n > 0 ? batch : 32;
+			for (int t0 = 0; t0 < n_eff; t0 += nb) {
+				const int i = t0 + c.lane;
+				if (c.lane < nb && i < n_eff) {
+					const int unit = n > 0 ? tile(cur, i, c.it + (uint32_t)i, HD, a.max_seq_len, B) : i;
+					if (ahead > 0 && unit >= 0) {
+						if (unit + dist < nu) prefetch_unit(cur, unit + dist, HD, a.max_seq_len, B);
+						else
+							for (int j = unit - max(0, nu - dist); j < npre; j += m) prefetch_unit(nxt, j, HD, a.max_seq_len, B);
+					}
+				}
+				__syncwarp();
+			}
+			c.it += (uint32_t)n;
+			cur = nxt;
+		}
 	}
 };
 
@@ -1095,25 +1175,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_c
 	if (c.warp >= kConsumerWarps) {
 		// ================================ producers ================================
 		Producer p{c, (a.debug & 8) ? 0ull : policy_evict_first(), min(c.S, 32), (a.debug & 8) ? 0 : a.l2_ahead};
-		const int n_phases = a.n_layers * 5 + (a.mode != kHydrate ? 1 : 0);
-		for (int ph = 0; ph < n_phases; ++ph) { // one call site per producer function (code size)
-			const int l = min(ph / 5, a.n_layers - 1), k = ph < a.n_layers * 5 ? ph % 5 : 5;
-			const Layer &L = a.layers[l];
-			if (k == 1) {
-				p.attention(L, HD, a.n_kv_heads, a.max_seq_len);
-				continue;
-			}
-			int kind = kQKV, rows0 = a.q_dim, rows1 = a.kv_dim, K = a.dim;
-			const char *m0 = L.wq, *m1 = L.wk, *m2 = L.wv;
-			switch (k) {
-			case 2: kind = kWO, m0 = L.wo, rows0 = a.dim, K = a.q_dim; break;
-			case 3: kind = kFFN, m0 = L.w1, m1 = L.w3, rows0 = a.hidden; break;
-			case 4: kind = kW2, m0 = L.w2, rows0 = a.dim, K = a.hidden; break;
-			case 5: kind = kLM, m0 = a.wcls, rows0 = a.vocab; break;
-			default: break;
-			}
-			p.gemv(a, kind, m0, m1, m2, rows0, rows1, K, B);
-		}
+		p.run(a, HD, B);
 		return;
 	}
 
