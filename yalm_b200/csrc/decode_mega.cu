@@ -13,7 +13,7 @@ namespace mega {
 // Pure streaming probe: the same ring and bulk copies over a flat buffer, consumers only wait and release.
 // Its GB/s is the ceiling the megakernel can reach on this part (yalm_bench_op("stream")).
 __global__ void __launch_bounds__(kThreads, 1) stream_probe_kernel(const char *buf, size_t bytes, int stages, unsigned *sink,
-                                                                      int copy_bytes) {
+                                                                      int copy_bytes, int ahead) {
 	extern __shared__ __align__(128) unsigned char smem_raw[];
 	uint64_t *bars = reinterpret_cast<uint64_t *>(smem_raw + (size_t)stages * kStageBytes);
 	const uint32_t full0 = smem_u32(bars), empty0 = full0 + 8 * kMaxStages, st0 = smem_u32(smem_raw);
@@ -33,6 +33,8 @@ __global__ void __launch_bounds__(kThreads, 1) stream_probe_kernel(const char *b
 		uint32_t it = 0;
 		for (size_t t = blockIdx.x; t < ntiles; t += gridDim.x, ++it) {
 			const uint32_t s = it % stages, par = ((it / stages) & 1u) ^ 1u;
+			if (ahead > 0 && t + (size_t)ahead * gridDim.x < ntiles) // experiment: L2 prefetch `ahead` tiles in front of the ring
+				bulk_prefetch_l2(buf + (t + (size_t)ahead * gridDim.x) * kStageBytes, kStageBytes);
 			mbar_wait(empty0 + 8 * s, par);
 			mbar_expect_tx(full0 + 8 * s, kStageBytes);
 			for (int o = 0; o < kStageBytes; o += copy_bytes) // one stage as kStageBytes / copy_bytes bulk copies
@@ -161,6 +163,7 @@ extern "C" int yalm_stream_probe(size_t bytes, int iters, double *usec) {
 	if (!usec || iters < 1 || bytes < (size_t)kStageBytes) return YALM_EINVAL;
 	int copy_bytes = getenv("YALM_PROBE_COPY") ? atoi(getenv("YALM_PROBE_COPY")) : kStageBytes;
 	if (copy_bytes < 16 || copy_bytes > kStageBytes || kStageBytes % copy_bytes) copy_bytes = kStageBytes;
+	const int ahead = getenv("YALM_PROBE_AHEAD") ? atoi(getenv("YALM_PROBE_AHEAD")) : 0;
 	const DeviceInfo &di = device_info();
 	const int stages = (int)std::min<long>(kMaxStages, ((long)di.max_smem_optin - 256) / kStageBytes);
 	const size_t smem = (size_t)stages * kStageBytes + 2 * kMaxStages * 8;
@@ -173,9 +176,9 @@ extern "C" int yalm_stream_probe(size_t bytes, int iters, double *usec) {
 	cudaEvent_t e0, e1;
 	cudaEventCreate(&e0);
 	cudaEventCreate(&e1);
-	for (int i = 0; i < 2; ++i) stream_probe_kernel<<<di.sms, kThreads, smem>>>(buf, bytes, stages, sink, copy_bytes);
+	for (int i = 0; i < 2; ++i) stream_probe_kernel<<<di.sms, kThreads, smem>>>(buf, bytes, stages, sink, copy_bytes, ahead);
 	cudaEventRecord(e0);
-	for (int i = 0; i < iters; ++i) stream_probe_kernel<<<di.sms, kThreads, smem>>>(buf, bytes, stages, sink, copy_bytes);
+	for (int i = 0; i < iters; ++i) stream_probe_kernel<<<di.sms, kThreads, smem>>>(buf, bytes, stages, sink, copy_bytes, ahead);
 	cudaEventRecord(e1);
 	cudaError_t err = cudaDeviceSynchronize();
 	float ms = 0.f;

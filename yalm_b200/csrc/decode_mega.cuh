@@ -35,7 +35,7 @@ namespace mega {
 // A wait longer than this many SM cycles (~4 s) is a bug: trap, never hang.
 constexpr long long kTimeoutCycles = 8000000000ll;
 constexpr int kCT = kConsumerWarps * 32;
-constexpr int kHeadSlots = 2; // a CTA's attention units span at most two KV heads (n_kv_heads <= grid)
+constexpr int kHeadSlots = 1; // a CTA's attention units belong to one KV head (attn_split; needs n_kv_heads <= grid)
 
 // ---- PTX helpers -------------------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void *p) {
@@ -272,6 +272,28 @@ __device__ __forceinline__ void my_groups(const Ctx &c, int G, int *g_first, int
 	*NL = *g_first < G ? (G - *g_first + c.ncta - 1) / c.ncta : 0;
 }
 
+// Attention work split: KV head h belongs to the CTAs [ceil(h*ncta/n_kv), ceil((h+1)*ncta/n_kv)) — a CTA never
+// spans two heads — and the head's nch row chunks are split contiguously over those CTAs.
+struct AttnSplit {
+	int kvh;    // this CTA's KV head
+	int c0, nc; // first CTA and number of CTAs of the head
+	int k0, nu; // this CTA's first chunk and number of chunks (units)
+};
+__host__ __device__ inline AttnSplit attn_split(int cta, int ncta, int n_kv, int nch) {
+	AttnSplit s;
+	s.kvh = (int)((unsigned)cta * n_kv / ncta);
+	s.c0 = (s.kvh * ncta + n_kv - 1) / n_kv;
+	s.nc = ((s.kvh + 1) * ncta + n_kv - 1) / n_kv - s.c0;
+	const int r = cta - s.c0;
+	s.k0 = (int)((unsigned)r * nch / s.nc);
+	s.nu = (int)((unsigned)(r + 1) * nch / s.nc) - s.k0;
+	return s;
+}
+// Does CTA c0 + r of a head with nc CTAs own a chunk?
+__device__ __forceinline__ bool attn_has_unit(int r, int nc, int nch) {
+	return nch >= nc || (unsigned)(r + 1) * nch / nc > (unsigned)r * nch / nc;
+}
+
 // ---- producer ---------------------------------------------------------------------------------------------
 // Ring order inside a GEMV phase: this CTA's groups in blocks of kConsumerWarps; inside a block the K-split index
 // is the slow axis and the group the fast one, so every consumer warp (one group each) has a tile in flight.
@@ -323,9 +345,9 @@ struct Producer {
 			const int C = kStageBytes / (4 * HD);
 			d.kind = kAttn;
 			d.nch = (c.kv_len + C - 1) / C;
-			const int U = a.n_kv_heads * d.nch;
-			d.u0 = (int)((unsigned)c.cta * U / c.ncta);
-			d.ntiles = (int)((unsigned)(c.cta + 1) * U / c.ncta) - d.u0;
+			const AttnSplit sp = attn_split(c.cta, c.ncta, a.n_kv_heads, d.nch);
+			d.u0 = sp.kvh * d.nch + sp.k0; // (head, chunk) as one index
+			d.ntiles = sp.nu;
 			d.nunits = d.ntiles;
 			d.kc = L.kc, d.vc = L.vc;
 			return d;
@@ -786,30 +808,25 @@ __device__ __forceinline__ void unpack8(uint4 v, float (&f)[8]) {
 	f[0] = a.x, f[1] = a.y, f[2] = b.x, f[3] = b.y, f[4] = c.x, f[5] = c.y, f[6] = d.x, f[7] = d.y;
 }
 
-__device__ __forceinline__ bool unit_overlap(int b, int ncta, int U, int X, int Y) {
-	const int b0 = (int)((unsigned)b * U / ncta), b1 = (int)((unsigned)(b + 1) * U / ncta);
-	return max(b0, X) < min(b1, Y);
-}
-
 // Last CTA of a KV head: combine the participating CTAs' partials (acc, max, sum) in CTA order into att_out.
 // Runs on 1 CTA per head and layer, so it is kept out of line: its registers do not weigh on the main loops.
 template <int HD, int G>
 __device__ __forceinline__ void combine_head(const float *ws_acc, const float *ws_ml, float *att_out, float *wts, float *scratch,
-                                          int kvh, int ncta, int nch, int U, int b_lo, int b_hi, long long *probe) {
+                                          int kvh, int ncta, int nch, int b_lo, int b_hi, long long *probe) {
 	constexpr int W = kConsumerWarps;
 	constexpr int kInFlight = 16;  // independent L2 reads per thread and output
 	const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-	const int X = kvh * nch, Y = X + nch;
+	const int nc = b_hi - b_lo + 1;
 	for (int g = warp; g < G; g += W) {
 		const float2 *mlp = reinterpret_cast<const float2 *>(ws_ml) + (size_t)kvh * ncta * G + g;
 		// the first 32 CTAs of the range stay in registers: one L2 round trip in the common case
 		const int b0 = b_lo + lane;
-		const bool p0 = b0 <= b_hi && unit_overlap(b0, ncta, U, X, Y);
+		const bool p0 = b0 <= b_hi && attn_has_unit(lane, nc, nch);
 		float2 ml0 = make_float2(-INFINITY, 0.f);
 		if (p0) ml0 = __ldcg(mlp + (size_t)b0 * G);
 		float M = ml0.x;
 		for (int b = b0 + 32; b <= b_hi; b += 32)
-			if (unit_overlap(b, ncta, U, X, Y)) M = fmaxf(M, __ldcg(mlp + (size_t)b * G).x);
+			if (attn_has_unit(b - b_lo, nc, nch)) M = fmaxf(M, __ldcg(mlp + (size_t)b * G).x);
 		M = warp_max(M);
 		float ls = 0.f;
 		if (b0 <= b_hi) {
@@ -819,7 +836,7 @@ __device__ __forceinline__ void combine_head(const float *ws_acc, const float *w
 		}
 		for (int b = b0 + 32; b <= b_hi; b += 32) {
 			float w = -1.f;
-			if (unit_overlap(b, ncta, U, X, Y)) {
+			if (attn_has_unit(b - b_lo, nc, nch)) {
 				const float2 ml = __ldcg(mlp + (size_t)b * G);
 				w = ml.x == -INFINITY ? 0.f : expf(ml.x - M);
 				ls += w * ml.y;
@@ -832,7 +849,8 @@ __device__ __forceinline__ void combine_head(const float *ws_acc, const float *w
 	cbar();
 	if (probe && tid == 0) probe[0] = clock64();
 	// two outputs per thread, kInFlight independent L2 reads each, summed in CTA order.  Branch-free: CTAs of the
-	// range that hold no unit of this head (weight -1) are read at b_lo's address and weighted 0.
+	// range that hold no unit of this head (weight -1) are read at b_hi's address (the last CTA of a head always
+	// owns a unit) and weighted 0.
 	for (int i0 = tid; i0 < G * HD; i0 += 2 * kCT) {
 		const bool two = i0 + kCT < G * HD;
 		const int i1 = two ? i0 + kCT : i0;
@@ -844,7 +862,7 @@ __device__ __forceinline__ void combine_head(const float *ws_acc, const float *w
 #pragma unroll
 			for (int k = 0; k < kInFlight; ++k) {
 				const int bk = min(b + k, b_hi);
-				const int ba = wts[bk * G + g0] < 0.f ? b_lo : bk, bb = wts[bk * G + g1] < 0.f ? b_lo : bk;
+				const int ba = wts[bk * G + g0] < 0.f ? b_hi : bk, bb = wts[bk * G + g1] < 0.f ? b_hi : bk;
 				p0[k] = __ldcg(src + (size_t)ba * G * HD + i0);
 				p1[k] = __ldcg(src + (size_t)bb * G * HD + i1);
 			}
@@ -890,25 +908,23 @@ __device__ __forceinline__ void attention_consume(Ctx &c, const Args &a, const L
 	const int lane = c.lane, warp = c.warp, ncta = c.ncta;
 	const int sub = lane % LPR, rgrp = lane / LPR;
 	const int my_g = sub / SB, my_st0 = (sub % SB) * NF; // this lane owns scores of head my_g, row steps my_st0 .. +NF
-	const int nch = (c.kv_len + C - 1) / C, U = a.n_kv_heads * nch;
-	const int u0 = (int)((unsigned)c.cta * U / ncta), u1 = (int)((unsigned)(c.cta + 1) * U / ncta);
-	const int NU = u1 - u0;
+	const int nch = (c.kv_len + C - 1) / C;
+	const AttnSplit sp = attn_split(c.cta, ncta, a.n_kv_heads, nch);
+	const int NU = sp.nu, kvh = sp.kvh;
 	const uint32_t base = c.it;
 	c.it = base + (uint32_t)NU;
 	if (NU == 0) return;
-	const int kv_first = u0 / nch, kv_last = (u1 - 1) / nch;
 	const float div = sqrtf((float)HD);
-	float *wsm = c.vec;                                            // [kHeadSlots][W][G][WS]
-	float *wts = wsm + kHeadSlots * W * G * WS;                    // combine: [ncta][G] weights, Lsum[G]
-	float *ps = wts + ncta * G + G + (size_t)warp * PS;            // this warp's p / corr scratch
-	if (lane < kHeadSlots * G) { // each warp initialises its own records, so a __syncwarp orders it against park()
-		float *rec = wsm + (((lane / G) * W + warp) * G + lane % G) * WS;
+	float *wsm = c.vec;                                 // [W][G][WS] warp records
+	float *wts = wsm + W * G * WS;                      // merge weights, then combine: [ncta][G] weights, Lsum[G]
+	float *ps = wts + ncta * G + G + (size_t)warp * PS; // this warp's p / corr scratch
+	if (lane < G) { // each warp initialises its own records, so a __syncwarp orders it against park()
+		float *rec = wsm + (warp * G + lane) * WS;
 		rec[HD] = -INFINITY, rec[HD + 1] = 0.f;
 	}
 	float2 qr[G][4], acc[G][4]; // q / sqrt(HD) and the output accumulators: this lane's 8 dims as 4 pairs
 	float m = -INFINITY, l = 0.f; // running max / partial sum of head my_g (max identical in all lanes of the head)
-	int cur = -1;
-	auto park = [&](int kvh) { // merge the warp's row groups and lanes, store its state for head kvh
+	auto park = [&]() { // merge the warp's row groups and lanes, store the warp's state
 #pragma unroll
 		for (int o = LPR; o < 32; o <<= 1) {
 			l += __shfl_xor_sync(kFull, l, o);
@@ -925,33 +941,30 @@ __device__ __forceinline__ void attention_consume(Ctx &c, const Args &a, const L
 		if (rgrp == 0) {
 #pragma unroll
 			for (int g = 0; g < G; ++g) {
-				float *rec = wsm + (((kvh - kv_first) * W + warp) * G + g) * WS;
+				float *rec = wsm + (warp * G + g) * WS;
 #pragma unroll
 				for (int j = 0; j < 4; ++j) rec[sub * 8 + 2 * j] = acc[g][j].x, rec[sub * 8 + 2 * j + 1] = acc[g][j].y;
 			}
 			if (sub % SB == 0) {
-				float *rec = wsm + (((kvh - kv_first) * W + warp) * G + my_g) * WS;
+				float *rec = wsm + (warp * G + my_g) * WS;
 				rec[HD] = m, rec[HD + 1] = l;
 			}
 		}
 	};
 	__syncwarp();
-	for (int i = warp; i < NU; i += W) {
-		const int u = u0 + i, kvh = u / nch, t0 = (u % nch) * C, n = min(C, c.kv_len - t0);
-		if (kvh != cur) {
-			if (cur >= 0) park(cur);
-			cur = kvh;
+	if (warp < NU) { // q / sqrt(HD) of the head group, accumulators
 #pragma unroll
-			for (int g = 0; g < G; ++g) {
-				const float *qp = a.q + (size_t)(kvh * G + g) * HD + sub * 8;
-				const float4 lo = __ldcg(reinterpret_cast<const float4 *>(qp)), hi = __ldcg(reinterpret_cast<const float4 *>(qp + 4));
-				qr[g][0] = make_float2(lo.x / div, lo.y / div), qr[g][1] = make_float2(lo.z / div, lo.w / div);
-				qr[g][2] = make_float2(hi.x / div, hi.y / div), qr[g][3] = make_float2(hi.z / div, hi.w / div);
+		for (int g = 0; g < G; ++g) {
+			const float *qp = a.q + (size_t)(kvh * G + g) * HD + sub * 8;
+			const float4 lo = __ldcg(reinterpret_cast<const float4 *>(qp)), hi = __ldcg(reinterpret_cast<const float4 *>(qp + 4));
+			qr[g][0] = make_float2(lo.x / div, lo.y / div), qr[g][1] = make_float2(lo.z / div, lo.w / div);
+			qr[g][2] = make_float2(hi.x / div, hi.y / div), qr[g][3] = make_float2(hi.z / div, hi.w / div);
 #pragma unroll
-				for (int j = 0; j < 4; ++j) acc[g][j] = make_float2(0.f, 0.f);
-			}
-			m = -INFINITY, l = 0.f;
+			for (int j = 0; j < 4; ++j) acc[g][j] = make_float2(0.f, 0.f);
 		}
+	}
+	for (int i = warp; i < NU; i += W) {
+		const int t0 = (sp.k0 + i) * C, n = min(C, c.kv_len - t0);
 		uint32_t slot;
 		const unsigned char *tile = wait_tile(c, base + (uint32_t)i, &slot);
 		const uint32_t ks = tile_u32(c, tile) + lane * 16, vs = ks + kStageBytes / 2; // row (st, rgrp) at + st * 512
@@ -1053,76 +1066,57 @@ __device__ __forceinline__ void attention_consume(Ctx &c, const Args &a, const L
 		}
 		release(c, slot);
 	}
-	if (cur >= 0) park(cur);
+	if (warp < NU) park();
 	cbar();
 	stamp(c, layer, 1, 5);
 
-	// ---- merge the warps per KV head, publish the partials, the last CTA of a head combines ---------------
-	// (participants of head h: the CTAs owning units [h*nch, (h+1)*nch); owner(u) = ceil((u+1)*ncta/U) - 1;
-	//  32-bit arithmetic: the host plan guarantees U * ncta < 2^31)
-	const int nh = kv_last - kv_first + 1; // <= kHeadSlots
-	float *ew = wts;                        // [nh][W][G] merge weights (wts is not in use before the combine)
-	if (warp == W - 1) { // misc[4h .. 4h+3]: participants, first and last participating CTA, last-arriver flag
-
-		for (int h = 0; h < nh; ++h) {
-			const int X = (kv_first + h) * nch, Y = X + nch;
-			const int lo = (int)(((unsigned)(X + 1) * ncta + U - 1) / U) - 1, hi = (int)(((unsigned)Y * ncta + U - 1) / U) - 1;
-			int cnt = 0;
-			for (int b = lo + lane; b <= hi; b += 32) cnt += unit_overlap(b, ncta, U, X, Y) ? 1 : 0;
-#pragma unroll
-			for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(kFull, cnt, o);
-			if (lane == 0) sm_misc()[4 * h] = cnt, sm_misc()[4 * h + 1] = lo, sm_misc()[4 * h + 2] = hi;
-		}
-	}
-	if (c.tid < nh * W * G) { // weights of the W warp records of (head slot, g), computed once
-		const int h = c.tid / (W * G), w = (c.tid / G) % W, g = c.tid % G;
-		const float *hs = wsm + (size_t)h * W * G * WS;
+	// ---- merge the warps, publish the CTA's partial, the last CTA of the head to arrive combines ------------
+	float *ew = wts; // [W][G] merge weights (wts is not in use before the combine)
+	if (c.tid < W * G) { // weight of warp w's record for head g, computed once
+		const int w = c.tid / G, g = c.tid % G;
 		float M = -INFINITY;
 #pragma unroll
-		for (int w2 = 0; w2 < W; ++w2) M = fmaxf(M, hs[(w2 * G + g) * WS + HD]);
-		const float mw = hs[(w * G + g) * WS + HD];
-		ew[c.tid] = mw == -INFINITY ? 0.f : expf(mw - M); // M is finite: every participating CTA has a non-empty unit
+		for (int w2 = 0; w2 < W; ++w2) M = fmaxf(M, wsm[(w2 * G + g) * WS + HD]);
+		const float mw = wsm[(w * G + g) * WS + HD];
+		ew[c.tid] = mw == -INFINITY ? 0.f : expf(mw - M); // M is finite: warp 0 of a participating CTA owns a unit
 		if (w == 0) {
 			float ls = 0.f;
 #pragma unroll
 			for (int w2 = 0; w2 < W; ++w2) {
-				const float m2 = hs[(w2 * G + g) * WS + HD];
-				if (m2 != -INFINITY) ls = fmaf(expf(m2 - M), hs[(w2 * G + g) * WS + HD + 1], ls);
+				const float m2 = wsm[(w2 * G + g) * WS + HD];
+				if (m2 != -INFINITY) ls = fmaf(expf(m2 - M), wsm[(w2 * G + g) * WS + HD + 1], ls);
 			}
-			float *pml = a.ws_ml + (((size_t)(kv_first + h) * ncta + c.cta) * G + g) * 2;
+			float *pml = a.ws_ml + (((size_t)kvh * ncta + c.cta) * G + g) * 2;
 			pml[0] = M, pml[1] = ls;
 		}
 	}
 	cbar();
-	for (int i = c.tid; i < nh * G * (HD / 2); i += kCT) { // two dims per thread
-		const int h = i / (G * (HD / 2)), g = (i / (HD / 2)) % G, d = (i % (HD / 2)) * 2;
-		const float *hs = wsm + (size_t)h * W * G * WS;
+	for (int i = c.tid; i < G * (HD / 2); i += kCT) { // two dims per thread
+		const int g = i / (HD / 2), d = (i % (HD / 2)) * 2;
 		float2 v = make_float2(0.f, 0.f);
 #pragma unroll
 		for (int w = 0; w < W; ++w) {
-			const float e = ew[(h * W + w) * G + g];
-			const float2 r = *reinterpret_cast<const float2 *>(hs + (w * G + g) * WS + d);
+			const float e = ew[w * G + g];
+			const float2 r = *reinterpret_cast<const float2 *>(wsm + (w * G + g) * WS + d);
 			if (e != 0.f) v.x = fmaf(e, r.x, v.x), v.y = fmaf(e, r.y, v.y); // empty records hold no data
 		}
-		*reinterpret_cast<float2 *>(a.ws_acc + (((size_t)(kv_first + h) * ncta + c.cta) * G + g) * HD + d) = v;
+		*reinterpret_cast<float2 *>(a.ws_acc + (((size_t)kvh * ncta + c.cta) * G + g) * HD + d) = v;
 	}
 	stamp(c, layer, 1, 7);
-	cbar(); // the partials' stores happen-before the releases below
-	if (warp == W - 1 && lane < nh) { // both heads' arrivals in flight together
+	cbar(); // the partial's stores happen-before the release below
+	if (c.tid == 0) {
+		const int cnt = min(sp.nc, nch); // CTAs of the head that own a chunk
 		unsigned prev;
-		asm volatile("atom.acq_rel.gpu.global.add.u32 %0, [%1], 1;" : "=r"(prev) : "l"(a.head_counters + kv_first + lane) : "memory");
-		const bool last = prev + 1 == (unsigned)sm_misc()[4 * lane];
-		sm_misc()[4 * lane + 3] = last ? 1 : 0;
-		if (last) a.head_counters[kv_first + lane] = 0; // every participant has arrived: ready for the next layer
+		asm volatile("atom.acq_rel.gpu.global.add.u32 %0, [%1], 1;" : "=r"(prev) : "l"(a.head_counters + kvh) : "memory");
+		const bool last = prev + 1 == (unsigned)cnt;
+		sm_misc()[0] = last ? 1 : 0;
+		if (last) a.head_counters[kvh] = 0; // every participant has arrived: ready for the next layer
 	}
 	cbar();
 	stamp(c, layer, 1, 6);
-	for (int h = 0; h < nh; ++h) {
-		if (!sm_misc()[4 * h + 3]) continue; // CTA-uniform
-		combine_head<HD, G>(a.ws_acc, a.ws_ml, a.att_out, wts, wsm, kv_first + h, ncta, nch, U, sm_misc()[4 * h + 1], sm_misc()[4 * h + 2],
+	if (sm_misc()[0]) // CTA-uniform
+		combine_head<HD, G>(a.ws_acc, a.ws_ml, a.att_out, wts, wsm, kvh, ncta, nch, sp.c0, sp.c0 + sp.nc - 1,
 		                    c.prof ? c.prof + ((size_t)layer * kProfPhases + 1) * kProfSlots + 4 : nullptr);
-		if (h + 1 < nh) cbar(); // wts / part are reused by the next head
-	}
 }
 
 __device__ __forceinline__ void derive_ring(int pos, int max_seq_len, int *kv_sink, int *kv_pos, int *kv_len) {
