@@ -814,7 +814,7 @@ template <int HD, int G>
 __device__ __forceinline__ void combine_head(const float *ws_acc, const float *ws_ml, float *att_out, float *wts, float *scratch,
                                           int kvh, int ncta, int nch, int b_lo, int b_hi, long long *probe) {
 	constexpr int W = kConsumerWarps;
-	constexpr int kInFlight = 16;  // independent L2 reads per thread and output
+	constexpr int kInFlight = 20;  // independent L2 reads per thread and output
 	const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 	const int nc = b_hi - b_lo + 1;
 	for (int g = warp; g < G; g += W) {
