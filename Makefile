@@ -1,6 +1,6 @@
 # yalm_b200 build: one shared library (kernels + C ABI + C++ API), plus the reference-shaped CLIs.
 #   make            -> yalm_b200/libyalm_b200.so
-#   make cli        -> build/main, build/test
+#   make cli        -> build/test (kernel benchmarks, the reference's `test -k <name>` command line)
 NVCC  ?= nvcc
 HOSTCXX := /usr/bin/g++
 ARCH  := -gencode arch=compute_100a,code=sm_100a
@@ -15,7 +15,7 @@ LIB_OBJS := $(patsubst $(CSRC)/%,$(BUILD)/%.o,$(LIB_SRCS))
 HDRS := $(wildcard $(CSRC)/*.h $(CSRC)/*.cuh include/*.h)
 
 all: lib
-cli: $(BUILD)/main $(BUILD)/test
+cli: $(BUILD)/test
 lib: $(LIB)
 
 $(BUILD)/%.cu.o: $(CSRC)/%.cu $(HDRS)
@@ -28,10 +28,6 @@ $(BUILD)/%.cpp.o: $(CSRC)/%.cpp $(HDRS)
 
 $(LIB): $(LIB_OBJS)
 	$(NVCC) $(ARCH) -ccbin $(HOSTCXX) -shared -o $@ $^ -lcudart -ldl -Xcompiler -fopenmp
-
-$(BUILD)/main: $(CSRC)/main.cpp $(CSRC)/sampler.cpp $(CSRC)/tokenizer.cpp $(LIB) $(HDRS)
-	$(NVCC) $(NVFLAGS) -x cu $(CSRC)/main.cpp $(CSRC)/sampler.cpp $(CSRC)/tokenizer.cpp -o $@ \
-	    -Lyalm_b200 -lyalm_b200 -Xlinker -rpath,'$$ORIGIN/../yalm_b200'
 
 $(BUILD)/test: $(CSRC)/test.cpp $(LIB) $(HDRS)
 	$(NVCC) $(NVFLAGS) -x cu $(CSRC)/test.cpp -o $@ -Lyalm_b200 -lyalm_b200 \

@@ -181,6 +181,12 @@ int yalm_mega_profile(yalm_model *m, yalm_state *s, int token, int pos, long lon
 int yalm_tp_unique_id(void *id128);
 int yalm_tp_init(const void *id128, int rank, int world);
 void yalm_tp_finalize(void);
+/* Shard arithmetic of the loader, callable without a device (tests): which bytes of an unsharded row-major tensor
+ * rank `rank` of `size` holds.  dims[7] = dim, hidden, head_dim, n_heads, n_kv_heads, vocab, bytes per weight;
+ * tensor: 0 wq, 1 wk, 2 wv, 3 wo, 4 w1, 5 w2, 6 w3, 7 wcls; out[4] = spitch, offset, width, height (bytes; `height`
+ * pieces of `width`, piece i at offset + i * spitch).  Column-parallel: wq wk wv w1 w3 wcls; row-parallel: wo w2
+ * (the reference is single-GPU). */
+int yalm_tp_shard_plan(const int *dims, int tensor, int rank, int size, long long *out);
 
 const char *yalm_error_string(int code);
 const char *yalm_version(void);

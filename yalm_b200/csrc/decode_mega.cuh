@@ -75,7 +75,14 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void *src, uint32_t
 }
 // Fire-and-forget L2 prefetch of a global range (no completion tracking, never blocks the issuing thread).
 __device__ __forceinline__ void bulk_prefetch_l2(const void *src, uint32_t bytes) {
+#ifdef YALM_PREFETCH_TMA
 	asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src), "r"(bytes) : "memory");
+#else
+	// per-line prefetches through the load/store unit: the bulk form goes through the copy engine, which then
+	// handles every byte twice (measured: slower than no prefetch at all)
+	const char *p = static_cast<const char *>(src);
+	for (uint32_t o = 0; o < bytes; o += 128) asm volatile("prefetch.global.L2 [%0];" ::"l"(p + o) : "memory");
+#endif
 }
 __device__ __forceinline__ uint64_t policy_evict_first() {
 	uint64_t p;
@@ -329,7 +336,8 @@ struct Producer {
 	Ctx &c;
 	uint64_t policy;
 	int batch; // min(stages, 32)
-	int ahead; // L2 look-ahead distance in tiles (0: off)
+	int ahead;   // L2 look-ahead distance in tiles (0: off)
+	bool steady; // false: only the next phase's prefix is fetched (during the phase-boundary bubble), nothing in-phase
 
 	__device__ __forceinline__ PhaseDesc describe(const Args &a, int ph, int rot, int HD, int B) {
 		PhaseDesc d;
@@ -500,8 +508,9 @@ struct Producer {
 				if (c.lane < nb && i < n_eff) {
 					const int unit = n > 0 ? tile(cur, i, c.it + (uint32_t)i, HD, a.max_seq_len, B) : i;
 					if (ahead > 0 && unit >= 0) {
-						if (unit + dist < nu) prefetch_unit(cur, unit + dist, HD, a.max_seq_len, B);
-						else
+						if (unit + dist < nu) {
+							if (steady) prefetch_unit(cur, unit + dist, HD, a.max_seq_len, B);
+						} else
 							for (int j = unit - max(0, nu - dist); j < npre; j += m) prefetch_unit(nxt, j, HD, a.max_seq_len, B);
 					}
 				}
@@ -1168,7 +1177,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_c
 
 	if (c.warp >= kConsumerWarps) {
 		// ================================ producers ================================
-		Producer p{c, (a.debug & 8) ? 0ull : policy_evict_first(), min(c.S, 32), (a.debug & 8) ? 0 : a.l2_ahead};
+		Producer p{c, (a.debug & 8) ? 0ull : policy_evict_first(), min(c.S, 32), (a.debug & 8) ? 0 : abs(a.l2_ahead), a.l2_ahead > 0};
 		p.run(a, HD, B);
 		return;
 	}

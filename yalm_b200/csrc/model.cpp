@@ -357,14 +357,19 @@ void Block::cuda() {
 	_rms_att_weight = (float *)up(_rms_att_weight, dim * 4, 0, dim * 4, 1);
 	_rms_ffn_weight = (float *)up(_rms_ffn_weight, dim * 4, 0, dim * 4, 1);
 	// column-parallel (rows of W): q/k/v by head, w1/w3 by hidden unit
-	_wq = up(_wq, lq * dim * B, r * lq * dim * B, lq * dim * B, 1);
-	_wk = up(_wk, lkv * dim * B, r * lkv * dim * B, lkv * dim * B, 1);
-	_wv = up(_wv, lkv * dim * B, r * lkv * dim * B, lkv * dim * B, 1);
-	_w1 = up(_w1, (size_t)c.hidden_dim * dim * B, r * lhid * dim * B, lhid * dim * B, E);
-	_w3 = up(_w3, (size_t)c.hidden_dim * dim * B, r * lhid * dim * B, lhid * dim * B, E);
+	const yalm::TpDims td{c.dim, c.hidden_dim, c.head_dim, c.n_heads, c.n_kv_heads, c.vocab_size, (int)B};
+	auto up_slice = [&](const void *h, int tensor, size_t repeat) { // `repeat` stacked experts
+		const yalm::TpSlice sl = yalm::tp_slice(td, tensor, c.tp_rank, c.tp_size);
+		return up(h, sl.spitch, sl.offset, sl.width, sl.height * repeat);
+	};
+	_wq = up_slice(_wq, yalm::kTpWq, 1);
+	_wk = up_slice(_wk, yalm::kTpWk, 1);
+	_wv = up_slice(_wv, yalm::kTpWv, 1);
+	_w1 = up_slice(_w1, yalm::kTpW1, E);
+	_w3 = up_slice(_w3, yalm::kTpW3, E);
 	// row-parallel (columns of W): wo over q_dim, w2 over hidden
-	_wo = up(_wo, q_dim * B, r * lq * B, lq * B, dim);
-	_w2 = up(_w2, (size_t)c.hidden_dim * B, r * lhid * B, lhid * B, E * dim);
+	_wo = up_slice(_wo, yalm::kTpWo, 1);
+	_w2 = up_slice(_w2, yalm::kTpW2, E);
 	if (c.n_experts > 0) _moegate = up(_moegate, E * dim * B, 0, E * dim * B, 1);
 	if (_sq) {
 		_sq = (float *)up(_sq, lq * 4, r * lq * 4, lq * 4, 1);
@@ -506,8 +511,8 @@ void Model::cuda() {
 void Model::cuda(int device, int tp_rank, int tp_size) {
 	if (_device != Device::CPU) return;
 	Config &c = *config;
-	if (tp_size < 1 || tp_rank < 0 || tp_rank >= tp_size || c.n_kv_heads % tp_size || c.n_heads % tp_size ||
-	    c.hidden_dim % tp_size || c.vocab_size % tp_size) {
+	const yalm::TpDims td{c.dim, c.hidden_dim, c.head_dim, c.n_heads, c.n_kv_heads, c.vocab_size, (int)dtype_size(c.weight_dtype)};
+	if (tp_size < 1 || tp_rank < 0 || tp_rank >= tp_size || !yalm::tp_shards(td, tp_size)) {
 		std::cerr << "FATAL: model does not shard " << tp_size << " ways (kv heads " << c.n_kv_heads << ", hidden "
 		          << c.hidden_dim << ", vocab " << c.vocab_size << ")" << std::endl;
 		abort();
@@ -527,7 +532,8 @@ void Model::cuda(int device, int tp_rank, int tp_size) {
 		wcls = static_cast<char *>(token_embedding_table) + (size_t)tp_rank * lv * dim * B;
 		wcls_scale = embed_scale ? embed_scale + (size_t)tp_rank * lv : nullptr;
 	} else {
-		wcls = upload_strided(_owned, _device_bytes, wcls, lv * dim * B, (size_t)tp_rank * lv * dim * B, lv * dim * B, 1);
+		const yalm::TpSlice sl = yalm::tp_slice(td, yalm::kTpWcls, tp_rank, tp_size);
+		wcls = upload_strided(_owned, _device_bytes, wcls, sl.spitch, sl.offset, sl.width, sl.height);
 		if (wcls_scale)
 			wcls_scale = (float *)upload_strided(_owned, _device_bytes, wcls_scale, lv * 4, (size_t)tp_rank * lv * 4, lv * 4, 1);
 	}

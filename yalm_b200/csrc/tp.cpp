@@ -119,3 +119,41 @@ extern "C" void yalm_tp_finalize(void) {
 	g_comm = nullptr;
 	g_rank = 0, g_world = 1;
 }
+
+// ---- shard arithmetic (pure; shared by the loader and the CPU tests) ---------------------------------------
+namespace yalm {
+
+bool tp_shards(const TpDims &d, int size) {
+	return size >= 1 && d.n_kv_heads % size == 0 && d.n_heads % size == 0 && d.hidden % size == 0 && d.vocab % size == 0;
+}
+
+TpSlice tp_slice(const TpDims &d, int tensor, int rank, int size) {
+	const size_t B = d.bytes_per_weight, T = size, r = rank, dim = d.dim, hid = d.hidden;
+	const size_t q_dim = (size_t)d.n_heads * d.head_dim, kv_dim = (size_t)d.n_kv_heads * d.head_dim;
+	const size_t lq = q_dim / T, lkv = kv_dim / T, lhid = hid / T, lv = (size_t)d.vocab / T;
+	switch (tensor) {
+	// column-parallel: whole output rows -> one contiguous piece (w1/w3: per expert, spitch = one expert)
+	case kTpWq: return {lq * dim * B, r * lq * dim * B, lq * dim * B, 1};
+	case kTpWk:
+	case kTpWv: return {lkv * dim * B, r * lkv * dim * B, lkv * dim * B, 1};
+	case kTpW1:
+	case kTpW3: return {hid * dim * B, r * lhid * dim * B, lhid * dim * B, 1};
+	case kTpWcls: return {lv * dim * B, r * lv * dim * B, lv * dim * B, 1};
+	// row-parallel: a column range of every output row
+	case kTpWo: return {q_dim * B, r * lq * B, lq * B, dim};
+	case kTpW2: return {hid * B, r * lhid * B, lhid * B, dim};
+	default: return {0, 0, 0, 0};
+	}
+}
+
+} // namespace yalm
+
+// dims[7]: dim, hidden, head_dim, n_heads, n_kv_heads, vocab, bytes per weight.  out[4]: spitch, offset, width, height.
+extern "C" int yalm_tp_shard_plan(const int *dims, int tensor, int rank, int size, long long *out) {
+	if (!dims || !out || tensor < 0 || tensor >= yalm::kTpTensors || rank < 0 || rank >= size) return YALM_EINVAL;
+	const yalm::TpDims d{dims[0], dims[1], dims[2], dims[3], dims[4], dims[5], dims[6]};
+	if (!yalm::tp_shards(d, size)) return YALM_EINVAL;
+	const yalm::TpSlice s = yalm::tp_slice(d, tensor, rank, size);
+	out[0] = (long long)s.spitch, out[1] = (long long)s.offset, out[2] = (long long)s.width, out[3] = (long long)s.height;
+	return 0;
+}
