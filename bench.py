@@ -135,7 +135,21 @@ def run_reference(args, arch, dtype, context, desc):
                       f"{'oracle/_ref (unmodified reference, OpenMP)' if kind == 'reference' else 'oracle C port'}"}, dt
 
 
+def _emit(line):
+    """The one JSON line of the contract, on the real stdout (see main: fd 1 is pointed at stderr meanwhile)."""
+    os.write(_REAL_STDOUT, (json.dumps(line) + "\n").encode())
+
+
+_REAL_STDOUT = 1
+
+
 def main():
+    # Native libraries (the loader's log line, NCCL's version banner, the reference's spdlog) write to fd 1:
+    # keep a private copy of stdout for the JSON line and send everything else to stderr.
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=128)
@@ -168,7 +182,7 @@ def main():
         line = dict(base, impl="reference", n_gpus=world, value=cb["value"], ms_per_step=1000 * dt / args.steps,
                     cpu_baseline=cb, gpu_launches=0,
                     e2e={"value": cb["value"], "unit": "tok/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0})
-        print(json.dumps(line))
+        _emit(line)
         return
 
     import torch
@@ -282,7 +296,7 @@ def main():
                                 "frac_of_nominal_8TBs_weights": wbytes * tok_s / 8e12 / world,
                                 "kv_len_range": [pos - K, pos]},
                     setup_s={"generate": round(t_gen, 1), "load_upload": round(t_load, 1)})
-        print(json.dumps(line))
+        _emit(line)
     state.close()
     model.close()
     if world > 1:
