@@ -604,22 +604,33 @@ __device__ __forceinline__ float4 load_in4(const Args &a, const float *src, int 
 	                   WTraits<DT>::to_float(a.embed, base + 2) * sc, WTraits<DT>::to_float(a.embed, base + 3) * sc);
 }
 
+// The norm weights were last touched a token ago (14 GB of evict-first traffic since): they are loaded before the
+// grid barrier, so that their DRAM latency hides behind the barrier instead of following it.
+constexpr int kNormCache = 4;
+__device__ __forceinline__ void load_norm_weights(const Ctx &c, const float *rms_w, int n, float4 (&wv)[kNormCache]) {
+#pragma unroll
+	for (int i = 0; i < kNormCache; ++i) {
+		const int e = (c.tid + i * kCT) * 4;
+		wv[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+		if (rms_w && e < n) wv[i] = *reinterpret_cast<const float4 *>(rms_w + e);
+	}
+}
+
+// `wv`: this thread's norm weights (load_norm_weights), fetched before the grid barrier.
 template <int DT>
-__device__ __forceinline__ void stage_vec(Ctx &c, const Args &a, const float *src, int n, const float *rms_w, int embed_token) {
+__device__ __forceinline__ void stage_vec(Ctx &c, const Args &a, const float *src, int n, const float *rms_w, int embed_token,
+                                          const float4 (&wv)[kNormCache]) {
 	constexpr int EP = WTraits<DT>::EP;
-	constexpr int NC = 4; // float4 per thread kept in registers between the two rmsnorm passes (n <= 4096)
+	constexpr int NC = kNormCache; // float4 per thread kept in registers between the two rmsnorm passes (n <= 4096)
 	if (rms_w) {
 		// reference formula and association order (src/infer.cpp:134-144): o = x * (1/sqrt(ss/n + eps)) * w
-		float4 cache[NC], wv[NC];
+		float4 cache[NC];
 		float ss = 0.f;
 #pragma unroll
 		for (int i = 0; i < NC; ++i) {
 			const int e = (c.tid + i * kCT) * 4;
-			cache[i] = make_float4(0.f, 0.f, 0.f, 0.f), wv[i] = cache[i];
-			if (e < n) {
-				cache[i] = load_in4<DT>(a, src, embed_token, e);
-				wv[i] = *reinterpret_cast<const float4 *>(rms_w + e);
-			}
+			cache[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+			if (e < n) cache[i] = load_in4<DT>(a, src, embed_token, e);
 		}
 #pragma unroll
 		for (int i = 0; i < NC; ++i)
@@ -1191,6 +1202,9 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_c
 		const Layer &L = a.layers[l];
 		ep.L = &L;
 		stamp(c, l, k, 0);
+		const float *rms = k == 0 ? L.rms_att : k == 3 ? L.rms_ffn : k == 5 ? a.rms_final : nullptr;
+		float4 wv[kNormCache];
+		load_norm_weights(c, rms, a.dim, wv); // in flight across the barrier
 		if (ph > 0) grid_barrier(c, a.sync);
 		stamp(c, l, k, 1);
 		if (k == 1) { // attention: q comes from registers, nothing to stage
@@ -1199,16 +1213,16 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_c
 			stamp(c, l, k, 3);
 			continue;
 		}
-		const float *src = a.x, *rms = nullptr;
+		const float *src = a.x;
 		int n = a.dim;
 		switch (k) {
-		case 0: rms = L.rms_att, ep.kind = kQKV, ep.scale0 = L.sq, ep.scale1 = L.sk, ep.scale2 = L.sv, ep.rows0 = a.q_dim, ep.rows1 = a.kv_dim; break;
+		case 0: ep.kind = kQKV, ep.scale0 = L.sq, ep.scale1 = L.sk, ep.scale2 = L.sv, ep.rows0 = a.q_dim, ep.rows1 = a.kv_dim; break;
 		case 2: src = a.att_out, n = a.q_dim, ep.kind = kWO, ep.scale0 = L.so; break;
-		case 3: rms = L.rms_ffn, ep.kind = kFFN, ep.scale0 = L.s1, ep.scale1 = L.s3; break;
+		case 3: ep.kind = kFFN, ep.scale0 = L.s1, ep.scale1 = L.s3; break;
 		case 4: src = a.hb, n = a.hidden, ep.kind = kW2, ep.scale0 = L.s2; break;
-		default: rms = a.rms_final, ep.kind = kLM, ep.scale0 = a.wcls_scale; break;
+		default: ep.kind = kLM, ep.scale0 = a.wcls_scale; break;
 		}
-		stage_vec<DT>(c, a, src, n, rms, ph == 0 ? c.token : -1);
+		stage_vec<DT>(c, a, src, n, rms, ph == 0 ? c.token : -1, wv);
 		stamp(c, l, k, 2);
 		if (k == 0 && c.kv_sink > 0 && c.cta == c.ncta - 1) {
 			// rotate each sink key forward by one position, fp16 -> fp32 -> fp16 (src/infer.cpp:303-317)
