@@ -277,7 +277,9 @@ def main():
         if mega:
             # one persistent kernel per token IS the step: algorithmic bytes = weights + KV rows it reads
             kname = "decode_mega_kernel (whole token: all GEMVs + flash-decode + LM head, TMA ring)"
-            ffn_bytes = wbytes + yf.kv_bytes_per_token(arch, min(context, pos - K // 2))
+            ffn_bytes = (wbytes + yf.kv_bytes_per_token(arch, min(context, pos - K // 2))) / world   # this rank's shard
+            if world > 1:
+                kname += f", tp{world}: all-reduce fused into the wo/w2 epilogues over NVLink peer memory"
             ffn_us = 1000.0 * dev_ms / K
         else:
             kname = "ffn_glu_kernel (rmsnorm + w1/w3 GEMV + GLU)"

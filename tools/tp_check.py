@@ -38,7 +38,7 @@ def main():
         toks, lg = s.generate(fx["prompt"].tolist(), len(fx["tokens"]), keep_logits=True)
         err = float(np.abs(lg[fx["keep"]] - fx["logits"]).max())
         ok = err < LOGIT_TOL and toks == fx["tokens"].tolist()
-        print(f"rank {rank}/{world} {name}: max |dlogit| {err:.2e} tokens {'identical' if toks == fx['tokens'].tolist() else 'DIFFER'} -> {'PASS' if ok else 'FAIL'}", flush=True)
+        print(f"rank {rank}/{world} mega={int(m.uses_megakernel())} {name}: max |dlogit| {err:.2e} tokens {'identical' if toks == fx['tokens'].tolist() else 'DIFFER'} -> {'PASS' if ok else 'FAIL'}", flush=True)
         bad += 0 if ok else 1
         s.close()
         m.close()

@@ -70,28 +70,30 @@ size_t attn_ws_floats(int grid, int n_heads, int head_dim) {
 	return (size_t)grid * n_heads * (head_dim + 2);
 }
 
-const void *kernel_f32(int head_dim, int g);
-const void *kernel_f16(int head_dim, int g);
-const void *kernel_f8(int head_dim, int g);
+const void *kernel_f32(int head_dim, int g, bool tp);
+const void *kernel_f16(int head_dim, int g, bool tp);
+const void *kernel_f8(int head_dim, int g, bool tp);
 
-static const void *kernel_of(int dtype, int head_dim, int g) {
+static const void *kernel_of(int dtype, int head_dim, int g, bool tp) {
 	switch (dtype) {
-	case YALM_F32: return kernel_f32(head_dim, g);
-	case YALM_F16: return kernel_f16(head_dim, g);
-	case YALM_F8E4M3: return kernel_f8(head_dim, g);
+	case YALM_F32: return kernel_f32(head_dim, g, tp);
+	case YALM_F16: return kernel_f16(head_dim, g, tp);
+	case YALM_F8E4M3: return kernel_f8(head_dim, g, tp);
 	}
 	return nullptr;
 }
 
 Plan plan(int dtype, int dim, int q_dim, int kv_dim, int head_dim, int hidden, int vocab, int n_heads, int n_kv_heads,
-          int n_experts, int n_active, int max_seq_len) {
+          int n_experts, int n_active, int max_seq_len, bool tp, int full_vocab) {
 	Plan p;
+	if (tp && (dim > kTpCapFloats || full_vocab > kTpMaxVocab)) return p;
+	p.tp = tp;
 	const int ep = ep_of(dtype), B = bytes_of(dtype);
 	if (!ep || n_experts > 0) return p;
 	(void)n_active;
 	if (n_kv_heads <= 0 || n_heads % n_kv_heads) return p;
 	const int G = n_heads / n_kv_heads;
-	p.kernel = kernel_of(dtype, head_dim, G);
+	p.kernel = kernel_of(dtype, head_dim, G, tp);
 	if (!p.kernel) return p;
 	if (dim % ep || q_dim % ep || hidden % ep || dim % 4 || q_dim % 4 || hidden % 4) return p;
 	Shape s[kNumKinds];
@@ -109,6 +111,7 @@ Plan plan(int dtype, int dim, int q_dim, int kv_dim, int head_dim, int hidden, i
 	cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
 	if (!coop || di.sms < 1) return p;
 	p.grid = di.sms;
+	if (tp && p.grid > kTpMaxGrid) return p;
 	int vf = std::max(padded(dim, ep), std::max(padded(q_dim, ep), padded(hidden, ep)));
 	if (n_kv_heads > p.grid) return p; // a CTA's attention units must span at most kHeadSlots KV heads
 	// the attention unit split runs in 32-bit arithmetic: (units) x (grid + 1) must stay below 2^31

@@ -233,6 +233,7 @@ struct Ctx {
 	uint32_t it; // ring index of the next tile of this role (same sequence for the producer and every consumer warp)
 	int rot;     // CTA rotation of the current GEMV phase
 	unsigned bar_gen;
+	unsigned xgen; // cross-GPU barriers passed, earlier launches included (tensor parallelism)
 	int token, pos, kv_sink, kv_pos, kv_len;
 };
 
@@ -554,6 +555,34 @@ __device__ __forceinline__ void grid_barrier(Ctx &c, unsigned *sync) {
 	cbar();
 }
 
+// Cross-GPU barrier of a tensor-parallel group: every CTA of every rank adds 1 to the arrival counter in EVERY rank's
+// region (NVLink atomics, fire and forget) and waits until its own region has seen all world * ncta arrivals of this
+// generation.  It is also the local grid barrier of the phase boundary.  The fence + relaxed atomics are a release at
+// system scope: the partial rows this CTA pushed into the peers' slots are visible before its arrival is.
+constexpr long long kTpTimeoutCycles = 120000000000ll; // ~60 s: ranks may enter a launch seconds apart; a lost peer traps
+__device__ __forceinline__ void tp_barrier(Ctx &c, const Args &a) {
+	++c.xgen;
+	cbar();
+	if (c.tid == 0) {
+		asm volatile("fence.acq_rel.sys;" ::: "memory");
+		for (int r = 0; r < a.tp_world; ++r)
+			asm volatile("red.relaxed.sys.global.add.u32 [%0], 1;" ::"l"(a.tp_peer[r] + kTpOffBar) : "memory");
+		const unsigned target = c.xgen * (unsigned)(c.ncta * a.tp_world);
+		const char *mine = a.tp_peer[a.tp_rank] + kTpOffBar;
+		unsigned v;
+		asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(mine) : "memory");
+		if ((int)(v - target) < 0) {
+			const long long t0 = clock64();
+			do {
+				asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(mine) : "memory");
+				if (clock64() - t0 > kTpTimeoutCycles) __trap();
+			} while ((int)(v - target) < 0);
+		}
+		asm volatile("fence.acq_rel.sys;" ::: "memory");
+	}
+	cbar();
+}
+
 // Wait until ring tile `idx` has landed; returns its shared-memory address.
 __device__ __forceinline__ const unsigned char *wait_tile(Ctx &c, uint32_t idx, uint32_t *slot) {
 	uint32_t s;
@@ -595,8 +624,20 @@ __device__ __forceinline__ void release(Ctx &c, uint32_t idx) {
 
 // Input vector -> permuted shared layout (xs_slot).  embed_token < 0: fp32 vector in global memory (read through
 // L2: other CTAs wrote it during this launch); >= 0: that row of the weight-typed embedding table (layer 0).
+// tp_slots != null: the vector is the residual `src` plus every rank's partial (slot r at tp_slots + r * kTpCapFloats),
+// added in rank order — the same bits on every rank.
 template <int DT>
-__device__ __forceinline__ float4 load_in4(const Args &a, const float *src, int embed_token, int e) {
+__device__ __forceinline__ float4 load_in4(const Args &a, const float *src, int embed_token, int e, const float *tp_slots = nullptr) {
+	if (tp_slots) {
+		float4 v = __ldcg(reinterpret_cast<const float4 *>(src + e));
+		for (int r0 = 0; r0 < a.tp_world; r0 += 2) { // world sizes are 2, 4, 8: two loads in flight per thread and float4
+			const float4 p0 = __ldcg(reinterpret_cast<const float4 *>(tp_slots + (size_t)r0 * kTpCapFloats + e));
+			const float4 p1 = __ldcg(reinterpret_cast<const float4 *>(tp_slots + (size_t)(r0 + 1) * kTpCapFloats + e));
+			v.x += p0.x, v.y += p0.y, v.z += p0.z, v.w += p0.w;
+			v.x += p1.x, v.y += p1.y, v.z += p1.z, v.w += p1.w;
+		}
+		return v;
+	}
 	if (embed_token < 0) return __ldcg(reinterpret_cast<const float4 *>(src + e));
 	const size_t base = (size_t)embed_token * a.dim + e;
 	const float sc = (DT == YALM_F8E4M3 && a.embed_scale) ? a.embed_scale[embed_token] : 1.0f;
@@ -619,7 +660,7 @@ __device__ __forceinline__ void load_norm_weights(const Ctx &c, const float *rms
 // `wv`: this thread's norm weights (load_norm_weights), fetched before the grid barrier.
 template <int DT>
 __device__ __forceinline__ void stage_vec(Ctx &c, const Args &a, const float *src, int n, const float *rms_w, int embed_token,
-                                          const float4 (&wv)[kNormCache]) {
+                                          const float4 (&wv)[kNormCache], const float *tp_slots = nullptr, float *x_out = nullptr) {
 	constexpr int EP = WTraits<DT>::EP;
 	constexpr int NC = kNormCache; // float4 per thread kept in registers between the two rmsnorm passes (n <= 4096)
 	if (rms_w) {
@@ -630,18 +671,21 @@ __device__ __forceinline__ void stage_vec(Ctx &c, const Args &a, const float *sr
 		for (int i = 0; i < NC; ++i) {
 			const int e = (c.tid + i * kCT) * 4;
 			cache[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-			if (e < n) cache[i] = load_in4<DT>(a, src, embed_token, e);
+			if (e < n) cache[i] = load_in4<DT>(a, src, embed_token, e, tp_slots);
 		}
 #pragma unroll
 		for (int i = 0; i < NC; ++i)
 			ss += cache[i].x * cache[i].x + cache[i].y * cache[i].y + cache[i].z * cache[i].z + cache[i].w * cache[i].w;
 		for (int e = (c.tid + NC * kCT) * 4; e < n; e += kCT * 4) {
-			const float4 v = load_in4<DT>(a, src, embed_token, e);
+			const float4 v = load_in4<DT>(a, src, embed_token, e, tp_slots);
 			ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
 		}
 		ss = cons_sum(c, ss);
 		const float scale = 1.0f / sqrtf(ss / n + a.eps);
-		const bool seed_x = embed_token >= 0 && c.cta == 0; // layer 0: the residual stream starts as the embedding row
+		// layer 0: the residual stream starts as the embedding row; after an in-kernel all-reduce: the reduced vector
+		// becomes the new residual (written to the other x buffer: CTAs still staging read the old one)
+		const bool seed_x = (embed_token >= 0 || tp_slots) && c.cta == 0;
+		if (!x_out) x_out = a.x;
 #pragma unroll
 		for (int i = 0; i < NC; ++i) {
 			const int e = (c.tid + i * kCT) * 4;
@@ -649,15 +693,15 @@ __device__ __forceinline__ void stage_vec(Ctx &c, const Args &a, const float *sr
 				const float4 v = cache[i], w = wv[i];
 				*reinterpret_cast<float4 *>(c.vec + xs_slot<EP>(e)) =
 				    make_float4(v.x * scale * w.x, v.y * scale * w.y, v.z * scale * w.z, v.w * scale * w.w);
-				if (seed_x) *reinterpret_cast<float4 *>(a.x + e) = v;
+				if (seed_x) *reinterpret_cast<float4 *>(x_out + e) = v;
 			}
 		}
 		for (int e = (c.tid + NC * kCT) * 4; e < n; e += kCT * 4) {
-			const float4 v = load_in4<DT>(a, src, embed_token, e);
+			const float4 v = load_in4<DT>(a, src, embed_token, e, tp_slots);
 			const float4 w = *reinterpret_cast<const float4 *>(rms_w + e);
 			*reinterpret_cast<float4 *>(c.vec + xs_slot<EP>(e)) =
 			    make_float4(v.x * scale * w.x, v.y * scale * w.y, v.z * scale * w.z, v.w * scale * w.w);
-			if (seed_x) *reinterpret_cast<float4 *>(a.x + e) = v;
+			if (seed_x) *reinterpret_cast<float4 *>(x_out + e) = v;
 		}
 	} else {
 		int e = c.tid * 4;
@@ -687,7 +731,7 @@ struct Epi {
 // All row groups of one GEMV phase owned by this CTA; the input vector is already staged in c.vec.
 // Warp w owns groups w, w+8, ... of the CTA's list: it adds up all K-split tiles of the group, shuffle-reduces,
 // and its first lanes run the epilogue.  Nothing here synchronises with the other warps.
-template <int DT, int R>
+template <int DT, int R, bool TP>
 __device__ __forceinline__ void gemv_consume(Ctx &c, const Args &a, Epi &ep) {
 	using T = WTraits<DT>;
 	constexpr int EP = T::EP, CH = 32 * EP, Q = EP / 4;
@@ -705,7 +749,7 @@ __device__ __forceinline__ void gemv_consume(Ctx &c, const Args &a, Epi &ep) {
 		const int g = g_first + (b8 + warp) * c.ncta;
 		// residual operand of the wo / w2 epilogue: issue the L2 read now, it is consumed after the tiles
 		float resid = 0.f;
-		if ((kind == kWO || kind == kW2) && lane < R) resid = __ldcg(a.x + (long)g * R + lane);
+		if (!TP && (kind == kWO || kind == kW2) && lane < R) resid = __ldcg(a.x + (long)g * R + lane);
 		float2 acc2[R];
 #pragma unroll
 		for (int r = 0; r < R; ++r) acc2[r] = make_float2(0.f, 0.f);
@@ -792,6 +836,33 @@ __device__ __forceinline__ void gemv_consume(Ctx &c, const Args &a, Epi &ep) {
 				gt = a.act == YALM_ACT_GELU ? act_gelu(gt) : act_silu(gt);
 				a.hb[row] = gt * up;
 			}
+		} else if (TP) {
+			// tensor parallel: the rows are partial sums (wo / w2: this rank's slice of the input dimension) or this
+			// rank's slice of the vocabulary.  Every lane holds all R sums, so lane r hands the group's R values to
+			// rank r — one vector store per peer over NVLink — into slot [set][rank] or the gathered logits.
+			const long row0 = (long)g * R;
+			float vv[R];
+#pragma unroll
+			for (int r = 0; r < R; ++r) {
+				vv[r] = acc[r];
+				if (DT == YALM_F8E4M3 && ep.scale0) vv[r] *= ep.scale0[row0 + r];
+			}
+			if (kind == kLM && t < R) {
+				float v = vv[0];
+#pragma unroll
+				for (int r = 1; r < R; ++r)
+					if (t == r) v = vv[r];
+				const int row = a.vocab_base + (int)row0 + t;
+				if (v > ep.best_v) ep.best_v = v, ep.best_i = row;
+			}
+			if (lane < a.tp_world) {
+				float *dst = kind == kLM ? reinterpret_cast<float *>(a.tp_peer[lane] + kTpOffLogits) + a.vocab_base + row0
+				                         : reinterpret_cast<float *>(a.tp_peer[lane] + kTpOffSlots) +
+				                               (size_t)((kind == kW2 ? a.tp_world : 0) + a.tp_rank) * kTpCapFloats + row0;
+				if (R == 4) *reinterpret_cast<float4 *>(dst) = make_float4(vv[0], vv[R > 1 ? 1 : 0], vv[R > 2 ? 2 : 0], vv[R > 3 ? 3 : 0]);
+				else if (R == 2) *reinterpret_cast<float2 *>(dst) = make_float2(vv[0], vv[R > 1 ? 1 : 0]);
+				else dst[0] = vv[0];
+			}
 		} else if (t < R) {
 			float v = acc[0];
 #pragma unroll
@@ -811,12 +882,12 @@ __device__ __forceinline__ void gemv_consume(Ctx &c, const Args &a, Epi &ep) {
 	c.rot = (c.rot + sh.G) % c.ncta;
 }
 
-template <int DT>
+template <int DT, bool TP>
 __device__ __forceinline__ void gemv_phase(Ctx &c, const Args &a, Epi &ep) {
 	const int R = a.shape[ep.kind][0];
-	if (R == 4) gemv_consume<DT, 4>(c, a, ep);
-	else if (R == 2) gemv_consume<DT, 2>(c, a, ep);
-	else gemv_consume<DT, 1>(c, a, ep);
+	if (R == 4) gemv_consume<DT, 4, TP>(c, a, ep);
+	else if (R == 2) gemv_consume<DT, 2, TP>(c, a, ep);
+	else gemv_consume<DT, 1, TP>(c, a, ep);
 }
 
 // ---- attention --------------------------------------------------------------------------------------------
@@ -1147,7 +1218,7 @@ __device__ __forceinline__ void derive_ring(int pos, int max_seq_len, int *kv_si
 }
 
 // ---- the kernel -----------------------------------------------------------------------------------------
-template <int DT, int HD, int G>
+template <int DT, int HD, int G, bool TP>
 __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_constant__ Args a) {
 	using T = WTraits<DT>;
 	constexpr int B = T::BYTES;
@@ -1159,6 +1230,8 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_c
 	c.cta = blockIdx.x, c.ncta = gridDim.x;
 	c.tid = threadIdx.x, c.warp = threadIdx.x >> 5, c.lane = threadIdx.x & 31;
 	c.it = 0, c.rot = 0, c.bar_gen = 0;
+	c.xgen = 0;
+	if (TP) c.xgen = *reinterpret_cast<const volatile unsigned *>(a.tp_peer[a.tp_rank] + kTpOffGen); // written by the previous launch
 	c.prof = a.prof ? a.prof + (size_t)blockIdx.x * a.n_layers * kProfPhases * kProfSlots : nullptr;
 	c.wait_cycles = 0;
 	c.debug = a.debug;
@@ -1205,7 +1278,10 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_c
 		const float *rms = k == 0 ? L.rms_att : k == 3 ? L.rms_ffn : k == 5 ? a.rms_final : nullptr;
 		float4 wv[kNormCache];
 		load_norm_weights(c, rms, a.dim, wv); // in flight across the barrier
-		if (ph > 0) grid_barrier(c, a.sync);
+		// tensor parallel: the boundaries behind wo (k == 3) and w2 (k == 0 of the next layer, k == 5) span the GPUs
+		const bool reduced = TP && ph > 0 && (k == 3 || k == 0 || k == 5);
+		if (reduced) tp_barrier(c, a);
+		else if (ph > 0) grid_barrier(c, a.sync);
 		stamp(c, l, k, 1);
 		if (k == 1) { // attention: q comes from registers, nothing to stage
 			stamp(c, l, k, 2);
@@ -1222,7 +1298,14 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_c
 		case 4: src = a.hb, n = a.hidden, ep.kind = kW2, ep.scale0 = L.s2; break;
 		default: ep.kind = kLM, ep.scale0 = a.wcls_scale; break;
 		}
-		stage_vec<DT>(c, a, src, n, rms, ph == 0 ? c.token : -1, wv);
+		if (reduced) {
+			// x ping-pongs: behind wo the residual is x and the sum goes to x2, behind w2 the other way round
+			const float *slots = reinterpret_cast<const float *>(a.tp_peer[a.tp_rank] + kTpOffSlots) +
+			                     (size_t)(k == 3 ? 0 : a.tp_world) * kTpCapFloats;
+			stage_vec<DT>(c, a, k == 3 ? a.x : a.x2, n, rms, -1, wv, slots, k == 3 ? a.x2 : a.x);
+		} else {
+			stage_vec<DT>(c, a, src, n, rms, ph == 0 ? c.token : -1, wv);
+		}
 		stamp(c, l, k, 2);
 		if (k == 0 && c.kv_sink > 0 && c.cta == c.ncta - 1) {
 			// rotate each sink key forward by one position, fp16 -> fp32 -> fp16 (src/infer.cpp:303-317)
@@ -1235,7 +1318,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_c
 				*ptr = __floats2half2_rn(v.x, v.y);
 			}
 		}
-		gemv_phase<DT>(c, a, ep);
+		gemv_phase<DT, TP>(c, a, ep);
 		stamp(c, l, k, 3);
 	}
 	if (a.mode == kGreedy) {
@@ -1254,11 +1337,31 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_c
 			bv = sm_red()[0], bi = sm_misc()[4];
 			for (int t = 1; t < kConsumerWarps; ++t)
 				if (sm_red()[t] > bv || (sm_red()[t] == bv && sm_misc()[4 + t] < bi)) bv = sm_red()[t], bi = sm_misc()[4 + t];
-			a.amax_val[c.cta] = bv, a.amax_idx[c.cta] = bi;
+			if (!TP) a.amax_val[c.cta] = bv, a.amax_idx[c.cta] = bi;
+			sm_red()[0] = bv, sm_misc()[4] = bi;
 		}
-		grid_barrier(c, a.sync);
+		if (TP) { // the CTA's candidate goes to every rank: each reduces all world * ncta of them to the same token
+			cbar();
+			if (c.tid < a.tp_world) {
+				char *peer = a.tp_peer[c.tid];
+				reinterpret_cast<float *>(peer + kTpOffAmaxV)[a.tp_rank * kTpMaxGrid + c.cta] = sm_red()[0];
+				reinterpret_cast<int *>(peer + kTpOffAmaxI)[a.tp_rank * kTpMaxGrid + c.cta] = sm_misc()[4];
+			}
+			tp_barrier(c, a); // also: every rank's logits rows have landed here
+		} else {
+			grid_barrier(c, a.sync);
+		}
 		if (c.cta == 0 && c.warp == 0) {
 			bv = -FLT_MAX, bi = 0x7fffffff;
+			if (TP) {
+				const char *mine = a.tp_peer[a.tp_rank];
+				for (int b = c.lane; b < c.ncta * a.tp_world; b += 32) {
+					const int at = b / c.ncta * kTpMaxGrid + b % c.ncta;
+					const float v = __ldcg(reinterpret_cast<const float *>(mine + kTpOffAmaxV) + at);
+					const int i = __ldcg(reinterpret_cast<const int *>(mine + kTpOffAmaxI) + at);
+					if (v > bv || (v == bv && i < bi)) bv = v, bi = i;
+				}
+			} else
 			for (int b = c.lane; b < c.ncta; b += 32) {
 				const float v = __ldcg(a.amax_val + b);
 				const int i = __ldcg(a.amax_idx + b);
@@ -1283,6 +1386,9 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_c
 			}
 		}
 	}
+	// every launch ends on a cross-GPU barrier (greedy: the one above): all ranks' logits rows have landed in this
+	// rank's region, and no rank starts pushing the next token's partials while another still reads this token's
+	if (TP && a.mode != kGreedy) tp_barrier(c, a);
 	// ---- leave the barrier words zeroed for the next launch ------------------------------------------
 	cbar();
 	if (c.tid == 0) {
@@ -1291,6 +1397,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_c
 		if (prev + 1 == (unsigned)c.ncta) {
 			a.sync[0] = 0;
 			a.sync[1] = 0;
+			if (TP) *reinterpret_cast<unsigned *>(a.tp_peer[a.tp_rank] + kTpOffGen) = c.xgen;
 			__threadfence();
 		}
 	}
@@ -1298,9 +1405,10 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_c
 
 // (head_dim, q heads per kv head) combinations compiled; others use the per-op kernel path.
 template <int DT>
-inline const void *kernel_for(int head_dim, int g) {
+inline const void *kernel_for(int head_dim, int g, bool tp) {
 #define YALM_MEGA_CASE(HD, GG)                                                                                \
-	if (head_dim == HD && g == GG) return (const void *)decode_mega_kernel<DT, HD, GG>;
+	if (head_dim == HD && g == GG)                                                                            \
+		return tp ? (const void *)decode_mega_kernel<DT, HD, GG, true> : (const void *)decode_mega_kernel<DT, HD, GG, false>;
 	YALM_MEGA_CASE(128, 4) YALM_MEGA_CASE(128, 8) YALM_MEGA_CASE(64, 4) YALM_MEGA_CASE(32, 4) YALM_MEGA_CASE(32, 2)
 #undef YALM_MEGA_CASE
 	return nullptr;

@@ -3,8 +3,8 @@
 
 namespace yalm {
 namespace mega {
-const void *kernel_f32(int head_dim, int g) {
-	return kernel_for<YALM_F32>(head_dim, g);
+const void *kernel_f32(int head_dim, int g, bool tp) {
+	return kernel_for<YALM_F32>(head_dim, g, tp);
 }
 } // namespace mega
 } // namespace yalm

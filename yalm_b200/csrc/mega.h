@@ -22,6 +22,24 @@ constexpr int kSmemHeader = 1280; // rope table, reduction scratch, release coun
 constexpr int kTraceEvents = 1 << 16;
 constexpr int kProfileSlots = 6 * 8; // per (CTA, layer): phases x slots, see decode_mega.cuh
 
+// ---- tensor parallelism inside the kernel (N GPUs of one NVSwitch domain) ---------------------------------------------
+// Every rank owns one region of device memory that all peers map (CUDA IPC, tp.cpp).  The wo / w2 epilogues push
+// their partial rows of x into slot [set][rank] of EVERY rank's region with plain stores over NVLink, the phase
+// boundary that follows is a cross-GPU barrier (one counter per region, every CTA of every rank adds 1 to each), and
+// the next phase's staging step sums the slots in rank order on top of the residual — the all-reduce has no kernel of
+// its own and no second pass over the data.  The LM head scatters its logits rows and arg-max candidates the same way.
+constexpr int kTpMaxWorld = 8;
+constexpr int kTpCapFloats = 8192;  // largest dim
+constexpr int kTpMaxGrid = 256;     // CTAs per rank (arg-max candidates)
+constexpr int kTpMaxVocab = 1 << 17;
+constexpr size_t kTpOffGen = 0;     // u32: cross-GPU barriers completed by earlier launches (same on every rank)
+constexpr size_t kTpOffBar = 128;   // u32: arrival counter, monotonic (wrap-safe compare)
+constexpr size_t kTpOffSlots = 1024; // float [2 sets][world][kTpCapFloats]
+constexpr size_t kTpOffAmaxV = kTpOffSlots + 2ull * kTpMaxWorld * kTpCapFloats * 4; // float [world][kTpMaxGrid]
+constexpr size_t kTpOffAmaxI = kTpOffAmaxV + (size_t)kTpMaxWorld * kTpMaxGrid * 4;   // int   [world][kTpMaxGrid]
+constexpr size_t kTpOffLogits = kTpOffAmaxI + (size_t)kTpMaxWorld * kTpMaxGrid * 4;  // float [vocab], all ranks' rows
+constexpr size_t kTpRegionBytes = kTpOffLogits + (size_t)kTpMaxVocab * 4;
+
 // Per-layer device pointers (weights are (out,in) row-major; KV cache is head-major, see yalm_b200.h).
 struct Layer {
 	const char *wq, *wk, *wv, *wo, *w1, *w2, *w3, *gate;
@@ -61,19 +79,26 @@ struct Args {
 	int debug;       // timing experiments only (YALM_MEGA_DEBUG): 1 skip GEMV math, 4 skip attention math, 8 no copies
 	long long *trace; // optional event trace of CTA 0: [0] count, then kTraceEvents (tag, clock) pairs; null = off
 	long long *prof; // optional phase profile, (grid, n_layers, 6 phases, 8 slots) clock64 values; null = off
+	// tensor parallelism (tp_world > 1: every dimension above is this rank's local share, dim excepted)
+	int tp_world, tp_rank;
+	int vocab_base;             // first vocabulary row of this rank
+	float *x2;                  // second residual buffer (x ping-pongs across the in-kernel all-reduces)
+	char *tp_peer[kTpMaxWorld]; // every rank's region (kTpOff*), [tp_rank] = this rank's own
 };
 
 struct Plan {
 	bool ok = false;
 	int dtype = 0, grid = 0, stages = 0, vec_floats = 0;
+	bool tp = false;
 	size_t smem = 0;
 	const void *kernel = nullptr;
 	int shape[5][4] = {};
 };
 
-// Can this (unsharded, dense or MoE) model shape run on the megakernel on the current device?
+// Can this model shape run on the megakernel on the current device?  Under tensor parallelism (`tp`) the dimensions
+// are the rank's local shares (q_dim, kv_dim, hidden, vocab, heads) and `full_vocab` the unsharded vocabulary.
 Plan plan(int dtype, int dim, int q_dim, int kv_dim, int head_dim, int hidden, int vocab, int n_heads,
-          int n_kv_heads, int n_experts, int n_active, int max_seq_len);
+          int n_kv_heads, int n_experts, int n_active, int max_seq_len, bool tp = false, int full_vocab = 0);
 // Bytes of the attention partial workspace (acc + ml) for `grid` CTAs.
 size_t attn_ws_floats(int grid, int n_heads, int head_dim);
 // One token.  Returns a cudaError_t.

@@ -240,6 +240,13 @@ void InferenceState::cuda() {
 		*s.ptr = static_cast<char *>(_arena) + off;
 		off += align_up(s.bytes, 256);
 	}
+	if (c.tp_size > 1) {
+		// tensor parallel: the gathered logits live in this rank's peer-mapped region, where the megakernel's LM
+		// head epilogues of all ranks write their rows (one inference state per process uses it)
+		const yalm::TpPeerView pv = yalm::tp_peer_view();
+		if (pv.ok && pv.world == c.tp_size && c.vocab_size <= yalm::mega::kTpMaxVocab)
+			_logits_dev = reinterpret_cast<float *>(pv.base[pv.rank] + yalm::mega::kTpOffLogits);
+	}
 	CUDA_CHECK(cudaHostAlloc((void **)&_logits, sizeof(float) * c.vocab_size, cudaHostAllocDefault));
 	memset(_logits, 0, sizeof(float) * c.vocab_size);
 }
@@ -552,11 +559,18 @@ void Model::plan_mega() {
 	const Config &c = *config;
 	const char *env = getenv("YALM_B200_MEGA");
 	if (env && env[0] == '0') return;
-	if (c.tp_size != 1) return;
+	// tensor parallel: the in-kernel all-reduce needs the peer-mapped regions (tp.cpp); without them the per-op
+	// kernels + NCCL run instead
+	const bool tp = c.tp_size > 1;
+	if (tp) {
+		const yalm::TpPeerView pv = yalm::tp_peer_view();
+		const char *e2 = getenv("YALM_TP_MEGA"); // 0: tensor parallel on the per-op kernels (A/B)
+		if ((e2 && e2[0] == '0') || !pv.ok || pv.world != c.tp_size || pv.rank != c.tp_rank || c.tp_size % 2) return;
+	}
 	auto ms = std::make_shared<MegaState>();
-	ms->plan = yalm::mega::plan(static_cast<int>(c.weight_dtype), c.dim, c.n_heads * c.head_dim, c.n_kv_heads * c.head_dim,
-	                            c.head_dim, c.hidden_dim, c.vocab_size, c.n_heads, c.n_kv_heads, c.n_experts,
-	                            c.n_experts_active, c.max_seq_len);
+	ms->plan = yalm::mega::plan(static_cast<int>(c.weight_dtype), c.dim, c.local_heads() * c.head_dim,
+	                            c.local_kv_heads() * c.head_dim, c.head_dim, c.local_hidden(), c.local_vocab(), c.local_heads(),
+	                            c.local_kv_heads(), c.n_experts, c.n_experts_active, c.max_seq_len, tp, c.vocab_size);
 	if (!ms->plan.ok) return;
 	std::vector<yalm::mega::Layer> host(blocks.size());
 	for (size_t i = 0; i < blocks.size(); ++i) {
@@ -616,8 +630,15 @@ int Model::launch_mega(InferenceState &s, int token, int pos, int mode, long lon
 	a.prof = prof;
 	a.trace = _mega_trace;
 	a.layers = _mega->layers, a.n_layers = c.n_layers;
-	a.dim = c.dim, a.q_dim = c.n_heads * c.head_dim, a.kv_dim = c.n_kv_heads * c.head_dim, a.head_dim = c.head_dim;
-	a.hidden = c.hidden_dim, a.vocab = c.vocab_size, a.n_heads = c.n_heads, a.n_kv_heads = c.n_kv_heads;
+	a.dim = c.dim, a.q_dim = c.local_heads() * c.head_dim, a.kv_dim = c.local_kv_heads() * c.head_dim, a.head_dim = c.head_dim;
+	a.hidden = c.local_hidden(), a.vocab = c.local_vocab(), a.n_heads = c.local_heads(), a.n_kv_heads = c.local_kv_heads();
+	a.tp_world = c.tp_size, a.tp_rank = c.tp_rank, a.vocab_base = c.tp_rank * c.local_vocab(), a.x2 = s.xb();
+	if (c.tp_size > 1) {
+		const yalm::TpPeerView pv = yalm::tp_peer_view();
+		if (!pv.ok || pv.world != c.tp_size || s.logits_dev() != reinterpret_cast<float *>(pv.base[pv.rank] + yalm::mega::kTpOffLogits))
+			return YALM_EINVAL; // the state must have been created after yalm_tp_init (its logits live in the peer region)
+		for (int r = 0; r < pv.world; ++r) a.tp_peer[r] = pv.base[r];
+	}
 	a.rotary_dim = c.rotary_dim, a.max_seq_len = c.max_seq_len;
 	a.act = c.act == ActivationType::SILU ? YALM_ACT_SILU : YALM_ACT_GELU;
 	a.n_experts = c.n_experts, a.n_active = c.n_experts_active;

@@ -2,6 +2,7 @@
 // NCCL is bound at run time (dlopen of the libnccl.so.2 that torch bundles, or the system one) so that
 // the single-GPU build has no link-time dependency on it.  Only the five calls the decode path needs.
 #include "tp.h"
+#include "mega.h"
 
 #include <dlfcn.h>
 
@@ -84,7 +85,10 @@ int check(int rc, const char *what) {
 constexpr int kPeerMaxWorld = 8;
 constexpr int kPeerCapFloats = 8192;                    // largest vector (dim) the one-shot path takes
 constexpr size_t kPeerFlagsOff = 256, kPeerSlotsOff = 1024;
-constexpr size_t kPeerRegionBytes = kPeerSlotsOff + 2ull * kPeerMaxWorld * kPeerCapFloats * sizeof(float);
+constexpr size_t kPeerOneShotBytes = kPeerSlotsOff + 2ull * kPeerMaxWorld * kPeerCapFloats * sizeof(float);
+constexpr size_t kPeerMegaOff = (kPeerOneShotBytes + 1023) / 1024 * 1024; // the decode megakernel's area (mega.h: kTpOff*)
+constexpr size_t kPeerRegionBytes = kPeerMegaOff + mega::kTpRegionBytes;
+static_assert(kPeerMaxWorld == mega::kTpMaxWorld, "one world-size limit");
 constexpr long long kPeerTimeoutCycles = 4000000000ll; // ~2 s: a lost peer traps instead of hanging the GPU
 
 struct PeerPtrs {
@@ -194,6 +198,13 @@ void peer_open(int rank, int world) {
 	if (rank == 0) fprintf(stderr, "yalm_b200: tensor-parallel all-reduce over %s\n", g_peer.ok ? "NVLink peer memory (one-shot kernel)" : "NCCL");
 }
 } // namespace
+
+TpPeerView tp_peer_view() {
+	TpPeerView v{};
+	v.ok = g_peer.ok, v.world = g_world, v.rank = g_rank;
+	for (int r = 0; r < kPeerMaxWorld; ++r) v.base[r] = g_peer.ok && g_peer.ptrs.p[r] ? g_peer.ptrs.p[r] + kPeerMegaOff : nullptr;
+	return v;
+}
 
 int tp_rank() { return g_rank; }
 int tp_world() { return g_world; }

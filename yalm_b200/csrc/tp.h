@@ -14,6 +14,15 @@ bool tp_active();
 int tp_allreduce_sum(const float *send, float *recv, size_t count, cudaStream_t st);
 int tp_allgather(const float *send, float *recv, size_t count_per_rank, cudaStream_t st);
 
+// Peer-mapped regions for the in-kernel all-reduce of the whole-token decode kernel (mega.h: kTpOff*): base[r] is
+// rank r's region as mapped into this process, base[rank] the local one.  ok == false: no peer mapping (NCCL only).
+struct TpPeerView {
+	bool ok;
+	int world, rank;
+	char *base[8];
+};
+TpPeerView tp_peer_view();
+
 // Which bytes of an unsharded (rows, cols) row-major tensor rank `rank` of `size` holds: `height` pieces of `width`
 // bytes, piece i starting at offset + i * spitch.  Pure arithmetic (no device): shared by the loader and the tests.
 // Column-parallel tensors (wq, wk, wv, w1, w3, wcls: split over output rows) are one contiguous piece; row-parallel
