@@ -1,12 +1,14 @@
 # yalm_b200 build: one shared library (kernels + C ABI + C++ API), plus the reference-shaped CLIs.
 #   make            -> yalm_b200/libyalm_b200.so
 #   make cli        -> build/test (kernel benchmarks, the reference's `test -k <name>` command line)
+#   make BUILD=build/x LIB=build/lib_x.so EXTRA=-DYALM_MEGA_LL=0   -> an A/B variant (YALM_B200_LIB=... selects it at run time)
 NVCC  ?= nvcc
 HOSTCXX := /usr/bin/g++
 ARCH  := -gencode arch=compute_100a,code=sm_100a
 CSRC  := yalm_b200/csrc
 BUILD := build
-NVFLAGS := -std=c++17 -O3 -lineinfo $(ARCH) -ccbin $(HOSTCXX) -Xcompiler -fPIC,-Wall,-fopenmp -Iinclude
+EXTRA ?=
+NVFLAGS := -std=c++17 -O3 -lineinfo $(EXTRA) $(ARCH) -ccbin $(HOSTCXX) -Xcompiler -fPIC,-Wall,-fopenmp -Iinclude
 LIB   := yalm_b200/libyalm_b200.so
 
 LIB_SRCS := $(CSRC)/ops_gemv.cu $(CSRC)/ops_attn.cu $(CSRC)/decode_mega.cu $(CSRC)/decode_mega_f32.cu $(CSRC)/decode_mega_f16.cu $(CSRC)/decode_mega_f8.cu $(CSRC)/model.cpp $(CSRC)/codec.cpp $(CSRC)/capi.cpp \

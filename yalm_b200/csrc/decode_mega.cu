@@ -119,7 +119,7 @@ Plan plan(int dtype, int dim, int q_dim, int kv_dim, int head_dim, int hidden, i
 	if (head_dim <= 0 || units * (p.grid + 1) >= (1ll << 31)) return p;
 	// attention: warp records, combine weights, per-warp probability scratch (C rows x G + G)
 	vf = std::max(vf, kHeadSlots * kConsumerWarps * G * (head_dim + 2) + p.grid * G + G +
-	                      kConsumerWarps * (kStageBytes / (4 * head_dim) * G + G) + 32);
+	                      kConsumerWarps * (kStageBytes / (4 * head_dim) * G + G) + G * head_dim + 32);
 	p.vec_floats = (vf + 31) / 32 * 32;
 	// header (rope table, scratch, release counters, mbarriers) | ring | vec
 	const size_t fixed = (size_t)p.vec_floats * 4 + kSmemHeader;

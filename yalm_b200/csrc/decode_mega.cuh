@@ -113,6 +113,72 @@ __device__ __forceinline__ unsigned ld_acquire(const unsigned *p) {
 	return v;
 }
 
+// ---- flagged hand-over (single GPU) -----------------------------------------------------------------------------
+// Between two phases of a layer a vector (x, hb, att_out, the attention partials) changes hands from the CTAs that
+// computed its rows to every CTA.  Instead of "all stores -> CTA barrier -> release counter -> poll -> fence -> CTA
+// barrier -> load", every element travels as ONE 64-bit word {fp32 value, u32 flag} written with a single store and
+// the readers poll the words themselves: a word whose flag matches is the value (64-bit accesses are single-copy
+// atomic), so the hand-over costs one L2 round trip after the last store lands and needs no fence.  flag =
+// launch number << 10 | (producing phase + 1) never repeats for a buffer within 4M launches, and a buffer is
+// rewritten every launch, so stale words never match.  Reuse of a buffer is safe because ONE grid barrier per layer
+// remains (QKV -> attention, where the appended K/V rows change hands anyway): no CTA can run a layer ahead of
+// another one, x alternates between two buffers (after wo / after w2), and hb, att_out and the partials are written
+// once per layer on the far side of that barrier from their previous readers.
+#ifndef YALM_MEGA_LL
+#define YALM_MEGA_LL 1
+#endif
+// 1: the attention partials are flagged too and every participating CTA combines a slice of the head's outputs
+// (ll_combine); 0: arrival counter + combine on the last CTA of the head (combine_head), only att_out is flagged.
+#ifndef YALM_MEGA_LL_ATTN
+#define YALM_MEGA_LL_ATTN 0
+#endif
+__device__ __forceinline__ unsigned long long ll_pack(float v, unsigned flag) {
+	return (unsigned long long)__float_as_uint(v) | ((unsigned long long)flag << 32);
+}
+__device__ __forceinline__ void ll_store(unsigned long long *p, float v, unsigned flag) {
+	asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(ll_pack(v, flag)) : "memory");
+}
+__device__ __forceinline__ void ll_store2(unsigned long long *p, float v0, float v1, unsigned flag) {
+	asm volatile("st.relaxed.gpu.global.v2.u64 [%0], {%1, %2};" ::"l"(p), "l"(ll_pack(v0, flag)), "l"(ll_pack(v1, flag)) : "memory");
+}
+__device__ __forceinline__ ulonglong2 ll_load2(const unsigned long long *p) {
+	ulonglong2 v;
+	asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(v.x), "=l"(v.y) : "l"(p) : "memory");
+	return v;
+}
+__device__ __forceinline__ unsigned long long ll_load1(const unsigned long long *p) {
+	unsigned long long v;
+	asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+	return v;
+}
+__device__ __forceinline__ bool ll_ok(unsigned long long w, unsigned flag) { return (unsigned)(w >> 32) == flag; }
+__device__ __forceinline__ float ll_val(unsigned long long w) { return __uint_as_float((unsigned)w); }
+// Four consecutive elements (32 bytes); true when all four carry `flag`.
+__device__ __forceinline__ bool ll_load4(const unsigned long long *p, unsigned flag, float4 *out) {
+	const ulonglong2 a = ll_load2(p), b = ll_load2(p + 2);
+	*out = make_float4(ll_val(a.x), ll_val(a.y), ll_val(b.x), ll_val(b.y));
+	return ll_ok(a.x, flag) && ll_ok(a.y, flag) && ll_ok(b.x, flag) && ll_ok(b.y, flag);
+}
+// Back-off between polling rounds (keeps the pollers' L2 traffic away from the weight stream); a wait of ~4 s traps.
+__device__ __forceinline__ void ll_backoff(int *round, long long *t0) {
+	if (*round == 0) *t0 = clock64();
+	else if (clock64() - *t0 > kTimeoutCycles) __trap();
+	__nanosleep(32u << min(*round, 4));
+	++*round;
+}
+__device__ __forceinline__ float ll_wait1(const unsigned long long *p, unsigned flag) {
+	unsigned long long w = ll_load1(p);
+	if (!ll_ok(w, flag)) {
+		int round = 0;
+		long long t0 = 0;
+		do {
+			ll_backoff(&round, &t0);
+			w = ll_load1(p);
+		} while (!ll_ok(w, flag));
+	}
+	return ll_val(w);
+}
+
 __device__ __forceinline__ uint4 lds128(uint32_t addr) {
 	uint4 v;
 	asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
@@ -215,6 +281,8 @@ __device__ __forceinline__ unsigned char *sm_base() {
 __device__ __forceinline__ float2 *sm_rope() { return reinterpret_cast<float2 *>(sm_base() + kOffRope); } // cos/sin of pos * freq_j
 __device__ __forceinline__ float *sm_red() { return reinterpret_cast<float *>(sm_base() + kOffRed); }
 __device__ __forceinline__ int *sm_misc() { return reinterpret_cast<int *>(sm_base() + kOffMisc); }
+// sm_misc slots: [0] combine flag, [4, 4 + consumer warps) arg-max indices, [16..] parked context
+constexpr int kMiscToken = 16, kMiscPos = 17, kMiscPark = 18;
 __device__ __forceinline__ int *sm_rel() { return reinterpret_cast<int *>(sm_base() + kOffRel); } // per-stage release counters
 __device__ __forceinline__ uint32_t sm_full0() { return smem_u32(sm_base() + kOffFull); }
 __device__ __forceinline__ uint32_t sm_empty0() { return smem_u32(sm_base() + kOffEmpty); }
@@ -223,9 +291,12 @@ __device__ __forceinline__ uint32_t sm_stages_u32() { return smem_u32(sm_base() 
 
 struct Ctx {
 	long long *prof;  // this CTA's profile rows or null
+#ifdef YALM_MEGA_TRACE
 	long long *trace; // event trace (CTA 0 only) or null
+#endif
+#ifdef YALM_MEGA_TRACE
 	long long wait_cycles;
-	int debug;
+#endif
 	uint32_t vec_u32;
 	float *vec;
 	int cta, ncta, warp, lane, tid, S;
@@ -234,7 +305,7 @@ struct Ctx {
 	int rot;     // CTA rotation of the current GEMV phase
 	unsigned bar_gen;
 	unsigned xgen; // cross-GPU barriers passed, earlier launches included (tensor parallelism)
-	int token, pos, kv_sink, kv_pos, kv_len;
+	int kv_sink, kv_pos, kv_len; // token and pos: sm_misc()[kMiscToken], [kMiscPos]
 };
 
 // Tile shape of a GEMV kind: planned on the host (tile_shape), read from the kernel-parameter constant bank
@@ -248,7 +319,10 @@ __device__ __forceinline__ Shape shape_of(const Args &a, int kind) {
 // Optional event trace of CTA 0 (Args.trace != null): trace[0] = event count, then (tag, clock64) pairs.
 // tag = type << 56 | warp << 48 | ring index.  Types: 1 producer issued, 2 consumer wait begin, 3 wait end, 4 release,
 // 5 phase stamp (index = layer * 64 + phase * 8 + slot).
+// Compiled in only with -DYALM_MEGA_TRACE (the trace pointer and the starvation counter cost four registers that the
+// attention unit loop does not have).
 __device__ __forceinline__ void trace(const Ctx &c, int type, uint32_t idx) {
+#ifdef YALM_MEGA_TRACE
 	if (c.trace) {
 		const unsigned long long k = atomicAdd(reinterpret_cast<unsigned long long *>(c.trace), 1ull);
 		if (k < (unsigned long long)kTraceEvents) {
@@ -256,6 +330,7 @@ __device__ __forceinline__ void trace(const Ctx &c, int type, uint32_t idx) {
 			c.trace[2 + 2 * k] = clock64();
 		}
 	}
+#endif
 }
 
 // (round, stage) of ring tile idx without an integer division
@@ -269,7 +344,9 @@ __device__ __forceinline__ void stamp(Ctx &c, int layer, int phase, int k) {
 	if (c.prof && c.tid == 0) {
 		long long *row = c.prof + ((size_t)layer * kProfPhases + phase) * kProfSlots;
 		row[k] = clock64();
+#ifdef YALM_MEGA_TRACE
 		if (k == 3 && phase != 1) row[4] = c.wait_cycles, c.wait_cycles = 0; // attention: slot 4 = combine probe
+#endif
 	}
 	if (c.tid == 0) trace(c, 5, (uint32_t)(layer * 64 + phase * 8 + k));
 }
@@ -401,7 +478,7 @@ struct Producer {
 		// the consumer's generic-proxy reads of the stage are ordered before the async-proxy refill
 		asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
 		*bar = sm_full0() + 8 * s;
-		if (c.debug & 8) mbar_arrive(*bar);
+		if (policy == 0) mbar_arrive(*bar); // debug & 8: no copies
 		else mbar_expect_tx(*bar, bytes);
 		trace(c, 1, idx);
 		return sm_stages_u32() + s * kStageBytes;
@@ -595,13 +672,14 @@ __device__ __forceinline__ const unsigned char *wait_tile(Ctx &c, uint32_t idx, 
 		while (ld_rel(sm_rel() + s) < r)
 			if (clock64() - t0 > kTimeoutCycles) __trap();
 	}
+#ifdef YALM_MEGA_TRACE
 	if (c.prof && c.tid == 0) {
 		const long long t0 = clock64();
 		mbar_wait(sm_full0() + 8 * s, par);
 		c.wait_cycles += clock64() - t0;
-	} else {
+	} else
+#endif
 		mbar_wait(sm_full0() + 8 * s, par);
-	}
 	if (c.lane == 0) trace(c, 3, idx);
 	*slot = idx;
 	return sm_stages() + (size_t)s * kStageBytes;
@@ -718,6 +796,75 @@ __device__ __forceinline__ void stage_vec(Ctx &c, const Args &a, const float *sr
 	cbar();
 }
 
+// stage_vec for a flagged vector (see "flagged hand-over"): the loads ARE the phase barrier.  Every thread polls its
+// own elements; round 0 issues all of a batch's loads back to back, later rounds only re-read what is still missing.
+// The CTA barrier in front of the first shared-memory store also ends the previous phase for this CTA (its warps may
+// still be reading c.vec in their tile loops).
+template <int DT>
+__device__ __forceinline__ void stage_vec_ll(Ctx &c, const Args &a, const unsigned long long *src, int n, const float *rms_w,
+                                             unsigned flag, const float4 (&wv)[kNormCache]) {
+	constexpr int EP = WTraits<DT>::EP;
+	constexpr int NC = kNormCache;
+	float4 cache[NC];
+	bool first = true;
+	float ss = 0.f;
+	for (int b0 = 0; b0 < n; b0 += NC * kCT * 4) { // one batch = NC float4 per thread (a single batch for n <= 5632); uniform trip count
+		const int e0 = b0 + c.tid * 4;
+		unsigned pending = 0;
+#pragma unroll
+		for (int i = 0; i < NC; ++i) {
+			const int e = e0 + i * kCT * 4;
+			cache[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+			if (e < n && !ll_load4(src + e, flag, &cache[i])) pending |= 1u << i;
+		}
+		if (pending) {
+			int round = 0;
+			long long t0 = 0;
+			do {
+				ll_backoff(&round, &t0);
+#pragma unroll
+				for (int i = 0; i < NC; ++i)
+					if ((pending >> i & 1u) && ll_load4(src + e0 + i * kCT * 4, flag, &cache[i])) pending &= ~(1u << i);
+			} while (pending);
+		}
+		if (rms_w) {
+#pragma unroll
+			for (int i = 0; i < NC; ++i)
+				ss += cache[i].x * cache[i].x + cache[i].y * cache[i].y + cache[i].z * cache[i].z + cache[i].w * cache[i].w;
+		} else {
+			if (first) cbar(); // CTA-uniform: every thread walks every batch
+			first = false;
+#pragma unroll
+			for (int i = 0; i < NC; ++i) {
+				const int e = e0 + i * kCT * 4;
+				if (e < n) *reinterpret_cast<float4 *>(c.vec + xs_slot<EP>(e)) = cache[i];
+			}
+		}
+	}
+	if (rms_w) {
+		// reference formula and association order (src/infer.cpp:134-144): o = x * (1/sqrt(ss/n + eps)) * w
+		ss = cons_sum(c, ss); // its CTA barriers come before any store to c.vec
+		const float scale = 1.0f / sqrtf(ss / n + a.eps);
+		const bool single = n <= NC * kCT * 4; // the only batch is still in registers, and so are its norm weights
+		for (int b0 = 0; b0 < n; b0 += NC * kCT * 4) {
+#pragma unroll
+			for (int i = 0; i < NC; ++i) {
+				const int e = b0 + (c.tid + i * kCT) * 4;
+				if (e < n) {
+					float4 v = cache[i], w = wv[i];
+					if (!single) {
+						ll_load4(src + e, flag, &v); // validated in the first pass
+						w = *reinterpret_cast<const float4 *>(rms_w + e);
+					}
+					*reinterpret_cast<float4 *>(c.vec + xs_slot<EP>(e)) =
+					    make_float4(v.x * scale * w.x, v.y * scale * w.y, v.z * scale * w.z, v.w * scale * w.w);
+				}
+			}
+		}
+	}
+	cbar();
+}
+
 // Per-phase epilogue state.
 struct Epi {
 	int kind;
@@ -732,7 +879,9 @@ struct Epi {
 // Warp w owns groups w, w+8, ... of the CTA's list: it adds up all K-split tiles of the group, shuffle-reduces,
 // and its first lanes run the epilogue.  Nothing here synchronises with the other warps.
 template <int DT, int R, bool TP>
-__device__ __forceinline__ void gemv_consume(Ctx &c, const Args &a, Epi &ep) {
+__device__ __forceinline__ void gemv_consume(Ctx &c, const Args &a, Epi &ep, int ph) {
+	constexpr bool LL = YALM_MEGA_LL && !TP;
+	const unsigned wflag = a.seq << 10 | (unsigned)(ph + 1); // flagged hand-over: the next phase polls for this
 	using T = WTraits<DT>;
 	constexpr int EP = T::EP, CH = 32 * EP, Q = EP / 4;
 	const Shape sh = shape_of(a, ep.kind);
@@ -749,14 +898,19 @@ __device__ __forceinline__ void gemv_consume(Ctx &c, const Args &a, Epi &ep) {
 		const int g = g_first + (b8 + warp) * c.ncta;
 		// residual operand of the wo / w2 epilogue: issue the L2 read now, it is consumed after the tiles
 		float resid = 0.f;
-		if (!TP && (kind == kWO || kind == kW2) && lane < R) resid = __ldcg(a.x + (long)g * R + lane);
+		if (!TP && (kind == kWO || kind == kW2) && lane < R) {
+			// flagged hand-over: x after wo lives in ll_x[0] (complete: this CTA polled all of it when it staged w1/w3);
+			// x before wo is the plain copy written behind w2 of the layer before, on the far side of a grid barrier
+			if (LL && kind == kW2) resid = ll_val(ll_load1(a.ll_x + (long)g * R + lane));
+			else resid = __ldcg(a.x + (long)g * R + lane);
+		}
 		float2 acc2[R];
 #pragma unroll
 		for (int r = 0; r < R; ++r) acc2[r] = make_float2(0.f, 0.f);
 		for (int kc = 0; kc < sh.nk; ++kc) {
 			uint32_t slot;
 			const unsigned char *tile = wait_tile(c, base + (uint32_t)(b8 * sh.nk + kc * nb + warp), &slot);
-			if (!(c.debug & 1)) {
+			if (!(a.debug & 1)) {
 				// shared-space addresses: this lane's 16 bytes of chunk 0 of row 0, and its x quarter 0
 				uint32_t wa = tile_u32(c, tile) + lane * 16;
 				uint32_t xa = c.vec_u32 + (uint32_t)(kc * chunks * CH) * 4 + lane * 16;
@@ -835,6 +989,7 @@ __device__ __forceinline__ void gemv_consume(Ctx &c, const Args &a, Epi &ep) {
 				if (DT == YALM_F8E4M3 && ep.scale0) gt *= ep.scale0[row], up *= ep.scale1[row];
 				gt = a.act == YALM_ACT_GELU ? act_gelu(gt) : act_silu(gt);
 				a.hb[row] = gt * up;
+				if (LL) ll_store(a.ll_hb + row, gt * up, wflag);
 			}
 		} else if (TP) {
 			// tensor parallel: the rows are partial sums (wo / w2: this rank's slice of the input dimension) or this
@@ -874,7 +1029,9 @@ __device__ __forceinline__ void gemv_consume(Ctx &c, const Args &a, Epi &ep) {
 				a.logits[row] = v;
 				if (v > ep.best_v) ep.best_v = v, ep.best_i = (int)row; // a lane's rows ascend: first maximum wins
 			} else {
-				a.x[row] = resid + v; // x += W v (src/infer.cpp:335-337, 381-383)
+				// x += W v (src/infer.cpp:335-337, 381-383)
+				if (LL) ll_store(a.ll_x + (kind == kW2 ? a.dim : 0) + row, resid + v, wflag);
+				if (!LL || kind == kW2) a.x[row] = resid + v;
 			}
 		}
 	}
@@ -883,11 +1040,11 @@ __device__ __forceinline__ void gemv_consume(Ctx &c, const Args &a, Epi &ep) {
 }
 
 template <int DT, bool TP>
-__device__ __forceinline__ void gemv_phase(Ctx &c, const Args &a, Epi &ep) {
+__device__ __forceinline__ void gemv_phase(Ctx &c, const Args &a, Epi &ep, int ph) {
 	const int R = a.shape[ep.kind][0];
-	if (R == 4) gemv_consume<DT, 4, TP>(c, a, ep);
-	else if (R == 2) gemv_consume<DT, 2, TP>(c, a, ep);
-	else gemv_consume<DT, 1, TP>(c, a, ep);
+	if (R == 4) gemv_consume<DT, 4, TP>(c, a, ep, ph);
+	else if (R == 2) gemv_consume<DT, 2, TP>(c, a, ep, ph);
+	else gemv_consume<DT, 1, TP>(c, a, ep, ph);
 }
 
 // ---- attention --------------------------------------------------------------------------------------------
@@ -903,7 +1060,8 @@ __device__ __forceinline__ void unpack8(uint4 v, float (&f)[8]) {
 // Runs on 1 CTA per head and layer, so it is kept out of line: its registers do not weigh on the main loops.
 template <int HD, int G>
 __device__ __forceinline__ void combine_head(const float *ws_acc, const float *ws_ml, float *att_out, float *wts, float *scratch,
-                                          int kvh, int ncta, int nch, int b_lo, int b_hi, long long *probe) {
+                                          int kvh, int ncta, int nch, int b_lo, int b_hi, long long *probe,
+                                          unsigned long long *ll_att = nullptr, unsigned wflag = 0) {
 	constexpr int W = kConsumerWarps;
 	constexpr int kInFlight = 20;  // independent L2 reads per thread and output
 	const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -966,8 +1124,72 @@ __device__ __forceinline__ void combine_head(const float *ws_acc, const float *w
 				v1 = fmaf(w1, p1[k], v1);
 			}
 		}
-		att_out[(size_t)kvh * G * HD + i0] = v0 / wts[ncta * G + g0];
-		if (two) att_out[(size_t)kvh * G * HD + i1] = v1 / wts[ncta * G + g1];
+		const float o0 = v0 / wts[ncta * G + g0], o1 = v1 / wts[ncta * G + g1];
+		att_out[(size_t)kvh * G * HD + i0] = o0;
+		if (two) att_out[(size_t)kvh * G * HD + i1] = o1;
+		if (ll_att) { // flagged hand-over: the wo staging step polls these
+			ll_store(ll_att + (size_t)kvh * G * HD + i0, o0, wflag);
+			if (two) ll_store(ll_att + (size_t)kvh * G * HD + i1, o1, wflag);
+		}
+	}
+}
+
+// Distributed combine of one KV head (flagged hand-over): this CTA is participant `pi` of the head's `cnt` CTAs that own
+// a chunk and produces outputs [pi, pi+1) * G*HD / cnt.  Out of line with scalar arguments: its registers must not
+// weigh on the attention unit loop.
+template <int HD, int G>
+__device__ __noinline__ void ll_combine(const unsigned long long *ll_ml, const unsigned long long *ll_acc, unsigned long long *ll_att,
+                                        float *att_out, int kvh, int ncta, int c0, int nc, int nch, int pi, unsigned wflag, int tid) {
+	const int cnt = min(nc, nch);
+	const int o_lo = (int)((unsigned)pi * (G * HD) / cnt), o_hi = (int)((unsigned)(pi + 1) * (G * HD) / cnt);
+	constexpr int U = 4; // participants in flight per thread
+	for (int o = o_lo + tid; o < o_hi; o += kCT) {
+		const int g = o / HD;
+		const unsigned long long *mlp = ll_ml + (((size_t)kvh * ncta + c0) * G + g) * 2; // + r * G * 2
+		const unsigned long long *acp = ll_acc + ((size_t)kvh * ncta + c0) * G * HD + o; // + r * G * HD
+		float M = -INFINITY;
+		for (int r0 = 0; r0 < nc; r0 += U) {
+			unsigned long long w[U];
+#pragma unroll
+			for (int j = 0; j < U; ++j) {
+				const int r = r0 + j;
+				if (r < nc && attn_has_unit(r, nc, nch)) w[j] = ll_load1(mlp + (size_t)r * G * 2);
+			}
+#pragma unroll
+			for (int j = 0; j < U; ++j) {
+				const int r = r0 + j;
+				if (r < nc && attn_has_unit(r, nc, nch))
+					M = fmaxf(M, ll_ok(w[j], wflag) ? ll_val(w[j]) : ll_wait1(mlp + (size_t)r * G * 2, wflag));
+			}
+		}
+		float ls = 0.f, v = 0.f;
+		for (int r0 = 0; r0 < nc; r0 += U) {
+			ulonglong2 ml[U];
+			unsigned long long ac[U];
+#pragma unroll
+			for (int j = 0; j < U; ++j) {
+				const int r = r0 + j;
+				if (r < nc && attn_has_unit(r, nc, nch)) {
+					ml[j] = ll_load2(mlp + (size_t)r * G * 2);
+					ac[j] = ll_load1(acp + (size_t)r * G * HD);
+				}
+			}
+#pragma unroll
+			for (int j = 0; j < U; ++j) {
+				const int r = r0 + j;
+				if (r < nc && attn_has_unit(r, nc, nch)) {
+					const float m_r = ll_val(ml[j].x); // validated by the first pass
+					const float l_r = ll_ok(ml[j].y, wflag) ? ll_val(ml[j].y) : ll_wait1(mlp + (size_t)r * G * 2 + 1, wflag);
+					const float p_r = ll_ok(ac[j], wflag) ? ll_val(ac[j]) : ll_wait1(acp + (size_t)r * G * HD, wflag);
+					const float wgt = m_r == -INFINITY ? 0.f : expf(m_r - M);
+					ls = fmaf(wgt, l_r, ls);
+					v = fmaf(wgt, p_r, v);
+				}
+			}
+		}
+		const float out = v / ls;
+		att_out[(size_t)kvh * G * HD + o] = out;
+		ll_store(ll_att + (size_t)kvh * G * HD + o, out, wflag); // polled by the wo staging step
 	}
 }
 
@@ -984,7 +1206,7 @@ __device__ __forceinline__ void combine_head(const float *ws_acc, const float *w
 // A warp that moves on to the next KV head parks its state in shared memory.  Warps, then CTAs, are merged with
 // the usual (max, sum, acc) rescaling in a fixed order, so results are run-to-run identical.  The last CTA to
 // publish a head's partial combines them (arrival counter).
-template <int HD, int G>
+template <int HD, int G, bool LL>
 __device__ __forceinline__ void attention_consume(Ctx &c, const Args &a, const Layer &L, int layer) {
 	constexpr int W = kConsumerWarps;
 	constexpr int LPR = HD / 8, RPS = 32 / LPR; // lanes per row, rows per warp step (= row groups)
@@ -1013,7 +1235,11 @@ __device__ __forceinline__ void attention_consume(Ctx &c, const Args &a, const L
 		float *rec = wsm + (warp * G + lane) * WS;
 		rec[HD] = -INFINITY, rec[HD + 1] = 0.f;
 	}
-	float2 qr[G][4], acc[G][4]; // q / sqrt(HD) and the output accumulators: this lane's 8 dims as 4 pairs
+	float2 acc[G][4]; // the output accumulators: this lane's 8 dims as 4 pairs
+	// q / sqrt(HD) of the head group lives in shared memory and is re-read per unit (8 LDS.128): held in registers it
+	// pushed the unit loop over the register ceiling, and the compiler's answer was to keep q in local memory instead
+	float *qs = wsm + ((W * G * WS + ncta * G + G + W * PS + 3) & ~3); // 16-byte aligned
+	const uint32_t qs_u32 = c.vec_u32 + (uint32_t)(qs - c.vec) * 4 + (uint32_t)sub * 32;
 	float m = -INFINITY, l = 0.f; // running max / partial sum of head my_g (max identical in all lanes of the head)
 	auto park = [&]() { // merge the warp's row groups and lanes, store the warp's state
 #pragma unroll
@@ -1043,16 +1269,21 @@ __device__ __forceinline__ void attention_consume(Ctx &c, const Args &a, const L
 		}
 	};
 	__syncwarp();
-	if (warp < NU) { // q / sqrt(HD) of the head group, accumulators
+	for (int e = c.tid * 4; e < G * HD; e += kCT * 4) {
+		const float4 v = __ldcg(reinterpret_cast<const float4 *>(a.q + (size_t)kvh * G * HD + e));
+		*reinterpret_cast<float4 *>(qs + e) = make_float4(v.x / div, v.y / div, v.z / div, v.w / div);
+	}
 #pragma unroll
-		for (int g = 0; g < G; ++g) {
-			const float *qp = a.q + (size_t)(kvh * G + g) * HD + sub * 8;
-			const float4 lo = __ldcg(reinterpret_cast<const float4 *>(qp)), hi = __ldcg(reinterpret_cast<const float4 *>(qp + 4));
-			qr[g][0] = make_float2(lo.x / div, lo.y / div), qr[g][1] = make_float2(lo.z / div, lo.w / div);
-			qr[g][2] = make_float2(hi.x / div, hi.y / div), qr[g][3] = make_float2(hi.z / div, hi.w / div);
+	for (int g = 0; g < G; ++g)
 #pragma unroll
-			for (int j = 0; j < 4; ++j) acc[g][j] = make_float2(0.f, 0.f);
-		}
+		for (int j = 0; j < 4; ++j) acc[g][j] = make_float2(0.f, 0.f);
+	cbar();
+	// The unit loop needs every register it can get: the CTA-uniform context it does not use waits in shared memory
+	// (the alternative is the compiler spilling inside the loop, and local memory is an L2 round trip here).
+	volatile int *pk = sm_misc() + kMiscPark;
+	if (c.tid == 0) {
+		pk[0] = c.rot, pk[1] = (int)c.bar_gen, pk[2] = (int)c.xgen;
+		pk[3] = (int)(unsigned)((unsigned long long)c.prof), pk[4] = (int)(unsigned)((unsigned long long)c.prof >> 32);
 	}
 	for (int i = warp; i < NU; i += W) {
 		const int t0 = (sp.k0 + i) * C, n = min(C, c.kv_len - t0);
@@ -1067,6 +1298,13 @@ __device__ __forceinline__ void attention_consume(Ctx &c, const Args &a, const L
 		const bool has_fresh = (c.kv_pos >= t0 && c.kv_pos < t0 + n) || t0 < c.kv_sink;
 		// ---- A: partial dots, value index = g * ST + st ---------------------------------------------------------
 		float d[V];
+		float2 qr[G][4];
+#pragma unroll
+		for (int g = 0; g < G; ++g) {
+			const float4 lo = lds128f(qs_u32 + g * HD * 4), hi = lds128f(qs_u32 + g * HD * 4 + 16);
+			qr[g][0] = make_float2(lo.x, lo.y), qr[g][1] = make_float2(lo.z, lo.w);
+			qr[g][2] = make_float2(hi.x, hi.y), qr[g][3] = make_float2(hi.z, hi.w);
+		}
 #pragma unroll
 		for (int st = 0; st < ST; ++st) {
 			const int row = st * RPS + rgrp, t = t0 + row;
@@ -1108,7 +1346,7 @@ __device__ __forceinline__ void attention_consume(Ctx &c, const Args &a, const L
 #pragma unroll
 		for (int i2 = 0; i2 < NF; ++i2) {
 			const int row = (my_st0 + i2) * RPS + rgrp;
-			if (row >= n || (c.debug & 4)) d[i2] = -INFINITY;
+			if (row >= n || (a.debug & 4)) d[i2] = -INFINITY;
 			mt = fmaxf(mt, d[i2]);
 		}
 #pragma unroll
@@ -1159,9 +1397,13 @@ __device__ __forceinline__ void attention_consume(Ctx &c, const Args &a, const L
 	}
 	if (warp < NU) park();
 	cbar();
+	c.rot = pk[0], c.bar_gen = (unsigned)pk[1], c.xgen = (unsigned)pk[2];
+	c.prof = reinterpret_cast<long long *>((unsigned long long)(unsigned)pk[3] | (unsigned long long)(unsigned)pk[4] << 32);
 	stamp(c, layer, 1, 5);
 
 	// ---- merge the warps, publish the CTA's partial, the last CTA of the head to arrive combines ------------
+	const unsigned wflag = a.seq << 10 | (unsigned)(layer * 5 + 2); // flagged hand-over: this phase is ph = 5 * layer + 1
+	constexpr bool LLC = LL && YALM_MEGA_LL_ATTN;
 	float *ew = wts; // [W][G] merge weights (wts is not in use before the combine)
 	if (c.tid < W * G) { // weight of warp w's record for head g, computed once
 		const int w = c.tid / G, g = c.tid % G;
@@ -1177,8 +1419,12 @@ __device__ __forceinline__ void attention_consume(Ctx &c, const Args &a, const L
 				const float m2 = wsm[(w2 * G + g) * WS + HD];
 				if (m2 != -INFINITY) ls = fmaf(expf(m2 - M), wsm[(w2 * G + g) * WS + HD + 1], ls);
 			}
-			float *pml = a.ws_ml + (((size_t)kvh * ncta + c.cta) * G + g) * 2;
-			pml[0] = M, pml[1] = ls;
+			if (LLC) {
+				ll_store2(a.ll_ml + (((size_t)kvh * ncta + c.cta) * G + g) * 2, M, ls, wflag);
+			} else {
+				float *pml = a.ws_ml + (((size_t)kvh * ncta + c.cta) * G + g) * 2;
+				pml[0] = M, pml[1] = ls;
+			}
 		}
 	}
 	cbar();
@@ -1191,9 +1437,20 @@ __device__ __forceinline__ void attention_consume(Ctx &c, const Args &a, const L
 			const float2 r = *reinterpret_cast<const float2 *>(wsm + (w * G + g) * WS + d);
 			if (e != 0.f) v.x = fmaf(e, r.x, v.x), v.y = fmaf(e, r.y, v.y); // empty records hold no data
 		}
-		*reinterpret_cast<float2 *>(a.ws_acc + (((size_t)kvh * ncta + c.cta) * G + g) * HD + d) = v;
+		if (LLC) ll_store2(a.ll_acc + (((size_t)kvh * ncta + c.cta) * G + g) * HD + d, v.x, v.y, wflag);
+		else *reinterpret_cast<float2 *>(a.ws_acc + (((size_t)kvh * ncta + c.cta) * G + g) * HD + d) = v;
 	}
 	stamp(c, layer, 1, 7);
+	if (LLC) {
+		// Distributed combine: the head's participating CTAs each own a slice of its G * HD outputs and poll the
+		// partials (max, sum, acc) of all participants directly — no arrival counter, no barrier, no fence.  Summed in
+		// CTA order with the same weights on every run: deterministic.
+		stamp(c, layer, 1, 6);
+		ll_combine<HD, G>(a.ll_ml, a.ll_acc, a.ll_att, a.att_out, kvh, ncta, sp.c0, sp.nc, nch, nch >= sp.nc ? c.cta - sp.c0 : sp.k0,
+		                  wflag, c.tid);
+		if (c.prof && c.tid == 0) c.prof[((size_t)layer * kProfPhases + 1) * kProfSlots + 4] = clock64();
+		return;
+	}
 	cbar(); // the partial's stores happen-before the release below
 	if (c.tid == 0) {
 		const int cnt = min(sp.nc, nch); // CTAs of the head that own a chunk
@@ -1207,7 +1464,7 @@ __device__ __forceinline__ void attention_consume(Ctx &c, const Args &a, const L
 	stamp(c, layer, 1, 6);
 	if (sm_misc()[0]) // CTA-uniform
 		combine_head<HD, G>(a.ws_acc, a.ws_ml, a.att_out, wts, wsm, kvh, ncta, nch, sp.c0, sp.c0 + sp.nc - 1,
-		                    c.prof ? c.prof + ((size_t)layer * kProfPhases + 1) * kProfSlots + 4 : nullptr);
+		                    c.prof ? c.prof + ((size_t)layer * kProfPhases + 1) * kProfSlots + 4 : nullptr, LL ? a.ll_att : nullptr, wflag);
 }
 
 __device__ __forceinline__ void derive_ring(int pos, int max_seq_len, int *kv_sink, int *kv_pos, int *kv_len) {
@@ -1233,13 +1490,15 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_c
 	c.xgen = 0;
 	if (TP) c.xgen = *reinterpret_cast<const volatile unsigned *>(a.tp_peer[a.tp_rank] + kTpOffGen); // written by the previous launch
 	c.prof = a.prof ? a.prof + (size_t)blockIdx.x * a.n_layers * kProfPhases * kProfSlots : nullptr;
+#ifdef YALM_MEGA_TRACE
 	c.wait_cycles = 0;
-	c.debug = a.debug;
 	c.trace = blockIdx.x == 0 ? a.trace : nullptr;
+#endif
 
-	c.token = a.token, c.pos = a.pos;
-	if (a.token < 0) c.token = a.ctl[CTL_TOKEN], c.pos = a.ctl[CTL_POS];
-	derive_ring(c.pos, a.max_seq_len, &c.kv_sink, &c.kv_pos, &c.kv_len);
+	int token = a.token, pos = a.pos;
+	if (a.token < 0) token = a.ctl[CTL_TOKEN], pos = a.ctl[CTL_POS];
+	derive_ring(pos, a.max_seq_len, &c.kv_sink, &c.kv_pos, &c.kv_len);
+	if (threadIdx.x == 0) sm_misc()[kMiscToken] = token, sm_misc()[kMiscPos] = pos; // needed at phase 0 / at the very end only
 
 	if (threadIdx.x == 0) {
 		for (int i = 0; i < c.S; ++i) {
@@ -1254,7 +1513,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_c
 	if (threadIdx.x < HD / 2) {
 		const int j = 2 * threadIdx.x;
 		const float freq = j >= a.rotary_dim ? 0.f : 1.0f / powf(a.theta, (float)j / (float)a.rotary_dim);
-		const float val = c.pos * freq;
+		const float val = pos * freq;
 		sm_rope()[threadIdx.x] = make_float2(cosf(val), sinf(val));
 	}
 	__syncthreads();
@@ -1268,7 +1527,6 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_c
 
 	// ================================ consumers ================================
 	Epi ep;
-	ep.best_v = -FLT_MAX, ep.best_i = 0x7fffffff;
 	const int n_phases = a.n_layers * 5 + (a.mode != kHydrate ? 1 : 0);
 	for (int ph = 0; ph < n_phases; ++ph) { // one loop body = one call site per phase function
 		const int l = min(ph / 5, a.n_layers - 1), k = ph < a.n_layers * 5 ? ph % 5 : 5;
@@ -1280,12 +1538,16 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_c
 		load_norm_weights(c, rms, a.dim, wv); // in flight across the barrier
 		// tensor parallel: the boundaries behind wo (k == 3) and w2 (k == 0 of the next layer, k == 5) span the GPUs
 		const bool reduced = TP && ph > 0 && (k == 3 || k == 0 || k == 5);
+		// flagged hand-over (single GPU): only the QKV -> attention boundary keeps its grid barrier, every other
+		// phase polls its input vector in the staging step
+		constexpr bool LL = YALM_MEGA_LL && !TP;
+		const unsigned rflag = a.seq << 10 | (unsigned)ph; // what the phase before this one produced
 		if (reduced) tp_barrier(c, a);
-		else if (ph > 0) grid_barrier(c, a.sync);
+		else if (ph > 0 && (!LL || k == 1)) grid_barrier(c, a.sync);
 		stamp(c, l, k, 1);
 		if (k == 1) { // attention: q comes from registers, nothing to stage
 			stamp(c, l, k, 2);
-			attention_consume<HD, G>(c, a, L, l);
+			attention_consume<HD, G, YALM_MEGA_LL && !TP>(c, a, L, l);
 			stamp(c, l, k, 3);
 			continue;
 		}
@@ -1296,15 +1558,18 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_c
 		case 2: src = a.att_out, n = a.q_dim, ep.kind = kWO, ep.scale0 = L.so; break;
 		case 3: ep.kind = kFFN, ep.scale0 = L.s1, ep.scale1 = L.s3; break;
 		case 4: src = a.hb, n = a.hidden, ep.kind = kW2, ep.scale0 = L.s2; break;
-		default: ep.kind = kLM, ep.scale0 = a.wcls_scale; break;
+		default: ep.kind = kLM, ep.scale0 = a.wcls_scale, ep.best_v = -FLT_MAX, ep.best_i = 0x7fffffff; break;
 		}
 		if (reduced) {
 			// x ping-pongs: behind wo the residual is x and the sum goes to x2, behind w2 the other way round
 			const float *slots = reinterpret_cast<const float *>(a.tp_peer[a.tp_rank] + kTpOffSlots) +
 			                     (size_t)(k == 3 ? 0 : a.tp_world) * kTpCapFloats;
 			stage_vec<DT>(c, a, k == 3 ? a.x : a.x2, n, rms, -1, wv, slots, k == 3 ? a.x2 : a.x);
+		} else if (LL && ph > 0) {
+			const unsigned long long *lsrc = k == 2 ? a.ll_att : k == 3 ? a.ll_x : k == 4 ? a.ll_hb : a.ll_x + a.dim;
+			stage_vec_ll<DT>(c, a, lsrc, n, rms, rflag, wv);
 		} else {
-			stage_vec<DT>(c, a, src, n, rms, ph == 0 ? c.token : -1, wv);
+			stage_vec<DT>(c, a, src, n, rms, ph == 0 ? sm_misc()[kMiscToken] : -1, wv);
 		}
 		stamp(c, l, k, 2);
 		if (k == 0 && c.kv_sink > 0 && c.cta == c.ncta - 1) {
@@ -1318,7 +1583,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_c
 				*ptr = __floats2half2_rn(v.x, v.y);
 			}
 		}
-		gemv_phase<DT, TP>(c, a, ep);
+		gemv_phase<DT, TP>(c, a, ep, ph);
 		stamp(c, l, k, 3);
 	}
 	if (a.mode == kGreedy) {
@@ -1379,9 +1644,10 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_c
 				if (a.tokens_out) a.tokens_out[step] = bi;
 				a.ctl[CTL_STEP] = step + 1;
 				a.ctl[CTL_TOKEN] = bi;
-				a.ctl[CTL_POS] = c.pos + 1;
+				const int pos1 = sm_misc()[kMiscPos] + 1;
+				a.ctl[CTL_POS] = pos1;
 				int ks, kp, kl;
-				derive_ring(c.pos + 1, a.max_seq_len, &ks, &kp, &kl);
+				derive_ring(pos1, a.max_seq_len, &ks, &kp, &kl);
 				a.ctl[CTL_SINK] = ks, a.ctl[CTL_KVPOS] = kp, a.ctl[CTL_KVLEN] = kl;
 			}
 		}

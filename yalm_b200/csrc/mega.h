@@ -83,6 +83,14 @@ struct Args {
 	int tp_world, tp_rank;
 	int vocab_base;             // first vocabulary row of this rank
 	float *x2;                  // second residual buffer (x ping-pongs across the in-kernel all-reduces)
+	// Flagged hand-over buffers (single GPU, see decode_mega.cuh "flagged hand-over"): every entry is one 64-bit word
+	// {fp32 value, u32 flag}, flag = seq << 10 | (producing phase + 1); zero before the first launch.
+	unsigned long long *ll_x;   // [2][dim]: [0] x after wo, [1] x after w2
+	unsigned long long *ll_hb;  // [hidden]
+	unsigned long long *ll_att; // [q_dim]
+	unsigned long long *ll_acc; // attention partials, (n_kv, grid, G, HD)
+	unsigned long long *ll_ml;  // (n_kv, grid, G, 2): {max, flag}, {sum, flag}
+	unsigned seq;               // launch number of this inference state, starts at 1
 	char *tp_peer[kTpMaxWorld]; // every rank's region (kTpOff*), [tp_rank] = this rank's own
 };
 

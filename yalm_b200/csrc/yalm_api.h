@@ -119,6 +119,8 @@ struct InferenceState {
 	unsigned *mega_sync() const { return _mega_sync; }
 	float *mega_amax_val() const { return _mega_amax_val; }
 	int *mega_amax_idx() const { return _mega_amax_idx; }
+	unsigned long long *mega_ll() const { return _mega_ll; }
+	unsigned next_mega_seq() { return ++_mega_seq; }
 
 private:
 	std::shared_ptr<Config> _config;
@@ -142,6 +144,8 @@ private:
 	float *_mega_acc = nullptr, *_mega_ml = nullptr, *_mega_amax_val = nullptr;
 	unsigned *_mega_counters = nullptr, *_mega_sync = nullptr;
 	int *_mega_amax_idx = nullptr;
+	unsigned long long *_mega_ll = nullptr; // flagged hand-over buffers: x[2][dim] | hb | att | acc | ml (mega.h: Args::ll_*)
+	unsigned _mega_seq = 0;
 	void *_arena = nullptr; // one device allocation behind all of the above
 };
 
