@@ -63,6 +63,23 @@ def main():
     cb = np.where(ok, (q[..., 3] - q[..., 6]) * us, np.nan)
     lines.append(f"attn detail: units {np.nanmean(un):.2f} [{np.nanmax(un, 0).mean():.2f}]  merge+publish {np.nanmean(mp):.2f} "
                  f"[{np.nanmax(mp, 0).mean():.2f}] (merge {np.nanmean(mg):.2f} [{np.nanmax(mg, 0).mean():.2f}])  combine(last CTA) {np.nanmean(cb):.2f} [{np.nanmax(cb, 0).mean():.2f}]")
+    # flagged hand-over detail (GEMV phases): slots 4 / 5 = tiles done / staged on the GPU-wide clock (ns), 6 / 7 = SM clock when
+    # the sampled words were there / when this thread's words were loaded and verified
+    if p[:, 1:, 2, 5].max() > 0:
+        prev = {0: 4, 2: None, 3: 2, 4: 3}
+        for ph in (0, 3, 4, 2):
+            q = p[:, 1:, ph, :]
+            smp = (q[..., 6] - q[..., 1]) * us
+            lod = (q[..., 7] - q[..., 6]) * us
+            rst = (q[..., 2] - q[..., 7]) * us
+            txt_ = f"hand-over into {PH[ph]:10s}: wait for sampled words {smp.mean():5.2f}  load+verify {lod.mean():5.2f}  norm/store {rst.mean():5.2f}"
+            if prev[ph] is not None:
+                e = p[:, 1:, prev[ph], 4] if ph != 0 else p[:, :-1, prev[ph], 4]          # producer phase: tiles done (ns)
+                st = q[..., 5]
+                last = e.max(0)
+                txt_ += (f" | producer end skew (last - mean) {(last - e.mean(0)).mean() / 1e3:5.2f} us, last producer end -> staged: "
+                         f"mean {(st - last).mean() / 1e3:5.2f} us, min {(st - last).min(0).mean() / 1e3:5.2f}, max {(st - last).max(0).mean() / 1e3:5.2f}")
+            lines.append(txt_)
     lines.append(f"{'token total':12s} {tot[0]:9.1f} {tot[1]:8.1f} {tot[2]:8.1f} {tot[3]:8.1f}   (us per token)")
     txt = "\n".join(lines)
     print(txt)

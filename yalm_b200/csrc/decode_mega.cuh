@@ -344,6 +344,11 @@ __device__ __forceinline__ void stamp(Ctx &c, int layer, int phase, int k) {
 	if (c.prof && c.tid == 0) {
 		long long *row = c.prof + ((size_t)layer * kProfPhases + phase) * kProfSlots;
 		row[k] = clock64();
+		if (phase != 1 && (k == 2 || k == 3)) { // GEMV phases: slots 4 / 5 = the same two events on the GPU-wide clock (cross-CTA skew)
+			unsigned long long g;
+			asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g));
+			row[k == 3 ? 4 : 5] = (long long)g;
+		}
 #ifdef YALM_MEGA_TRACE
 		if (k == 3 && phase != 1) row[4] = c.wait_cycles, c.wait_cycles = 0; // attention: slot 4 = combine probe
 #endif
@@ -802,12 +807,29 @@ __device__ __forceinline__ void stage_vec(Ctx &c, const Args &a, const float *sr
 // still be reading c.vec in their tile loops).
 template <int DT>
 __device__ __forceinline__ void stage_vec_ll(Ctx &c, const Args &a, const unsigned long long *src, int n, const float *rms_w,
-                                             unsigned flag, const float4 (&wv)[kNormCache]) {
+                                             unsigned flag, const float4 (&wv)[kNormCache], long long *probe) {
 	constexpr int EP = WTraits<DT>::EP;
-	constexpr int NC = kNormCache;
+	constexpr int NC = kNormCache; // wider batches (8, 12 float4 per thread) made ptxas spill all over the kernel
 	float4 cache[NC];
-	bool first = true;
 	float ss = 0.f;
+	// 148 CTAs x 352 threads polling the same few KB slow down the very stores they wait for (measured: ~5 us per
+	// hand-over).  So one warp per CTA samples 32 words spread over the vector until they are there, everybody else
+	// waits at the CTA barrier — which also ends the previous phase for this CTA: its warps may still be reading c.vec
+	// in their tile loops — and only then all threads load (and verify: stragglers are re-read below).
+	if (c.warp == 0) {
+		const int at = max(0, (int)((long)(c.lane + 1) * n / 32) - 1);
+		unsigned long long w = ll_load1(src + at);
+		if (!ll_ok(w, flag)) {
+			const long long t0 = clock64();
+			do {
+				__nanosleep(40);
+				if (clock64() - t0 > kTimeoutCycles) __trap();
+				w = ll_load1(src + at);
+			} while (!ll_ok(w, flag));
+		}
+	}
+	if (probe && c.tid == 0) probe[6] = clock64(); // profile: the sampled words are there
+	cbar();
 	for (int b0 = 0; b0 < n; b0 += NC * kCT * 4) { // one batch = NC float4 per thread (a single batch for n <= 5632); uniform trip count
 		const int e0 = b0 + c.tid * 4;
 		unsigned pending = 0;
@@ -832,8 +854,6 @@ __device__ __forceinline__ void stage_vec_ll(Ctx &c, const Args &a, const unsign
 			for (int i = 0; i < NC; ++i)
 				ss += cache[i].x * cache[i].x + cache[i].y * cache[i].y + cache[i].z * cache[i].z + cache[i].w * cache[i].w;
 		} else {
-			if (first) cbar(); // CTA-uniform: every thread walks every batch
-			first = false;
 #pragma unroll
 			for (int i = 0; i < NC; ++i) {
 				const int e = e0 + i * kCT * 4;
@@ -841,6 +861,7 @@ __device__ __forceinline__ void stage_vec_ll(Ctx &c, const Args &a, const unsign
 			}
 		}
 	}
+	if (probe && c.tid == 0) probe[7] = clock64(); // profile: this thread's words are loaded and verified
 	if (rms_w) {
 		// reference formula and association order (src/infer.cpp:134-144): o = x * (1/sqrt(ss/n + eps)) * w
 		ss = cons_sum(c, ss); // its CTA barriers come before any store to c.vec
@@ -1135,10 +1156,10 @@ __device__ __forceinline__ void combine_head(const float *ws_acc, const float *w
 }
 
 // Distributed combine of one KV head (flagged hand-over): this CTA is participant `pi` of the head's `cnt` CTAs that own
-// a chunk and produces outputs [pi, pi+1) * G*HD / cnt.  Out of line with scalar arguments: its registers must not
-// weigh on the attention unit loop.
+// a chunk and produces outputs [pi, pi+1) * G*HD / cnt.  Called from the phase loop (in front of the wo staging step)
+// with a recomputed split rather than from attention_consume: nothing of it may be live across the attention unit loop.
 template <int HD, int G>
-__device__ __noinline__ void ll_combine(const unsigned long long *ll_ml, const unsigned long long *ll_acc, unsigned long long *ll_att,
+__device__ __forceinline__ void ll_combine(const unsigned long long *ll_ml, const unsigned long long *ll_acc, unsigned long long *ll_att,
                                         float *att_out, int kvh, int ncta, int c0, int nc, int nch, int pi, unsigned wflag, int tid) {
 	const int cnt = min(nc, nch);
 	const int o_lo = (int)((unsigned)pi * (G * HD) / cnt), o_hi = (int)((unsigned)(pi + 1) * (G * HD) / cnt);
@@ -1446,9 +1467,6 @@ __device__ __forceinline__ void attention_consume(Ctx &c, const Args &a, const L
 		// partials (max, sum, acc) of all participants directly — no arrival counter, no barrier, no fence.  Summed in
 		// CTA order with the same weights on every run: deterministic.
 		stamp(c, layer, 1, 6);
-		ll_combine<HD, G>(a.ll_ml, a.ll_acc, a.ll_att, a.att_out, kvh, ncta, sp.c0, sp.nc, nch, nch >= sp.nc ? c.cta - sp.c0 : sp.k0,
-		                  wflag, c.tid);
-		if (c.prof && c.tid == 0) c.prof[((size_t)layer * kProfPhases + 1) * kProfSlots + 4] = clock64();
 		return;
 	}
 	cbar(); // the partial's stores happen-before the release below
@@ -1566,8 +1584,15 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_c
 			                     (size_t)(k == 3 ? 0 : a.tp_world) * kTpCapFloats;
 			stage_vec<DT>(c, a, k == 3 ? a.x : a.x2, n, rms, -1, wv, slots, k == 3 ? a.x2 : a.x);
 		} else if (LL && ph > 0) {
+			if (YALM_MEGA_LL_ATTN && k == 2) { // distributed attention combine of this CTA's head slice (flags of phase ph - 1)
+				const int C = kStageBytes / (4 * HD), nch = (c.kv_len + C - 1) / C;
+				const AttnSplit sp = attn_split(c.cta, c.ncta, a.n_kv_heads, nch);
+				if (sp.nu > 0)
+					ll_combine<HD, G>(a.ll_ml, a.ll_acc, a.ll_att, a.att_out, sp.kvh, c.ncta, sp.c0, sp.nc, nch,
+					                  nch >= sp.nc ? c.cta - sp.c0 : sp.k0, rflag, c.tid);
+			}
 			const unsigned long long *lsrc = k == 2 ? a.ll_att : k == 3 ? a.ll_x : k == 4 ? a.ll_hb : a.ll_x + a.dim;
-			stage_vec_ll<DT>(c, a, lsrc, n, rms, rflag, wv);
+			stage_vec_ll<DT>(c, a, lsrc, n, rms, rflag, wv, c.prof ? c.prof + ((size_t)l * kProfPhases + k) * kProfSlots : nullptr);
 		} else {
 			stage_vec<DT>(c, a, src, n, rms, ph == 0 ? sm_misc()[kMiscToken] : -1, wv);
 		}
