@@ -129,6 +129,10 @@ __device__ __forceinline__ unsigned ld_acquire(const unsigned *p) {
 #endif
 // 1: the attention partials are flagged too and every participating CTA combines a slice of the head's outputs
 // (ll_combine); 0: arrival counter + combine on the last CTA of the head (combine_head), only att_out is flagged.
+// Every CTA reads every word of a flagged vector at the same moment, and an L2 slice hands out a line to one reader at a
+// time: measured 1.5 us for the 32 KB of x and 5 us for the 112 KB of hb, three times the aggregate L2 rate.  So the
+// producers write kLLRep copies (different lines, different slices; the copies cost no instructions — the otherwise
+// idle lanes of the epilogue store them) and CTA c reads copy c % kLLRep.
 #ifndef YALM_MEGA_LL_ATTN
 #define YALM_MEGA_LL_ATTN 0
 #endif
@@ -902,6 +906,7 @@ struct Epi {
 template <int DT, int R, bool TP>
 __device__ __forceinline__ void gemv_consume(Ctx &c, const Args &a, Epi &ep, int ph) {
 	constexpr bool LL = YALM_MEGA_LL && !TP;
+	constexpr int NREP = LL ? kLLRep : 1; // flagged vectors are written kLLRep times (lane -> replica): see kLLRep
 	const unsigned wflag = a.seq << 10 | (unsigned)(ph + 1); // flagged hand-over: the next phase polls for this
 	using T = WTraits<DT>;
 	constexpr int EP = T::EP, CH = 32 * EP, Q = EP / 4;
@@ -919,11 +924,11 @@ __device__ __forceinline__ void gemv_consume(Ctx &c, const Args &a, Epi &ep, int
 		const int g = g_first + (b8 + warp) * c.ncta;
 		// residual operand of the wo / w2 epilogue: issue the L2 read now, it is consumed after the tiles
 		float resid = 0.f;
-		if (!TP && (kind == kWO || kind == kW2) && lane < R) {
+		if (!TP && (kind == kWO || kind == kW2) && lane < R * NREP) { // lane = replica * R + row of the group (epilogue below)
 			// flagged hand-over: x after wo lives in ll_x[0] (complete: this CTA polled all of it when it staged w1/w3);
 			// x before wo is the plain copy written behind w2 of the layer before, on the far side of a grid barrier
-			if (LL && kind == kW2) resid = ll_val(ll_load1(a.ll_x + (long)g * R + lane));
-			else resid = __ldcg(a.x + (long)g * R + lane);
+			if (LL && kind == kW2) resid = ll_val(ll_load1(a.ll_x + (size_t)(lane / R) * a.dim + (long)g * R + lane % R));
+			else resid = __ldcg(a.x + (long)g * R + lane % R);
 		}
 		float2 acc2[R];
 #pragma unroll
@@ -1001,16 +1006,17 @@ __device__ __forceinline__ void gemv_consume(Ctx &c, const Args &a, Epi &ep, int
 			}
 		} else if (kind == kFFN) {
 			constexpr int RH = R > 1 ? R / 2 : 1;
-			if (t < RH) {
+			if (t < RH * NREP) { // every lane holds all sums: lane = replica * RH + row
+				const int tr = t % RH;
 				float gt = acc[0], up = acc[RH < R ? RH : 0];
 #pragma unroll
 				for (int r = 1; r < RH; ++r)
-					if (t == r) gt = acc[r], up = acc[RH + r < R ? RH + r : 0];
-				const long row = (long)g * RH + t;
+					if (tr == r) gt = acc[r], up = acc[RH + r < R ? RH + r : 0];
+				const long row = (long)g * RH + tr;
 				if (DT == YALM_F8E4M3 && ep.scale0) gt *= ep.scale0[row], up *= ep.scale1[row];
 				gt = a.act == YALM_ACT_GELU ? act_gelu(gt) : act_silu(gt);
-				a.hb[row] = gt * up;
-				if (LL) ll_store(a.ll_hb + row, gt * up, wflag);
+				if (t < RH) a.hb[row] = gt * up;
+				if (LL) ll_store(a.ll_hb + (size_t)(t / RH) * a.hidden + row, gt * up, wflag);
 			}
 		} else if (TP) {
 			// tensor parallel: the rows are partial sums (wo / w2: this rank's slice of the input dimension) or this
@@ -1039,20 +1045,21 @@ __device__ __forceinline__ void gemv_consume(Ctx &c, const Args &a, Epi &ep, int
 				else if (R == 2) *reinterpret_cast<float2 *>(dst) = make_float2(vv[0], vv[R > 1 ? 1 : 0]);
 				else dst[0] = vv[0];
 			}
-		} else if (t < R) {
+		} else if (t < (kind == kLM ? R : R * NREP)) { // wo / w2: lane = replica * R + row
+			const int tr = t % R;
 			float v = acc[0];
 #pragma unroll
 			for (int r = 1; r < R; ++r)
-				if (t == r) v = acc[r];
-			const long row = (long)g * R + t;
+				if (tr == r) v = acc[r];
+			const long row = (long)g * R + tr;
 			if (DT == YALM_F8E4M3 && ep.scale0) v *= ep.scale0[row];
 			if (kind == kLM) {
 				a.logits[row] = v;
 				if (v > ep.best_v) ep.best_v = v, ep.best_i = (int)row; // a lane's rows ascend: first maximum wins
 			} else {
 				// x += W v (src/infer.cpp:335-337, 381-383)
-				if (LL) ll_store(a.ll_x + (kind == kW2 ? a.dim : 0) + row, resid + v, wflag);
-				if (!LL || kind == kW2) a.x[row] = resid + v;
+				if (LL) ll_store(a.ll_x + (size_t)((kind == kW2 ? kLLRep : 0) + t / R) * a.dim + row, resid + v, wflag);
+				if ((!LL || kind == kW2) && t < R) a.x[row] = resid + v;
 			}
 		}
 	}
@@ -1082,7 +1089,7 @@ __device__ __forceinline__ void unpack8(uint4 v, float (&f)[8]) {
 template <int HD, int G>
 __device__ __forceinline__ void combine_head(const float *ws_acc, const float *ws_ml, float *att_out, float *wts, float *scratch,
                                           int kvh, int ncta, int nch, int b_lo, int b_hi, long long *probe,
-                                          unsigned long long *ll_att = nullptr, unsigned wflag = 0) {
+                                          unsigned long long *ll_att = nullptr, unsigned wflag = 0, int n_q = 0) {
 	constexpr int W = kConsumerWarps;
 	constexpr int kInFlight = 20;  // independent L2 reads per thread and output
 	const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -1149,8 +1156,11 @@ __device__ __forceinline__ void combine_head(const float *ws_acc, const float *w
 		att_out[(size_t)kvh * G * HD + i0] = o0;
 		if (two) att_out[(size_t)kvh * G * HD + i1] = o1;
 		if (ll_att) { // flagged hand-over: the wo staging step polls these
-			ll_store(ll_att + (size_t)kvh * G * HD + i0, o0, wflag);
-			if (two) ll_store(ll_att + (size_t)kvh * G * HD + i1, o1, wflag);
+#pragma unroll
+			for (int rp = 0; rp < kLLRep; ++rp) {
+				ll_store(ll_att + (size_t)rp * n_q + (size_t)kvh * G * HD + i0, o0, wflag);
+				if (two) ll_store(ll_att + (size_t)rp * n_q + (size_t)kvh * G * HD + i1, o1, wflag);
+			}
 		}
 	}
 }
@@ -1160,7 +1170,7 @@ __device__ __forceinline__ void combine_head(const float *ws_acc, const float *w
 // with a recomputed split rather than from attention_consume: nothing of it may be live across the attention unit loop.
 template <int HD, int G>
 __device__ __forceinline__ void ll_combine(const unsigned long long *ll_ml, const unsigned long long *ll_acc, unsigned long long *ll_att,
-                                        float *att_out, int kvh, int ncta, int c0, int nc, int nch, int pi, unsigned wflag, int tid) {
+                                        float *att_out, int kvh, int ncta, int c0, int nc, int nch, int pi, unsigned wflag, int tid, int n_q) {
 	const int cnt = min(nc, nch);
 	const int o_lo = (int)((unsigned)pi * (G * HD) / cnt), o_hi = (int)((unsigned)(pi + 1) * (G * HD) / cnt);
 	constexpr int U = 4; // participants in flight per thread
@@ -1210,7 +1220,8 @@ __device__ __forceinline__ void ll_combine(const unsigned long long *ll_ml, cons
 		}
 		const float out = v / ls;
 		att_out[(size_t)kvh * G * HD + o] = out;
-		ll_store(ll_att + (size_t)kvh * G * HD + o, out, wflag); // polled by the wo staging step
+#pragma unroll
+		for (int rp = 0; rp < kLLRep; ++rp) ll_store(ll_att + (size_t)rp * n_q + (size_t)kvh * G * HD + o, out, wflag); // polled by the wo staging step
 	}
 }
 
@@ -1482,7 +1493,7 @@ __device__ __forceinline__ void attention_consume(Ctx &c, const Args &a, const L
 	stamp(c, layer, 1, 6);
 	if (sm_misc()[0]) // CTA-uniform
 		combine_head<HD, G>(a.ws_acc, a.ws_ml, a.att_out, wts, wsm, kvh, ncta, nch, sp.c0, sp.c0 + sp.nc - 1,
-		                    c.prof ? c.prof + ((size_t)layer * kProfPhases + 1) * kProfSlots + 4 : nullptr, LL ? a.ll_att : nullptr, wflag);
+		                    c.prof ? c.prof + ((size_t)layer * kProfPhases + 1) * kProfSlots + 4 : nullptr, LL ? a.ll_att : nullptr, wflag, a.q_dim);
 }
 
 __device__ __forceinline__ void derive_ring(int pos, int max_seq_len, int *kv_sink, int *kv_pos, int *kv_len) {
@@ -1589,9 +1600,10 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_c
 				const AttnSplit sp = attn_split(c.cta, c.ncta, a.n_kv_heads, nch);
 				if (sp.nu > 0)
 					ll_combine<HD, G>(a.ll_ml, a.ll_acc, a.ll_att, a.att_out, sp.kvh, c.ncta, sp.c0, sp.nc, nch,
-					                  nch >= sp.nc ? c.cta - sp.c0 : sp.k0, rflag, c.tid);
+					                  nch >= sp.nc ? c.cta - sp.c0 : sp.k0, rflag, c.tid, a.q_dim);
 			}
-			const unsigned long long *lsrc = k == 2 ? a.ll_att : k == 3 ? a.ll_x : k == 4 ? a.ll_hb : a.ll_x + a.dim;
+			const unsigned long long *lsrc = k == 2 ? a.ll_att : k == 3 ? a.ll_x : k == 4 ? a.ll_hb : a.ll_x + (size_t)kLLRep * a.dim;
+			lsrc += (size_t)(c.cta % kLLRep) * n; // this CTA's replica
 			stage_vec_ll<DT>(c, a, lsrc, n, rms, rflag, wv, c.prof ? c.prof + ((size_t)l * kProfPhases + k) * kProfSlots : nullptr);
 		} else {
 			stage_vec<DT>(c, a, src, n, rms, ph == 0 ? sm_misc()[kMiscToken] : -1, wv);

@@ -20,6 +20,10 @@ constexpr int kThreads = (kConsumerWarps + kProducerWarps) * 32;
 constexpr int kMaxStages = 24;
 constexpr int kSmemHeader = 1280; // rope table, reduction scratch, release counters, mbarriers in front of the ring
 constexpr int kTraceEvents = 1 << 16;
+#ifndef YALM_MEGA_LL_REP
+#define YALM_MEGA_LL_REP 4
+#endif
+constexpr int kLLRep = YALM_MEGA_LL_REP; // copies of every flagged hand-over vector (decode_mega.cuh); 1, 2 or 4
 constexpr int kProfileSlots = 6 * 8; // per (CTA, layer): phases x slots, see decode_mega.cuh
 
 // ---- tensor parallelism inside the kernel (N GPUs of one NVSwitch domain) ---------------------------------------------
@@ -85,9 +89,9 @@ struct Args {
 	float *x2;                  // second residual buffer (x ping-pongs across the in-kernel all-reduces)
 	// Flagged hand-over buffers (single GPU, see decode_mega.cuh "flagged hand-over"): every entry is one 64-bit word
 	// {fp32 value, u32 flag}, flag = seq << 10 | (producing phase + 1); zero before the first launch.
-	unsigned long long *ll_x;   // [2][dim]: [0] x after wo, [1] x after w2
-	unsigned long long *ll_hb;  // [hidden]
-	unsigned long long *ll_att; // [q_dim]
+	unsigned long long *ll_x;   // [2][kLLRep][dim]: [0] x after wo, [1] x after w2
+	unsigned long long *ll_hb;  // [kLLRep][hidden]
+	unsigned long long *ll_att; // [kLLRep][q_dim]
 	unsigned long long *ll_acc; // attention partials, (n_kv, grid, G, HD)
 	unsigned long long *ll_ml;  // (n_kv, grid, G, 2): {max, flag}, {sum, flag}
 	unsigned seq;               // launch number of this inference state, starts at 1

@@ -230,7 +230,8 @@ void InferenceState::cuda() {
 	    {(void **)&_mega_sync, 256},
 	    {(void **)&_mega_amax_val, sizeof(float) * (size_t)sms},
 	    {(void **)&_mega_amax_idx, sizeof(int) * (size_t)sms},
-	    {(void **)&_mega_ll, 8 * ((size_t)2 * c.dim + lhid + (size_t)lh * c.head_dim + (size_t)sms * lh * c.head_dim + (size_t)sms * lh * 2)},
+	    {(void **)&_mega_ll, 8 * (yalm::mega::kLLRep * ((size_t)2 * c.dim + lhid + (size_t)lh * c.head_dim) +
+	                              (size_t)sms * lh * c.head_dim + (size_t)sms * lh * 2)},
 	};
 	size_t total = 0;
 	for (auto &s : slots) total += align_up(s.bytes, 256);
@@ -650,8 +651,9 @@ int Model::launch_mega(InferenceState &s, int token, int pos, int mode, long lon
 	a.moe_logits = s.moe_weights(), a.active_w = s.active_experts_weights(), a.active_e = s.active_experts();
 	a.ws_acc = s.mega_acc(), a.ws_ml = s.mega_ml(), a.head_counters = s.mega_counters(), a.sync = s.mega_sync();
 	a.amax_val = s.mega_amax_val(), a.amax_idx = s.mega_amax_idx();
-	a.ll_x = s.mega_ll(), a.ll_hb = a.ll_x + (size_t)2 * c.dim, a.ll_att = a.ll_hb + c.local_hidden();
-	a.ll_acc = a.ll_att + (size_t)a.q_dim, a.ll_ml = a.ll_acc + (size_t)_mega->plan.grid * a.q_dim;
+	constexpr size_t rep = yalm::mega::kLLRep;
+	a.ll_x = s.mega_ll(), a.ll_hb = a.ll_x + rep * 2 * c.dim, a.ll_att = a.ll_hb + rep * c.local_hidden();
+	a.ll_acc = a.ll_att + rep * a.q_dim, a.ll_ml = a.ll_acc + (size_t)_mega->plan.grid * a.q_dim;
 	a.seq = s.next_mega_seq();
 	a.ctl = s.ctl(), a.tokens_out = s.tokens_dev();
 	a.token = token, a.pos = pos, a.mode = mode;
