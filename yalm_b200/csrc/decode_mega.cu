@@ -146,10 +146,10 @@ int launch(const Plan &p, const Args &a, cudaStream_t st) {
 	Args args = a;
 	args.stages = p.stages, args.vec_floats = p.vec_floats;
 	memcpy(args.shape, p.shape, sizeof(args.shape));
-	static const int debug = getenv("YALM_MEGA_DEBUG") ? atoi(getenv("YALM_MEGA_DEBUG")) : 0;
-	static const int max_stages = getenv("YALM_MEGA_STAGES") ? atoi(getenv("YALM_MEGA_STAGES")) : 0;
+	const int debug = getenv("YALM_MEGA_DEBUG") ? atoi(getenv("YALM_MEGA_DEBUG")) : 0;
+	const int max_stages = getenv("YALM_MEGA_STAGES") ? atoi(getenv("YALM_MEGA_STAGES")) : 0;
 	args.debug = debug;
-	static const int ahead = getenv("YALM_MEGA_L2_AHEAD") ? atoi(getenv("YALM_MEGA_L2_AHEAD")) : 0;
+	const int ahead = getenv("YALM_MEGA_L2_AHEAD") ? atoi(getenv("YALM_MEGA_L2_AHEAD")) : 0;
 	args.l2_ahead = ahead;
 	if (max_stages >= 2 && max_stages < args.stages) args.stages = max_stages;
 	void *params[] = {&args};

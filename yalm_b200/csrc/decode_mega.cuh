@@ -74,15 +74,17 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void *src, uint32_t
 	    : "memory");
 }
 // Fire-and-forget L2 prefetch of a global range (no completion tracking, never blocks the issuing thread).
-__device__ __forceinline__ void bulk_prefetch_l2(const void *src, uint32_t bytes) {
-#ifdef YALM_PREFETCH_TMA
-	asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src), "r"(bytes) : "memory");
-#else
+__device__ __forceinline__ void bulk_prefetch_l2(const void *src, uint32_t bytes, bool tma = false) {
+	if (tma) { // one request to the copy engine (debug & 16)
+		asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src), "r"(bytes) : "memory");
+		return;
+	}
+	{
 	// per-line prefetches through the load/store unit: the bulk form goes through the copy engine, which then
 	// handles every byte twice (measured: slower than no prefetch at all)
 	const char *p = static_cast<const char *>(src);
 	for (uint32_t o = 0; o < bytes; o += 128) asm volatile("prefetch.global.L2 [%0];" ::"l"(p + o) : "memory");
-#endif
+	}
 }
 __device__ __forceinline__ uint64_t policy_evict_first() {
 	uint64_t p;
@@ -133,6 +135,9 @@ __device__ __forceinline__ unsigned ld_acquire(const unsigned *p) {
 // time: measured 1.5 us for the 32 KB of x and 5 us for the 112 KB of hb, three times the aggregate L2 rate.  So the
 // producers write kLLRep copies (different lines, different slices; the copies cost no instructions — the otherwise
 // idle lanes of the epilogue store them) and CTA c reads copy c % kLLRep.
+#ifndef YALM_MEGA_LL_SAMPLE
+#define YALM_MEGA_LL_SAMPLE 1 // 0: every thread polls its own words from the start (A/B)
+#endif
 #ifndef YALM_MEGA_LL_ATTN
 #define YALM_MEGA_LL_ATTN 0
 #endif
@@ -425,6 +430,7 @@ struct Producer {
 	int batch; // min(stages, 32)
 	int ahead;   // L2 look-ahead distance in tiles (0: off)
 	bool steady; // false: only the next phase's prefix is fetched (during the phase-boundary bubble), nothing in-phase
+	bool pf_tma; // L2 look-ahead through cp.async.bulk.prefetch.L2 (one request per range) instead of per-line prefetches
 
 	__device__ __forceinline__ PhaseDesc describe(const Args &a, int ph, int rot, int HD, int B) {
 		PhaseDesc d;
@@ -499,13 +505,13 @@ struct Producer {
 		const size_t row_bytes = (size_t)K * B;
 		if (nk == 1) {
 			if (bar) bulk_g2s(dst, m + row0 * row_bytes, (uint32_t)(nrows * row_bytes), bar, policy);
-			else bulk_prefetch_l2(m + row0 * row_bytes, (uint32_t)(nrows * row_bytes));
+			else bulk_prefetch_l2(m + row0 * row_bytes, (uint32_t)(nrows * row_bytes), pf_tma);
 		} else {
 			const uint32_t tb = (uint32_t)KT * B;
 			for (int r = 0; r < nrows; ++r) {
 				const char *src = m + (row0 + r) * row_bytes + (size_t)kc * tb;
 				if (bar) bulk_g2s(dst + r * tb, src, tb, bar, policy);
-				else bulk_prefetch_l2(src, tb);
+				else bulk_prefetch_l2(src, tb, pf_tma);
 			}
 		}
 	}
@@ -556,16 +562,16 @@ struct Producer {
 			const int u = d.u0 + unit, kvh = u / d.nch, r0 = (u % d.nch) * (kStageBytes / (4 * HD));
 			const uint32_t bytes = (uint32_t)min(kStageBytes / (4 * HD), c.kv_len - r0) * HD * 2;
 			const size_t off = ((size_t)kvh * max_seq + r0) * HD;
-			bulk_prefetch_l2(d.kc + off, bytes);
-			bulk_prefetch_l2(d.vc + off, bytes);
+			bulk_prefetch_l2(d.kc + off, bytes, pf_tma);
+			bulk_prefetch_l2(d.vc + off, bytes, pf_tma);
 			return;
 		}
 		const int g = d.g_first + unit * c.ncta;
 		const size_t row_bytes = (size_t)d.K * B;
 		if (d.kind == kFFN) {
 			const int rh = d.sh.R / 2;
-			bulk_prefetch_l2(d.m0 + (size_t)g * rh * row_bytes, (uint32_t)(rh * row_bytes));
-			bulk_prefetch_l2(d.m1 + (size_t)g * rh * row_bytes, (uint32_t)(rh * row_bytes));
+			bulk_prefetch_l2(d.m0 + (size_t)g * rh * row_bytes, (uint32_t)(rh * row_bytes), pf_tma);
+			bulk_prefetch_l2(d.m1 + (size_t)g * rh * row_bytes, (uint32_t)(rh * row_bytes), pf_tma);
 		} else {
 			long row = (long)g * d.sh.R;
 			const char *m = d.m0;
@@ -573,7 +579,7 @@ struct Producer {
 				if (row >= d.rows0 + d.rows1) row -= d.rows0 + d.rows1, m = d.m2;
 				else if (row >= d.rows0) row -= d.rows0, m = d.m1;
 			}
-			bulk_prefetch_l2(m + row * row_bytes, (uint32_t)(d.sh.R * row_bytes));
+			bulk_prefetch_l2(m + row * row_bytes, (uint32_t)(d.sh.R * row_bytes), pf_tma);
 		}
 	}
 	// Every phase of the token, in order (phase -1 is empty: it only fetches the prefix of phase 0).
@@ -820,7 +826,7 @@ __device__ __forceinline__ void stage_vec_ll(Ctx &c, const Args &a, const unsign
 	// hand-over).  So one warp per CTA samples 32 words spread over the vector until they are there, everybody else
 	// waits at the CTA barrier — which also ends the previous phase for this CTA: its warps may still be reading c.vec
 	// in their tile loops — and only then all threads load (and verify: stragglers are re-read below).
-	if (c.warp == 0) {
+	if (YALM_MEGA_LL_SAMPLE && c.warp == 0) {
 		const int at = max(0, (int)((long)(c.lane + 1) * n / 32) - 1);
 		unsigned long long w = ll_load1(src + at);
 		if (!ll_ok(w, flag)) {
@@ -1549,7 +1555,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_c
 
 	if (c.warp >= kConsumerWarps) {
 		// ================================ producers ================================
-		Producer p{c, (a.debug & 8) ? 0ull : policy_evict_first(), min(c.S, 32), (a.debug & 8) ? 0 : abs(a.l2_ahead), a.l2_ahead > 0};
+		Producer p{c, (a.debug & 8) ? 0ull : policy_evict_first(), min(c.S, 32), (a.debug & 8) ? 0 : abs(a.l2_ahead), a.l2_ahead > 0, (a.debug & 16) != 0};
 		p.run(a, HD, B);
 		return;
 	}
