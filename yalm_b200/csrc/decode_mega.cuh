@@ -135,8 +135,14 @@ __device__ __forceinline__ unsigned ld_acquire(const unsigned *p) {
 // time: measured 1.5 us for the 32 KB of x and 5 us for the 112 KB of hb, three times the aggregate L2 rate.  So the
 // producers write kLLRep copies (different lines, different slices; the copies cost no instructions — the otherwise
 // idle lanes of the epilogue store them) and CTA c reads copy c % kLLRep.
+#ifndef YALM_MEGA_LL_NS
+#define YALM_MEGA_LL_NS 32 // first back-off of a polling thread in ns (doubles up to x16)
+#endif
+#ifndef YALM_MEGA_LL_FIRST
+#define YALM_MEGA_LL_FIRST 0 // 1: a thread polls only its first float4 until it is there, then loads the rest (A/B)
+#endif
 #ifndef YALM_MEGA_LL_SAMPLE
-#define YALM_MEGA_LL_SAMPLE 1 // 0: every thread polls its own words from the start (A/B)
+#define YALM_MEGA_LL_SAMPLE 0 // 1: one warp samples the vector first, the others wait at the CTA barrier (A/B: 333 vs 341 tok/s once the vectors are replicated)
 #endif
 #ifndef YALM_MEGA_LL_ATTN
 #define YALM_MEGA_LL_ATTN 0
@@ -172,7 +178,7 @@ __device__ __forceinline__ bool ll_load4(const unsigned long long *p, unsigned f
 __device__ __forceinline__ void ll_backoff(int *round, long long *t0) {
 	if (*round == 0) *t0 = clock64();
 	else if (clock64() - *t0 > kTimeoutCycles) __trap();
-	__nanosleep(32u << min(*round, 4));
+	__nanosleep((unsigned)YALM_MEGA_LL_NS << min(*round, 4));
 	++*round;
 }
 __device__ __forceinline__ float ll_wait1(const unsigned long long *p, unsigned flag) {
@@ -840,6 +846,15 @@ __device__ __forceinline__ void stage_vec_ll(Ctx &c, const Args &a, const unsign
 	}
 	if (probe && c.tid == 0) probe[6] = clock64(); // profile: the sampled words are there
 	cbar();
+	if (YALM_MEGA_LL_FIRST && c.tid * 4 < n) {
+		float4 t;
+		if (!ll_load4(src + c.tid * 4, flag, &t)) {
+			int round = 0;
+			long long t0 = 0;
+			do ll_backoff(&round, &t0);
+			while (!ll_load4(src + c.tid * 4, flag, &t));
+		}
+	}
 	for (int b0 = 0; b0 < n; b0 += NC * kCT * 4) { // one batch = NC float4 per thread (a single batch for n <= 5632); uniform trip count
 		const int e0 = b0 + c.tid * 4;
 		unsigned pending = 0;
