@@ -926,8 +926,10 @@ struct Epi {
 // and its first lanes run the epilogue.  Nothing here synchronises with the other warps.
 template <int DT, int R, bool TP>
 __device__ __forceinline__ void gemv_consume(Ctx &c, const Args &a, Epi &ep, int ph) {
-	constexpr bool LL = YALM_MEGA_LL && !TP;
-	constexpr int NREP = LL ? kLLRep : 1; // flagged vectors are written kLLRep times (lane -> replica): see kLLRep
+	constexpr bool LL = YALM_MEGA_LL && !TP; // x: single GPU only (tensor parallel: x crosses the GPUs through the peer slots)
+	constexpr bool LLH = YALM_MEGA_LL;       // hb (and att_out): local vectors, flagged in both modes
+	constexpr int NREP = LL ? kLLRep : 1;    // flagged vectors are written kLLRep times (lane -> replica): see kLLRep
+	constexpr int NREPH = LLH ? kLLRep : 1;
 	const unsigned wflag = a.seq << 10 | (unsigned)(ph + 1); // flagged hand-over: the next phase polls for this
 	using T = WTraits<DT>;
 	constexpr int EP = T::EP, CH = 32 * EP, Q = EP / 4;
@@ -1027,7 +1029,7 @@ __device__ __forceinline__ void gemv_consume(Ctx &c, const Args &a, Epi &ep, int
 			}
 		} else if (kind == kFFN) {
 			constexpr int RH = R > 1 ? R / 2 : 1;
-			if (t < RH * NREP) { // every lane holds all sums: lane = replica * RH + row
+			if (t < RH * NREPH) { // every lane holds all sums: lane = replica * RH + row
 				const int tr = t % RH;
 				float gt = acc[0], up = acc[RH < R ? RH : 0];
 #pragma unroll
@@ -1037,7 +1039,7 @@ __device__ __forceinline__ void gemv_consume(Ctx &c, const Args &a, Epi &ep, int
 				if (DT == YALM_F8E4M3 && ep.scale0) gt *= ep.scale0[row], up *= ep.scale1[row];
 				gt = a.act == YALM_ACT_GELU ? act_gelu(gt) : act_silu(gt);
 				if (t < RH) a.hb[row] = gt * up;
-				if (LL) ll_store(a.ll_hb + (size_t)(t / RH) * a.hidden + row, gt * up, wflag);
+				if (LLH) ll_store(a.ll_hb + (size_t)(t / RH) * a.hidden + row, gt * up, wflag);
 			}
 		} else if (TP) {
 			// tensor parallel: the rows are partial sums (wo / w2: this rank's slice of the input dimension) or this
@@ -1590,14 +1592,15 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_c
 		const bool reduced = TP && ph > 0 && (k == 3 || k == 0 || k == 5);
 		// flagged hand-over (single GPU): only the QKV -> attention boundary keeps its grid barrier, every other
 		// phase polls its input vector in the staging step
-		constexpr bool LL = YALM_MEGA_LL && !TP;
+		constexpr bool LL = YALM_MEGA_LL != 0;
+		const bool flagged = LL && ph > 0 && (TP ? k == 2 || k == 4 : k != 1); // this phase polls its input instead of a barrier
 		const unsigned rflag = a.seq << 10 | (unsigned)ph; // what the phase before this one produced
 		if (reduced) tp_barrier(c, a);
-		else if (ph > 0 && (!LL || k == 1)) grid_barrier(c, a.sync);
+		else if (ph > 0 && !flagged) grid_barrier(c, a.sync);
 		stamp(c, l, k, 1);
 		if (k == 1) { // attention: q comes from registers, nothing to stage
 			stamp(c, l, k, 2);
-			attention_consume<HD, G, YALM_MEGA_LL && !TP>(c, a, L, l);
+			attention_consume<HD, G, YALM_MEGA_LL != 0>(c, a, L, l);
 			stamp(c, l, k, 3);
 			continue;
 		}
@@ -1615,7 +1618,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_c
 			const float *slots = reinterpret_cast<const float *>(a.tp_peer[a.tp_rank] + kTpOffSlots) +
 			                     (size_t)(k == 3 ? 0 : a.tp_world) * kTpCapFloats;
 			stage_vec<DT>(c, a, k == 3 ? a.x : a.x2, n, rms, -1, wv, slots, k == 3 ? a.x2 : a.x);
-		} else if (LL && ph > 0) {
+		} else if (flagged) {
 			if (YALM_MEGA_LL_ATTN && k == 2) { // distributed attention combine of this CTA's head slice (flags of phase ph - 1)
 				const int C = kStageBytes / (4 * HD), nch = (c.kv_len + C - 1) / C;
 				const AttnSplit sp = attn_split(c.cta, c.ncta, a.n_kv_heads, nch);
