@@ -18,7 +18,7 @@ def main():
     import torch
     import torch.distributed as dist
     from conftest import LOGIT_TOL, golden_case
-    from yalm_b200 import api
+    from yalm_b200 import api, yalm_file as yf
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
@@ -33,6 +33,11 @@ def main():
     bad = 0
     for name in ["tiny-fp32", "tiny-fp16", "tiny-moe-fp16", "tiny-gelu-clip-fp16"]:
         fx, img = golden_case(name)
+        md = yf.load(img)[0]
+        if int(md["n_kv_heads"]) % world or int(md["hidden_dim"]) % world or int(md["vocab_size"]) % world:
+            if rank == 0:
+                print(f"{name}: {md['n_kv_heads']} KV heads / hidden {md['hidden_dim']} / vocab {md['vocab_size']} do not split {world} ways -> SKIP", flush=True)
+            continue
         m = api.Model(img, 0).cuda(local, rank, world)
         s = api.InferenceState(m)
         toks, lg = s.generate(fx["prompt"].tolist(), len(fx["tokens"]), keep_logits=True)
