@@ -50,6 +50,25 @@ def peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def ncu_traffic():
+    """dram__bytes_read.sum + dram__bytes_write.sum of one megakernel launch on the headline workload, from the newest
+    committed `ncu --set full` summary (profiles/*_full_summary.txt, written by tools/ncu_summary.py).  None if absent."""
+    import glob
+    import re
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "*mega*full_summary.txt")))
+    if not files:
+        return None, None
+    txt = open(files[-1]).read()
+    unit = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "Tbyte": 1e12}
+    tot = 0.0
+    for key in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+        m = re.search(rf"^{re.escape(key)}\s+([0-9.]+)\s+(\w+)\s*$", txt, re.M)
+        if not m or m.group(2) not in unit:
+            return None, None
+        tot += float(m.group(1)) * unit[m.group(2)]
+    return tot, os.path.relpath(files[-1], ROOT) + " (captured launch: hydrate step at pos 3 = no LM head, no KV: 13.96 GB algorithmic)"
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
@@ -284,12 +303,15 @@ def main():
         else:
             kname = "ffn_glu_kernel (rmsnorm + w1/w3 GEMV + GLU)"
         achieved = ffn_bytes / (ffn_us * 1e-6) / 1e9
+        # DRAM bytes of one launch from the committed ncu capture: only for the workload it was taken on
+        traffic, traffic_src = ncu_traffic() if (mega and world == 1 and args.workload == "mistral-7b-fp16-4k" and not args.layers) else (None, None)
         line = dict(base, impl="ours", value=tok_s, ms_per_step=dev_ms / K, clocks=clk,
                     e2e={"value": K / e2e_s, "unit": "tok/s", "h2d_bytes_per_step": 8, "d2h_bytes_per_step": 4 * V},
                     gpu_launches=(model.launches(api.MODE_LOGITS) + (0 if mega else 1)) * K,
                     roofline={"bound": "hbm", "kernel": kname,
                               "achieved": achieved, "peak": peak, "peak_source": peak_src, "unit": "GB/s",
-                              "frac": achieved / peak, "traffic": None, "bytes_per_launch": ffn_bytes,
+                              "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src,
+                              "bytes_per_launch": ffn_bytes,
                               "launch_us": ffn_us},
                     cpu_baseline=cpu_baseline,
                     whole_step={"weight_bytes_per_token": wbytes, "kv_bytes_per_token": kvbytes,

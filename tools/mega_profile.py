@@ -43,17 +43,17 @@ def main():
     t_end = p[:, -1, 5, 3]
     lines.append(f"{desc}; pos {args.pos}; grid {p.shape[0]} CTAs; {p.shape[1]} layers")
     lines.append(f"kernel span per CTA (first stamp -> last): mean {np.mean(t_end - t_begin) * us:.1f} us")
-    lines.append(f"{'phase':12s} {'barrier':>9s} {'stage':>8s} {'tiles':>8s} {'starved':>8s}   (us per layer, mean over CTAs; max over CTAs in brackets)")
+    lines.append(f"{'phase':12s} {'barrier':>9s} {'stage':>8s} {'tiles':>8s}   (us per layer, mean over CTAs; max over CTAs in brackets; stage = poll + load + norm of the flagged input vector)")
     tot = np.zeros(4)
     for ph in range(6):
         q = p[:, :, ph, :] if ph < 5 else p[:, -1:, ph, :]
         bar = (q[..., 1] - q[..., 0]) * us
         stg = (q[..., 2] - q[..., 1]) * us
         til = (q[..., 3] - q[..., 2]) * us
-        stv = q[..., 4] * us
+        stv = np.zeros_like(til)  # slot 4 is the GPU-wide clock now (the starvation counter needs -DYALM_MEGA_TRACE)
         nl = q.shape[1]
-        lines.append(f"{PH[ph]:12s} {bar.mean():9.2f} {stg.mean():8.2f} {til.mean():8.2f} {stv.mean():8.2f}   "
-                     f"[{bar.max(0).mean():.2f} {stg.max(0).mean():.2f} {til.max(0).mean():.2f} {stv.max(0).mean():.2f}] x{nl}")
+        lines.append(f"{PH[ph]:12s} {bar.mean():9.2f} {stg.mean():8.2f} {til.mean():8.2f}   "
+                     f"[{bar.max(0).mean():.2f} {stg.max(0).mean():.2f} {til.max(0).mean():.2f}] x{nl}")
         tot += np.array([bar.mean() * nl, stg.mean() * nl, til.mean() * nl, stv.mean() * nl])
     q = p[:, :, 1, :]
     ok = q[..., 5] > 0
@@ -72,7 +72,7 @@ def main():
             smp = (q[..., 6] - q[..., 1]) * us
             lod = (q[..., 7] - q[..., 6]) * us
             rst = (q[..., 2] - q[..., 7]) * us
-            txt_ = f"hand-over into {PH[ph]:10s}: wait for sampled words {smp.mean():5.2f}  load+verify {lod.mean():5.2f}  norm/store {rst.mean():5.2f}"
+            txt_ = f"hand-over into {PH[ph]:10s}: entry -> polling starts {smp.mean():5.2f}  poll+load+verify {lod.mean():5.2f}  norm/store {rst.mean():5.2f}"
             if prev[ph] is not None:
                 e = p[:, 1:, prev[ph], 4] if ph != 0 else p[:, :-1, prev[ph], 4]          # producer phase: tiles done (ns)
                 st = q[..., 5]
@@ -80,7 +80,7 @@ def main():
                 txt_ += (f" | producer end skew (last - mean) {(last - e.mean(0)).mean() / 1e3:5.2f} us, last producer end -> staged: "
                          f"mean {(st - last).mean() / 1e3:5.2f} us, min {(st - last).min(0).mean() / 1e3:5.2f}, max {(st - last).max(0).mean() / 1e3:5.2f}")
             lines.append(txt_)
-    lines.append(f"{'token total':12s} {tot[0]:9.1f} {tot[1]:8.1f} {tot[2]:8.1f} {tot[3]:8.1f}   (us per token)")
+    lines.append(f"{'token total':12s} {tot[0]:9.1f} {tot[1]:8.1f} {tot[2]:8.1f}   (us per token)")
     txt = "\n".join(lines)
     print(txt)
     if args.out:
