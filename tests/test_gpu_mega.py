@@ -116,6 +116,55 @@ def test_mega_deterministic():
     assert (a == b).all()
 
 
+def test_mega_flagged_handover_two_states_interleaved():
+    """The phase hand-over words carry (launch number of the state, phase) flags and live in per-state buffers: a second
+    inference state of the same model driven in between — repeating every step in hydrate and in device-greedy mode; the
+    KV cache belongs to the model (src/model.h:193-301), so it rewrites the same rows with the same bits — must not
+    change a single bit of the first state's run (a stale word of the other state, an earlier launch or an earlier
+    phase accepted as current would show up here)."""
+    fx, img = golden_case("tiny-fp16")
+    prompt = fx["prompt"].tolist()
+    m = api.Model(img, 0).cuda()
+    assert m.uses_megakernel()
+    ref_state = api.InferenceState(m)
+    ref_t, ref_l = ref_state.generate(prompt, 12, keep_logits=True)
+    ref_state.close()
+    sa, sb = api.InferenceState(m), api.InferenceState(m)
+
+    def step(tok, pos, mode):
+        sa.forward(tok, pos, mode)
+        sb.forward(tok, pos, api.MODE_HYDRATE)
+        sb.generate_greedy(tok, pos, 1)
+
+    for pos in range(len(prompt)):
+        step(prompt[pos], pos, api.MODE_LOGITS if pos + 1 == len(prompt) else api.MODE_HYDRATE)
+    toks, lgs = [], []
+    for i in range(12):
+        lg = sa.logits().copy()
+        toks.append(int(np.argmax(lg)))
+        lgs.append(lg)
+        if i + 1 < 12:
+            step(toks[-1], len(prompt) + i, api.MODE_LOGITS)
+    assert toks == ref_t
+    assert (np.stack(lgs) == ref_l).all()
+    sa.close()
+    sb.close()
+    m.close()
+
+
+def test_mega_many_launches_stay_deterministic():
+    """600 launches on one state (the flag's launch number keeps growing): the same 40 tokens at the start and at the end."""
+    fx, img = golden_case("tiny-fp16")
+    m = api.Model(img, 0).cuda()
+    s = api.InferenceState(m)
+    first = s.generate_greedy(1, 0, 40)
+    for _ in range(13):
+        s.generate_greedy(1, 0, 40)
+    assert s.generate_greedy(1, 0, 40) == first
+    s.close()
+    m.close()
+
+
 def test_stream_probe_runs():
     us, by = api.bench_op("stream", iters=3, warmup=0)
     assert by / us / 1e3 > 1000.0        # GB/s: anything on a B200 streams faster than 1 TB/s
