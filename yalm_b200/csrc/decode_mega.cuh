@@ -1,17 +1,17 @@
 // Whole-token persistent decode kernel for sm_100a (see mega.h for the idea).
 //
-// Roles inside a CTA (one CTA per SM, cooperative launch so grid barriers are safe):
-//   warp 8      producer (all 32 lanes, one tile per lane and batch): walks this CTA's tile list for the WHOLE forward pass and issues
-//               cp.async.bulk (1-D TMA) copies global -> shared ring, completion on mbarriers.  It never
+// Roles inside a CTA (one CTA per SM, cooperative launch so grid barriers and flag polling are safe):
+//   last warp   producer (all 32 lanes, one tile per lane and batch): walks this CTA's tile list for the WHOLE forward pass and
+//               issues cp.async.bulk (1-D TMA) copies global -> shared ring, completion on mbarriers.  It never
 //               waits for activations, only for free ring stages, so weight tiles of phase p+1 are in
-//               flight while the consumers are still finishing (or barrier-waiting for) phase p.
-//   warps 0-7   consumers.  Per phase: grid barrier -> stage the input vector (rmsnorm fused) into shared
-//               memory -> tile loop.  In the tile loop every warp OWNS whole row groups (all K-split tiles
-//               of a group land on the same warp), so there is no intra-CTA synchronisation at all between
-//               two grid barriers: wait(full) -> fp32 dot products straight out of shared memory ->
+//               flight while the consumers are still finishing (or waiting for the input of) phase p.
+//   warps 0-10  consumers (kConsumerWarps).  Per phase: wait for the input vector — by polling its flagged words
+//               ("flagged hand-over" below; one grid barrier per layer remains, in front of attention) -> stage it
+//               (rmsnorm fused) into shared memory -> tile loop.  In the tile loop every warp OWNS whole row groups
+//               (all K-split tiles of a group land on the same warp), so there is no intra-CTA synchronisation at all
+//               inside a tile loop: wait(full) -> fp32 dot products straight out of shared memory ->
 //               release(empty) -> shuffle reduce -> the warp's own lanes run the fused epilogue (clip +
-//               RoPE + KV append / residual add / GLU / logits + arg-max).  Eight tiles are in progress per
-//               SM at any time, which is what hides the per-tile latency chain (mbarrier wait, LDS, shuffles).
+//               RoPE + KV append / residual add / GLU / logits + arg-max) and store the flagged result words.
 // Phases per layer: QKV | attention (split-K flash-decode over the head-major KV ring) | wo+residual |
 // w1/w3+GLU | w2+residual; then final norm + LM head (+ greedy arg-max and control-block advance).
 // Replaces, for one token, everything Model::_forward_cuda_build_graph launches (src/infer.cu:1041-1128,

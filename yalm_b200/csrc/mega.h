@@ -1,8 +1,9 @@
 // Whole-token persistent decode kernel ("megakernel"): one cooperative launch per token, one CTA per SM.
 // A producer warp streams every weight / KV tile of the forward pass through a shared-memory ring with
 // 1-D bulk async copies (TMA engine, mbarrier completion) in a fixed per-CTA order, running ahead of the
-// eight consumer warps by the depth of the ring, so the HBM pipe stays full across the ~160 phase
-// boundaries (grid barriers) of a 32-layer model instead of draining at every kernel launch.
+// consumer warps by the depth of the ring, so the HBM pipe stays full across the ~160 phase
+// boundaries of a 32-layer model instead of draining at every kernel launch.  Phases hand their vectors over as
+// flagged 64-bit words (Args::ll_*); one grid barrier per layer remains.
 // Host-side planning and launch; the kernel is in decode_mega.cu.
 #pragma once
 
