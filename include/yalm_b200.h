@@ -188,6 +188,15 @@ void yalm_tp_finalize(void);
  * (the reference is single-GPU). */
 int yalm_tp_shard_plan(const int *dims, int tensor, int rank, int size, long long *out);
 
+/* Planning arithmetic of the whole-token kernel, callable without a device (tests).  It replaces the launch geometry
+ * the reference hard-codes per kernel (src/infer.cu:745-880: one warp per output row, grids of d / 32 CTAs).
+ * yalm_mega_tile_plan: out20 = 5 GEMV kinds (qkv, wo, w1/w3, w2, lm head) x {rows per tile, columns per tile, K splits,
+ * row groups} for one rank's dimensions; row group g of a phase goes to CTA (rotation + g) % grid.
+ * yalm_mega_attn_split: out5 = {kv head, first CTA of the head, CTAs of the head, first chunk, chunks} of CTA `cta` for a
+ * context of `n_chunks` KV row chunks per head.  Both return YALM_EINVAL for shapes the kernel does not take. */
+int yalm_mega_tile_plan(int dtype, int dim, int q_dim, int kv_dim, int hidden, int vocab, int *out20);
+int yalm_mega_attn_split(int cta, int ncta, int n_kv_heads, int n_chunks, int *out5);
+
 const char *yalm_error_string(int code);
 const char *yalm_version(void);
 

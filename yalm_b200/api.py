@@ -30,7 +30,7 @@ SYMBOLS = [
     "yalm_model_device_bytes", "yalm_state_new", "yalm_state_free", "yalm_forward", "yalm_logits",
     "yalm_generate_greedy", "yalm_state_read", "yalm_forward_launches", "yalm_model_uses_megakernel", "yalm_mega_profile",
     "yalm_profile_ffn",
-    "yalm_tp_unique_id", "yalm_tp_init", "yalm_tp_finalize", "yalm_tp_shard_plan", "yalm_error_string", "yalm_version",
+    "yalm_tp_unique_id", "yalm_tp_init", "yalm_tp_finalize", "yalm_tp_shard_plan", "yalm_mega_tile_plan", "yalm_mega_attn_split", "yalm_error_string", "yalm_version",
 ]
 
 

@@ -83,12 +83,29 @@ static const void *kernel_of(int dtype, int head_dim, int g, bool tp) {
 	return nullptr;
 }
 
+// Tile shapes of the five GEMV kinds (qkv, wo, w1/w3, w2, lm head) for one rank's dimensions: rows per tile, columns per
+// tile, K splits, row groups.  Pure arithmetic (no device): plan() and the CPU tests (yalm_mega_tile_plan) share it.
+static bool plan_shapes(int dtype, int dim, int q_dim, int kv_dim, int hidden, int vocab, int (*shape)[4]) {
+	const int ep = ep_of(dtype), B = bytes_of(dtype);
+	if (!ep) return false;
+	Shape s[kNumKinds];
+	if (!tile_shape(q_dim, kv_dim, dim, B, ep, false, true, &s[kQKV])) return false;
+	if (!tile_shape(dim, 0, q_dim, B, ep, false, false, &s[kWO])) return false;
+	if (!tile_shape(hidden, 0, dim, B, ep, true, true, &s[kFFN])) return false;
+	if (!tile_shape(dim, 0, hidden, B, ep, false, false, &s[kW2])) return false;
+	if (!tile_shape(vocab, 0, dim, B, ep, false, false, &s[kLM])) return false;
+	s[kQKV].G = (q_dim + 2 * kv_dim) / s[kQKV].R, s[kWO].G = dim / s[kWO].R, s[kFFN].G = hidden / (s[kFFN].R / 2);
+	s[kW2].G = dim / s[kW2].R, s[kLM].G = vocab / s[kLM].R;
+	for (int k = 0; k < kNumKinds; ++k) shape[k][0] = s[k].R, shape[k][1] = s[k].KT, shape[k][2] = s[k].nk, shape[k][3] = s[k].G;
+	return true;
+}
+
 Plan plan(int dtype, int dim, int q_dim, int kv_dim, int head_dim, int hidden, int vocab, int n_heads, int n_kv_heads,
           int n_experts, int n_active, int max_seq_len, bool tp, int full_vocab) {
 	Plan p;
 	if (tp && (dim > kTpCapFloats || full_vocab > kTpMaxVocab)) return p;
 	p.tp = tp;
-	const int ep = ep_of(dtype), B = bytes_of(dtype);
+	const int ep = ep_of(dtype);
 	if (!ep || n_experts > 0) return p;
 	(void)n_active;
 	if (n_kv_heads <= 0 || n_heads % n_kv_heads) return p;
@@ -96,15 +113,7 @@ Plan plan(int dtype, int dim, int q_dim, int kv_dim, int head_dim, int hidden, i
 	p.kernel = kernel_of(dtype, head_dim, G, tp);
 	if (!p.kernel) return p;
 	if (dim % ep || q_dim % ep || hidden % ep || dim % 4 || q_dim % 4 || hidden % 4) return p;
-	Shape s[kNumKinds];
-	if (!tile_shape(q_dim, kv_dim, dim, B, ep, false, true, &s[kQKV])) return p;
-	if (!tile_shape(dim, 0, q_dim, B, ep, false, false, &s[kWO])) return p;
-	if (!tile_shape(hidden, 0, dim, B, ep, true, true, &s[kFFN])) return p;
-	if (!tile_shape(dim, 0, hidden, B, ep, false, false, &s[kW2])) return p;
-	if (!tile_shape(vocab, 0, dim, B, ep, false, false, &s[kLM])) return p;
-	s[kQKV].G = (q_dim + 2 * kv_dim) / s[kQKV].R, s[kWO].G = dim / s[kWO].R, s[kFFN].G = hidden / (s[kFFN].R / 2);
-	s[kW2].G = dim / s[kW2].R, s[kLM].G = vocab / s[kLM].R;
-	for (int k = 0; k < kNumKinds; ++k) p.shape[k][0] = s[k].R, p.shape[k][1] = s[k].KT, p.shape[k][2] = s[k].nk, p.shape[k][3] = s[k].G;
+	if (!plan_shapes(dtype, dim, q_dim, kv_dim, hidden, vocab, p.shape)) return p;
 	const DeviceInfo &di = device_info();
 	int coop = 0, dev = 0;
 	cudaGetDevice(&dev);
@@ -158,6 +167,22 @@ int launch(const Plan &p, const Args &a, cudaStream_t st) {
 
 } // namespace mega
 } // namespace yalm
+
+// Host-only planning arithmetic of the whole-token kernel, for tests without a device.
+extern "C" int yalm_mega_tile_plan(int dtype, int dim, int q_dim, int kv_dim, int hidden, int vocab, int *out20) {
+	if (!out20) return YALM_EINVAL;
+	int shape[5][4];
+	if (!yalm::mega::plan_shapes(dtype, dim, q_dim, kv_dim, hidden, vocab, shape)) return YALM_EINVAL;
+	for (int k = 0; k < 5; ++k)
+		for (int j = 0; j < 4; ++j) out20[4 * k + j] = shape[k][j];
+	return 0;
+}
+extern "C" int yalm_mega_attn_split(int cta, int ncta, int n_kv_heads, int n_chunks, int *out5) {
+	if (!out5 || ncta < 1 || cta < 0 || cta >= ncta || n_kv_heads < 1 || n_kv_heads > ncta || n_chunks < 1) return YALM_EINVAL;
+	const yalm::mega::AttnSplit sp = yalm::mega::attn_split(cta, ncta, n_kv_heads, n_chunks);
+	out5[0] = sp.kvh, out5[1] = sp.c0, out5[2] = sp.nc, out5[3] = sp.k0, out5[4] = sp.nu;
+	return 0;
+}
 
 // Streaming ceiling of the ring (GB/s = bytes / usec / 1e3): `iters` timed launches over a `bytes` buffer.
 extern "C" int yalm_stream_probe(size_t bytes, int iters, double *usec) {
