@@ -1,9 +1,11 @@
 #!/usr/bin/env python
-"""Sweep of the megakernel's run-time knobs on one loaded model (the knobs are read from the environment at every
-launch): tok/s of the on-device greedy loop at 4k context per setting.
+"""Sweep of the megakernel's run-time knobs on one loaded model (with YALM_MEGA_TUNE=1 the knobs are read from the
+environment at every launch): tok/s of the on-device greedy loop at 4k context per setting.
     python tools/mega_sweep.py "YALM_MEGA_L2_AHEAD=-16" "YALM_MEGA_L2_AHEAD=-16 YALM_MEGA_DEBUG=16" ..."""
 import os
 import sys
+
+os.environ["YALM_MEGA_TUNE"] = "1"  # the library re-reads its knobs at every launch
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)

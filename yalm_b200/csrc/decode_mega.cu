@@ -155,11 +155,21 @@ int launch(const Plan &p, const Args &a, cudaStream_t st) {
 	Args args = a;
 	args.stages = p.stages, args.vec_floats = p.vec_floats;
 	memcpy(args.shape, p.shape, sizeof(args.shape));
-	const int debug = getenv("YALM_MEGA_DEBUG") ? atoi(getenv("YALM_MEGA_DEBUG")) : 0;
-	const int max_stages = getenv("YALM_MEGA_STAGES") ? atoi(getenv("YALM_MEGA_STAGES")) : 0;
-	args.debug = debug;
-	const int ahead = getenv("YALM_MEGA_L2_AHEAD") ? atoi(getenv("YALM_MEGA_L2_AHEAD")) : 0;
-	args.l2_ahead = ahead;
+	// Timing-experiment knobs.  Read once; with YALM_MEGA_TUNE=1 (tools/mega_sweep.py) they are re-read at every launch.
+	struct Knobs {
+		int debug, max_stages, ahead;
+		static int env(const char *name) {
+			const char *v = getenv(name);
+			return v ? atoi(v) : 0;
+		}
+		static Knobs read() { return {env("YALM_MEGA_DEBUG"), env("YALM_MEGA_STAGES"), env("YALM_MEGA_L2_AHEAD")}; }
+	};
+	static const bool tune = Knobs::env("YALM_MEGA_TUNE") != 0;
+	static const Knobs fixed = Knobs::read();
+	const Knobs kn = tune ? Knobs::read() : fixed;
+	const int max_stages = kn.max_stages;
+	args.debug = kn.debug;
+	args.l2_ahead = kn.ahead;
 	if (max_stages >= 2 && max_stages < args.stages) args.stages = max_stages;
 	void *params[] = {&args};
 	return (int)cudaLaunchCooperativeKernel(p.kernel, dim3(p.grid), dim3(kThreads), params, p.smem, st);
