@@ -92,7 +92,9 @@ static bool plan_shapes(int dtype, int dim, int q_dim, int kv_dim, int hidden, i
 	if (!tile_shape(q_dim, kv_dim, dim, B, ep, false, true, &s[kQKV])) return false;
 	if (!tile_shape(dim, 0, q_dim, B, ep, false, false, &s[kWO])) return false;
 	if (!tile_shape(hidden, 0, dim, B, ep, true, true, &s[kFFN])) return false;
-	if (!tile_shape(dim, 0, hidden, B, ep, false, false, &s[kW2])) return false;
+	// w2 split: the tiles of a phase cover one column half (K = hidden / 2)
+	if (YALM_MEGA_W2_SPLIT && hidden % (2 * ep)) return false;
+	if (!tile_shape(dim, 0, YALM_MEGA_W2_SPLIT ? hidden / 2 : hidden, B, ep, false, false, &s[kW2])) return false;
 	if (!tile_shape(vocab, 0, dim, B, ep, false, false, &s[kLM])) return false;
 	s[kQKV].G = (q_dim + 2 * kv_dim) / s[kQKV].R, s[kWO].G = dim / s[kWO].R, s[kFFN].G = hidden / (s[kFFN].R / 2);
 	s[kW2].G = dim / s[kW2].R, s[kLM].G = vocab / s[kLM].R;
@@ -121,7 +123,7 @@ Plan plan(int dtype, int dim, int q_dim, int kv_dim, int head_dim, int hidden, i
 	if (!coop || di.sms < 1) return p;
 	p.grid = di.sms;
 	if (tp && p.grid > kTpMaxGrid) return p;
-	int vf = std::max(padded(dim, ep), std::max(padded(q_dim, ep), padded(hidden, ep)));
+	int vf = std::max(padded(dim, ep), std::max(padded(q_dim, ep), padded(YALM_MEGA_W2_SPLIT ? hidden / 2 : hidden, ep)));
 	if (n_kv_heads > p.grid) return p; // a CTA's attention units must span at most kHeadSlots KV heads
 	// the attention unit split runs in 32-bit arithmetic: (units) x (grid + 1) must stay below 2^31
 	const long long units = (long long)n_kv_heads * (max_seq_len / (kStageBytes / (4 * head_dim)) + 1);

@@ -281,6 +281,14 @@ __host__ __device__ inline bool tile_shape(int rows, int rows_b, int K, int B, i
 // Optional phase profile (Args.prof != null): per CTA, per (layer, phase) kProfSlots clock64 values written by
 // consumer thread 0: [0] phase entered (before the grid barrier) [1] barrier passed [2] input vector staged
 // [3] tiles + epilogue done; [4] cycles warp 0 spent waiting for full ring stages (starvation = HBM-bound).
+// Phase index of a launch -> (layer, kind of phase k, column half).  k: 0 qkv, 1 attention, 2 wo, 3 w1/w3, 4 w2, 5 LM head.
+constexpr int kPPL = YALM_MEGA_W2_SPLIT ? 6 : 5; // phases per layer
+__device__ __forceinline__ void phase_of(int ph, int n_layers, int *l, int *k, int *half) {
+	const int j = ph % kPPL;
+	*l = min(ph / kPPL, n_layers - 1);
+	*half = j == 5 ? 1 : 0;
+	*k = ph < n_layers * kPPL ? (j == 5 ? 4 : j) : 5;
+}
 constexpr int kProfSlots = 8, kProfPhases = 6; // phases: qkv, attn, wo, ffn, w2, lm(+argmax) (last layer slot only)
 
 // Shared-memory layout: the small arrays sit at fixed offsets in front of the ring, so their addresses are
@@ -444,9 +452,10 @@ struct Producer {
 		d.m0 = d.m1 = d.m2 = nullptr, d.rows0 = d.rows1 = d.K = 0, d.g_first = d.full_groups = d.full_tiles = d.nb_last = 0;
 		d.kc = d.vc = nullptr, d.nch = 1, d.u0 = 0;
 		d.sh.R = d.sh.KT = d.sh.nk = d.sh.G = 1;
-		const int n_phases = a.n_layers * 5 + (a.mode != kHydrate ? 1 : 0);
+		const int n_phases = a.n_layers * kPPL + (a.mode != kHydrate ? 1 : 0);
 		if (ph >= n_phases) return d;
-		const int l = min(ph / 5, a.n_layers - 1), k = ph < a.n_layers * 5 ? ph % 5 : 5;
+		int l, k, half;
+		phase_of(ph, a.n_layers, &l, &k, &half);
 		const Layer &L = a.layers[l];
 		if (k == 1) {
 			const int C = kStageBytes / (4 * HD);
@@ -463,7 +472,9 @@ struct Producer {
 		switch (k) {
 		case 2: d.kind = kWO, d.m0 = L.wo, d.rows0 = a.dim, d.K = a.q_dim; break;
 		case 3: d.kind = kFFN, d.m0 = L.w1, d.m1 = L.w3, d.rows0 = a.hidden; break;
-		case 4: d.kind = kW2, d.m0 = L.w2, d.rows0 = a.dim, d.K = a.hidden; break;
+		case 4: // d.K stays the row stride; with the split the tiles cover the columns of one half (shape kW2: K = hidden / 2)
+			d.kind = kW2, d.m0 = L.w2 + (YALM_MEGA_W2_SPLIT ? (size_t)half * (a.hidden / 2) * B : 0), d.rows0 = a.dim, d.K = a.hidden;
+			break;
 		case 5: d.kind = kLM, d.m0 = a.wcls, d.rows0 = a.vocab; break;
 		default: break;
 		}
@@ -476,6 +487,7 @@ struct Producer {
 		d.full_groups = NL / kConsumerWarps * kConsumerWarps, d.full_tiles = d.full_groups * d.sh.nk;
 		d.nb_last = NL - d.full_groups;
 		d.rot_next = (rot + d.sh.G) % c.ncta;
+		if (YALM_MEGA_W2_SPLIT && k == 4 && half == 0) d.rot_next = rot; // the second half keeps the row -> CTA map
 		return d;
 	}
 
@@ -509,7 +521,7 @@ struct Producer {
 	__device__ __forceinline__ void rows_copy(uint32_t dst, uint32_t bar, const char *m, long row0, int nrows, int K, int KT,
 	                                          int kc, int nk, int B) {
 		const size_t row_bytes = (size_t)K * B;
-		if (nk == 1) {
+		if (nk == 1 && KT == K) { // whole rows: one contiguous range
 			if (bar) bulk_g2s(dst, m + row0 * row_bytes, (uint32_t)(nrows * row_bytes), bar, policy);
 			else bulk_prefetch_l2(m + row0 * row_bytes, (uint32_t)(nrows * row_bytes), pf_tma);
 		} else {
@@ -591,7 +603,7 @@ struct Producer {
 	// Every phase of the token, in order (phase -1 is empty: it only fetches the prefix of phase 0).
 	// `ahead` is in ring stages (kStageBytes); per phase it becomes a whole number of look-ahead units.
 	__device__ __forceinline__ void run(const Args &a, int HD, int B) {
-		const int n_phases = a.n_layers * 5 + (a.mode != kHydrate ? 1 : 0);
+		const int n_phases = a.n_layers * kPPL + (a.mode != kHydrate ? 1 : 0);
 		const uint32_t ahead_bytes = (uint32_t)ahead * kStageBytes;
 		PhaseDesc cur = describe(a, n_phases, 0, HD, B); // kNone
 		for (int ph = -1; ph < n_phases; ++ph) {
@@ -917,6 +929,7 @@ struct Epi {
 	const Layer *L;
 	const float *scale0, *scale1, *scale2; // fp8 row scales per matrix
 	int rows0, rows1;                      // QKV boundaries
+	int half;                              // w2 split: 0 / 1 = column half of this phase, -1 = w2 in one piece
 	float best_v;                          // LM head: running arg-max of this lane's rows
 	int best_i;
 };
@@ -950,7 +963,8 @@ __device__ __forceinline__ void gemv_consume(Ctx &c, const Args &a, Epi &ep, int
 		if (!TP && (kind == kWO || kind == kW2) && lane < R * NREP) { // lane = replica * R + row of the group (epilogue below)
 			// flagged hand-over: x after wo lives in ll_x[0] (complete: this CTA polled all of it when it staged w1/w3);
 			// x before wo is the plain copy written behind w2 of the layer before, on the far side of a grid barrier
-			if (LL && kind == kW2) resid = ll_val(ll_load1(a.ll_x + (size_t)(lane / R) * a.dim + (long)g * R + lane % R));
+			if (YALM_MEGA_W2_SPLIT && kind == kW2 && ep.half == 1) resid = __ldcg(a.w2_tmp + (long)g * R + lane % R); // x + first half
+			else if (LL && kind == kW2) resid = ll_val(ll_load1(a.ll_x + (size_t)(lane / R) * a.dim + (long)g * R + lane % R));
 			else resid = __ldcg(a.x + (long)g * R + lane % R);
 		}
 		float2 acc2[R];
@@ -1060,7 +1074,17 @@ __device__ __forceinline__ void gemv_consume(Ctx &c, const Args &a, Epi &ep, int
 				const int row = a.vocab_base + (int)row0 + t;
 				if (v > ep.best_v) ep.best_v = v, ep.best_i = row;
 			}
-			if (lane < a.tp_world) {
+			if (YALM_MEGA_W2_SPLIT && kind == kW2 && ep.half == 1) { // add the first half's sums (same warp, earlier phase)
+#pragma unroll
+				for (int r = 0; r < R; ++r) vv[r] += __ldcg(a.w2_tmp + row0 + r);
+			}
+			if (YALM_MEGA_W2_SPLIT && kind == kW2 && ep.half == 0) { // first half: park the sums, nothing crosses the GPUs yet
+				float v = vv[0];
+#pragma unroll
+				for (int r = 1; r < R; ++r)
+					if (t == r) v = vv[r];
+				if (t < R) a.w2_tmp[row0 + t] = v;
+			} else if (lane < a.tp_world) {
 				float *dst = kind == kLM ? reinterpret_cast<float *>(a.tp_peer[lane] + kTpOffLogits) + a.vocab_base + row0
 				                         : reinterpret_cast<float *>(a.tp_peer[lane] + kTpOffSlots) +
 				                               (size_t)((kind == kW2 ? a.tp_world : 0) + a.tp_rank) * kTpCapFloats + row0;
@@ -1081,13 +1105,17 @@ __device__ __forceinline__ void gemv_consume(Ctx &c, const Args &a, Epi &ep, int
 				if (v > ep.best_v) ep.best_v = v, ep.best_i = (int)row; // a lane's rows ascend: first maximum wins
 			} else {
 				// x += W v (src/infer.cpp:335-337, 381-383)
+				if (YALM_MEGA_W2_SPLIT && kind == kW2 && ep.half == 0) {
+					if (t < R) a.w2_tmp[row] = resid + v; // x + first column half; the second half's phase finishes the row
+				} else {
 				if (LL) ll_store(a.ll_x + (size_t)((kind == kW2 ? kLLRep : 0) + t / R) * a.dim + row, resid + v, wflag);
 				if ((!LL || kind == kW2) && t < R) a.x[row] = resid + v;
+				}
 			}
 		}
 	}
 	c.it = base + (uint32_t)(NL * sh.nk);
-	c.rot = (c.rot + sh.G) % c.ncta;
+	if (!(YALM_MEGA_W2_SPLIT && kind == kW2 && ep.half == 0)) c.rot = (c.rot + sh.G) % c.ncta; // second half: same row -> CTA map
 }
 
 template <int DT, bool TP>
@@ -1457,7 +1485,7 @@ __device__ __forceinline__ void attention_consume(Ctx &c, const Args &a, const L
 	stamp(c, layer, 1, 5);
 
 	// ---- merge the warps, publish the CTA's partial, the last CTA of the head to arrive combines ------------
-	const unsigned wflag = a.seq << 10 | (unsigned)(layer * 5 + 2); // flagged hand-over: this phase is ph = 5 * layer + 1
+	const unsigned wflag = a.seq << 10 | (unsigned)(layer * kPPL + 2); // flagged hand-over: this phase is ph = kPPL * layer + 1
 	constexpr bool LLC = LL && YALM_MEGA_LL_ATTN;
 	float *ew = wts; // [W][G] merge weights (wts is not in use before the combine)
 	if (c.tid < W * G) { // weight of warp w's record for head g, computed once
@@ -1579,9 +1607,11 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_c
 
 	// ================================ consumers ================================
 	Epi ep;
-	const int n_phases = a.n_layers * 5 + (a.mode != kHydrate ? 1 : 0);
+	const int n_phases = a.n_layers * kPPL + (a.mode != kHydrate ? 1 : 0);
 	for (int ph = 0; ph < n_phases; ++ph) { // one loop body = one call site per phase function
-		const int l = min(ph / 5, a.n_layers - 1), k = ph < a.n_layers * 5 ? ph % 5 : 5;
+		int l, k, half;
+		phase_of(ph, a.n_layers, &l, &k, &half);
+		ep.half = YALM_MEGA_W2_SPLIT && k == 4 ? half : -1; // -1: w2 in one piece
 		const Layer &L = a.layers[l];
 		ep.L = &L;
 		stamp(c, l, k, 0);
@@ -1610,7 +1640,10 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_c
 		case 0: ep.kind = kQKV, ep.scale0 = L.sq, ep.scale1 = L.sk, ep.scale2 = L.sv, ep.rows0 = a.q_dim, ep.rows1 = a.kv_dim; break;
 		case 2: src = a.att_out, n = a.q_dim, ep.kind = kWO, ep.scale0 = L.so; break;
 		case 3: ep.kind = kFFN, ep.scale0 = L.s1, ep.scale1 = L.s3; break;
-		case 4: src = a.hb, n = a.hidden, ep.kind = kW2, ep.scale0 = L.s2; break;
+		case 4:
+			src = a.hb, n = a.hidden, ep.kind = kW2, ep.scale0 = L.s2;
+			if (YALM_MEGA_W2_SPLIT) n = a.hidden / 2, src += (size_t)half * n; // this phase's half of hb
+			break;
 		default: ep.kind = kLM, ep.scale0 = a.wcls_scale, ep.best_v = -FLT_MAX, ep.best_i = 0x7fffffff; break;
 		}
 		if (reduced) {
@@ -1627,8 +1660,10 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_c
 					                  nch >= sp.nc ? c.cta - sp.c0 : sp.k0, rflag, c.tid, a.q_dim);
 			}
 			const unsigned long long *lsrc = k == 2 ? a.ll_att : k == 3 ? a.ll_x : k == 4 ? a.ll_hb : a.ll_x + (size_t)kLLRep * a.dim;
-			lsrc += (size_t)(c.cta % kLLRep) * n; // this CTA's replica
-			stage_vec_ll<DT>(c, a, lsrc, n, rms, rflag, wv, c.prof ? c.prof + ((size_t)l * kProfPhases + k) * kProfSlots : nullptr);
+			lsrc += (size_t)(c.cta % kLLRep) * (k == 4 ? a.hidden : n); // this CTA's replica
+			if (YALM_MEGA_W2_SPLIT && k == 4) lsrc += (size_t)half * n;
+			// (the second half of hb carries the flag of the w1/w3 phase too: two phases back)
+			stage_vec_ll<DT>(c, a, lsrc, n, rms, YALM_MEGA_W2_SPLIT && k == 4 && half ? rflag - 1 : rflag, wv, c.prof ? c.prof + ((size_t)l * kProfPhases + k) * kProfSlots : nullptr);
 		} else {
 			stage_vec<DT>(c, a, src, n, rms, ph == 0 ? sm_misc()[kMiscToken] : -1, wv);
 		}

@@ -21,6 +21,13 @@ constexpr int kThreads = (kConsumerWarps + kProducerWarps) * 32;
 constexpr int kMaxStages = 24;
 constexpr int kSmemHeader = 1280; // rope table, reduction scratch, release counters, mbarriers in front of the ring
 constexpr int kTraceEvents = 1 << 16;
+// 1: w2 runs as two phases over the two column halves of the matrix with the same row -> CTA / warp / lane map; the
+// half-sums wait in Args::w2_tmp with the lane that made them (no hand-over in between).  The fp32 hb vector in shared
+// memory halves, which buys 3 ring stages.  Parity-green on B200 (all megakernel tests), but 4 % SLOWER on an 8-layer slice
+// of the 7B model (1218 vs 1271 tok/s): the extra phase costs more than the three stages give.  Off.
+#ifndef YALM_MEGA_W2_SPLIT
+#define YALM_MEGA_W2_SPLIT 0
+#endif
 #ifndef YALM_MEGA_LL_REP
 #define YALM_MEGA_LL_REP 4
 #endif
@@ -96,6 +103,7 @@ struct Args {
 	unsigned long long *ll_acc; // attention partials, (n_kv, grid, G, HD)
 	unsigned long long *ll_ml;  // (n_kv, grid, G, 2): {max, flag}, {sum, flag}
 	unsigned seq;               // launch number of this inference state, starts at 1
+	float *w2_tmp;              // [dim]: x + first column half of w2 (YALM_MEGA_W2_SPLIT), private to the lane that wrote it
 	char *tp_peer[kTpMaxWorld]; // every rank's region (kTpOff*), [tp_rank] = this rank's own
 };
 

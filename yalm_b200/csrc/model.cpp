@@ -230,6 +230,7 @@ void InferenceState::cuda() {
 	    {(void **)&_mega_sync, 256},
 	    {(void **)&_mega_amax_val, sizeof(float) * (size_t)sms},
 	    {(void **)&_mega_amax_idx, sizeof(int) * (size_t)sms},
+	    {(void **)&_mega_tmp, sizeof(float) * c.dim},
 	    {(void **)&_mega_ll, 8 * (yalm::mega::kLLRep * ((size_t)2 * c.dim + lhid + (size_t)lh * c.head_dim) +
 	                              (size_t)sms * lh * c.head_dim + (size_t)sms * lh * 2)},
 	};
@@ -655,6 +656,7 @@ int Model::launch_mega(InferenceState &s, int token, int pos, int mode, long lon
 	a.ll_x = s.mega_ll(), a.ll_hb = a.ll_x + rep * 2 * c.dim, a.ll_att = a.ll_hb + rep * c.local_hidden();
 	a.ll_acc = a.ll_att + rep * a.q_dim, a.ll_ml = a.ll_acc + (size_t)_mega->plan.grid * a.q_dim;
 	a.seq = s.next_mega_seq();
+	a.w2_tmp = s.mega_tmp();
 	a.ctl = s.ctl(), a.tokens_out = s.tokens_dev();
 	a.token = token, a.pos = pos, a.mode = mode;
 	return yalm::mega::launch(_mega->plan, a, s.stream());

@@ -120,6 +120,7 @@ struct InferenceState {
 	float *mega_amax_val() const { return _mega_amax_val; }
 	int *mega_amax_idx() const { return _mega_amax_idx; }
 	unsigned long long *mega_ll() const { return _mega_ll; }
+	float *mega_tmp() const { return _mega_tmp; }
 	unsigned next_mega_seq() { return ++_mega_seq; }
 
 private:
@@ -144,6 +145,7 @@ private:
 	float *_mega_acc = nullptr, *_mega_ml = nullptr, *_mega_amax_val = nullptr;
 	unsigned *_mega_counters = nullptr, *_mega_sync = nullptr;
 	int *_mega_amax_idx = nullptr;
+	float *_mega_tmp = nullptr; // x + first column half of w2 (YALM_MEGA_W2_SPLIT)
 	unsigned long long *_mega_ll = nullptr; // flagged hand-over buffers: x[2][dim] | hb | att | acc | ml (mega.h: Args::ll_*)
 	unsigned _mega_seq = 0;
 	void *_arena = nullptr; // one device allocation behind all of the above
