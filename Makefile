@@ -1,6 +1,7 @@
 # yalm_b200 build: one shared library (kernels + C ABI + C++ API), plus the reference-shaped CLIs.
 #   make            -> yalm_b200/libyalm_b200.so
-#   make cli        -> build/test (kernel benchmarks, the reference's `test -k <name>` command line)
+#   make cli        -> build/main (the reference's `main <ckpt> -d cuda ...` command line) and build/test (kernel
+#                      benchmarks, the reference's `test -k <name>` command line)
 #   make BUILD=build/x LIB=build/lib_x.so EXTRA=-DYALM_MEGA_LL=0   -> an A/B variant (YALM_B200_LIB=... selects it at run time)
 NVCC  ?= nvcc
 HOSTCXX := /usr/bin/g++
@@ -12,12 +13,12 @@ NVFLAGS := -std=c++17 -O3 -lineinfo $(EXTRA) $(ARCH) -ccbin $(HOSTCXX) -Xcompile
 LIB   := yalm_b200/libyalm_b200.so
 
 LIB_SRCS := $(CSRC)/ops_gemv.cu $(CSRC)/ops_attn.cu $(CSRC)/decode_mega.cu $(CSRC)/decode_mega_f32.cu $(CSRC)/decode_mega_f16.cu $(CSRC)/decode_mega_f8.cu $(CSRC)/model.cpp $(CSRC)/codec.cpp $(CSRC)/capi.cpp \
-            $(CSRC)/mem.cpp $(CSRC)/tp.cpp
+            $(CSRC)/mem.cpp $(CSRC)/tp.cpp $(CSRC)/ops_sample.cu $(CSRC)/sampler.cpp $(CSRC)/tokenizer.cpp
 LIB_OBJS := $(patsubst $(CSRC)/%,$(BUILD)/%.o,$(LIB_SRCS))
 HDRS := $(wildcard $(CSRC)/*.h $(CSRC)/*.cuh include/*.h)
 
 all: lib
-cli: $(BUILD)/test
+cli: $(BUILD)/test $(BUILD)/main
 lib: $(LIB)
 
 $(BUILD)/%.cu.o: $(CSRC)/%.cu $(HDRS)
@@ -33,6 +34,10 @@ $(LIB): $(LIB_OBJS)
 
 $(BUILD)/test: $(CSRC)/test.cpp $(LIB) $(HDRS)
 	$(NVCC) $(NVFLAGS) -x cu $(CSRC)/test.cpp -o $@ -Lyalm_b200 -lyalm_b200 \
+	    -Xlinker -rpath,'$$ORIGIN/../yalm_b200'
+
+$(BUILD)/main: $(CSRC)/main.cpp $(LIB) $(HDRS)
+	$(NVCC) $(NVFLAGS) -x cu $(CSRC)/main.cpp -o $@ -Lyalm_b200 -lyalm_b200 \
 	    -Xlinker -rpath,'$$ORIGIN/../yalm_b200'
 
 clean:

@@ -117,6 +117,18 @@ int yalm_lm_head(float *logits, const float *x, const float *rms_weight, const v
 int yalm_argmax_advance(const float *logits, int vocab, int *ctl, int max_seq_len, int *tokens_out,
                         yalm_stream_t s);
 
+/* Sampler::sample on the device (src/sampler.cpp:40-65): p_i = exp((l_i - max) / T) / sum, the first index whose
+ * running sum reaches r wins (vocab - 1 if none); r = uniform(seed, ctl.step) from a counter-based generator (the
+ * reference draws std::rand()).  Then the same control-block advance as yalm_argmax_advance.  temperature 0 = greedy. */
+int yalm_sample_advance(const float *logits, int vocab, int *ctl, int max_seq_len, int *tokens_out, float temperature,
+                        unsigned long long seed, yalm_stream_t s);
+/* One draw into *token_dev (device int) with r = uniform(seed, counter); temperature 0 = first-max arg-max. */
+int yalm_sample_device1(const float *logits, int vocab, float temperature, unsigned long long seed,
+                        unsigned long long counter, int *token_dev, yalm_stream_t s);
+/* Sampler::sample_prob (src/sampler.cpp:11-25) for n_rows logit rows (device, row stride vocab):
+ * probs[i] = softmax(logits[i, :])[targets[i]] — what perplexity mode needs per position (src/main.cpp:174-184). */
+int yalm_token_probs(const float *logits, int vocab, int n_rows, const int *targets, float *probs, yalm_stream_t s);
+
 /* Bare GEMV xout = W x (matmul<T>, src/infer.cu:234-248), device pointers. */
 int yalm_gemv(float *xout, const float *x, const void *w, const float *scale, int n, int d, int dtype,
               yalm_stream_t s);
@@ -127,6 +139,10 @@ int yalm_mha_host(float *xout, float *att, const uint16_t *kb, const uint16_t *v
                   int kv_len, int max_seq_len, int n_heads, int n_kv_heads);
 int yalm_ffn_host(float *xout, const float *x, const void *w1, const void *w2, const void *w3, const float *s1,
                   const float *s2, const float *s3, int hidden_dim, int dim, int act, int dtype);
+/* Host-pointer test entries of the device sampler: one draw with a caller-supplied r in [0, 1] (Sampler::sample with
+ * std::rand() / RAND_MAX replaced by r), and sample_prob for n_rows rows. */
+int yalm_sample_host(const float *logits, int vocab, float temperature, float r, int *token);
+int yalm_token_probs_host(const float *logits, int vocab, int n_rows, const int *targets, float *probs);
 /* Same ops timed on the device: `iters` launches after `warmup`, returns mean microseconds per
  * launch (CUDA events) in *usec.  This is what `./build/test -k <name>` prints. */
 int yalm_bench_op(const char *name, int iters, int warmup, double *usec, double *bytes);
@@ -157,6 +173,12 @@ float *yalm_logits(yalm_state *s); /* host, vocab_size fp32 */
  * each step's logits are copied back too (parity mode).  *device_ms (optional) = CUDA-event time. */
 int yalm_generate_greedy(yalm_model *m, yalm_state *s, int token, int pos, int n_gen, int *tokens_out,
                          float *logits_out, float *device_ms);
+/* The same loop with Sampler::sample on the device: temperature 0 = greedy, > 0 = one draw per step with
+ * r = uniform(seed, step).  4 bytes per token come back (the reference moves vocab * 4, src/model.cpp:338). */
+int yalm_generate(yalm_model *m, yalm_state *s, int token, int pos, int n_gen, float temperature,
+                  unsigned long long seed, int *tokens_out, float *logits_out, float *device_ms);
+/* Tests only: set the launch counter behind the megakernel's hand-over flags (exercises its wrap). */
+void yalm_state_debug_set_launch_seq(yalm_state *s, unsigned seq);
 /* Debug/parity taps: copy a device activation or one layer's KV rows to the host.
  * which: 0 x, 1 xb2(attn out), 2 hb, 3 q, 4 key_cache(layer), 5 value_cache(layer),
  * 6 active_experts (int), 7 active_experts_weights */
@@ -196,6 +218,12 @@ int yalm_tp_shard_plan(const int *dims, int tensor, int rank, int size, long lon
  * context of `n_chunks` KV row chunks per head.  Both return YALM_EINVAL for shapes the kernel does not take. */
 int yalm_mega_tile_plan(int dtype, int dim, int q_dim, int kv_dim, int hidden, int vocab, int *out20);
 int yalm_mega_attn_split(int cta, int ncta, int n_kv_heads, int n_chunks, int *out5);
+
+/* The CLI's tokenizer (greedy longest-prefix match + byte fallback, src/tokenizer.cpp:57-94; decode_one :44-55) over an
+ * in-memory .yalm image; host only.  yalm_tokenize returns the number of ids (out receives at most cap of them),
+ * yalm_detokenize the byte length of the text (out receives at most cap - 1 bytes + NUL); negative = error. */
+int yalm_tokenize(const void *image, size_t size, const char *text, int add_bos, int *out, int cap);
+int yalm_detokenize(const void *image, size_t size, const int *ids, int n, char *out, int cap);
 
 const char *yalm_error_string(int code);
 const char *yalm_version(void);

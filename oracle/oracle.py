@@ -109,6 +109,75 @@ def moe_gate(logits, n_active):
     return w, e
 
 
+def sample(logits, temperature: float, r: float) -> int:
+    """Sampler::sample (src/sampler.cpp:40-65) with the std::rand() draw replaced by `r`: fp32 running sum in index
+    order, first index whose sum reaches r, vocab - 1 if none.  temperature 0 = first-max arg-max (:27-38)."""
+    l = np.ascontiguousarray(logits, np.float32)
+    if temperature == 0:
+        return int(np.argmax(l))
+    m = l.max()
+    e = np.exp(((l - m) / np.float32(temperature)).astype(np.float32)).astype(np.float32)
+    s = np.float32(0)
+    for v in e:                       # sequential fp32 sum, as the reference accumulates it
+        s = np.float32(s + v)
+    c = np.cumsum((e / s).astype(np.float32), dtype=np.float32)   # numpy's cumsum is sequential in index order
+    hit = np.nonzero(c >= np.float32(r))[0]
+    return int(hit[0]) if len(hit) else len(l) - 1
+
+
+def sample_prob(logits, index: int) -> float:
+    """Sampler::sample_prob (src/sampler.cpp:11-25)."""
+    l = np.ascontiguousarray(logits, np.float32)
+    e = np.exp((l - l.max()).astype(np.float32)).astype(np.float32)
+    s = np.float32(0)
+    for v in e:
+        s = np.float32(s + v)
+    return float(e[index] / s)
+
+
+def tokenize(vocab, text: bytes, bos_id: int, add_bos: bool = True):
+    """Tokenizer::encode (src/tokenizer.cpp:57-94): greedy longest match over the pieces, byte fallback through
+    "<0x00>".."<0xFF>"; later duplicates of a piece win (trie insertion order, :32-41).  vocab: list of bytes."""
+    ids = {}
+    for i, p in enumerate(vocab):
+        ids[p] = i
+    maxlen = max((len(p) for p in vocab), default=0)
+    prefixes = {p[:k] for p in vocab for k in range(1, len(p) + 1)}
+    fb = ids.get(b"<0x00>", -1)
+    out = [bos_id] if add_bos else []
+    i = 0
+    while i < len(text):
+        best, l = None, 0
+        while i + l < len(text) and l < maxlen and text[i:i + l + 1] in prefixes:
+            l += 1
+            if text[i:i + l] in ids:
+                best = l
+        if best is None:
+            if fb >= 0:
+                out.append(text[i] + fb)
+            i += 1
+        else:
+            out.append(ids[text[i:i + best]])
+            i += best
+    return out
+
+
+def detokenize(vocab, ids, bos_id: int) -> bytes:
+    """Tokenizer::decode_one chained (src/tokenizer.cpp:44-55)."""
+    fb = {p: i for i, p in enumerate(vocab)}.get(b"<0x00>", -1)
+    out, prev = b"", -1
+    for t in ids:
+        p = vocab[t]
+        if prev == bos_id and p[:1] == b" ":
+            out += p[1:]
+        elif fb >= 0 and fb <= t < fb + 256:
+            out += bytes([t - fb])
+        else:
+            out += p
+        prev = t
+    return out
+
+
 class OracleModel:
     """Our C restatement driven over a parsed .yalm (path or in-memory image)."""
 
@@ -218,6 +287,11 @@ def ref_lib():
         for n in ("ref_matmul_cpu_f32", "ref_matmul_cpu_f16", "ref_matmul_cuda_f32", "ref_matmul_cuda_f16"):
             getattr(L, n).argtypes = [C.c_void_p] * 3 + [C.c_int] * 2
         L.ref_ffn_cpu.argtypes = [C.c_void_p] * 5 + [C.c_int] * 3
+        L.ref_set_threads.argtypes = [C.c_int]
+        L.ref_tokenize.argtypes = [C.c_void_p, C.c_char_p, C.c_int, C.c_void_p, C.c_int]
+        L.ref_detokenize.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_char_p, C.c_int]
+        L.ref_sample_prob.restype = C.c_float
+        L.ref_sample_prob.argtypes = [C.c_void_p, C.c_int]
         _ref = L
     return _ref
 
@@ -269,6 +343,20 @@ class RefModel:
         secs = ref_lib().ref_generate(self.h, _ptr(prompt), len(prompt), n_gen, _ptr(toks), _ptr(lg))
         self.decode_seconds = secs
         return (toks.tolist(), lg) if keep_logits else toks.tolist()
+
+    def tokenize(self, text: bytes, add_bos: bool = True):
+        out = np.zeros(2 * len(text) + 2, np.int32)
+        n = ref_lib().ref_tokenize(self.h, text, int(add_bos), _ptr(out), out.size)
+        return out[:n].tolist()
+
+    def detokenize(self, ids) -> bytes:
+        ids = np.ascontiguousarray(ids, np.int32)
+        buf = C.create_string_buffer(64 * len(ids) + 16)
+        n = ref_lib().ref_detokenize(self.h, _ptr(ids), len(ids), buf, len(buf))
+        return buf.raw[:n]
+
+    def sample_prob(self, index: int) -> float:
+        return float(ref_lib().ref_sample_prob(self.h, index))
 
     def close(self):
         if self.h:

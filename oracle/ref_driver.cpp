@@ -17,12 +17,14 @@
 
 #include "model.h"
 #include "sampler.h"
+#include "tokenizer.h"
 
 #include <cstdio>
 #include <cstring>
 #include <memory>
 #include <omp.h>
 #include <string>
+#include <vector>
 
 namespace {
 struct RefHandle {
@@ -185,6 +187,31 @@ void ref_mha_cuda(float *xout, float *att, uint16_t *kb, uint16_t *vb, float *q,
 
 int ref_omp_threads() {
 	return omp_get_max_threads();
+}
+
+// torchrun exports OMP_NUM_THREADS=1 to its workers; the reference arm of bench.py sets the team size explicitly.
+void ref_set_threads(int n) {
+	if (n > 0) omp_set_num_threads(n);
+}
+
+// The reference Tokenizer (src/tokenizer.cpp:57-94, 44-55) on the opened checkpoint: ids of `text`, and the
+// concatenated decode_one() pieces of `ids`.  Return the count / byte length.
+int ref_tokenize(void *hv, const char *text, int add_bos, int *out, int cap) {
+	auto *h = static_cast<RefHandle *>(hv);
+	Tokenizer t(h->data);
+	std::vector<int> ids = t.encode(text, add_bos != 0);
+	for (size_t i = 0; i < ids.size() && (int)i < cap; i++) out[i] = ids[i];
+	return (int)ids.size();
+}
+int ref_detokenize(void *hv, const int *ids, int n, char *out, int cap) {
+	auto *h = static_cast<RefHandle *>(hv);
+	Tokenizer t(h->data);
+	std::string s;
+	for (int i = 0; i < n; i++) s += t.decode_one(i > 0 ? ids[i - 1] : -1, ids[i]);
+	int len = (int)s.size() < cap - 1 ? (int)s.size() : cap - 1;
+	memcpy(out, s.data(), len);
+	out[len] = 0;
+	return (int)s.size();
 }
 
 } // extern "C"

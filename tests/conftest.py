@@ -39,7 +39,8 @@ def golden_case(name):
     return fx, img
 
 
-GOLDEN_CASES = ["tiny-fp32", "tiny-fp16", "tiny-moe-fp32", "tiny-moe-fp16", "tiny-gelu-clip-fp32", "tiny-gelu-clip-fp16"]
+GOLDEN_CASES = ["tiny-fp32", "tiny-fp16", "tiny-moe-fp32", "tiny-moe-fp16", "tiny-gelu-clip-fp32", "tiny-gelu-clip-fp16",
+                "tiny-kv8-fp16", "tiny-kv8-fp32"]
 
 # North-star tolerance: logits within max |delta| <= 2e-2 of the reference CPU path (BASELINE.json).
 LOGIT_TOL = 2e-2

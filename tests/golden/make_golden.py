@@ -21,15 +21,20 @@ sys.path.insert(0, ROOT)
 from oracle import oracle as O  # noqa: E402
 from yalm_b200 import yalm_file as yf  # noqa: E402
 
-CASES = [(a, d) for a in ("tiny", "tiny-moe", "tiny-gelu-clip") for d in ("fp32", "fp16")]
+CASES = [(a, d) for a in ("tiny", "tiny-moe", "tiny-gelu-clip") for d in ("fp32", "fp16")] + [("tiny-kv8", "fp16"), ("tiny-kv8", "fp32")]
 SEED, PROMPT, N_GEN = 14, [1, 17, 300, 42, 5], 72
+SEEDS = {"tiny-kv8": 39}     # per-architecture seed where 14 leaves a near-tie (top-1 minus top-2 margin >= 0.02 wanted)
 KEEP = [0, 1, 2, 30, 58, 59, 60, 61, 71]   # steps whose logits are stored (pos = len(prompt)-1+step)
 
 
 def main():
     out_dir = os.path.dirname(os.path.abspath(__file__))
+    only = sys.argv[1:]          # optional: regenerate just these cases, e.g. `make_golden.py tiny-kv8-fp16`
     for arch, dt in CASES:
-        img = bytes(yf.random_model(yf.ARCHS[arch], dt, seed=SEED))
+        if only and f"{arch}-{dt}" not in only:
+            continue
+        seed = SEEDS.get(arch, SEED)
+        img = bytes(yf.random_model(yf.ARCHS[arch], dt, seed=seed))
         ref = O.RefModel(img)
         toks, logits = ref.generate(PROMPT, N_GEN, keep_logits=True)
         kv = [np.stack(ref.kv(l)) for l in range(ref.n_layers)]
@@ -37,7 +42,7 @@ def main():
         np.savez_compressed(os.path.join(out_dir, f"{arch}-{dt}.npz"), prompt=np.array(PROMPT, np.int32),
                             tokens=np.array(toks, np.int32), keep=np.array(KEEP, np.int32),
                             logits=logits[KEEP].astype(np.float32), kv_layer0=kv[0],
-                            sha256=np.frombuffer(hashlib.sha256(img).digest(), np.uint8), seed=SEED)
+                            sha256=np.frombuffer(hashlib.sha256(img).digest(), np.uint8), seed=seed)
         print(arch, dt, toks[:8], "...", "margin(top1-top2) min over steps:",
               float(np.min(np.sort(logits, axis=1)[:, -1] - np.sort(logits, axis=1)[:, -2])))
 

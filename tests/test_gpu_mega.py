@@ -109,6 +109,66 @@ def test_mega_long_context_many_tiles(oracle):
     assert tg == to
 
 
+def test_mega_attention_at_depth_head_dim_128(oracle):
+    """Mistral attention geometry (head_dim 128, 4 query heads per KV head) at kv_len 3000+: 190 16-row KV tiles per
+    head spread over all CTAs, split partials merged by the last CTA of each head — the whole-token kernel's own
+    attention phase, not the per-op flash-decode kernel."""
+    arch = yf.Arch(1024, 2048, 128, 2, 8, 2, 512, 4096, 1000000.0, name="deep-hd128")
+    img = bytes(yf.random_model(arch, "fp16", seed=5))
+    prompt = [(i * 131 + 7) % 509 + 3 for i in range(3050)]
+    to, lo = oracle.OracleModel(img).generate(prompt, 12, keep_logits=True)
+    tg, lg, used = run(img, prompt, 12)
+    assert used
+    assert np.abs(lg - lo).max() < LOGIT_TOL
+    assert tg == to
+
+
+def test_mega_fp8_window_1024_two_wraps(oracle):
+    """fp8 weights, -T 1024, 2300 positions: the ring wraps twice and the two sink keys are re-rotated ~1300 times
+    (src/infer.cpp:303-317, 483-485); oracle = the reference fp32 arithmetic on the de-quantised weights."""
+    arch = yf.Arch(1024, 2048, 128, 2, 8, 2, 512, 4096, 1000000.0, name="win-hd128")
+    img = bytes(yf.random_model(arch, "fp8", seed=9))
+    ref_img = bytes(yf.dequantized_fp32_image(img))
+    prompt = [(i * 57 + 5) % 509 + 3 for i in range(2290)]
+    to, lo = oracle.OracleModel(ref_img, context=1024).generate(prompt, 10, keep_logits=True)
+    tg, lg, used = run(img, prompt, 10, context=1024)
+    assert used
+    assert np.abs(lg - lo).max() < LOGIT_TOL
+    assert tg == to
+
+
+def test_mega_mistral_geometry_8_layers(oracle):
+    """The headline model's exact layer shape (dim 4096, hidden 14336, 32 / 8 heads x 128, vocab 32000) on 8 layers:
+    every tile shape, K split and rotation the 32-layer bench uses."""
+    arch = yf.slim(yf.ARCHS["mistral-7b"], 8)
+    img = memoryview(yf.random_model_streamed(arch, "fp16", seed=0, device="cuda"))     # 4 GB: drawn on the GPU
+    prompt = [1, 5, 9, 200, 77, 3100, 31999]
+    to, lo = oracle.OracleModel(img).generate(prompt, 10, keep_logits=True)
+    tg, lg, used = run(img, prompt, 10)
+    assert used
+    assert np.abs(lg - lo).max() < LOGIT_TOL
+    assert tg == to
+    td, _, _ = run(img, prompt, 10, device_loop=True)
+    assert td == to
+
+
+def test_mega_launch_counter_wrap():
+    """The hand-over flags carry the state's launch number in 32 - kFlagPhaseBits = 20 bits: seed it just below the wrap
+    and decode across it — same tokens, same logits bits as a fresh state."""
+    fx, img = golden_case("tiny-fp16")
+    m = api.Model(img, 0).cuda()
+    s = api.InferenceState(m)
+    first_t, first_l = s.generate_greedy(1, 0, 40, keep_logits=True)
+    s.close()
+    s = api.InferenceState(m)
+    s.set_launch_seq((1 << 20) - 17)
+    t, l = s.generate_greedy(1, 0, 40, keep_logits=True)
+    assert t == first_t
+    assert (l == first_l).all()
+    s.close()
+    m.close()
+
+
 def test_mega_deterministic():
     fx, img = golden_case("tiny-fp16")
     a = run(img, fx["prompt"].tolist(), 30)[1]

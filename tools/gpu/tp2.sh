@@ -3,7 +3,7 @@
 # all-reduce (megakernel) and, for comparison, on the per-op kernels + one-shot all-reduce.
 N=${1:-2}
 cd /root/repo
-timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29513 tools/tp_check.py 2>&1 | grep -E "PASS|FAIL|Error|error|all-reduce over|Traceback" | head -40
+timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29513 tests/tp_worker.py 2>&1 | grep -E "PASS|FAIL|Error|error|all-reduce over|Traceback" | head -40
 for mega in ${2:-1 0}; do
 YALM_TP_MEGA=$mega timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus $N --steps 64 --warmup 3 --no-cpu-baseline > gpurun_out/bench_tp${N}_mega$mega.json 2> gpurun_out/bench_tp${N}_mega$mega.err
 echo "mega=$mega rc=$?"; python -c "

@@ -29,7 +29,8 @@ SYMBOLS = [
     "yalm_model_open_file", "yalm_model_open_memory", "yalm_model_cuda", "yalm_model_close", "yalm_model_config",
     "yalm_model_device_bytes", "yalm_state_new", "yalm_state_free", "yalm_forward", "yalm_logits",
     "yalm_generate_greedy", "yalm_state_read", "yalm_forward_launches", "yalm_model_uses_megakernel", "yalm_mega_profile",
-    "yalm_profile_ffn",
+    "yalm_profile_ffn", "yalm_sample_advance", "yalm_sample_device1", "yalm_token_probs", "yalm_sample_host",
+    "yalm_token_probs_host", "yalm_generate", "yalm_state_debug_set_launch_seq", "yalm_tokenize", "yalm_detokenize",
     "yalm_tp_unique_id", "yalm_tp_init", "yalm_tp_finalize", "yalm_tp_shard_plan", "yalm_mega_tile_plan", "yalm_mega_attn_split", "yalm_error_string", "yalm_version",
 ]
 
@@ -75,6 +76,13 @@ def lib():
     L.yalm_logits.argtypes = [vp]
     L.yalm_logits.restype = C.POINTER(f)
     L.yalm_generate_greedy.argtypes = [vp, vp, i, i, i, vp, vp, C.POINTER(f)]
+    L.yalm_generate.argtypes = [vp, vp, i, i, i, f, C.c_ulonglong, vp, vp, C.POINTER(f)]
+    L.yalm_state_debug_set_launch_seq.argtypes = [vp, C.c_uint]
+    L.yalm_state_debug_set_launch_seq.restype = None
+    L.yalm_sample_host.argtypes = [vp, i, f, f, C.POINTER(i)]
+    L.yalm_token_probs_host.argtypes = [vp, i, i, vp, vp]
+    L.yalm_tokenize.argtypes = [vp, sz, C.c_char_p, i, vp, i]
+    L.yalm_detokenize.argtypes = [vp, sz, vp, i, C.c_char_p, i]
     L.yalm_state_read.argtypes = [vp, vp, i, i, vp, sz]
     L.yalm_forward_launches.argtypes = [vp, i]
     L.yalm_model_uses_megakernel.argtypes = [vp]
@@ -131,6 +139,42 @@ def ffn_cuda(x, w1, w2, w3, act=ACT_GELU, dtype=F32, s1=None, s2=None, s3=None):
                                _p(np.ascontiguousarray(w3)), _p(s1), _p(s2), _p(s3), hidden, dim, act, dtype),
            "ffn_cuda")
     return out
+
+
+def sample_cuda(logits: np.ndarray, temperature: float, r: float) -> int:
+    """Sampler::sample (src/sampler.cpp:40-65) on the device with the uniform draw supplied by the caller."""
+    logits = np.ascontiguousarray(logits, np.float32)
+    tok = C.c_int()
+    _check(lib().yalm_sample_host(_p(logits), logits.size, temperature, r, C.byref(tok)), "sample_cuda")
+    return tok.value
+
+
+def token_probs_cuda(logits: np.ndarray, targets) -> np.ndarray:
+    """Sampler::sample_prob per row (src/sampler.cpp:11-25) on the device."""
+    logits = np.ascontiguousarray(logits, np.float32)
+    targets = np.ascontiguousarray(targets, np.int32)
+    out = np.empty(len(targets), np.float32)
+    _check(lib().yalm_token_probs_host(_p(logits), logits.shape[1], logits.shape[0], _p(targets), _p(out)), "token_probs_cuda")
+    return out
+
+
+def tokenize(image, text: bytes, add_bos: bool = True):
+    img = np.frombuffer(image, dtype=np.uint8)
+    out = np.zeros(max(16, 2 * len(text) + 2), np.int32)
+    n = lib().yalm_tokenize(_p(img), img.nbytes, text, int(add_bos), _p(out), out.size)
+    if n < 0:
+        raise YalmError(n, "tokenize")
+    return out[:n].tolist()
+
+
+def detokenize(image, ids) -> bytes:
+    img = np.frombuffer(image, dtype=np.uint8)
+    ids = np.ascontiguousarray(ids, np.int32)
+    buf = C.create_string_buffer(64 * len(ids) + 16)
+    n = lib().yalm_detokenize(_p(img), img.nbytes, _p(ids), len(ids), buf, len(buf))
+    if n < 0:
+        raise YalmError(n, "detokenize")
+    return buf.raw[:n]
 
 
 def bench_op(name: str, iters: int = 20, warmup: int = 3):
@@ -214,6 +258,18 @@ class InferenceState:
                "generate_greedy")
         self.device_ms = ms.value
         return (toks.tolist(), lg) if keep_logits else toks.tolist()
+
+    def generate_sampled(self, token: int, pos: int, n_gen: int, temperature: float, seed: int = 0):
+        """n_gen steps with Sampler::sample on the device (temperature 0 = greedy); only token ids come back."""
+        toks = np.zeros(n_gen, np.int32)
+        ms = C.c_float()
+        _check(lib().yalm_generate(self.model.h, self.h, token, pos, n_gen, temperature, seed, _p(toks), None, C.byref(ms)),
+               "generate")
+        self.device_ms = ms.value
+        return toks.tolist()
+
+    def set_launch_seq(self, seq: int):
+        lib().yalm_state_debug_set_launch_seq(self.h, seq)
 
     def mega_profile(self, token: int, pos: int) -> np.ndarray:
         """(grid, n_layers, 6 phases, 8 slots) clock64 stamps of one forward pass on the megakernel."""

@@ -1,9 +1,11 @@
 // C ABI layer (3): host-pointer test entry points (reference semantics: src/infer.cu:890-1007) and
 // opaque handles over Model / InferenceState for ctypes / cgo / JNI style bindings.
 #include "yalm_api.h"
+#include "tokenizer.h"
 
 #include <cuda_runtime.h>
 
+#include <algorithm>
 #include <cstdio>
 #include <cstring>
 #include <memory>
@@ -350,6 +352,16 @@ extern "C" int yalm_generate_greedy(yalm_model *m, yalm_state *s, int token, int
 	return m->model->generate_greedy(*s->state, token, pos, n_gen, tokens_out, logits_out, device_ms);
 }
 
+extern "C" int yalm_generate(yalm_model *m, yalm_state *s, int token, int pos, int n_gen, float temperature,
+                             unsigned long long seed, int *tokens_out, float *logits_out, float *device_ms) {
+	if (!m || !s) return YALM_EINVAL;
+	return m->model->generate(*s->state, token, pos, n_gen, temperature, seed, tokens_out, logits_out, device_ms);
+}
+
+extern "C" void yalm_state_debug_set_launch_seq(yalm_state *s, unsigned seq) {
+	if (s) s->state->set_mega_seq(seq);
+}
+
 extern "C" int yalm_state_read(yalm_model *m, yalm_state *sh, int which, int layer, void *dst, size_t bytes) {
 	if (!m || !sh || !dst) return YALM_EINVAL;
 	InferenceState &s = *sh->state;
@@ -405,4 +417,31 @@ extern "C" int yalm_mega_profile(yalm_model *m, yalm_state *s, int token, int po
 extern "C" int yalm_profile_ffn(yalm_model *m, yalm_state *s, int token, int pos, int n_steps, double *mean_us) {
 	if (!m || !s) return YALM_EINVAL;
 	return m->model->profile_ffn(*s->state, token, pos, n_steps, mean_us);
+}
+
+// ---- tokenizer taps (host only; the CLI's Tokenizer over an in-memory .yalm image) -------------------------------------
+extern "C" int yalm_tokenize(const void *image, size_t size, const char *text, int add_bos, int *out, int cap) {
+	if (!image || !text || !out || cap < 0) return YALM_EINVAL;
+	YALMData d;
+	if (d.from_memory(image, size) != 0 || !d.metadata.contains("bos_token_id") || !d.metadata.contains("eos_token_id")) return YALM_EFORMAT;
+	Tokenizer t(d);
+	const std::vector<int> ids = t.encode(text, add_bos != 0);
+	for (size_t i = 0; i < ids.size() && (int)i < cap; ++i) out[i] = ids[i];
+	return (int)ids.size();
+}
+
+extern "C" int yalm_detokenize(const void *image, size_t size, const int *ids, int n, char *out, int cap) {
+	if (!image || !ids || !out || n < 0 || cap < 1) return YALM_EINVAL;
+	YALMData d;
+	if (d.from_memory(image, size) != 0 || !d.metadata.contains("bos_token_id") || !d.metadata.contains("eos_token_id")) return YALM_EFORMAT;
+	Tokenizer t(d);
+	std::string s;
+	for (int i = 0; i < n; ++i) {
+		if (ids[i] < 0 || ids[i] >= (int)t.vocab.size()) return YALM_EINVAL;
+		s += t.decode_one(i > 0 ? ids[i - 1] : -1, ids[i]);
+	}
+	const int len = (int)s.size();
+	memcpy(out, s.data(), std::min(len, cap - 1));
+	out[std::min(len, cap - 1)] = 0;
+	return len;
 }

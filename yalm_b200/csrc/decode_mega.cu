@@ -103,8 +103,9 @@ static bool plan_shapes(int dtype, int dim, int q_dim, int kv_dim, int hidden, i
 }
 
 Plan plan(int dtype, int dim, int q_dim, int kv_dim, int head_dim, int hidden, int vocab, int n_heads, int n_kv_heads,
-          int n_experts, int n_active, int max_seq_len, bool tp, int full_vocab) {
+          int n_experts, int n_active, int max_seq_len, int n_layers, bool tp, int full_vocab) {
 	Plan p;
+	if (n_layers < 1 || n_layers * (YALM_MEGA_W2_SPLIT ? 6 : 5) + 2 >= (1 << kFlagPhaseBits)) return p; // phase field of the hand-over flags
 	if (tp && (dim > kTpCapFloats || full_vocab > kTpMaxVocab)) return p;
 	p.tp = tp;
 	const int ep = ep_of(dtype);

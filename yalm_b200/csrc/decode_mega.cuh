@@ -121,8 +121,10 @@ __device__ __forceinline__ unsigned ld_acquire(const unsigned *p) {
 // barrier -> load", every element travels as ONE 64-bit word {fp32 value, u32 flag} written with a single store and
 // the readers poll the words themselves: a word whose flag matches is the value (64-bit accesses are single-copy
 // atomic), so the hand-over costs one L2 round trip after the last store lands and needs no fence.  flag =
-// launch number << 10 | (producing phase + 1) never repeats for a buffer within 4M launches, and a buffer is
-// rewritten every launch, so stale words never match.  Reuse of a buffer is safe because ONE grid barrier per layer
+// ll_flag(launch number, producing phase + 1) = seq << kFlagPhaseBits | phase + 1.  It is never 0 (fresh buffers never
+// match) and differs between any two launches less than 2^(32 - kFlagPhaseBits) = 1M apart; every word of a buffer is
+// rewritten by every launch, so the only words a poller can meet are this launch's and the previous launch's: the
+// launch counter may wrap (tests seed it just below the wrap).  plan() rejects models with >= 2^kFlagPhaseBits phases.  Reuse of a buffer is safe because ONE grid barrier per layer
 // remains (QKV -> attention, where the appended K/V rows change hands anyway): no CTA can run a layer ahead of
 // another one, x alternates between two buffers (after wo / after w2), and hb, att_out and the partials are written
 // once per layer on the far side of that barrier from their previous readers.
@@ -147,6 +149,9 @@ __device__ __forceinline__ unsigned ld_acquire(const unsigned *p) {
 #ifndef YALM_MEGA_LL_ATTN
 #define YALM_MEGA_LL_ATTN 0
 #endif
+__device__ __forceinline__ unsigned ll_flag(unsigned seq, int phase_plus_1) {
+	return seq << kFlagPhaseBits | (unsigned)phase_plus_1;
+}
 __device__ __forceinline__ unsigned long long ll_pack(float v, unsigned flag) {
 	return (unsigned long long)__float_as_uint(v) | ((unsigned long long)flag << 32);
 }
@@ -943,7 +948,7 @@ __device__ __forceinline__ void gemv_consume(Ctx &c, const Args &a, Epi &ep, int
 	constexpr bool LLH = YALM_MEGA_LL;       // hb (and att_out): local vectors, flagged in both modes
 	constexpr int NREP = LL ? kLLRep : 1;    // flagged vectors are written kLLRep times (lane -> replica): see kLLRep
 	constexpr int NREPH = LLH ? kLLRep : 1;
-	const unsigned wflag = a.seq << 10 | (unsigned)(ph + 1); // flagged hand-over: the next phase polls for this
+	const unsigned wflag = ll_flag(a.seq, ph + 1); // flagged hand-over: the next phase polls for this
 	using T = WTraits<DT>;
 	constexpr int EP = T::EP, CH = 32 * EP, Q = EP / 4;
 	const Shape sh = shape_of(a, ep.kind);
@@ -964,7 +969,7 @@ __device__ __forceinline__ void gemv_consume(Ctx &c, const Args &a, Epi &ep, int
 			// flagged hand-over: x after wo lives in ll_x[0] (complete: this CTA polled all of it when it staged w1/w3);
 			// x before wo is the plain copy written behind w2 of the layer before, on the far side of a grid barrier
 			if (YALM_MEGA_W2_SPLIT && kind == kW2 && ep.half == 1) resid = __ldcg(a.w2_tmp + (long)g * R + lane % R); // x + first half
-			else if (LL && kind == kW2) resid = ll_val(ll_load1(a.ll_x + (size_t)(lane / R) * a.dim + (long)g * R + lane % R));
+			else if (LL && kind == kW2) resid = ll_val(ll_load1(a.ll_x + (size_t)(c.cta % kLLRep) * a.dim + (long)g * R + lane % R)); // the replica this CTA polled and verified
 			else resid = __ldcg(a.x + (long)g * R + lane % R);
 		}
 		float2 acc2[R];
@@ -1485,7 +1490,7 @@ __device__ __forceinline__ void attention_consume(Ctx &c, const Args &a, const L
 	stamp(c, layer, 1, 5);
 
 	// ---- merge the warps, publish the CTA's partial, the last CTA of the head to arrive combines ------------
-	const unsigned wflag = a.seq << 10 | (unsigned)(layer * kPPL + 2); // flagged hand-over: this phase is ph = kPPL * layer + 1
+	const unsigned wflag = ll_flag(a.seq, layer * kPPL + 2); // flagged hand-over: this phase is ph = kPPL * layer + 1
 	constexpr bool LLC = LL && YALM_MEGA_LL_ATTN;
 	float *ew = wts; // [W][G] merge weights (wts is not in use before the combine)
 	if (c.tid < W * G) { // weight of warp w's record for head g, computed once
@@ -1624,7 +1629,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_c
 		// phase polls its input vector in the staging step
 		constexpr bool LL = YALM_MEGA_LL != 0;
 		const bool flagged = LL && ph > 0 && (TP ? k == 2 || k == 4 : k != 1); // this phase polls its input instead of a barrier
-		const unsigned rflag = a.seq << 10 | (unsigned)ph; // what the phase before this one produced
+		const unsigned rflag = ll_flag(a.seq, ph); // what the phase before this one produced
 		if (reduced) tp_barrier(c, a);
 		else if (ph > 0 && !flagged) grid_barrier(c, a.sync);
 		stamp(c, l, k, 1);

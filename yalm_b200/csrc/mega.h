@@ -31,6 +31,7 @@ constexpr int kTraceEvents = 1 << 16;
 #ifndef YALM_MEGA_LL_REP
 #define YALM_MEGA_LL_REP 4
 #endif
+constexpr int kFlagPhaseBits = 12;  // hand-over flag = launch number << kFlagPhaseBits | (phase + 1), see decode_mega.cuh
 constexpr int kLLRep = YALM_MEGA_LL_REP; // copies of every flagged hand-over vector (decode_mega.cuh); 1, 2 or 4
 constexpr int kProfileSlots = 6 * 8; // per (CTA, layer): phases x slots, see decode_mega.cuh
 
@@ -96,7 +97,7 @@ struct Args {
 	int vocab_base;             // first vocabulary row of this rank
 	float *x2;                  // second residual buffer (x ping-pongs across the in-kernel all-reduces)
 	// Flagged hand-over buffers (single GPU, see decode_mega.cuh "flagged hand-over"): every entry is one 64-bit word
-	// {fp32 value, u32 flag}, flag = seq << 10 | (producing phase + 1); zero before the first launch.
+	// {fp32 value, u32 flag}, flag = seq << kFlagPhaseBits | (producing phase + 1); zero before the first launch.
 	unsigned long long *ll_x;   // [2][kLLRep][dim]: [0] x after wo, [1] x after w2
 	unsigned long long *ll_hb;  // [kLLRep][hidden]
 	unsigned long long *ll_att; // [kLLRep][q_dim]
@@ -119,7 +120,7 @@ struct Plan {
 // Can this model shape run on the megakernel on the current device?  Under tensor parallelism (`tp`) the dimensions
 // are the rank's local shares (q_dim, kv_dim, hidden, vocab, heads) and `full_vocab` the unsharded vocabulary.
 Plan plan(int dtype, int dim, int q_dim, int kv_dim, int head_dim, int hidden, int vocab, int n_heads,
-          int n_kv_heads, int n_experts, int n_active, int max_seq_len, bool tp = false, int full_vocab = 0);
+          int n_kv_heads, int n_experts, int n_active, int max_seq_len, int n_layers, bool tp = false, int full_vocab = 0);
 // Bytes of the attention partial workspace (acc + ml) for `grid` CTAs.
 size_t attn_ws_floats(int grid, int n_heads, int head_dim);
 // One token.  Returns a cudaError_t.

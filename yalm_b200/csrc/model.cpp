@@ -146,6 +146,8 @@ InferenceState::~InferenceState() {
 	_hydrate_graph.destroy();
 	_output_graph.destroy();
 	_greedy_graph.destroy();
+	_device_graph.destroy();
+	_output_dev_graph.destroy();
 	_profile_graph.destroy();
 	for (cudaEvent_t e : _ffn_events) cudaEventDestroy(e);
 	if (_device == Device::CPU) {
@@ -237,7 +239,9 @@ void InferenceState::cuda() {
 	size_t total = 0;
 	for (auto &s : slots) total += align_up(s.bytes, 256);
 	CUDA_CHECK(cudaMalloc(&_arena, total));
-	CUDA_CHECK(cudaMemset(_arena, 0, total));
+	// zeroed on the state's own (non-blocking) stream: the megakernel's barrier words, head counters and flagged
+	// hand-over buffers must read 0 at the first launch, which is enqueued on that stream
+	CUDA_CHECK(cudaMemsetAsync(_arena, 0, total, _stream));
 	size_t off = 0;
 	for (auto &s : slots) {
 		*s.ptr = static_cast<char *>(_arena) + off;
@@ -252,6 +256,7 @@ void InferenceState::cuda() {
 	}
 	CUDA_CHECK(cudaHostAlloc((void **)&_logits, sizeof(float) * c.vocab_size, cudaHostAllocDefault));
 	memset(_logits, 0, sizeof(float) * c.vocab_size);
+	CUDA_CHECK(cudaStreamSynchronize(_stream)); // the arena is zero before anybody can see its pointers
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -573,7 +578,7 @@ void Model::plan_mega() {
 	auto ms = std::make_shared<MegaState>();
 	ms->plan = yalm::mega::plan(static_cast<int>(c.weight_dtype), c.dim, c.local_heads() * c.head_dim,
 	                            c.local_kv_heads() * c.head_dim, c.head_dim, c.local_hidden(), c.local_vocab(), c.local_heads(),
-	                            c.local_kv_heads(), c.n_experts, c.n_experts_active, c.max_seq_len, tp, c.vocab_size);
+	                            c.local_kv_heads(), c.n_experts, c.n_experts_active, c.max_seq_len, c.n_layers, tp, c.vocab_size);
 	if (!ms->plan.ok) return;
 	std::vector<yalm::mega::Layer> host(blocks.size());
 	for (size_t i = 0; i < blocks.size(); ++i) {
@@ -600,14 +605,14 @@ int Model::mega_profile(InferenceState &s, int token, int pos, long long *out, s
 	if (count < need) return YALM_EINVAL;
 	long long *dev = nullptr;
 	CUDA_CHECK(cudaMalloc((void **)&dev, need * sizeof(long long)));
-	CUDA_CHECK(cudaMemset(dev, 0, need * sizeof(long long)));
+	CUDA_CHECK(cudaMemsetAsync(dev, 0, need * sizeof(long long), s.stream())); // same stream as the launch below
 	// YALM_MEGA_TRACE=<file>: also dump CTA 0's event trace (decode_mega.cuh: trace()) as raw int64
 	const char *tf = getenv("YALM_MEGA_TRACE");
 	long long *tdev = nullptr;
 	const size_t tn = 1 + 2 * (size_t)yalm::mega::kTraceEvents;
 	if (tf) {
 		CUDA_CHECK(cudaMalloc((void **)&tdev, tn * sizeof(long long)));
-		CUDA_CHECK(cudaMemset(tdev, 0, tn * sizeof(long long)));
+		CUDA_CHECK(cudaMemsetAsync(tdev, 0, tn * sizeof(long long), s.stream()));
 	}
 	_mega_trace = tdev;
 	int rc = launch_mega(s, token, pos, yalm::mega::kLogits, dev);
@@ -662,6 +667,10 @@ int Model::launch_mega(InferenceState &s, int token, int pos, int mode, long lon
 	return yalm::mega::launch(_mega->plan, a, s.stream());
 }
 
+bool Model::supports_batch() const { return false; }
+int Model::batch_capacity() const { return 0; }
+int Model::forward_batch(InferenceState &, const int *, int, int, const int *, float *) { return YALM_EINVAL; }
+
 int Model::launches_per_forward(InferenceMode mode) const {
 	if (_mega_ok) return 1;
 	// embed + 5 kernels per block (qkv+rope+append, flash-decode, wo+res, ffn-glu, w2+res) [+ lm head]
@@ -673,12 +682,13 @@ int Model::launches_per_forward(InferenceMode mode) const {
 }
 
 // Enqueue (eagerly or into a capturing stream) everything after the embedding.
-int Model::enqueue_forward(InferenceState &s, InferenceMode mode, bool /*from_host*/, bool greedy_tail) {
+int Model::enqueue_forward(InferenceState &s, InferenceMode mode, bool /*from_host*/, int tail) {
 	const Config &c = *config;
 	const int dt = static_cast<int>(c.weight_dtype);
 	yalm_stream_t st = s.stream();
 	int rc;
-	if (greedy_tail) { // token/pos come from the device-side control block
+	const bool greedy_tail = tail == kTailGreedy;
+	if (tail != kTailHost) { // token/pos come from the device-side control block
 		rc = yalm_embed(s.x(), token_embedding_table, embed_scale, c.dim, dt, s.ctl(), -1, 0, c.max_seq_len, st);
 		if (rc) return rc;
 	}
@@ -696,6 +706,7 @@ int Model::enqueue_forward(InferenceState &s, InferenceMode mode, bool /*from_ho
 		if (rc) return rc;
 	}
 	if (greedy_tail) return yalm_argmax_advance(s.logits_dev(), c.vocab_size, s.ctl(), c.max_seq_len, s.tokens_dev(), st);
+	if (tail == kTailDevice || !s.host_logits()) return 0; // the caller samples on the device (yalm_sample_advance / Sampler::*_device)
 	return (int)cudaMemcpyAsync(s.logits(), s.logits_dev(), sizeof(float) * c.vocab_size, cudaMemcpyDeviceToHost,
 	                            s.stream());
 }
@@ -722,14 +733,15 @@ void Model::forward(InferenceState &s, int token, int pos, InferenceMode mode) {
 		OP_CHECK(launch_mega(s, token, pos,
 		                     mode == InferenceMode::OUTPUT_LOGITS ? yalm::mega::kLogits : yalm::mega::kHydrate));
 		if (mode == InferenceMode::OUTPUT_LOGITS) {
-			CUDA_CHECK(cudaMemcpyAsync(s.logits(), s.logits_dev(), sizeof(float) * c.vocab_size, cudaMemcpyDeviceToHost,
-			                           s.stream()));
+			if (s.host_logits())
+				CUDA_CHECK(cudaMemcpyAsync(s.logits(), s.logits_dev(), sizeof(float) * c.vocab_size, cudaMemcpyDeviceToHost,
+				                           s.stream()));
 			CUDA_CHECK(cudaStreamSynchronize(s.stream()));
 		}
 		CUDA_CHECK(cudaGetLastError());
 		return;
 	}
-	CudaGraph &g = s.graph();
+	CudaGraph &g = s.host_logits() || mode == InferenceMode::HYDRATE_KV_CACHE ? s.graph() : s.output_dev_graph();
 	// The embedding is an ordinary launch: token and pos travel as kernel arguments (copied at launch
 	// time), everything after it reads positions from the device control block and is one graph replay.
 	OP_CHECK(yalm_embed(s.x(), token_embedding_table, embed_scale, c.dim, static_cast<int>(c.weight_dtype), s.ctl(),
@@ -737,9 +749,9 @@ void Model::forward(InferenceState &s, int token, int pos, InferenceMode mode) {
 	if (!g.is_created) {
 		// First call in this mode: run eagerly (this also sizes every kernel's shared memory and
 		// occupancy), then capture the same sequence for all later calls.
-		OP_CHECK(enqueue_forward(s, mode, true, false));
+		OP_CHECK(enqueue_forward(s, mode, true, kTailHost));
 		CUDA_CHECK(cudaStreamSynchronize(s.stream()));
-		capture_graph(g, s.stream(), [&]() { return enqueue_forward(s, mode, true, false); });
+		capture_graph(g, s.stream(), [&]() { return enqueue_forward(s, mode, true, kTailHost); });
 	} else {
 		g.launch(s.stream());
 	}
@@ -761,10 +773,20 @@ static void capture_graph(CudaGraph &g, cudaStream_t st, const std::function<int
 
 int Model::generate_greedy(InferenceState &s, int token, int pos, int n_gen, int *tokens_out, float *logits_out,
                            float *device_ms) {
+	return generate(s, token, pos, n_gen, 0.f, 0ull, tokens_out, logits_out, device_ms);
+}
+
+// n_gen decode steps without host round trips.  temperature == 0: greedy (first-max arg-max inside the megakernel, or
+// yalm_argmax_advance behind the per-op graph); > 0: Sampler::sample on the device (yalm_sample_advance) with
+// r = uniform(seed, step).  Only the token ids (4 bytes each) come back.
+int Model::generate(InferenceState &s, int token, int pos, int n_gen, float temperature, unsigned long long seed,
+                    int *tokens_out, float *logits_out, float *device_ms) {
 	if (_device != Device::CUDA || s.device() != Device::CUDA) return YALM_ENOGPU;
 	const Config &c = *config;
-	if (n_gen < 1 || n_gen > s.tokens_capacity() || token < 0 || token >= c.vocab_size || pos < 0 || !tokens_out)
+	if (n_gen < 1 || n_gen > s.tokens_capacity() || token < 0 || token >= c.vocab_size || pos < 0 || !tokens_out ||
+	    !(temperature >= 0.f))
 		return YALM_EINVAL;
+	const bool greedy = temperature == 0.f;
 	cudaStream_t st = s.stream();
 	// seed the device control block: token, pos, ring position, step = 0
 	const int kv_sink = pos >= c.max_seq_len ? KV_SINKS : 0;
@@ -772,57 +794,60 @@ int Model::generate_greedy(InferenceState &s, int token, int pos, int n_gen, int
 	                        pos >= c.max_seq_len ? c.max_seq_len : pos + 1, 0, 0, 0};
 	CUDA_CHECK(cudaMemcpyAsync(s.ctl(), h, sizeof(h), cudaMemcpyHostToDevice, st));
 	CUDA_CHECK(cudaStreamSynchronize(st));
-	if (_mega_ok) {
-		cudaEvent_t e0, e1;
-		CUDA_CHECK(cudaEventCreate(&e0));
-		CUDA_CHECK(cudaEventCreate(&e1));
-		CUDA_CHECK(cudaEventRecord(e0, st));
-		for (int i = 0; i < n_gen; ++i) {
-			int rc = launch_mega(s, -1, 0, yalm::mega::kGreedy); // token / pos from the device control block
-			if (rc) return rc;
-			if (logits_out)
-				CUDA_CHECK(cudaMemcpyAsync(logits_out + (size_t)i * c.vocab_size, s.logits_dev(),
-				                           sizeof(float) * c.vocab_size, cudaMemcpyDeviceToHost, st));
-		}
-		CUDA_CHECK(cudaEventRecord(e1, st));
-		CUDA_CHECK(cudaMemcpyAsync(tokens_out, s.tokens_dev(), sizeof(int) * n_gen, cudaMemcpyDeviceToHost, st));
-		CUDA_CHECK(cudaStreamSynchronize(st));
-		if (device_ms) CUDA_CHECK(cudaEventElapsedTime(device_ms, e0, e1));
-		cudaEventDestroy(e0);
-		cudaEventDestroy(e1);
-		return (int)cudaGetLastError();
-	}
-	CudaGraph &g = s.greedy_graph();
-	int done = 0;
-	if (!g.is_created) {
-		int rc = enqueue_forward(s, InferenceMode::OUTPUT_LOGITS, false, true);
-		if (rc) return rc;
-		if (logits_out)
-			CUDA_CHECK(cudaMemcpyAsync(logits_out, s.logits_dev(), sizeof(float) * c.vocab_size, cudaMemcpyDeviceToHost, st));
-		CUDA_CHECK(cudaStreamSynchronize(st));
-		capture_graph(g, st, [&]() { return enqueue_forward(s, InferenceMode::OUTPUT_LOGITS, false, true); });
-		done = 1;
-	}
 	cudaEvent_t e0, e1;
 	CUDA_CHECK(cudaEventCreate(&e0));
 	CUDA_CHECK(cudaEventCreate(&e1));
+	auto finish = [&](int done) -> int {
+		CUDA_CHECK(cudaEventRecord(e1, st));
+		CUDA_CHECK(cudaMemcpyAsync(tokens_out, s.tokens_dev(), sizeof(int) * n_gen, cudaMemcpyDeviceToHost, st));
+		CUDA_CHECK(cudaStreamSynchronize(st));
+		if (device_ms) {
+			CUDA_CHECK(cudaEventElapsedTime(device_ms, e0, e1));
+			if (done && n_gen > done) *device_ms = *device_ms * n_gen / (n_gen - done); // scale to n_gen steps when step 0 ran eagerly
+		}
+		cudaEventDestroy(e0);
+		cudaEventDestroy(e1);
+		return (int)cudaGetLastError();
+	};
+	auto sample = [&]() { return yalm_sample_advance(s.logits_dev(), c.vocab_size, s.ctl(), c.max_seq_len, s.tokens_dev(), temperature, seed, st); };
+	auto keep_logits = [&](int i) {
+		if (logits_out)
+			CUDA_CHECK(cudaMemcpyAsync(logits_out + (size_t)i * c.vocab_size, s.logits_dev(), sizeof(float) * c.vocab_size,
+			                           cudaMemcpyDeviceToHost, st));
+	};
+	if (_mega_ok) {
+		CUDA_CHECK(cudaEventRecord(e0, st));
+		for (int i = 0; i < n_gen; ++i) {
+			// token / pos from the device control block; greedy: the arg-max and the advance happen inside the kernel
+			int rc = launch_mega(s, -1, 0, greedy ? yalm::mega::kGreedy : yalm::mega::kLogits);
+			if (rc) return rc;
+			keep_logits(i);
+			if (!greedy && (rc = sample())) return rc;
+		}
+		return finish(0);
+	}
+	CudaGraph &g = greedy ? s.greedy_graph() : s.device_graph();
+	const int tail = greedy ? kTailGreedy : kTailDevice;
+	int done = 0;
+	if (!g.is_created) {
+		int rc = enqueue_forward(s, InferenceMode::OUTPUT_LOGITS, false, tail);
+		if (rc) return rc;
+		keep_logits(0);
+		if (!greedy && (rc = sample())) return rc;
+		CUDA_CHECK(cudaStreamSynchronize(st));
+		capture_graph(g, st, [&]() { return enqueue_forward(s, InferenceMode::OUTPUT_LOGITS, false, tail); });
+		done = 1;
+	}
 	CUDA_CHECK(cudaEventRecord(e0, st));
 	for (int i = done; i < n_gen; ++i) {
 		g.launch(st);
-		if (logits_out)
-			CUDA_CHECK(cudaMemcpyAsync(logits_out + (size_t)i * c.vocab_size, s.logits_dev(),
-			                           sizeof(float) * c.vocab_size, cudaMemcpyDeviceToHost, st));
+		keep_logits(i);
+		if (!greedy) {
+			int rc = sample();
+			if (rc) return rc;
+		}
 	}
-	CUDA_CHECK(cudaEventRecord(e1, st));
-	CUDA_CHECK(cudaMemcpyAsync(tokens_out, s.tokens_dev(), sizeof(int) * n_gen, cudaMemcpyDeviceToHost, st));
-	CUDA_CHECK(cudaStreamSynchronize(st));
-	if (device_ms) {
-		CUDA_CHECK(cudaEventElapsedTime(device_ms, e0, e1));
-		if (n_gen > done) *device_ms = *device_ms * n_gen / (n_gen - done); // scale to n_gen steps when step 0 ran eagerly
-	}
-	cudaEventDestroy(e0);
-	cudaEventDestroy(e1);
-	return (int)cudaGetLastError();
+	return finish(done);
 }
 
 int Model::profile_ffn(InferenceState &s, int token, int pos, int n_steps, double *mean_us) {
@@ -838,7 +863,7 @@ int Model::profile_ffn(InferenceState &s, int token, int pos, int n_steps, doubl
 	CUDA_CHECK(cudaStreamSynchronize(st));
 	s.enable_ffn_timing(true);
 	CudaGraph &g = s.profile_graph();
-	if (!g.is_created) capture_graph(g, st, [&]() { return enqueue_forward(s, InferenceMode::OUTPUT_LOGITS, false, true); });
+	if (!g.is_created) capture_graph(g, st, [&]() { return enqueue_forward(s, InferenceMode::OUTPUT_LOGITS, false, kTailGreedy); });
 	s.enable_ffn_timing(false);
 	double total = 0;
 	for (int i = 0; i < n_steps; ++i) {

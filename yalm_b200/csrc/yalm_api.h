@@ -104,6 +104,12 @@ struct InferenceState {
 	int *tokens_dev() const { return _tokens_dev; }
 	int tokens_capacity() const { return _tokens_cap; }
 	CudaGraph &greedy_graph() { return _greedy_graph; }
+	CudaGraph &output_dev_graph() { return _output_dev_graph; } // forward(OUTPUT_LOGITS) with host_logits() off
+	CudaGraph &device_graph() { return _device_graph; } // forward pass whose logits stay on the device (device-side sampling)
+	// false: OUTPUT_LOGITS forwards leave the logits on the device only (logits_dev()); the caller samples there
+	// (Sampler::sample_device / sample_prob_device) and 4 bytes per token cross PCIe instead of vocab * 4
+	void set_host_logits(bool on) { _host_logits = on; }
+	bool host_logits() const { return _host_logits; }
 	const Config &config() const { return *_config; }
 	// Optional kernel timing: when enabled, Block::enqueue brackets the w1/w3 GLU kernel (the dominant
 	// kernel: 54 % of a layer's weight bytes) with an event pair per layer.
@@ -122,13 +128,15 @@ struct InferenceState {
 	unsigned long long *mega_ll() const { return _mega_ll; }
 	float *mega_tmp() const { return _mega_tmp; }
 	unsigned next_mega_seq() { return ++_mega_seq; }
+	void set_mega_seq(unsigned v) { _mega_seq = v; } // tests: start the hand-over flags' launch counter near its wrap
 
 private:
 	std::shared_ptr<Config> _config;
 	Device _device = Device::CPU;
 	cudaStream_t _stream = nullptr;
 	InferenceMode _mode = InferenceMode::OUTPUT_LOGITS;
-	CudaGraph _hydrate_graph, _output_graph, _greedy_graph, _profile_graph;
+	CudaGraph _hydrate_graph, _output_graph, _greedy_graph, _profile_graph, _device_graph, _output_dev_graph;
+	bool _host_logits = true;
 	bool _ffn_timing = false;
 	std::vector<cudaEvent_t> _ffn_events;
 
@@ -224,9 +232,22 @@ struct Model {
 	// Returns 0 or an error code; see yalm_generate_greedy in include/yalm_b200.h.
 	int generate_greedy(InferenceState &s, int token, int pos, int n_gen, int *tokens_out, float *logits_out,
 	                    float *device_ms);
+	// Same loop with Sampler::sample (src/sampler.cpp:40-65) on the device: temperature 0 = greedy, > 0 = draw with
+	// r = uniform(seed, step).  See yalm_generate in include/yalm_b200.h.
+	int generate(InferenceState &s, int token, int pos, int n_gen, float temperature, unsigned long long seed,
+	             int *tokens_out, float *logits_out, float *device_ms);
 	// n_steps greedy steps with an event pair around every layer's w1/w3 GLU kernel; returns the mean
 	// duration of that kernel in microseconds (CUDA events on the launching stream).
 	int profile_ffn(InferenceState &s, int token, int pos, int n_steps, double *mean_us);
+	// Batched prefill / perplexity (net-new; the reference scores and hydrates token by token,
+	// src/main.cpp:91-97, 174-184): n consecutive positions pos0 .. pos0 + n - 1 in one pass — dense tcgen05 GEMMs over the
+	// chunk, causal attention over the KV ring, bulk KV append.  On return the KV cache holds the chunk, logits() /
+	// logits_dev() hold the LAST position's logits, and, if targets != null, probs_out[i] = softmax(logits_i)[targets[i]]
+	// (Sampler::sample_prob per position).  Returns 0 or an error code; supports_batch() says whether this model /
+	// shard shape has the path (dense fp16 weights, unsharded), batch_capacity() the largest n per call.
+	bool supports_batch() const;
+	int batch_capacity() const;
+	int forward_batch(InferenceState &s, const int *tokens, int n, int pos0, const int *targets, float *probs_out);
 	size_t device_bytes() const { return _device_bytes; }
 	int launches_per_forward(InferenceMode mode) const;
 	// true when forward() runs as ONE persistent cooperative kernel per token (decode_mega.cu) instead of
@@ -238,7 +259,8 @@ struct Model {
 	int mega_profile(InferenceState &s, int token, int pos, long long *out, size_t count, int *grid);
 
 private:
-	int enqueue_forward(InferenceState &s, InferenceMode mode, bool from_host, bool greedy_tail);
+	enum { kTailHost = 0, kTailGreedy = 1, kTailDevice = 2 }; // what follows the LM head: D2H copy of the logits | device arg-max + advance | nothing
+	int enqueue_forward(InferenceState &s, InferenceMode mode, bool from_host, int tail);
 	int launch_mega(InferenceState &s, int token, int pos, int mode, long long *prof = nullptr);
 	void plan_mega();
 	bool _mega_ok = false;

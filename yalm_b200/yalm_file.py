@@ -64,6 +64,8 @@ ARCHS = {
     "tiny": Arch(256, 512, 32, 2, 8, 2, 512, 64, 10000.0, name="tiny"),
     "tiny-moe": Arch(256, 512, 32, 2, 8, 2, 512, 64, 10000.0, n_experts=4, n_experts_active=2,
                      name="tiny-moe"),
+    # 8 KV heads x 2 query heads each (q_dim = dim: the reference sizes xb2 by dim): splits 2 / 4 / 8 ways for the tensor-parallel parity tests
+    "tiny-kv8": Arch(512, 1024, 32, 2, 16, 8, 512, 64, 10000.0, name="tiny-kv8"),
     "tiny-gelu-clip": Arch(256, 512, 32, 2, 8, 4, 512, 64, 10000.0, act_type="gelu", qkv_clip=1.5,
                            rotary_dim=16, tied=True, name="tiny-gelu-clip"),
 }
