@@ -162,6 +162,10 @@ void yalm_model_close(yalm_model *m);
  * rotary_dim, n_experts, n_experts_active, weight dtype, act, tp_rank, tp_size, reserved */
 void yalm_model_config(const yalm_model *m, int *out);
 size_t yalm_model_device_bytes(const yalm_model *m);
+/* Loader facts (the reference: one cudaMalloc + one pageable copy per tensor, src/model.cpp:185-211):
+ * out[0] = device allocations behind the model's weights and KV caches (1: one arena per rank),
+ * out[1] = 1 if the upload went through the pinned double-buffered staging stream, 0 if it fell back to pageable copies. */
+void yalm_model_load_info(const yalm_model *m, int *out2);
 
 int yalm_state_new(yalm_model *m, yalm_state **out);
 void yalm_state_free(yalm_state *s);

@@ -91,3 +91,25 @@ def test_determinism_and_state_reuse():
         s.close()
     m.close()
     assert (outs[0] == outs[1]).all()
+
+
+def test_loader_is_one_arena_through_pinned_staging(tmp_path):
+    """the reference does one cudaMalloc + one pageable copy per tensor (src/model.cpp:185-211); here a
+    model is one device allocation filled through pinned double-buffered staging — from memory and from an mmap'd file,
+    with a staging buffer smaller than the tensors (YALM_LOAD_STAGING_MB) so that pieces span several buffers."""
+    import os
+    fx, img = golden_case("tiny-moe-fp16")
+    path = tmp_path / "m.yalm"
+    path.write_bytes(img)
+    os.environ["YALM_LOAD_STAGING_MB"] = "1"
+    try:
+        for src in (img, str(path)):
+            m = api.Model(src).cuda()
+            assert m.load_info() == {"device_allocations": 1, "pinned_staging": True}
+            s = api.InferenceState(m)
+            toks = s.generate(fx["prompt"].tolist(), 16)
+            assert toks == fx["tokens"].tolist()[:16]
+            s.close()
+            m.close()
+    finally:
+        del os.environ["YALM_LOAD_STAGING_MB"]

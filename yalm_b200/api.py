@@ -27,7 +27,7 @@ SYMBOLS = [
     "yalm_ffn_glu", "yalm_lm_head", "yalm_argmax_advance", "yalm_gemv",
     "yalm_matmul_host", "yalm_mha_host", "yalm_ffn_host", "yalm_bench_op",
     "yalm_model_open_file", "yalm_model_open_memory", "yalm_model_cuda", "yalm_model_close", "yalm_model_config",
-    "yalm_model_device_bytes", "yalm_state_new", "yalm_state_free", "yalm_forward", "yalm_logits",
+    "yalm_model_device_bytes", "yalm_model_load_info", "yalm_state_new", "yalm_state_free", "yalm_forward", "yalm_logits",
     "yalm_generate_greedy", "yalm_state_read", "yalm_forward_launches", "yalm_model_uses_megakernel", "yalm_mega_profile",
     "yalm_profile_ffn", "yalm_sample_advance", "yalm_sample_device1", "yalm_token_probs", "yalm_sample_host",
     "yalm_token_probs_host", "yalm_generate", "yalm_state_debug_set_launch_seq", "yalm_tokenize", "yalm_detokenize",
@@ -67,6 +67,8 @@ def lib():
     L.yalm_model_close.restype = None
     L.yalm_model_config.argtypes = [vp, C.POINTER(i)]
     L.yalm_model_config.restype = None
+    L.yalm_model_load_info.argtypes = [vp, C.POINTER(i)]
+    L.yalm_model_load_info.restype = None
     L.yalm_model_device_bytes.argtypes = [vp]
     L.yalm_model_device_bytes.restype = sz
     L.yalm_state_new.argtypes = [vp, C.POINTER(vp)]
@@ -214,6 +216,11 @@ class Model:
 
     def device_bytes(self) -> int:
         return lib().yalm_model_device_bytes(self.h)
+
+    def load_info(self):
+        v = (C.c_int * 2)()
+        lib().yalm_model_load_info(self.h, v)
+        return {"device_allocations": v[0], "pinned_staging": bool(v[1])}
 
     def uses_megakernel(self) -> bool:
         return bool(lib().yalm_model_uses_megakernel(self.h))

@@ -319,6 +319,11 @@ extern "C" size_t yalm_model_device_bytes(const yalm_model *m) {
 	return m->model->device_bytes();
 }
 
+extern "C" void yalm_model_load_info(const yalm_model *m, int *out2) {
+	out2[0] = m->model->device_allocations();
+	out2[1] = m->model->upload_was_pinned() ? 1 : 0;
+}
+
 extern "C" int yalm_state_new(yalm_model *m, yalm_state **out) {
 	if (!m || !out) return YALM_EINVAL;
 	if (!have_gpu() || m->model->device() != Device::CUDA) return YALM_ENOGPU;

@@ -2,6 +2,7 @@
 // op sequencing and CUDA-graph capture.  See yalm_api.h for how this maps onto the reference API.
 #include "yalm_api.h"
 
+#include "loader.h"
 #include "mega.h"
 #include "tp.h"
 
@@ -341,69 +342,100 @@ void Block::set_scales(const Tensor *sq, const Tensor *sk, const Tensor *sv, con
 	}
 }
 
-Block::~Block() {
-	for (void *p : _owned) cudaFree(p);
-}
+Block::~Block() = default; // device memory belongs to the model's arena (or to _own_arena)
 
-// `height` pieces of `width` bytes, piece i read at host + i*spitch + offset -> one dense device buffer.
-static void *upload_strided(std::vector<void *> &owned, size_t &acct, const void *host, size_t spitch, size_t offset,
-                            size_t width, size_t height) {
+// `height` pieces of `width` bytes, piece i read at host + i*spitch + offset -> one dense range of the arena.
+static void *upload_strided(yalm::DeviceArena &arena, yalm::Uploader &up, size_t &acct, const void *host, size_t spitch,
+                            size_t offset, size_t width, size_t height) {
 	if (!host) return nullptr;
-	void *dev = nullptr;
-	CUDA_CHECK(cudaMalloc(&dev, width * height));
-	if (width == spitch) CUDA_CHECK(cudaMemcpy(dev, static_cast<const char *>(host) + offset, width * height, cudaMemcpyHostToDevice));
-	else CUDA_CHECK(cudaMemcpy2D(dev, width, static_cast<const char *>(host) + offset, spitch, width, height, cudaMemcpyHostToDevice));
-	owned.push_back(dev);
+	void *dev = arena.take(width * height);
+	if (!dev) {
+		std::cerr << "FATAL: device arena exhausted (loader sizing bug)" << std::endl;
+		abort();
+	}
+	OP_CHECK(up.put(dev, host, spitch, offset, width, height));
 	acct += width * height;
 	return dev;
 }
 
-void Block::cuda() {
-	if (_device != Device::CPU) return;
-	_device = Device::CUDA;
+// Which host bytes of every tensor this rank keeps.  One list drives both the sizing pass (device_bytes_needed) and the
+// upload pass (cuda), so the arena is exactly as large as what goes into it.
+struct Block::Piece {
+	void **slot;
+	size_t spitch, offset, width, height;
+};
+
+std::vector<Block::Piece> Block::pieces() {
 	const Config &c = *_config;
 	const size_t B = dtype_size(c.weight_dtype), T = c.tp_size, r = c.tp_rank;
 	const size_t q_dim = (size_t)c.n_heads * c.head_dim, kv_dim = (size_t)c.n_kv_heads * c.head_dim;
 	const size_t lq = q_dim / T, lkv = kv_dim / T, lhid = (size_t)c.hidden_dim / T, dim = c.dim;
 	const size_t E = std::max(1, c.n_experts);
-	auto up = [&](const void *h, size_t spitch, size_t off, size_t width, size_t height) {
-		return upload_strided(_owned, _device_bytes, h, spitch, off, width, height);
-	};
-	_rms_att_weight = (float *)up(_rms_att_weight, dim * 4, 0, dim * 4, 1);
-	_rms_ffn_weight = (float *)up(_rms_ffn_weight, dim * 4, 0, dim * 4, 1);
-	// column-parallel (rows of W): q/k/v by head, w1/w3 by hidden unit
 	const yalm::TpDims td{c.dim, c.hidden_dim, c.head_dim, c.n_heads, c.n_kv_heads, c.vocab_size, (int)B};
-	auto up_slice = [&](const void *h, int tensor, size_t repeat) { // `repeat` stacked experts
+	std::vector<Piece> out;
+	auto whole = [&](void **slot, size_t bytes) { out.push_back({slot, bytes, 0, bytes, 1}); };
+	auto slice = [&](void **slot, int tensor, size_t repeat) { // `repeat` stacked experts
 		const yalm::TpSlice sl = yalm::tp_slice(td, tensor, c.tp_rank, c.tp_size);
-		return up(h, sl.spitch, sl.offset, sl.width, sl.height * repeat);
+		out.push_back({slot, sl.spitch, sl.offset, sl.width, sl.height * repeat});
 	};
-	_wq = up_slice(_wq, yalm::kTpWq, 1);
-	_wk = up_slice(_wk, yalm::kTpWk, 1);
-	_wv = up_slice(_wv, yalm::kTpWv, 1);
-	_w1 = up_slice(_w1, yalm::kTpW1, E);
-	_w3 = up_slice(_w3, yalm::kTpW3, E);
+	whole((void **)&_rms_att_weight, dim * 4);
+	whole((void **)&_rms_ffn_weight, dim * 4);
+	// column-parallel (rows of W): q/k/v by head, w1/w3 by hidden unit
+	slice(&_wq, yalm::kTpWq, 1);
+	slice(&_wk, yalm::kTpWk, 1);
+	slice(&_wv, yalm::kTpWv, 1);
+	slice(&_w1, yalm::kTpW1, E);
+	slice(&_w3, yalm::kTpW3, E);
 	// row-parallel (columns of W): wo over q_dim, w2 over hidden
-	_wo = up_slice(_wo, yalm::kTpWo, 1);
-	_w2 = up_slice(_w2, yalm::kTpW2, E);
-	if (c.n_experts > 0) _moegate = up(_moegate, E * dim * B, 0, E * dim * B, 1);
+	slice(&_wo, yalm::kTpWo, 1);
+	slice(&_w2, yalm::kTpW2, E);
+	if (c.n_experts > 0) whole(&_moegate, E * dim * B);
 	if (_sq) {
-		_sq = (float *)up(_sq, lq * 4, r * lq * 4, lq * 4, 1);
-		_sk = (float *)up(_sk, lkv * 4, r * lkv * 4, lkv * 4, 1);
-		_sv = (float *)up(_sv, lkv * 4, r * lkv * 4, lkv * 4, 1);
-		_so = (float *)up(_so, dim * 4, 0, dim * 4, 1);
-		_s1 = (float *)up(_s1, (size_t)c.hidden_dim * 4, r * lhid * 4, lhid * 4, E);
-		_s3 = (float *)up(_s3, (size_t)c.hidden_dim * 4, r * lhid * 4, lhid * 4, E);
-		_s2 = (float *)up(_s2, E * dim * 4, 0, E * dim * 4, 1);
-		if (_sgate) _sgate = (float *)up(_sgate, E * 4, 0, E * 4, 1);
+		out.push_back({(void **)&_sq, lq * 4, r * lq * 4, lq * 4, 1});
+		out.push_back({(void **)&_sk, lkv * 4, r * lkv * 4, lkv * 4, 1});
+		out.push_back({(void **)&_sv, lkv * 4, r * lkv * 4, lkv * 4, 1});
+		whole((void **)&_so, dim * 4);
+		out.push_back({(void **)&_s1, (size_t)c.hidden_dim * 4, r * lhid * 4, lhid * 4, E});
+		out.push_back({(void **)&_s3, (size_t)c.hidden_dim * 4, r * lhid * 4, lhid * 4, E});
+		whole((void **)&_s2, E * dim * 4);
+		if (_sgate) whole((void **)&_sgate, E * 4);
 	}
-	const size_t kv_bytes = (size_t)c.max_seq_len * lkv * sizeof(f16_t);
-	CUDA_CHECK(cudaMalloc((void **)&_key_cache, kv_bytes));
-	CUDA_CHECK(cudaMalloc((void **)&_value_cache, kv_bytes));
-	CUDA_CHECK(cudaMemset(_key_cache, 0, kv_bytes));
-	CUDA_CHECK(cudaMemset(_value_cache, 0, kv_bytes));
-	_owned.push_back(_key_cache);
-	_owned.push_back(_value_cache);
+	return out;
+}
+
+size_t Block::device_bytes_needed() {
+	const Config &c = *_config;
+	size_t n = 0;
+	for (const Piece &p : pieces()) n += yalm::DeviceArena::padded(p.width * p.height);
+	const size_t kv_bytes = (size_t)c.max_seq_len * (c.n_kv_heads / c.tp_size) * c.head_dim * sizeof(f16_t);
+	return n + 2 * yalm::DeviceArena::padded(kv_bytes);
+}
+
+void Block::cuda(yalm::DeviceArena &arena, yalm::Uploader &up) {
+	if (_device != Device::CPU) return;
+	_device = Device::CUDA;
+	const Config &c = *_config;
+	for (const Piece &p : pieces()) *p.slot = upload_strided(arena, up, _device_bytes, *p.slot, p.spitch, p.offset, p.width, p.height);
+	const size_t kv_bytes = (size_t)c.max_seq_len * c.local_kv_heads() * c.head_dim * sizeof(f16_t);
+	_key_cache = static_cast<f16_t *>(arena.take(kv_bytes));
+	_value_cache = static_cast<f16_t *>(arena.take(kv_bytes));
+	if (!_key_cache || !_value_cache) {
+		std::cerr << "FATAL: device arena exhausted (KV cache)" << std::endl;
+		abort();
+	}
+	OP_CHECK(up.zero(_key_cache, kv_bytes));
+	OP_CHECK(up.zero(_value_cache, kv_bytes));
 	_device_bytes += 2 * kv_bytes;
+}
+
+// Stand-alone use of a Block (reference signature, src/model.h:246): its own small arena.
+void Block::cuda() {
+	if (_device != Device::CPU) return;
+	_own_arena = std::make_shared<yalm::DeviceArena>();
+	CUDA_CHECK((cudaError_t)_own_arena->reserve(device_bytes_needed()));
+	yalm::Uploader up(64u << 20);
+	cuda(*_own_arena, up);
+	OP_CHECK(up.finish());
 }
 
 int Block::enqueue(InferenceState &s) const {
@@ -508,9 +540,7 @@ Model::Model(YALMData &yalm, int context) {
 	}
 }
 
-Model::~Model() {
-	for (void *p : _owned) cudaFree(p);
-}
+Model::~Model() = default; // the arena frees the one device allocation
 
 void Model::cuda() {
 	int count = 0;
@@ -536,22 +566,34 @@ void Model::cuda(int device, int tp_rank, int tp_size) {
 	_device = Device::CUDA;
 	set_cuda_device(device);
 	const size_t B = dtype_size(c.weight_dtype), dim = c.dim, V = c.vocab_size, lv = V / tp_size;
-	void *host_embed = token_embedding_table;
-	token_embedding_table = upload_strided(_owned, _device_bytes, host_embed, V * dim * B, 0, V * dim * B, 1);
-	if (embed_scale) embed_scale = (float *)upload_strided(_owned, _device_bytes, embed_scale, V * 4, 0, V * 4, 1);
-	for (auto &b : blocks) b->cuda();
+	// ---- sizing pass: one device allocation for everything this rank holds ------------------------------------
+	using yalm::DeviceArena;
+	const yalm::TpSlice cls = yalm::tp_slice(td, yalm::kTpWcls, tp_rank, tp_size);
+	size_t need = DeviceArena::padded(V * dim * B) + DeviceArena::padded(dim * 4);
+	if (embed_scale) need += DeviceArena::padded(V * 4);
+	for (auto &b : blocks) need += b->device_bytes_needed();
+	if (!_tied) need += DeviceArena::padded(cls.width * cls.height) + (wcls_scale ? DeviceArena::padded(lv * 4) : 0);
+	_arena = std::make_shared<DeviceArena>();
+	CUDA_CHECK((cudaError_t)_arena->reserve(need));
+	// ---- upload pass: pinned double-buffered staging, slices cut on the host side ---------------------------------
+	yalm::Uploader up;
+	DeviceArena &ar = *_arena;
+	token_embedding_table = upload_strided(ar, up, _device_bytes, token_embedding_table, V * dim * B, 0, V * dim * B, 1);
+	if (embed_scale) embed_scale = (float *)upload_strided(ar, up, _device_bytes, embed_scale, V * 4, 0, V * 4, 1);
+	for (auto &b : blocks) b->cuda(ar, up);
 	for (auto &b : blocks) _device_bytes += b->device_bytes();
-	rms_final_weight = (float *)upload_strided(_owned, _device_bytes, rms_final_weight, dim * 4, 0, dim * 4, 1);
+	rms_final_weight = (float *)upload_strided(ar, up, _device_bytes, rms_final_weight, dim * 4, 0, dim * 4, 1);
 	// LM head: vocabulary rows are split across ranks; tied heads alias the (replicated) embedding table.
 	if (_tied) {
 		wcls = static_cast<char *>(token_embedding_table) + (size_t)tp_rank * lv * dim * B;
 		wcls_scale = embed_scale ? embed_scale + (size_t)tp_rank * lv : nullptr;
 	} else {
-		const yalm::TpSlice sl = yalm::tp_slice(td, yalm::kTpWcls, tp_rank, tp_size);
-		wcls = upload_strided(_owned, _device_bytes, wcls, sl.spitch, sl.offset, sl.width, sl.height);
+		wcls = upload_strided(ar, up, _device_bytes, wcls, cls.spitch, cls.offset, cls.width, cls.height);
 		if (wcls_scale)
-			wcls_scale = (float *)upload_strided(_owned, _device_bytes, wcls_scale, lv * 4, (size_t)tp_rank * lv * 4, lv * 4, 1);
+			wcls_scale = (float *)upload_strided(ar, up, _device_bytes, wcls_scale, lv * 4, (size_t)tp_rank * lv * 4, lv * 4, 1);
 	}
+	OP_CHECK(up.finish());
+	_upload_pinned = up.pinned();
 	plan_mega();
 	CUDA_CHECK(cudaDeviceSynchronize());
 }

@@ -18,6 +18,11 @@
 
 #include "../../include/yalm_b200.h"
 
+namespace yalm {
+class DeviceArena;
+class Uploader;
+} // namespace yalm
+
 constexpr int KV_SINKS = 2; // src/model.h:12
 
 enum class ActivationType { GELU, SILU };
@@ -185,8 +190,11 @@ struct Block {
 	void block(InferenceState &s, int pos, int kv_sink, int kv_pos, int kv_len) const;
 	// Enqueue the block's kernels, coordinates taken from s.ctl() on the device.
 	int enqueue(InferenceState &s) const;
-	// Upload this block's (shard of the) weights into `arena` (if null: own allocations).
+	// Upload this block's (shard of the) weights and create its KV cache: stand-alone (own arena), or into the
+	// model's arena through the model's pinned staging stream (csrc/loader.h).
 	void cuda();
+	void cuda(yalm::DeviceArena &arena, yalm::Uploader &up);
+	size_t device_bytes_needed(); // arena bytes cuda() will take (padded)
 
 	// fp8 per-row scales (null unless weight_dtype == F8E4M3)
 	void set_scales(const Tensor *sq, const Tensor *sk, const Tensor *sv, const Tensor *so, const Tensor *s1,
@@ -204,8 +212,10 @@ private:
 	float *_sq = nullptr, *_sk = nullptr, *_sv = nullptr, *_so = nullptr, *_s1 = nullptr, *_s2 = nullptr, *_s3 = nullptr,
 	      *_sgate = nullptr;
 	f16_t *_key_cache = nullptr, *_value_cache = nullptr;
-	std::vector<void *> _owned; // device allocations to free
+	std::shared_ptr<yalm::DeviceArena> _own_arena; // stand-alone cuda() only
 	size_t _device_bytes = 0;
+	struct Piece;
+	std::vector<Piece> pieces();
 };
 
 struct Model {
@@ -249,6 +259,9 @@ struct Model {
 	int batch_capacity() const;
 	int forward_batch(InferenceState &s, const int *tokens, int n, int pos0, const int *targets, float *probs_out);
 	size_t device_bytes() const { return _device_bytes; }
+	// loader facts for tests / bench: number of device allocations behind the model (1) and whether the upload went through pinned staging
+	int device_allocations() const { return _arena ? 1 : 0; }
+	bool upload_was_pinned() const { return _upload_pinned; }
 	int launches_per_forward(InferenceMode mode) const;
 	// true when forward() runs as ONE persistent cooperative kernel per token (decode_mega.cu) instead of
 	// the per-op kernel graph: unsharded dense models whose shapes the tile planner accepts.  Set
@@ -269,7 +282,8 @@ private:
 	std::shared_ptr<MegaState> _mega;
 	Device _device = Device::CPU;
 	bool _tied = false;
-	std::vector<void *> _owned;
+	std::shared_ptr<yalm::DeviceArena> _arena; // ONE device allocation: every weight shard + every KV cache of this rank
+	bool _upload_pinned = false;
 	size_t _device_bytes = 0;
 };
 
