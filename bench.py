@@ -10,10 +10,14 @@ hydrating the KV cache through the same forward path.
   value    device-timed (CUDA events) tok/s of the on-device greedy loop, inputs resident in HBM
   e2e      same metric through the public per-token API Model::forward(token, pos) driven from the host:
            token/pos travel host->device every step and the logits come back device->host (host arg-max)
-  roofline dominant kernel (fused rmsnorm + w1/w3 + SwiGLU GEMV), algorithmic bytes / CUDA-event duration
+  roofline the whole-token kernel (one launch per token): algorithmic bytes (weights + KV rows) / CUDA-event duration
+  parity   N = 1: the first tokens + logits of the SAME full-size image against the unmodified reference's CPU backend;
+           N > 1: the K timed greedy tokens identical on every rank, and a 2-layer slim model of the same architecture,
+           sharded the same way, against the reference
   cpu_baseline  the unmodified reference CPU backend (oracle/_ref) timed on this box's host cores
-N > 1 (torchrun, one process per GPU): the same model tensor-parallel over N ranks (strong scaling),
-NCCL all-reduce after the row-parallel wo / w2 GEMVs.
+  gpu_reference the unmodified reference's own `-d cuda` path on this GPU (reported beside the CPU baseline)
+N > 1 (torchrun, one process per GPU): the same model tensor-parallel over N ranks (strong scaling); the
+all-reduce behind the row-parallel wo / w2 GEMVs happens inside the kernel over NVLink peer memory.
 
 --impl reference: the reference's own CPU implementation of the path (oracle/_ref; the oracle port if the
 reference library is absent) on the host cores, same metric / unit / config; rank 0 only.
@@ -41,6 +45,7 @@ WORKLOADS = {
     "llama-3.2-1b-fp32": ("llama-3.2-1b", "fp32", 4096, "Llama-3.2-1B fp32 random-init, batch-1 decode"),
     "tiny": ("tiny-moe", "fp16", 64, "tiny MoE test model (debug only)"),
 }
+HEADLINE = "mistral-7b-fp16-4k"
 
 
 def peaks():
@@ -51,11 +56,12 @@ def peaks():
 
 
 def ncu_traffic():
-    """dram__bytes_read.sum + dram__bytes_write.sum of one megakernel launch on the headline workload, from the newest
-    committed `ncu --set full` summary (profiles/*_full_summary.txt, written by tools/ncu_summary.py).  None if absent."""
+    """dram__bytes_read.sum + dram__bytes_write.sum of ONE timed-shape launch of the whole-token kernel on the headline
+    workload — logits mode at pos ~4090, captured by tools/gpu/ncu_full_logits.sh with `ncu --set full` and summarised
+    into profiles/*logits*_full_summary.txt (tools/ncu_summary.py).  None if no such capture is committed."""
     import glob
     import re
-    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "*mega*full_summary.txt")))
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "*logits*full_summary.txt")))
     if not files:
         return None, None
     txt = open(files[-1]).read()
@@ -66,7 +72,7 @@ def ncu_traffic():
         if not m or m.group(2) not in unit:
             return None, None
         tot += float(m.group(1)) * unit[m.group(2)]
-    return tot, os.path.relpath(files[-1], ROOT) + " (captured launch: hydrate step at pos 3 = no LM head, no KV: 13.96 GB algorithmic)"
+    return tot, os.path.relpath(files[-1], ROOT) + " (one logits-mode launch at pos ~4090, ncu --set full)"
 
 
 class ClockSampler:
@@ -115,43 +121,95 @@ def shm_path(name):
     return os.path.join(d, name)
 
 
-def run_reference(args, arch, dtype, context, desc):
-    """Reference arm / cpu_baseline: the reference's CPU backend on the host cores.  One step = one decoded
-    token (weights streamed once) at a short context: the CPU path is weight-bound, KV at 4k adds < 4 %."""
-    from oracle import oracle as O
+def host_threads():
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def write_model(path, arch, dtype):
+    """Seeded random-init image of `arch` straight into `path` (large tensors drawn on the GPU when there is one)."""
     import torch
     dev = "cuda" if torch.cuda.is_available() else "cpu"
-    img = yf.random_model_streamed(arch, dtype, seed=0, device=dev)
-    path = shm_path(f"yalm_bench_{arch.name}_{dtype}.yalm")
-    with open(path, "wb") as f:
-        f.write(memoryview(img))
+    img = yf.random_model_streamed(arch, dtype, seed=0, device=dev, path=path)
     del img
+
+
+def run_reference(args, path, context, start=(1, 0), want_logits=False):
+    """Reference arm / cpu_baseline: the reference's CPU backend on the host cores over the image at `path`.  One step =
+    one decoded token (weights streamed once) at a short context: the CPU path is weight-bound (KV at 4k context adds
+    3.8 % to the bytes of the headline model: stated in BASELINE.md).  Returns (record, seconds, tokens, last logits)."""
+    # torchrun exports OMP_NUM_THREADS=1 to its workers: the reference arm uses every host thread it can get
+    n_thr = host_threads()
+    os.environ["OMP_NUM_THREADS"] = str(n_thr)
+    from oracle import oracle as O
     kind = "reference" if O.ref_available() else "port"
-    try:
-        if kind == "reference":
-            m = O.RefModel(path, context)
-            cores = O.ref_lib().ref_omp_threads()
-            step = lambda tok, pos: (m.forward(tok, pos, 1), m.argmax())[1]
-        else:
-            m = O.OracleModel(path, context)
-            cores = os.cpu_count()
-            step = lambda tok, pos: (m.forward(tok, pos, 1), m.argmax())[1]
-        tok, pos = 1, 0
-        for _ in range(args.warmup):
-            tok = step(tok, pos)
-            pos += 1
-        t0 = time.perf_counter()
-        for _ in range(args.steps):
-            tok = step(tok, pos)
-            pos += 1
-        dt = time.perf_counter() - t0
-    finally:
-        os.unlink(path)
+    if kind == "reference":
+        O.ref_lib().ref_set_threads(n_thr)
+        m = O.RefModel(path, context)
+        cores = O.ref_lib().ref_omp_threads()
+    else:
+        m = O.OracleModel(path, context)
+        cores = n_thr
+    tok, pos = start
+    toks, lg = [], None
+    for _ in range(args.warmup):
+        lg = m.forward(tok, pos, 1)
+        tok = m.argmax()
+        toks.append(tok)
+        pos += 1
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        lg = m.forward(tok, pos, 1)
+        tok = m.argmax()
+        toks.append(tok)
+        pos += 1
+    dt = time.perf_counter() - t0
+    last = np.array(lg, np.float32, copy=True) if want_logits else None
+    if kind == "reference":
+        m.close()
     v = args.steps / dt
-    return {"value": v, "unit": "tok/s", "cores": cores, "kind": kind,
-            "sample": f"{args.steps} greedy decode steps of the same model after {args.warmup} warm-up steps, "
-                      f"positions {args.warmup}..{args.warmup + args.steps - 1} (short context), "
-                      f"{'oracle/_ref (unmodified reference, OpenMP)' if kind == 'reference' else 'oracle C port'}"}, dt
+    rec = {"value": v, "unit": "tok/s", "cores": cores, "kind": kind,
+           "sample": f"{args.steps} greedy decode steps of the same model after {args.warmup} warm-up steps, "
+                     f"positions {start[1] + args.warmup}..{start[1] + args.warmup + args.steps - 1} (short context), "
+                     f"{'oracle/_ref (unmodified reference, OpenMP)' if kind == 'reference' else 'oracle C port'}"}
+    return rec, dt, toks, last
+
+
+GPU_REF_SNIPPET = r"""
+import json, sys, time
+sys.path.insert(0, {root!r})
+from oracle import oracle as O
+m = O.RefModel({path!r}, {context})
+m.cuda()
+prompt = [1, 17, 300, 42, 5, 9, 77, 4]
+m.generate(prompt, {warm})                 # captures + instantiates the reference's CUDA graph, warms up
+t = m.generate([3], {steps})                 # positions restart at 0: decode-only seconds of {steps} greedy steps
+print("GPUREF " + json.dumps({{"tok_s": ({steps} - 1) / m.decode_seconds}}))   # its timed loop holds steps - 1 forwards
+"""
+
+
+def run_gpu_reference(path, context, steps=32, warm=8):
+    """The unmodified reference's own `-d cuda` path (src/infer.cu, compiled for sm_100 by oracle/Makefile) on this GPU, in
+    a subprocess (its error convention is abort()).  Short context, decode-only seconds from its own greedy loop."""
+    from oracle import oracle as O
+    if not O.ref_available():
+        return {"value": None, "unit": "tok/s", "note": "oracle/_ref not built"}
+    code = GPU_REF_SNIPPET.format(root=ROOT, path=path, context=context, steps=steps, warm=warm)
+    try:
+        r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300)
+    except subprocess.TimeoutExpired:
+        return {"value": None, "unit": "tok/s", "note": "reference -d cuda timed out (300 s)"}
+    for ln in r.stdout.splitlines():
+        if ln.startswith("GPUREF "):
+            v = json.loads(ln[7:])["tok_s"]
+            return {"value": v, "unit": "tok/s",
+                    "note": f"unmodified reference, Device::CUDA (src/infer.cu built -gencode arch=compute_100,code=sm_100), same image, "
+                            f"{steps} greedy decode steps at positions 1..{steps} after warm-up (short context: favours the reference), "
+                            "host-timed around its own loop incl. its per-token stream sync; reference: unsupported for MoE / fp8 / "
+                            "multi-GPU / positions past the window (BASELINE.md 4.5)"}
+    return {"value": None, "unit": "tok/s", "note": f"reference -d cuda failed (rc {r.returncode}): {(r.stderr or r.stdout)[-300:]}"}
 
 
 def _emit(line):
@@ -160,6 +218,16 @@ def _emit(line):
 
 
 _REAL_STDOUT = 1
+
+
+def greedy_host_loop(state, tok, pos, n):
+    toks, lg = [], None
+    for _ in range(n):
+        lg = state.forward(tok, pos)
+        tok = int(np.argmax(lg))
+        toks.append(tok)
+        pos += 1
+    return toks, np.array(lg, np.float32, copy=True)
 
 
 def main():
@@ -174,9 +242,11 @@ def main():
     ap.add_argument("--steps", type=int, default=128)
     ap.add_argument("--warmup", type=int, default=8)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="mistral-7b-fp16-4k", choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default=HEADLINE, choices=sorted(WORKLOADS))
     ap.add_argument("--layers", type=int, default=0, help="debug: truncate the model to this many layers")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-gpu-reference", action="store_true")
+    ap.add_argument("--no-parity", action="store_true", help="skip the parity legs (ncu captures: keeps launch indices simple)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
 
@@ -193,11 +263,17 @@ def main():
             "config": {"workload": desc, "arch": arch.name, "weights": dtype, "context": context,
                        "parallelism": f"tp{world}" if world > 1 else "single-gpu",
                        "l2": "inputs larger than L2 (weights streamed per token >> 126 MB)"}}
+    tag = f"{arch.name}_{dtype}_{os.environ.get('MASTER_PORT', '0')}_{os.getppid() if world > 1 else os.getpid()}"
+    path = shm_path(f"yalm_bench_{tag}.yalm")
 
     if args.impl == "reference":
         if rank != 0:
             return
-        cb, dt = run_reference(args, arch, dtype, context, desc)
+        write_model(path, arch, dtype)
+        try:
+            cb, dt, _, _ = run_reference(args, path, context)
+        finally:
+            os.unlink(path)
         line = dict(base, impl="reference", n_gpus=world, value=cb["value"], ms_per_step=1000 * dt / args.steps,
                     cpu_baseline=cb, gpu_launches=0,
                     e2e={"value": cb["value"], "unit": "tok/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0})
@@ -226,28 +302,78 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    def load(p, ctx):
+        m = api.Model(p, ctx).cuda(local_rank, rank, world)
+        return m, api.InferenceState(m)
+
+    # ---- the model image: ONE copy per node (rank 0 writes it under /dev/shm, every rank maps it and uploads its slices)
     t_gen = time.perf_counter()
-    img = yf.random_model_streamed(arch, dtype, seed=0, device="cuda")
-    torch.cuda.empty_cache()
+    if rank == 0:
+        write_model(path, arch, dtype)
+        torch.cuda.empty_cache()
+    barrier()
     t_gen = time.perf_counter() - t_gen
 
-    cpu_baseline = None
-    if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        # bounded sample of the same workload on the host cores (reported baseline, not the target)
-        sub = argparse.Namespace(steps=12, warmup=2)
-        try:
-            cpu_baseline, _ = run_reference(sub, arch, dtype, context, desc)
-        except Exception as e:  # the checker failing must not hide the GPU number
-            cpu_baseline = {"value": None, "unit": "tok/s", "cores": os.cpu_count(), "kind": "reference",
-                            "sample": f"failed: {e}"}
+    cpu_baseline = gpu_reference = parity = None
+    ref_toks = ref_last = None
+    try:
+        if rank == 0 and world == 1 and not args.no_cpu_baseline:
+            # bounded sample of the same workload on the host cores (reported baseline, not the target); its tokens and last
+            # logits are what the GPU arm is checked against below
+            sub = argparse.Namespace(steps=12, warmup=2)
+            try:
+                cpu_baseline, _, ref_toks, ref_last = run_reference(sub, path, context, want_logits=True)
+            except Exception as e:  # the checker failing must not hide the GPU number
+                cpu_baseline = {"value": None, "unit": "tok/s", "cores": host_threads(), "kind": "reference",
+                                "sample": f"failed: {e}"}
+        if rank == 0 and world == 1 and not args.no_gpu_reference and not arch.n_experts and dtype != "fp8":
+            gpu_reference = run_gpu_reference(path, context)
 
-    t_load = time.perf_counter()
-    model = api.Model(img, context).cuda(local_rank, rank, world)
-    del img
-    state = api.InferenceState(model)
-    t_load = time.perf_counter() - t_load
+        t_load = time.perf_counter()
+        model, state = load(path, context)
+        t_load = time.perf_counter() - t_load
+        load_info = model.load_info()
+        barrier()                       # every rank has uploaded its slices: the image can go
+    finally:
+        if rank == 0 and os.path.exists(path):
+            os.unlink(path)
 
     K, W, V = args.steps, args.warmup, model.vocab_size
+    # ---- parity, N = 1: the full-size image, first tokens from (token 1, pos 0), vs the unmodified reference (CPU) -----
+    if ref_toks is not None and not args.no_parity:
+        sp = api.InferenceState(model)
+        got, last = greedy_host_loop(sp, 1, 0, len(ref_toks))
+        sp.close()
+        parity = {"tokens_identical": got == ref_toks, "max_abs_dlogit": float(np.abs(last - ref_last).max()),
+                  "n_tokens": len(ref_toks), "tolerance": 2e-2,
+                  "vs": f"oracle/_ref (unmodified reference, CPU backend) on the same {arch.n_layers}-layer image, positions 0..{len(ref_toks) - 1}"}
+    # ---- parity, N > 1: a 2-layer slim model of the same architecture, sharded the same way, vs the reference on rank 0 -----
+    slim_par = None
+    if world > 1 and not args.no_parity:
+        sarch = yf.slim(arch, 2)
+        spath = shm_path(f"yalm_bench_slim_{tag}.yalm")
+        want = None
+        if rank == 0:
+            write_model(spath, sarch, dtype)
+        barrier()
+        try:
+            if rank == 0:
+                try:
+                    _, _, want, want_last = run_reference(argparse.Namespace(steps=6, warmup=2), spath, context, want_logits=True)
+                except Exception as e:
+                    slim_par = {"tokens_identical": None, "note": f"reference failed: {e}"}
+            sm, ss = load(spath, context)
+            got, last = greedy_host_loop(ss, 1, 0, 8)
+            ss.close()
+            sm.close()
+            barrier()
+        finally:
+            if rank == 0 and os.path.exists(spath):
+                os.unlink(spath)
+        if rank == 0 and want is not None:
+            slim_par = {"tokens_identical": got == want, "max_abs_dlogit": float(np.abs(last - want_last).max()), "n_tokens": 8,
+                        "tolerance": 2e-2, "vs": f"oracle/_ref (CPU) on a 2-layer slim {arch.name}, tp{world} vs unsharded reference"}
+
     p0 = max(1, context - 2 * (K + W))
     for pos in range(p0):                                   # prompt hydrate, same forward path, untimed
         state.forward((pos * 7919 + 1) % V, pos, api.MODE_HYDRATE)
@@ -281,11 +407,18 @@ def main():
     mega = model.uses_megakernel()
     ffn_us = 0.0 if mega else state.profile_ffn(tok, pos - 1, min(K, 8))
 
+    ranks_agree = None
     if world > 1:
         t = torch.tensor([dev_ms, e2e_s, ffn_us], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         dev_ms, e2e_s, ffn_us = t.tolist()
+        mine = torch.tensor(toks, dtype=torch.int32, device="cuda")
+        allt = [torch.empty_like(mine) for _ in range(world)]
+        dist.all_gather(allt, mine)
+        ranks_agree = all(bool((a == allt[0]).all().item()) for a in allt)
     if rank == 0:
+        if world > 1:
+            parity = {"timed_tokens_identical_on_all_ranks": ranks_agree, "n_tokens": K, "slim": slim_par}
         peak, peak_src = peaks()
         wsize = {"fp32": 4, "fp16": 2, "fp8": 1}[dtype]
         k_act = max(1, arch.n_experts_active)
@@ -304,7 +437,7 @@ def main():
             kname = "ffn_glu_kernel (rmsnorm + w1/w3 GEMV + GLU)"
         achieved = ffn_bytes / (ffn_us * 1e-6) / 1e9
         # DRAM bytes of one launch from the committed ncu capture: only for the workload it was taken on
-        traffic, traffic_src = ncu_traffic() if (mega and world == 1 and args.workload == "mistral-7b-fp16-4k" and not args.layers) else (None, None)
+        traffic, traffic_src = ncu_traffic() if (mega and world == 1 and args.workload == HEADLINE and not args.layers) else (None, None)
         line = dict(base, impl="ours", value=tok_s, ms_per_step=dev_ms / K, clocks=clk,
                     e2e={"value": K / e2e_s, "unit": "tok/s", "h2d_bytes_per_step": 8, "d2h_bytes_per_step": 4 * V},
                     gpu_launches=(model.launches(api.MODE_LOGITS) + (0 if mega else 1)) * K,
@@ -313,19 +446,21 @@ def main():
                               "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src,
                               "bytes_per_launch": ffn_bytes,
                               "launch_us": ffn_us},
-                    cpu_baseline=cpu_baseline,
+                    parity=parity, cpu_baseline=cpu_baseline, gpu_reference=gpu_reference,
                     whole_step={"weight_bytes_per_token": wbytes, "kv_bytes_per_token": kvbytes,
                                 "gbs_weights": wbytes * tok_s / 1e9 / world, "frac_of_measured_peak_weights": wbytes * tok_s / 1e9 / world / peak,
                                 "frac_of_measured_peak_weights_kv": (wbytes + kvbytes) * tok_s / 1e9 / world / peak,
                                 "frac_of_nominal_8TBs_weights": wbytes * tok_s / 8e12 / world,
                                 "kv_len_range": [pos - K, pos]},
-                    setup_s={"generate": round(t_gen, 1), "load_upload": round(t_load, 1)})
+                    setup_s={"generate": round(t_gen, 1), "load_upload": round(t_load, 1), "loader": load_info})
         _emit(line)
     state.close()
     model.close()
     if world > 1:
         api.lib().yalm_tp_finalize()
         dist.destroy_process_group()
+    if parity and (parity.get("tokens_identical") is False or parity.get("timed_tokens_identical_on_all_ranks") is False):
+        raise SystemExit("bench.py: PARITY FAILURE (see the parity key of the line above)")
 
 
 if __name__ == "__main__":

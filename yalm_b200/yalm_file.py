@@ -345,9 +345,10 @@ def kv_bytes_per_token(arch: Arch, kv_len: int) -> int:
 
 
 def random_model_streamed(arch: Arch, dtype: str = "fp16", seed: int = 0, lm_scale: float = 4.0,
-                          device: str = "cpu", pinned: bool = False) -> np.ndarray:
+                          device: str = "cpu", pinned: bool = False, path: str | None = None) -> np.ndarray:
     """Same model as random_model() (identical bytes), built straight into one preallocated uint8 array so
-    peak host memory is 1x the image (bench-size models: 14 GB Mistral-7B, 93 GB Mixtral)."""
+    peak host memory is 1x the image (bench-size models: 14 GB Mistral-7B, 93 GB Mixtral, 141 GB Llama-3-70B).
+    `path`: build it in that file instead (np.memmap; e.g. under /dev/shm so that several ranks can map one copy)."""
     st = _ST_OF_DTYPE[dtype]
     esz = {"F32": 4, "F16": 2, "F8_E4M3": 1}[st]
     entries = []          # (name, st dtype, shape, nbytes)
@@ -369,7 +370,9 @@ def random_model_streamed(arch: Arch, dtype: str = "fp16", seed: int = 0, lm_sca
     hj = json.dumps(header, separators=(",", ":")).encode()
     hj += b" " * ((-(8 + len(hj))) % 64)
     total = 8 + len(hj) + off
-    if pinned:
+    if path:
+        img = np.memmap(path, dtype=np.uint8, mode="w+", shape=(total,))
+    elif pinned:
         import torch
         img = torch.empty(total, dtype=torch.uint8, pin_memory=True).numpy()
     else:
@@ -380,4 +383,6 @@ def random_model_streamed(arch: Arch, dtype: str = "fp16", seed: int = 0, lm_sca
     for name, arr, _ in random_tensors(arch, dtype, seed, lm_scale, device):
         s, e = header[name]["data_offsets"]
         img[base + s: base + e] = np.ascontiguousarray(arr).view(np.uint8).reshape(-1)
+    if path:
+        img.flush()
     return img
