@@ -43,7 +43,14 @@ def test_kernel_bench_cli_rejects_unknown():
 
 
 def _ids(text):
-    return [int(x) for x in re.findall(r" ?t(\d+)", text)]
+    """Synthetic vocabulary (yalm_file.synthetic_tokens): "<unk>", "<s>", "</s>", then " t<id>"."""
+    special = {"<unk>": 0, "<s>": 1, "</s>": 2}
+    return [special[p] if p in special else int(p.strip()[1:]) for p in re.findall(r"<unk>|<s>|</s>| ?t\d+", text)]
+
+
+def _until_eos(toks):
+    """The completion loop stops after printing an end-of-sequence token (src/main.cpp:107-109)."""
+    return toks[:toks.index(2) + 1] if 2 in toks else toks
 
 
 def _completion_ids(out):
@@ -57,16 +64,15 @@ def test_main_completion_greedy_matches_reference_golden(tmp_path):
     path.write_bytes(img)
     prompt = "".join(f" t{t}" for t in fx["prompt"].tolist()[1:])        # BOS (id 1) is added by the tokenizer
     want = fx["tokens"].tolist()
-    n = 16
-    assert all(t > 2 for t in want[:n]), "golden run hits a special token early; pick another window"
+    n = 24
     out = _run(_exe("main"), str(path), "-d", "cuda", "-m", "completion", "-i", prompt, "-n", str(n), "-t", "0")
     assert "Using CUDA" in out and "Generation stats:" in out and "bandwidth:" in out
-    assert _ids(_completion_ids(out)) == want[:n]
+    assert _ids(_completion_ids(out)) == _until_eos(want[:n])
     # prefix matching of -m / -d and the prompt file flag
     pf = tmp_path / "prompt.txt"
     pf.write_text(prompt)
     out2 = _run(_exe("main"), str(path), "-d", "cu", "-m", "c", "-f", str(pf), "-n", str(n), "-t", "0")
-    assert _ids(_completion_ids(out2)) == want[:n]
+    assert _ids(_completion_ids(out2)) == _until_eos(want[:n])
 
 
 def test_main_sliding_window_flag(tmp_path, oracle):
@@ -76,9 +82,8 @@ def test_main_sliding_window_flag(tmp_path, oracle):
     path.write_bytes(img)
     prompt_ids = fx["prompt"].tolist()
     want = oracle.OracleModel(img, context=24).generate(prompt_ids, 60)
-    stop = next((i for i, t in enumerate(want) if t <= 2), len(want))
     out = _run(_exe("main"), str(path), "-T", "24", "-i", "".join(f" t{t}" for t in prompt_ids[1:]), "-n", "60", "-t", "0")
-    assert _ids(_completion_ids(out))[:stop] == want[:stop]
+    assert _ids(_completion_ids(out)) == _until_eos(want)
 
 
 def test_main_perplexity_matches_oracle(tmp_path, oracle):

@@ -42,10 +42,12 @@ def test_path_selection():
     assert run(img, [1, 2], 2)[2] is True
     assert run(img, [1, 2], 2, mega=False)[2] is False
     _, moe = golden_case("tiny-moe-fp16")
-    assert run(moe, [1, 2], 2)[2] is False          # MoE stays on the per-op path
+    assert run(moe, [1, 2], 2)[2] is True           # MoE: router + expert-indirect rows inside the whole-token kernel
+    assert run(moe, [1, 2], 2, mega=False)[2] is False
 
 
-@pytest.mark.parametrize("name", ["tiny-fp32", "tiny-fp16", "tiny-gelu-clip-fp32", "tiny-gelu-clip-fp16"])
+@pytest.mark.parametrize("name", ["tiny-fp32", "tiny-fp16", "tiny-gelu-clip-fp32", "tiny-gelu-clip-fp16", "tiny-moe-fp32", "tiny-moe-fp16",
+                                  "tiny-kv8-fp16"])
 def test_mega_matches_reference_golden_and_per_op_path(name):
     fx, img = golden_case(name)
     prompt, n = fx["prompt"].tolist(), len(fx["tokens"])

@@ -85,18 +85,17 @@ static const void *kernel_of(int dtype, int head_dim, int g, bool tp) {
 
 // Tile shapes of the five GEMV kinds (qkv, wo, w1/w3, w2, lm head) for one rank's dimensions: rows per tile, columns per
 // tile, K splits, row groups.  Pure arithmetic (no device): plan() and the CPU tests (yalm_mega_tile_plan) share it.
-static bool plan_shapes(int dtype, int dim, int q_dim, int kv_dim, int hidden, int vocab, int (*shape)[4]) {
+static bool plan_shapes(int dtype, int dim, int q_dim, int kv_dim, int hidden, int vocab, int n_sub, int (*shape)[4]) {
 	const int ep = ep_of(dtype), B = bytes_of(dtype);
 	if (!ep) return false;
 	Shape s[kNumKinds];
 	if (!tile_shape(q_dim, kv_dim, dim, B, ep, false, true, &s[kQKV])) return false;
 	if (!tile_shape(dim, 0, q_dim, B, ep, false, false, &s[kWO])) return false;
 	if (!tile_shape(hidden, 0, dim, B, ep, true, true, &s[kFFN])) return false;
-	// w2 split: the tiles of a phase cover one column half (K = hidden / 2)
-	if (YALM_MEGA_W2_SPLIT && hidden % (2 * ep)) return false;
-	if (!tile_shape(dim, 0, YALM_MEGA_W2_SPLIT ? hidden / 2 : hidden, B, ep, false, false, &s[kW2])) return false;
+	if (!tile_shape(dim, 0, hidden, B, ep, false, false, &s[kW2])) return false;
 	if (!tile_shape(vocab, 0, dim, B, ep, false, false, &s[kLM])) return false;
-	s[kQKV].G = (q_dim + 2 * kv_dim) / s[kQKV].R, s[kWO].G = dim / s[kWO].R, s[kFFN].G = hidden / (s[kFFN].R / 2);
+	// MoE: the w1/w3 phase covers the n_sub selected experts (n_sub x hidden rows of hb); w2 runs once per expert
+	s[kQKV].G = (q_dim + 2 * kv_dim) / s[kQKV].R, s[kWO].G = dim / s[kWO].R, s[kFFN].G = n_sub * (hidden / (s[kFFN].R / 2));
 	s[kW2].G = dim / s[kW2].R, s[kLM].G = vocab / s[kLM].R;
 	for (int k = 0; k < kNumKinds; ++k) shape[k][0] = s[k].R, shape[k][1] = s[k].KT, shape[k][2] = s[k].nk, shape[k][3] = s[k].G;
 	return true;
@@ -105,18 +104,19 @@ static bool plan_shapes(int dtype, int dim, int q_dim, int kv_dim, int hidden, i
 Plan plan(int dtype, int dim, int q_dim, int kv_dim, int head_dim, int hidden, int vocab, int n_heads, int n_kv_heads,
           int n_experts, int n_active, int max_seq_len, int n_layers, bool tp, int full_vocab) {
 	Plan p;
-	if (n_layers < 1 || n_layers * (YALM_MEGA_W2_SPLIT ? 6 : 5) + 2 >= (1 << kFlagPhaseBits)) return p; // phase field of the hand-over flags
+	const int n_sub = n_experts > 0 ? n_active : 1;
+	if (n_experts < 0 || n_experts > kMegaMaxExperts || (n_experts > 0 && (n_active < 1 || n_active > kMegaMaxActive || n_active > n_experts))) return p;
+	if (n_layers < 1 || n_layers * (4 + n_sub) + 2 >= (1 << kFlagPhaseBits)) return p; // phase field of the hand-over flags
 	if (tp && (dim > kTpCapFloats || full_vocab > kTpMaxVocab)) return p;
 	p.tp = tp;
 	const int ep = ep_of(dtype);
-	if (!ep || n_experts > 0) return p;
-	(void)n_active;
+	if (!ep) return p;
 	if (n_kv_heads <= 0 || n_heads % n_kv_heads) return p;
 	const int G = n_heads / n_kv_heads;
 	p.kernel = kernel_of(dtype, head_dim, G, tp);
 	if (!p.kernel) return p;
 	if (dim % ep || q_dim % ep || hidden % ep || dim % 4 || q_dim % 4 || hidden % 4) return p;
-	if (!plan_shapes(dtype, dim, q_dim, kv_dim, hidden, vocab, p.shape)) return p;
+	if (!plan_shapes(dtype, dim, q_dim, kv_dim, hidden, vocab, n_sub, p.shape)) return p;
 	const DeviceInfo &di = device_info();
 	int coop = 0, dev = 0;
 	cudaGetDevice(&dev);
@@ -124,7 +124,7 @@ Plan plan(int dtype, int dim, int q_dim, int kv_dim, int head_dim, int hidden, i
 	if (!coop || di.sms < 1) return p;
 	p.grid = di.sms;
 	if (tp && p.grid > kTpMaxGrid) return p;
-	int vf = std::max(padded(dim, ep), std::max(padded(q_dim, ep), padded(YALM_MEGA_W2_SPLIT ? hidden / 2 : hidden, ep)));
+	int vf = std::max(padded(dim, ep), std::max(padded(q_dim, ep), padded(hidden, ep)));
 	if (n_kv_heads > p.grid) return p; // a CTA's attention units must span at most kHeadSlots KV heads
 	// the attention unit split runs in 32-bit arithmetic: (units) x (grid + 1) must stay below 2^31
 	const long long units = (long long)n_kv_heads * (max_seq_len / (kStageBytes / (4 * head_dim)) + 1);
@@ -185,7 +185,7 @@ int launch(const Plan &p, const Args &a, cudaStream_t st) {
 extern "C" int yalm_mega_tile_plan(int dtype, int dim, int q_dim, int kv_dim, int hidden, int vocab, int *out20) {
 	if (!out20) return YALM_EINVAL;
 	int shape[5][4];
-	if (!yalm::mega::plan_shapes(dtype, dim, q_dim, kv_dim, hidden, vocab, shape)) return YALM_EINVAL;
+	if (!yalm::mega::plan_shapes(dtype, dim, q_dim, kv_dim, hidden, vocab, 1, shape)) return YALM_EINVAL;
 	for (int k = 0; k < 5; ++k)
 		for (int j = 0; j < 4; ++j) out20[4 * k + j] = shape[k][j];
 	return 0;

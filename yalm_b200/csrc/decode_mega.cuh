@@ -287,12 +287,13 @@ __host__ __device__ inline bool tile_shape(int rows, int rows_b, int K, int B, i
 // consumer thread 0: [0] phase entered (before the grid barrier) [1] barrier passed [2] input vector staged
 // [3] tiles + epilogue done; [4] cycles warp 0 spent waiting for full ring stages (starvation = HBM-bound).
 // Phase index of a launch -> (layer, kind of phase k, column half).  k: 0 qkv, 1 attention, 2 wo, 3 w1/w3, 4 w2, 5 LM head.
-constexpr int kPPL = YALM_MEGA_W2_SPLIT ? 6 : 5; // phases per layer
-__device__ __forceinline__ void phase_of(int ph, int n_layers, int *l, int *k, int *half) {
-	const int j = ph % kPPL;
-	*l = min(ph / kPPL, n_layers - 1);
-	*half = j == 5 ? 1 : 0;
-	*k = ph < n_layers * kPPL ? (j == 5 ? 4 : j) : 5;
+// phases per layer: qkv, attention, wo, w1/w3, then n_sub w2 sub-phases (dense 1; MoE one per selected expert)
+__device__ __forceinline__ int ppl_of(const Args &a) { return 4 + a.n_sub; }
+__device__ __forceinline__ void phase_of(int ph, const Args &a, int *l, int *k, int *sub) {
+	const int ppl = ppl_of(a), j = ph % ppl;
+	*l = min(ph / ppl, a.n_layers - 1);
+	*sub = j >= 4 ? j - 4 : 0;
+	*k = ph < a.n_layers * ppl ? min(j, 4) : 5;
 }
 constexpr int kProfSlots = 8, kProfPhases = 6; // phases: qkv, attn, wo, ffn, w2, lm(+argmax) (last layer slot only)
 
@@ -311,6 +312,10 @@ __device__ __forceinline__ float *sm_red() { return reinterpret_cast<float *>(sm
 __device__ __forceinline__ int *sm_misc() { return reinterpret_cast<int *>(sm_base() + kOffMisc); }
 // sm_misc slots: [0] combine flag, [4, 4 + consumer warps) arg-max indices, [16..] parked context
 constexpr int kMiscToken = 16, kMiscPos = 17, kMiscPark = 18;
+// MoE router record (written by consumer thread 0 in the w1/w3 staging step, polled by the producer warp):
+// [kMiscRouter] = layer + 1 once [kMiscExpert + k] (ids) and [kMiscExpertW + k] (weights, as float bits) are set
+constexpr int kMiscRouter = 23, kMiscExpert = 24, kMiscExpertW = 28;
+static_assert(kMiscExpertW + kMegaMaxActive <= 32 && kMiscPark + 5 <= kMiscRouter, "sm_misc has 32 slots");
 __device__ __forceinline__ int *sm_rel() { return reinterpret_cast<int *>(sm_base() + kOffRel); } // per-stage release counters
 __device__ __forceinline__ uint32_t sm_full0() { return smem_u32(sm_base() + kOffFull); }
 __device__ __forceinline__ uint32_t sm_empty0() { return smem_u32(sm_base() + kOffEmpty); }
@@ -441,6 +446,10 @@ struct PhaseDesc {
 	const uint16_t *kc, *vc;
 	int nch, u0;
 	int rot_next; // CTA rotation after this phase
+	// mixture of experts: the matrices hold n_experts stacked experts of `estride` bytes; which of them a tile reads is
+	// known only once the router of `layer` has run (Producer::expert waits for it).  gpe: row groups per expert (w1/w3).
+	int layer, sub, gpe;
+	size_t estride;
 };
 
 struct Producer {
@@ -457,10 +466,12 @@ struct Producer {
 		d.m0 = d.m1 = d.m2 = nullptr, d.rows0 = d.rows1 = d.K = 0, d.g_first = d.full_groups = d.full_tiles = d.nb_last = 0;
 		d.kc = d.vc = nullptr, d.nch = 1, d.u0 = 0;
 		d.sh.R = d.sh.KT = d.sh.nk = d.sh.G = 1;
-		const int n_phases = a.n_layers * kPPL + (a.mode != kHydrate ? 1 : 0);
+		d.layer = 0, d.sub = 0, d.gpe = 0, d.estride = 0;
+		const int n_phases = a.n_layers * ppl_of(a) + (a.mode != kHydrate ? 1 : 0);
 		if (ph >= n_phases) return d;
-		int l, k, half;
-		phase_of(ph, a.n_layers, &l, &k, &half);
+		int l, k, sub;
+		phase_of(ph, a, &l, &k, &sub);
+		d.layer = l, d.sub = sub;
 		const Layer &L = a.layers[l];
 		if (k == 1) {
 			const int C = kStageBytes / (4 * HD);
@@ -477,13 +488,15 @@ struct Producer {
 		switch (k) {
 		case 2: d.kind = kWO, d.m0 = L.wo, d.rows0 = a.dim, d.K = a.q_dim; break;
 		case 3: d.kind = kFFN, d.m0 = L.w1, d.m1 = L.w3, d.rows0 = a.hidden; break;
-		case 4: // d.K stays the row stride; with the split the tiles cover the columns of one half (shape kW2: K = hidden / 2)
-			d.kind = kW2, d.m0 = L.w2 + (YALM_MEGA_W2_SPLIT ? (size_t)half * (a.hidden / 2) * B : 0), d.rows0 = a.dim, d.K = a.hidden;
-			break;
+		case 4: d.kind = kW2, d.m0 = L.w2, d.rows0 = a.dim, d.K = a.hidden; break;
 		case 5: d.kind = kLM, d.m0 = a.wcls, d.rows0 = a.vocab; break;
 		default: break;
 		}
 		d.sh = shape_of(a, d.kind);
+		if (a.n_experts > 0 && (k == 3 || k == 4)) {
+			d.estride = (size_t)a.dim * a.hidden * B;
+			d.gpe = k == 3 ? d.sh.G / a.n_sub : 0; // w1/w3: the phase's groups are n_sub experts x gpe groups
+		}
 		d.tile_bytes = (uint32_t)d.sh.R * d.sh.KT * B;
 		d.g_first = (c.cta - rot + c.ncta) % c.ncta;
 		const int NL = d.g_first < d.sh.G ? (d.sh.G - d.g_first + c.ncta - 1) / c.ncta : 0;
@@ -492,10 +505,23 @@ struct Producer {
 		d.full_groups = NL / kConsumerWarps * kConsumerWarps, d.full_tiles = d.full_groups * d.sh.nk;
 		d.nb_last = NL - d.full_groups;
 		d.rot_next = (rot + d.sh.G) % c.ncta;
-		if (YALM_MEGA_W2_SPLIT && k == 4 && half == 0) d.rot_next = rot; // the second half keeps the row -> CTA map
+		if (k == 4 && sub + 1 < a.n_sub) d.rot_next = rot; // every w2 sub-phase keeps the row -> CTA map
 		return d;
 	}
 
+	// Expert chosen for slot `slot` of layer `layer`: waits until the consumers' router step of that layer has published it
+	// (the producer cannot run ahead of the router: which rows the w1/w3 and w2 phases read depends on it).
+	__device__ __forceinline__ int expert(int layer, int slot) {
+		volatile int *misc = sm_misc();
+		if (misc[kMiscRouter] != layer + 1) {
+			const long long t0 = clock64();
+			while (misc[kMiscRouter] != layer + 1) {
+				__nanosleep(32);
+				if (clock64() - t0 > kTimeoutCycles) __trap();
+			}
+		}
+		return misc[kMiscExpert + slot];
+	}
 	// Stage of ring tile idx is free (every earlier round consumed): expect `bytes` on its full barrier.
 	__device__ __forceinline__ uint32_t acquire(uint32_t idx, uint32_t bytes, uint32_t *bar) {
 		uint32_t s;
@@ -560,16 +586,22 @@ struct Producer {
 			const int r = i - d.full_tiles;
 			gl = d.full_groups + r % d.nb_last, kc = r / d.nb_last;
 		}
-		const int g = d.g_first + gl * c.ncta;
+		int g = d.g_first + gl * c.ncta;
+		size_t eoff = 0; // byte offset of the selected expert inside the stacked matrices
+		if (d.estride) {
+			const int slot = d.kind == kFFN ? g / d.gpe : d.sub;
+			if (d.kind == kFFN) g -= slot * d.gpe;
+			eoff = (size_t)expert(d.layer, slot) * d.estride;
+		}
 		uint32_t bar;
 		const uint32_t dst = acquire(ring_idx, d.tile_bytes, &bar);
 		if (d.kind == kFFN) {
 			const int rh = d.sh.R / 2;
-			rows_copy(dst, bar, d.m0, (long)g * rh, rh, d.K, d.sh.KT, kc, d.sh.nk, B);
-			rows_copy(dst + rh * d.sh.KT * B, bar, d.m1, (long)g * rh, rh, d.K, d.sh.KT, kc, d.sh.nk, B);
+			rows_copy(dst, bar, d.m0 + eoff, (long)g * rh, rh, d.K, d.sh.KT, kc, d.sh.nk, B);
+			rows_copy(dst + rh * d.sh.KT * B, bar, d.m1 + eoff, (long)g * rh, rh, d.K, d.sh.KT, kc, d.sh.nk, B);
 		} else {
 			long row = (long)g * d.sh.R;
-			const char *m = d.m0;
+			const char *m = d.m0 + eoff;
 			if (d.kind == kQKV) {
 				if (row >= d.rows0 + d.rows1) row -= d.rows0 + d.rows1, m = d.m2;
 				else if (row >= d.rows0) row -= d.rows0, m = d.m1;
@@ -608,7 +640,7 @@ struct Producer {
 	// Every phase of the token, in order (phase -1 is empty: it only fetches the prefix of phase 0).
 	// `ahead` is in ring stages (kStageBytes); per phase it becomes a whole number of look-ahead units.
 	__device__ __forceinline__ void run(const Args &a, int HD, int B) {
-		const int n_phases = a.n_layers * kPPL + (a.mode != kHydrate ? 1 : 0);
+		const int n_phases = a.n_layers * ppl_of(a) + (a.mode != kHydrate ? 1 : 0);
 		const uint32_t ahead_bytes = (uint32_t)ahead * kStageBytes;
 		PhaseDesc cur = describe(a, n_phases, 0, HD, B); // kNone
 		for (int ph = -1; ph < n_phases; ++ph) {
@@ -934,7 +966,9 @@ struct Epi {
 	const Layer *L;
 	const float *scale0, *scale1, *scale2; // fp8 row scales per matrix
 	int rows0, rows1;                      // QKV boundaries
-	int half;                              // w2 split: 0 / 1 = column half of this phase, -1 = w2 in one piece
+	int sub, n_sub;                        // w2 sub-phase (MoE: one per selected expert; dense: 0 of 1)
+	float ew;                              // MoE: gate weight of this sub-phase's expert (1 for dense models)
+	int gpe;                               // MoE w1/w3: row groups per expert (0: dense)
 	float best_v;                          // LM head: running arg-max of this lane's rows
 	int best_i;
 };
@@ -968,7 +1002,7 @@ __device__ __forceinline__ void gemv_consume(Ctx &c, const Args &a, Epi &ep, int
 		if (!TP && (kind == kWO || kind == kW2) && lane < R * NREP) { // lane = replica * R + row of the group (epilogue below)
 			// flagged hand-over: x after wo lives in ll_x[0] (complete: this CTA polled all of it when it staged w1/w3);
 			// x before wo is the plain copy written behind w2 of the layer before, on the far side of a grid barrier
-			if (YALM_MEGA_W2_SPLIT && kind == kW2 && ep.half == 1) resid = __ldcg(a.w2_tmp + (long)g * R + lane % R); // x + first half
+			if (kind == kW2 && ep.sub > 0) resid = __ldcg(a.w2_tmp + (long)g * R + lane % R); // x + the earlier experts' contributions
 			else if (LL && kind == kW2) resid = ll_val(ll_load1(a.ll_x + (size_t)(c.cta % kLLRep) * a.dim + (long)g * R + lane % R)); // the replica this CTA polled and verified
 			else resid = __ldcg(a.x + (long)g * R + lane % R);
 		}
@@ -1054,11 +1088,18 @@ __device__ __forceinline__ void gemv_consume(Ctx &c, const Args &a, Epi &ep, int
 #pragma unroll
 				for (int r = 1; r < RH; ++r)
 					if (tr == r) gt = acc[r], up = acc[RH + r < R ? RH + r : 0];
-				const long row = (long)g * RH + tr;
-				if (DT == YALM_F8E4M3 && ep.scale0) gt *= ep.scale0[row], up *= ep.scale1[row];
+				const long row = (long)g * RH + tr; // MoE: row of hb = slot * hidden + i
+				if (DT == YALM_F8E4M3 && ep.scale0) {
+					long srow = row;
+					if (ep.gpe) { // scales are stacked per expert like the weights
+						const int slot = g / ep.gpe;
+						srow = (long)sm_misc()[kMiscExpert + slot] * a.hidden + (row - (long)slot * a.hidden);
+					}
+					gt *= ep.scale0[srow], up *= ep.scale1[srow];
+				}
 				gt = a.act == YALM_ACT_GELU ? act_gelu(gt) : act_silu(gt);
 				if (t < RH) a.hb[row] = gt * up;
-				if (LLH) ll_store(a.ll_hb + (size_t)(t / RH) * a.hidden + row, gt * up, wflag);
+				if (LLH) ll_store(a.ll_hb + (size_t)(t / RH) * a.hb_len + row, gt * up, wflag);
 			}
 		} else if (TP) {
 			// tensor parallel: the rows are partial sums (wo / w2: this rank's slice of the input dimension) or this
@@ -1079,11 +1120,11 @@ __device__ __forceinline__ void gemv_consume(Ctx &c, const Args &a, Epi &ep, int
 				const int row = a.vocab_base + (int)row0 + t;
 				if (v > ep.best_v) ep.best_v = v, ep.best_i = row;
 			}
-			if (YALM_MEGA_W2_SPLIT && kind == kW2 && ep.half == 1) { // add the first half's sums (same warp, earlier phase)
+			if (kind == kW2 && ep.n_sub > 1) { // MoE: gate weight, then on top of the earlier experts' sums (same lanes, earlier sub-phase)
 #pragma unroll
-				for (int r = 0; r < R; ++r) vv[r] += __ldcg(a.w2_tmp + row0 + r);
+				for (int r = 0; r < R; ++r) vv[r] = ep.sub > 0 ? fmaf(ep.ew, vv[r], __ldcg(a.w2_tmp + row0 + r)) : ep.ew * vv[r];
 			}
-			if (YALM_MEGA_W2_SPLIT && kind == kW2 && ep.half == 0) { // first half: park the sums, nothing crosses the GPUs yet
+			if (kind == kW2 && ep.sub + 1 < ep.n_sub) { // not the last expert: park the sums, nothing crosses the GPUs yet
 				float v = vv[0];
 #pragma unroll
 				for (int r = 1; r < R; ++r)
@@ -1109,18 +1150,19 @@ __device__ __forceinline__ void gemv_consume(Ctx &c, const Args &a, Epi &ep, int
 				a.logits[row] = v;
 				if (v > ep.best_v) ep.best_v = v, ep.best_i = (int)row; // a lane's rows ascend: first maximum wins
 			} else {
-				// x += W v (src/infer.cpp:335-337, 381-383)
-				if (YALM_MEGA_W2_SPLIT && kind == kW2 && ep.half == 0) {
-					if (t < R) a.w2_tmp[row] = resid + v; // x + first column half; the second half's phase finishes the row
+				// x += W v (src/infer.cpp:335-337); MoE: x += weight * (W2[e] hb_e), expert after expert (:377-383)
+				const float xn = kind == kW2 && ep.n_sub > 1 ? fmaf(ep.ew, v, resid) : resid + v;
+				if (kind == kW2 && ep.sub + 1 < ep.n_sub) {
+					if (t < R) a.w2_tmp[row] = xn; // the next expert's sub-phase continues the row (same lane)
 				} else {
-				if (LL) ll_store(a.ll_x + (size_t)((kind == kW2 ? kLLRep : 0) + t / R) * a.dim + row, resid + v, wflag);
-				if ((!LL || kind == kW2) && t < R) a.x[row] = resid + v;
+					if (LL) ll_store(a.ll_x + (size_t)((kind == kW2 ? kLLRep : 0) + t / R) * a.dim + row, xn, wflag);
+					if ((!LL || kind == kW2) && t < R) a.x[row] = xn;
 				}
 			}
 		}
 	}
 	c.it = base + (uint32_t)(NL * sh.nk);
-	if (!(YALM_MEGA_W2_SPLIT && kind == kW2 && ep.half == 0)) c.rot = (c.rot + sh.G) % c.ncta; // second half: same row -> CTA map
+	if (!(kind == kW2 && ep.sub + 1 < ep.n_sub)) c.rot = (c.rot + sh.G) % c.ncta; // w2 sub-phases share one row -> CTA map
 }
 
 template <int DT, bool TP>
@@ -1490,7 +1532,7 @@ __device__ __forceinline__ void attention_consume(Ctx &c, const Args &a, const L
 	stamp(c, layer, 1, 5);
 
 	// ---- merge the warps, publish the CTA's partial, the last CTA of the head to arrive combines ------------
-	const unsigned wflag = ll_flag(a.seq, layer * kPPL + 2); // flagged hand-over: this phase is ph = kPPL * layer + 1
+	const unsigned wflag = ll_flag(a.seq, layer * ppl_of(a) + 2); // flagged hand-over: this phase is ph = ppl * layer + 1
 	constexpr bool LLC = LL && YALM_MEGA_LL_ATTN;
 	float *ew = wts; // [W][G] merge weights (wts is not in use before the combine)
 	if (c.tid < W * G) { // weight of warp w's record for head g, computed once
@@ -1552,6 +1594,62 @@ __device__ __forceinline__ void attention_consume(Ctx &c, const Args &a, const L
 		                    c.prof ? c.prof + ((size_t)layer * kProfPhases + 1) * kProfSlots + 4 : nullptr, LL ? a.ll_att : nullptr, wflag, a.q_dim);
 }
 
+// Mixture-of-experts router, run by every CTA on the normalised vector it has just staged (c.vec): the n_experts gate
+// logits (one warp per expert row, weights from L2), then moe_gate (src/infer.cpp:100-132): top-k by repeated strict-'>'
+// arg-max (lowest index wins ties), weights = softmax over the SELECTED experts with exponentials relative to the global
+// maximum.  Same instruction sequence in every CTA -> the same bits everywhere; nothing crosses CTAs.  The record in
+// sm_misc releases the producer warp, which has been waiting for the expert ids (Producer::expert).
+template <int DT>
+__device__ __forceinline__ void moe_router(Ctx &c, const Args &a, const Layer &L, int layer) {
+	using T = WTraits<DT>;
+	constexpr int EP = T::EP, CH = 32 * EP, Q = EP / 4;
+	float *gl = sm_red(); // 16 floats: kMegaMaxExperts
+	for (int e = c.warp; e < a.n_experts; e += kConsumerWarps) {
+		const char *row = L.gate + (size_t)e * a.dim * T::BYTES;
+		float2 acc = make_float2(0.f, 0.f);
+		for (int c0 = 0; c0 < a.dim; c0 += CH) {
+			if (c0 + c.lane * EP < a.dim) {
+				const uint4 w = __ldcg(reinterpret_cast<const uint4 *>(row + (size_t)(c0 + c.lane * EP) * T::BYTES));
+				float4 xv[Q];
+#pragma unroll
+				for (int q = 0; q < Q; ++q) xv[q] = lds128f(c.vec_u32 + (uint32_t)(c0 + q * 128) * 4 + c.lane * 16);
+				acc = fma16x2<DT>(w, xv, acc);
+			}
+		}
+		float v = warp_sum(acc.x + acc.y);
+		if (DT == YALM_F8E4M3 && L.sgate) v *= L.sgate[e];
+		if (c.lane == 0) gl[e] = v;
+	}
+	cbar();
+	if (c.tid == 0) {
+		volatile int *misc = sm_misc();
+		float max_val = -FLT_MAX;
+		for (int j = 0; j < a.n_experts; ++j)
+			if (gl[j] > max_val) max_val = gl[j];
+		unsigned mask = 0;
+		float wsum = 0.f;
+		for (int k = 0; k < a.n_active; ++k) {
+			int best = -1;
+			for (int j = 0; j < a.n_experts; ++j)
+				if (!(mask >> j & 1u) && (best == -1 || gl[j] > gl[best])) best = j;
+			misc[kMiscExpert + k] = best;
+			wsum += expf(gl[best] - max_val);
+			mask |= 1u << best;
+		}
+		for (int k = 0; k < a.n_active; ++k) {
+			const int e = misc[kMiscExpert + k];
+			const float w = expf(gl[e] - max_val) / wsum;
+			misc[kMiscExpertW + k] = __float_as_int(w);
+			if (c.cta == 0) a.active_e[k] = e, a.active_w[k] = w; // state taps (InferenceState::active_experts*)
+		}
+		if (c.cta == 0 && a.moe_logits)
+			for (int j = 0; j < a.n_experts; ++j) a.moe_logits[j] = gl[j];
+		__threadfence_block();
+		misc[kMiscRouter] = layer + 1; // releases the producer warp
+	}
+	cbar();
+}
+
 __device__ __forceinline__ void derive_ring(int pos, int max_seq_len, int *kv_sink, int *kv_pos, int *kv_len) {
 	// src/infer.cu:1081-1083
 	*kv_sink = pos >= max_seq_len ? KV_SINKS : 0;
@@ -1583,7 +1681,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_c
 	int token = a.token, pos = a.pos;
 	if (a.token < 0) token = a.ctl[CTL_TOKEN], pos = a.ctl[CTL_POS];
 	derive_ring(pos, a.max_seq_len, &c.kv_sink, &c.kv_pos, &c.kv_len);
-	if (threadIdx.x == 0) sm_misc()[kMiscToken] = token, sm_misc()[kMiscPos] = pos; // needed at phase 0 / at the very end only
+	if (threadIdx.x == 0) sm_misc()[kMiscToken] = token, sm_misc()[kMiscPos] = pos, sm_misc()[kMiscRouter] = 0; // token / pos: needed at phase 0 / at the very end only
 
 	if (threadIdx.x == 0) {
 		for (int i = 0; i < c.S; ++i) {
@@ -1605,18 +1703,20 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_c
 
 	if (c.warp >= kConsumerWarps) {
 		// ================================ producers ================================
-		Producer p{c, (a.debug & 8) ? 0ull : policy_evict_first(), min(c.S, 32), (a.debug & 8) ? 0 : abs(a.l2_ahead), a.l2_ahead > 0, (a.debug & 16) != 0};
+		// (the L2 look-ahead experiment does not know about expert-indirect rows: off for MoE)
+		Producer p{c, (a.debug & 8) ? 0ull : policy_evict_first(), min(c.S, 32), (a.debug & 8) || a.n_experts > 0 ? 0 : abs(a.l2_ahead), a.l2_ahead > 0, (a.debug & 16) != 0};
 		p.run(a, HD, B);
 		return;
 	}
 
 	// ================================ consumers ================================
 	Epi ep;
-	const int n_phases = a.n_layers * kPPL + (a.mode != kHydrate ? 1 : 0);
+	const int n_phases = a.n_layers * ppl_of(a) + (a.mode != kHydrate ? 1 : 0);
+	const bool moe = a.n_experts > 0;
 	for (int ph = 0; ph < n_phases; ++ph) { // one loop body = one call site per phase function
-		int l, k, half;
-		phase_of(ph, a.n_layers, &l, &k, &half);
-		ep.half = YALM_MEGA_W2_SPLIT && k == 4 ? half : -1; // -1: w2 in one piece
+		int l, k, sub;
+		phase_of(ph, a, &l, &k, &sub);
+		ep.sub = k == 4 ? sub : 0, ep.n_sub = k == 4 ? a.n_sub : 1, ep.ew = 1.0f, ep.gpe = 0;
 		const Layer &L = a.layers[l];
 		ep.L = &L;
 		stamp(c, l, k, 0);
@@ -1624,12 +1724,12 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_c
 		float4 wv[kNormCache];
 		load_norm_weights(c, rms, a.dim, wv); // in flight across the barrier
 		// tensor parallel: the boundaries behind wo (k == 3) and w2 (k == 0 of the next layer, k == 5) span the GPUs
-		const bool reduced = TP && ph > 0 && (k == 3 || k == 0 || k == 5);
+		const bool reduced = TP && ph > 0 && (k == 3 || k == 0 || k == 5) && sub == 0;
 		// flagged hand-over (single GPU): only the QKV -> attention boundary keeps its grid barrier, every other
 		// phase polls its input vector in the staging step
 		constexpr bool LL = YALM_MEGA_LL != 0;
 		const bool flagged = LL && ph > 0 && (TP ? k == 2 || k == 4 : k != 1); // this phase polls its input instead of a barrier
-		const unsigned rflag = ll_flag(a.seq, ph); // what the phase before this one produced
+		const unsigned rflag = ll_flag(a.seq, ph - sub); // what the phase before this one produced (w2 sub-phases: all of hb comes from the w1/w3 phase)
 		if (reduced) tp_barrier(c, a);
 		else if (ph > 0 && !flagged) grid_barrier(c, a.sync);
 		stamp(c, l, k, 1);
@@ -1644,10 +1744,13 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_c
 		switch (k) {
 		case 0: ep.kind = kQKV, ep.scale0 = L.sq, ep.scale1 = L.sk, ep.scale2 = L.sv, ep.rows0 = a.q_dim, ep.rows1 = a.kv_dim; break;
 		case 2: src = a.att_out, n = a.q_dim, ep.kind = kWO, ep.scale0 = L.so; break;
-		case 3: ep.kind = kFFN, ep.scale0 = L.s1, ep.scale1 = L.s3; break;
+		case 3: ep.kind = kFFN, ep.scale0 = L.s1, ep.scale1 = L.s3, ep.gpe = moe ? a.shape[kFFN][3] / a.n_sub : 0; break;
 		case 4:
-			src = a.hb, n = a.hidden, ep.kind = kW2, ep.scale0 = L.s2;
-			if (YALM_MEGA_W2_SPLIT) n = a.hidden / 2, src += (size_t)half * n; // this phase's half of hb
+			src = a.hb + (size_t)sub * a.hidden, n = a.hidden, ep.kind = kW2, ep.scale0 = L.s2; // MoE: the sub-th selected expert's slice of hb
+			if (moe) {
+				ep.ew = __int_as_float(sm_misc()[kMiscExpertW + sub]);
+				if (L.s2) ep.scale0 = L.s2 + (size_t)sm_misc()[kMiscExpert + sub] * a.dim;
+			}
 			break;
 		default: ep.kind = kLM, ep.scale0 = a.wcls_scale, ep.best_v = -FLT_MAX, ep.best_i = 0x7fffffff; break;
 		}
@@ -1665,13 +1768,13 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_c
 					                  nch >= sp.nc ? c.cta - sp.c0 : sp.k0, rflag, c.tid, a.q_dim);
 			}
 			const unsigned long long *lsrc = k == 2 ? a.ll_att : k == 3 ? a.ll_x : k == 4 ? a.ll_hb : a.ll_x + (size_t)kLLRep * a.dim;
-			lsrc += (size_t)(c.cta % kLLRep) * (k == 4 ? a.hidden : n); // this CTA's replica
-			if (YALM_MEGA_W2_SPLIT && k == 4) lsrc += (size_t)half * n;
-			// (the second half of hb carries the flag of the w1/w3 phase too: two phases back)
-			stage_vec_ll<DT>(c, a, lsrc, n, rms, YALM_MEGA_W2_SPLIT && k == 4 && half ? rflag - 1 : rflag, wv, c.prof ? c.prof + ((size_t)l * kProfPhases + k) * kProfSlots : nullptr);
+			lsrc += (size_t)(c.cta % kLLRep) * (k == 4 ? a.hb_len : n); // this CTA's replica
+			if (k == 4) lsrc += (size_t)sub * n;
+			stage_vec_ll<DT>(c, a, lsrc, n, rms, rflag, wv, c.prof ? c.prof + ((size_t)l * kProfPhases + k) * kProfSlots : nullptr);
 		} else {
 			stage_vec<DT>(c, a, src, n, rms, ph == 0 ? sm_misc()[kMiscToken] : -1, wv);
 		}
+		if (moe && k == 3) moe_router<DT>(c, a, L, l); // on the vector just staged; releases the producer's w1/w3 and w2 tiles
 		stamp(c, l, k, 2);
 		if (k == 0 && c.kv_sink > 0 && c.cta == c.ncta - 1) {
 			// rotate each sink key forward by one position, fp16 -> fp32 -> fp16 (src/infer.cpp:303-317)

@@ -21,13 +21,13 @@ constexpr int kThreads = (kConsumerWarps + kProducerWarps) * 32;
 constexpr int kMaxStages = 24;
 constexpr int kSmemHeader = 1280; // rope table, reduction scratch, release counters, mbarriers in front of the ring
 constexpr int kTraceEvents = 1 << 16;
-// 1: w2 runs as two phases over the two column halves of the matrix with the same row -> CTA / warp / lane map; the
-// half-sums wait in Args::w2_tmp with the lane that made them (no hand-over in between).  The fp32 hb vector in shared
-// memory halves, which buys 3 ring stages.  Parity-green on B200 (all megakernel tests), but 4 % SLOWER on an 8-layer slice
-// of the 7B model (1218 vs 1271 tok/s): the extra phase costs more than the three stages give.  Off.
-#ifndef YALM_MEGA_W2_SPLIT
-#define YALM_MEGA_W2_SPLIT 0
-#endif
+// Mixture of experts (Mixtral: 8 experts, 2 active; the reference has MoE on the CPU only, src/infer.cpp:100-132, 347-384;
+// its CUDA path asserts, src/infer.cu:865-867).  The router runs in the staging step of the w1/w3 phase (every CTA
+// recomputes the n_experts logits and the top-k, bit-identically), the producer waits for it and streams the rows of the
+// SELECTED experts (expert-indirect bases), and w2 runs as n_active sub-phases — one per selected expert, same row -> CTA
+// -> warp -> lane map, the running sum x + w_0 W2[e_0] hb_0 (+ ...) waits in Args::w2_tmp with the lane that made it —
+// so the summation order is the reference's (src/infer.cpp:377-383).  Dense models: n_sub = 1.
+constexpr int kMegaMaxExperts = 16, kMegaMaxActive = 4;
 #ifndef YALM_MEGA_LL_REP
 #define YALM_MEGA_LL_REP 4
 #endif
@@ -68,6 +68,8 @@ struct Args {
 	int n_layers;
 	int dim, q_dim, kv_dim, head_dim, hidden, vocab, n_heads, n_kv_heads, rotary_dim, max_seq_len, act;
 	int n_experts, n_active;
+	int n_sub;  // w2 sub-phases per layer: 1 (dense) or n_active (MoE)
+	int hb_len; // n_sub * hidden: hb holds act(w1 x) * (w3 x) of every selected expert
 	float theta, eps, clip;
 	const char *embed;
 	const float *embed_scale, *rms_final;
@@ -99,12 +101,12 @@ struct Args {
 	// Flagged hand-over buffers (single GPU, see decode_mega.cuh "flagged hand-over"): every entry is one 64-bit word
 	// {fp32 value, u32 flag}, flag = seq << kFlagPhaseBits | (producing phase + 1); zero before the first launch.
 	unsigned long long *ll_x;   // [2][kLLRep][dim]: [0] x after wo, [1] x after w2
-	unsigned long long *ll_hb;  // [kLLRep][hidden]
+	unsigned long long *ll_hb;  // [kLLRep][hb_len]
 	unsigned long long *ll_att; // [kLLRep][q_dim]
 	unsigned long long *ll_acc; // attention partials, (n_kv, grid, G, HD)
 	unsigned long long *ll_ml;  // (n_kv, grid, G, 2): {max, flag}, {sum, flag}
 	unsigned seq;               // launch number of this inference state, starts at 1
-	float *w2_tmp;              // [dim]: x + first column half of w2 (YALM_MEGA_W2_SPLIT), private to the lane that wrote it
+	float *w2_tmp;              // [dim]: MoE, x + the earlier experts' contributions, private to the lane that wrote it
 	char *tp_peer[kTpMaxWorld]; // every rank's region (kTpOff*), [tp_rank] = this rank's own
 };
 

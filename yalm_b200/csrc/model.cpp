@@ -234,7 +234,7 @@ void InferenceState::cuda() {
 	    {(void **)&_mega_amax_val, sizeof(float) * (size_t)sms},
 	    {(void **)&_mega_amax_idx, sizeof(int) * (size_t)sms},
 	    {(void **)&_mega_tmp, sizeof(float) * c.dim},
-	    {(void **)&_mega_ll, 8 * (yalm::mega::kLLRep * ((size_t)2 * c.dim + lhid + (size_t)lh * c.head_dim) +
+	    {(void **)&_mega_ll, 8 * (yalm::mega::kLLRep * ((size_t)2 * c.dim + (size_t)k_act * lhid + (size_t)lh * c.head_dim) +
 	                              (size_t)sms * lh * c.head_dim + (size_t)sms * lh * 2)},
 	};
 	size_t total = 0;
@@ -692,6 +692,7 @@ int Model::launch_mega(InferenceState &s, int token, int pos, int mode, long lon
 	a.rotary_dim = c.rotary_dim, a.max_seq_len = c.max_seq_len;
 	a.act = c.act == ActivationType::SILU ? YALM_ACT_SILU : YALM_ACT_GELU;
 	a.n_experts = c.n_experts, a.n_active = c.n_experts_active;
+	a.n_sub = c.n_experts > 0 ? c.n_experts_active : 1, a.hb_len = a.n_sub * a.hidden;
 	a.theta = c.rope_theta, a.eps = c.norm_eps, a.clip = c.qkv_clip;
 	a.embed = (const char *)token_embedding_table, a.embed_scale = embed_scale, a.rms_final = rms_final_weight;
 	a.wcls = (const char *)wcls, a.wcls_scale = wcls_scale;
@@ -700,7 +701,7 @@ int Model::launch_mega(InferenceState &s, int token, int pos, int mode, long lon
 	a.ws_acc = s.mega_acc(), a.ws_ml = s.mega_ml(), a.head_counters = s.mega_counters(), a.sync = s.mega_sync();
 	a.amax_val = s.mega_amax_val(), a.amax_idx = s.mega_amax_idx();
 	constexpr size_t rep = yalm::mega::kLLRep;
-	a.ll_x = s.mega_ll(), a.ll_hb = a.ll_x + rep * 2 * c.dim, a.ll_att = a.ll_hb + rep * c.local_hidden();
+	a.ll_x = s.mega_ll(), a.ll_hb = a.ll_x + rep * 2 * c.dim, a.ll_att = a.ll_hb + rep * (size_t)a.hb_len;
 	a.ll_acc = a.ll_att + rep * a.q_dim, a.ll_ml = a.ll_acc + (size_t)_mega->plan.grid * a.q_dim;
 	a.seq = s.next_mega_seq();
 	a.w2_tmp = s.mega_tmp();
