@@ -128,11 +128,12 @@ def host_threads():
         return os.cpu_count() or 1
 
 
-def write_model(path, arch, dtype):
-    """Seeded random-init image of `arch` straight into `path` (large tensors drawn on the GPU when there is one)."""
+def write_model(path, arch, dtype, part=None, create=True):
+    """Seeded random-init image of `arch` straight into `path` (large tensors drawn on the GPU when there is one).
+    part = (rank, world): this process draws every world-th tensor (all ranks of a node fill one file together)."""
     import torch
     dev = "cuda" if torch.cuda.is_available() else "cpu"
-    img = yf.random_model_streamed(arch, dtype, seed=0, device=dev, path=path)
+    img = yf.random_model_streamed(arch, dtype, seed=0, device=dev, path=path, part=part, create=create)
     del img
 
 
@@ -309,8 +310,11 @@ def main():
     # ---- the model image: ONE copy per node (rank 0 writes it under /dev/shm, every rank maps it and uploads its slices)
     t_gen = time.perf_counter()
     if rank == 0:
-        write_model(path, arch, dtype)
-        torch.cuda.empty_cache()
+        write_model(path, arch, dtype, part=(0, world))     # sizes the file, writes the header and its share of the tensors
+    barrier()
+    if rank != 0:
+        write_model(path, arch, dtype, part=(rank, world), create=False)
+    torch.cuda.empty_cache()
     barrier()
     t_gen = time.perf_counter() - t_gen
 

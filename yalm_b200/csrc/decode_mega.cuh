@@ -171,6 +171,18 @@ __device__ __forceinline__ unsigned long long ll_load1(const unsigned long long 
 	asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
 	return v;
 }
+// The same words across GPUs (tensor parallelism): stores into a peer's region over NVLink, polls of this rank's own region.
+__device__ __forceinline__ void ll_store_sys(unsigned long long *p, float v, unsigned flag) {
+	asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(ll_pack(v, flag)) : "memory");
+}
+__device__ __forceinline__ void ll_store2_sys(unsigned long long *p, float v0, float v1, unsigned flag) {
+	asm volatile("st.relaxed.sys.global.v2.u64 [%0], {%1, %2};" ::"l"(p), "l"(ll_pack(v0, flag)), "l"(ll_pack(v1, flag)) : "memory");
+}
+__device__ __forceinline__ unsigned long long ll_load1_sys(const unsigned long long *p) {
+	unsigned long long v;
+	asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+	return v;
+}
 __device__ __forceinline__ bool ll_ok(unsigned long long w, unsigned flag) { return (unsigned)(w >> 32) == flag; }
 __device__ __forceinline__ float ll_val(unsigned long long w) { return __uint_as_float((unsigned)w); }
 // Four consecutive elements (32 bytes); true when all four carry `flag`.
@@ -772,20 +784,8 @@ __device__ __forceinline__ void release(Ctx &c, uint32_t idx) {
 
 // Input vector -> permuted shared layout (xs_slot).  embed_token < 0: fp32 vector in global memory (read through
 // L2: other CTAs wrote it during this launch); >= 0: that row of the weight-typed embedding table (layer 0).
-// tp_slots != null: the vector is the residual `src` plus every rank's partial (slot r at tp_slots + r * kTpCapFloats),
-// added in rank order — the same bits on every rank.
 template <int DT>
-__device__ __forceinline__ float4 load_in4(const Args &a, const float *src, int embed_token, int e, const float *tp_slots = nullptr) {
-	if (tp_slots) {
-		float4 v = __ldcg(reinterpret_cast<const float4 *>(src + e));
-		for (int r0 = 0; r0 < a.tp_world; r0 += 2) { // world sizes are 2, 4, 8: two loads in flight per thread and float4
-			const float4 p0 = __ldcg(reinterpret_cast<const float4 *>(tp_slots + (size_t)r0 * kTpCapFloats + e));
-			const float4 p1 = __ldcg(reinterpret_cast<const float4 *>(tp_slots + (size_t)(r0 + 1) * kTpCapFloats + e));
-			v.x += p0.x, v.y += p0.y, v.z += p0.z, v.w += p0.w;
-			v.x += p1.x, v.y += p1.y, v.z += p1.z, v.w += p1.w;
-		}
-		return v;
-	}
+__device__ __forceinline__ float4 load_in4(const Args &a, const float *src, int embed_token, int e) {
 	if (embed_token < 0) return __ldcg(reinterpret_cast<const float4 *>(src + e));
 	const size_t base = (size_t)embed_token * a.dim + e;
 	const float sc = (DT == YALM_F8E4M3 && a.embed_scale) ? a.embed_scale[embed_token] : 1.0f;
@@ -808,7 +808,7 @@ __device__ __forceinline__ void load_norm_weights(const Ctx &c, const float *rms
 // `wv`: this thread's norm weights (load_norm_weights), fetched before the grid barrier.
 template <int DT>
 __device__ __forceinline__ void stage_vec(Ctx &c, const Args &a, const float *src, int n, const float *rms_w, int embed_token,
-                                          const float4 (&wv)[kNormCache], const float *tp_slots = nullptr, float *x_out = nullptr) {
+                                          const float4 (&wv)[kNormCache]) {
 	constexpr int EP = WTraits<DT>::EP;
 	constexpr int NC = kNormCache; // float4 per thread kept in registers between the two rmsnorm passes (n <= 4096)
 	if (rms_w) {
@@ -819,21 +819,20 @@ __device__ __forceinline__ void stage_vec(Ctx &c, const Args &a, const float *sr
 		for (int i = 0; i < NC; ++i) {
 			const int e = (c.tid + i * kCT) * 4;
 			cache[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-			if (e < n) cache[i] = load_in4<DT>(a, src, embed_token, e, tp_slots);
+			if (e < n) cache[i] = load_in4<DT>(a, src, embed_token, e);
 		}
 #pragma unroll
 		for (int i = 0; i < NC; ++i)
 			ss += cache[i].x * cache[i].x + cache[i].y * cache[i].y + cache[i].z * cache[i].z + cache[i].w * cache[i].w;
 		for (int e = (c.tid + NC * kCT) * 4; e < n; e += kCT * 4) {
-			const float4 v = load_in4<DT>(a, src, embed_token, e, tp_slots);
+			const float4 v = load_in4<DT>(a, src, embed_token, e);
 			ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
 		}
 		ss = cons_sum(c, ss);
 		const float scale = 1.0f / sqrtf(ss / n + a.eps);
-		// layer 0: the residual stream starts as the embedding row; after an in-kernel all-reduce: the reduced vector
-		// becomes the new residual (written to the other x buffer: CTAs still staging read the old one)
-		const bool seed_x = (embed_token >= 0 || tp_slots) && c.cta == 0;
-		if (!x_out) x_out = a.x;
+		// layer 0: the residual stream starts as the embedding row
+		const bool seed_x = embed_token >= 0 && c.cta == 0;
+		float *x_out = a.x;
 #pragma unroll
 		for (int i = 0; i < NC; ++i) {
 			const int e = (c.tid + i * kCT) * 4;
@@ -845,7 +844,7 @@ __device__ __forceinline__ void stage_vec(Ctx &c, const Args &a, const float *sr
 			}
 		}
 		for (int e = (c.tid + NC * kCT) * 4; e < n; e += kCT * 4) {
-			const float4 v = load_in4<DT>(a, src, embed_token, e, tp_slots);
+			const float4 v = load_in4<DT>(a, src, embed_token, e);
 			const float4 w = *reinterpret_cast<const float4 *>(rms_w + e);
 			*reinterpret_cast<float4 *>(c.vec + xs_slot<EP>(e)) =
 			    make_float4(v.x * scale * w.x, v.y * scale * w.y, v.z * scale * w.z, v.w * scale * w.w);
@@ -978,8 +977,9 @@ struct Epi {
 // and its first lanes run the epilogue.  Nothing here synchronises with the other warps.
 template <int DT, int R, bool TP>
 __device__ __forceinline__ void gemv_consume(Ctx &c, const Args &a, Epi &ep, int ph) {
-	constexpr bool LL = YALM_MEGA_LL && !TP; // x: single GPU only (tensor parallel: x crosses the GPUs through the peer slots)
-	constexpr bool LLH = YALM_MEGA_LL;       // hb (and att_out): local vectors, flagged in both modes
+	static_assert(YALM_MEGA_LL || !TP, "tensor parallelism rides on the flagged hand-over");
+	constexpr bool LL = YALM_MEGA_LL;  // x: flagged words (tensor parallel: the finished rows, after the exchange at the end of the phase)
+	constexpr bool LLH = YALM_MEGA_LL; // hb (and att_out): flagged too
 	constexpr int NREP = LL ? kLLRep : 1;    // flagged vectors are written kLLRep times (lane -> replica): see kLLRep
 	constexpr int NREPH = LLH ? kLLRep : 1;
 	const unsigned wflag = ll_flag(a.seq, ph + 1); // flagged hand-over: the next phase polls for this
@@ -999,7 +999,7 @@ __device__ __forceinline__ void gemv_consume(Ctx &c, const Args &a, Epi &ep, int
 		const int g = g_first + (b8 + warp) * c.ncta;
 		// residual operand of the wo / w2 epilogue: issue the L2 read now, it is consumed after the tiles
 		float resid = 0.f;
-		if (!TP && (kind == kWO || kind == kW2) && lane < R * NREP) { // lane = replica * R + row of the group (epilogue below)
+		if (!TP && (kind == kWO || kind == kW2) && lane < R * NREP) { // lane = replica * R + row of the group (epilogue below; tensor parallel: tp_collect)
 			// flagged hand-over: x after wo lives in ll_x[0] (complete: this CTA polled all of it when it staged w1/w3);
 			// x before wo is the plain copy written behind w2 of the layer before, on the far side of a grid barrier
 			if (kind == kW2 && ep.sub > 0) resid = __ldcg(a.w2_tmp + (long)g * R + lane % R); // x + the earlier experts' contributions
@@ -1104,7 +1104,8 @@ __device__ __forceinline__ void gemv_consume(Ctx &c, const Args &a, Epi &ep, int
 		} else if (TP) {
 			// tensor parallel: the rows are partial sums (wo / w2: this rank's slice of the input dimension) or this
 			// rank's slice of the vocabulary.  Every lane holds all R sums, so lane r hands the group's R values to
-			// rank r — one vector store per peer over NVLink — into slot [set][rank] or the gathered logits.
+			// rank r over NVLink: flagged words into mailbox [set][this rank] (collected by the warp that owns the same
+			// rows there: tp_collect below), or plain stores into the gathered logits.
 			const long row0 = (long)g * R;
 			float vv[R];
 #pragma unroll
@@ -1130,13 +1131,17 @@ __device__ __forceinline__ void gemv_consume(Ctx &c, const Args &a, Epi &ep, int
 				for (int r = 1; r < R; ++r)
 					if (t == r) v = vv[r];
 				if (t < R) a.w2_tmp[row0 + t] = v;
-			} else if (lane < a.tp_world) {
-				float *dst = kind == kLM ? reinterpret_cast<float *>(a.tp_peer[lane] + kTpOffLogits) + a.vocab_base + row0
-				                         : reinterpret_cast<float *>(a.tp_peer[lane] + kTpOffSlots) +
-				                               (size_t)((kind == kW2 ? a.tp_world : 0) + a.tp_rank) * kTpCapFloats + row0;
+			} else if (lane < a.tp_world && kind == kLM) {
+				float *dst = reinterpret_cast<float *>(a.tp_peer[lane] + kTpOffLogits) + a.vocab_base + row0;
 				if (R == 4) *reinterpret_cast<float4 *>(dst) = make_float4(vv[0], vv[R > 1 ? 1 : 0], vv[R > 2 ? 2 : 0], vv[R > 3 ? 3 : 0]);
 				else if (R == 2) *reinterpret_cast<float2 *>(dst) = make_float2(vv[0], vv[R > 1 ? 1 : 0]);
 				else dst[0] = vv[0];
+			} else if (lane < a.tp_world) {
+				unsigned long long *dst = reinterpret_cast<unsigned long long *>(a.tp_peer[lane] + kTpOffMail) +
+				                          (size_t)((kind == kW2 ? kTpMaxWorld : 0) + a.tp_rank) * kTpCapFloats + row0;
+				if (R == 4) ll_store2_sys(dst, vv[0], vv[R > 1 ? 1 : 0], wflag), ll_store2_sys(dst + 2, vv[R > 2 ? 2 : 0], vv[R > 3 ? 3 : 0], wflag);
+				else if (R == 2) ll_store2_sys(dst, vv[0], vv[R > 1 ? 1 : 0], wflag);
+				else ll_store_sys(dst, vv[0], wflag);
 			}
 		} else if (t < (kind == kLM ? R : R * NREP)) { // wo / w2: lane = replica * R + row
 			const int tr = t % R;
@@ -1158,6 +1163,44 @@ __device__ __forceinline__ void gemv_consume(Ctx &c, const Args &a, Epi &ep, int
 					if (LL) ll_store(a.ll_x + (size_t)((kind == kW2 ? kLLRep : 0) + t / R) * a.dim + row, xn, wflag);
 					if ((!LL || kind == kW2) && t < R) a.x[row] = xn;
 				}
+			}
+		}
+	}
+	if (TP && (kind == kWO || (kind == kW2 && ep.sub + 1 == ep.n_sub))) {
+		// ---- tensor parallel: finish this warp's rows.  Every rank's partial of group g has been (or is being) pushed into
+		// this rank's mailbox by the warp that owns g there; lane = rank * R + row polls its word, the sums run in rank
+		// order on top of the residual (the same bits on every rank), and the finished rows go out as local flagged words.
+		const unsigned long long *mail = reinterpret_cast<const unsigned long long *>(a.tp_peer[a.tp_rank] + kTpOffMail) +
+		                                 (size_t)(kind == kW2 ? kTpMaxWorld : 0) * kTpCapFloats;
+		const int W = a.tp_world;
+		for (int b8 = 0; b8 < NL; b8 += kConsumerWarps) {
+			if (warp >= min(kConsumerWarps, NL - b8)) break;
+			const int g = g_first + (b8 + warp) * c.ncta;
+			const int tr = lane % R;
+			const long row = (long)g * R + tr;
+			float part = 0.f;
+			if (lane < W * R) {
+				const unsigned long long *p = mail + (size_t)(lane / R) * kTpCapFloats + row;
+				unsigned long long w = ll_load1_sys(p);
+				if (!ll_ok(w, wflag)) {
+					const long long t0 = clock64();
+					do {
+						__nanosleep(64);
+						if (clock64() - t0 > kTpTimeoutCycles) __trap();
+						w = ll_load1_sys(p);
+					} while (!ll_ok(w, wflag));
+				}
+				part = ll_val(w);
+			}
+			// residual: x before wo is the plain copy behind w2 of the layer before (far side of the attention grid barrier);
+			// x before w2 is ll_x[0], complete in the replica this CTA verified when it staged w1/w3
+			float xn = 0.f;
+			if (lane < R * NREP)
+				xn = kind == kW2 ? ll_val(ll_load1(a.ll_x + (size_t)(c.cta % kLLRep) * a.dim + row)) : __ldcg(a.x + row);
+			for (int r = 0; r < W; ++r) xn += __shfl_sync(kFull, part, r * R + tr);
+			if (lane < R * NREP) {
+				ll_store(a.ll_x + (size_t)((kind == kW2 ? kLLRep : 0) + lane / R) * a.dim + row, xn, wflag);
+				if (kind == kW2 && lane < R) a.x[row] = xn;
 			}
 		}
 	}
@@ -1723,15 +1766,13 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_c
 		const float *rms = k == 0 ? L.rms_att : k == 3 ? L.rms_ffn : k == 5 ? a.rms_final : nullptr;
 		float4 wv[kNormCache];
 		load_norm_weights(c, rms, a.dim, wv); // in flight across the barrier
-		// tensor parallel: the boundaries behind wo (k == 3) and w2 (k == 0 of the next layer, k == 5) span the GPUs
-		const bool reduced = TP && ph > 0 && (k == 3 || k == 0 || k == 5) && sub == 0;
-		// flagged hand-over (single GPU): only the QKV -> attention boundary keeps its grid barrier, every other
-		// phase polls its input vector in the staging step
+		// flagged hand-over: only the QKV -> attention boundary keeps its (local) grid barrier, every other phase polls its
+		// input vector in the staging step.  Tensor parallel: the vectors behind wo / w2 were finished by the exchange at
+		// the end of those phases (gemv_consume) and travel the same way — no cross-GPU barrier at any phase boundary.
 		constexpr bool LL = YALM_MEGA_LL != 0;
-		const bool flagged = LL && ph > 0 && (TP ? k == 2 || k == 4 : k != 1); // this phase polls its input instead of a barrier
+		const bool flagged = LL && ph > 0 && k != 1; // this phase polls its input instead of a barrier
 		const unsigned rflag = ll_flag(a.seq, ph - sub); // what the phase before this one produced (w2 sub-phases: all of hb comes from the w1/w3 phase)
-		if (reduced) tp_barrier(c, a);
-		else if (ph > 0 && !flagged) grid_barrier(c, a.sync);
+		if (ph > 0 && !flagged) grid_barrier(c, a.sync);
 		stamp(c, l, k, 1);
 		if (k == 1) { // attention: q comes from registers, nothing to stage
 			stamp(c, l, k, 2);
@@ -1754,12 +1795,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_c
 			break;
 		default: ep.kind = kLM, ep.scale0 = a.wcls_scale, ep.best_v = -FLT_MAX, ep.best_i = 0x7fffffff; break;
 		}
-		if (reduced) {
-			// x ping-pongs: behind wo the residual is x and the sum goes to x2, behind w2 the other way round
-			const float *slots = reinterpret_cast<const float *>(a.tp_peer[a.tp_rank] + kTpOffSlots) +
-			                     (size_t)(k == 3 ? 0 : a.tp_world) * kTpCapFloats;
-			stage_vec<DT>(c, a, k == 3 ? a.x : a.x2, n, rms, -1, wv, slots, k == 3 ? a.x2 : a.x);
-		} else if (flagged) {
+		if (flagged) {
 			if (YALM_MEGA_LL_ATTN && k == 2) { // distributed attention combine of this CTA's head slice (flags of phase ph - 1)
 				const int C = kStageBytes / (4 * HD), nch = (c.kv_len + C - 1) / C;
 				const AttnSplit sp = attn_split(c.cta, c.ncta, a.n_kv_heads, nch);

@@ -36,19 +36,23 @@ constexpr int kLLRep = YALM_MEGA_LL_REP; // copies of every flagged hand-over ve
 constexpr int kProfileSlots = 6 * 8; // per (CTA, layer): phases x slots, see decode_mega.cuh
 
 // ---- tensor parallelism inside the kernel (N GPUs of one NVSwitch domain) ---------------------------------------------
-// Every rank owns one region of device memory that all peers map (CUDA IPC, tp.cpp).  The wo / w2 epilogues push
-// their partial rows of x into slot [set][rank] of EVERY rank's region with plain stores over NVLink, the phase
-// boundary that follows is a cross-GPU barrier (one counter per region, every CTA of every rank adds 1 to each), and
-// the next phase's staging step sums the slots in rank order on top of the residual — the all-reduce has no kernel of
-// its own and no second pass over the data.  The LM head scatters its logits rows and arg-max candidates the same way.
+// Every rank owns one region of device memory that all peers map (CUDA IPC, tp.cpp).  The row -> CTA -> warp map of a
+// phase is the same on every rank, so the all-reduce behind wo / w2 is an exchange between the warps that own the same
+// rows: the epilogue pushes the warp's partial rows into mailbox [set][rank] of EVERY rank's region over NVLink as
+// flagged 64-bit words {fp32 value, flag} (the hand-over protocol of decode_mega.cuh; NCCL's LL protocol relies on the
+// same 8-byte atomicity), and at the end of the phase the warp polls the world's words for ITS rows in its own region,
+// adds them to the residual in rank order — the same bits on every rank — and publishes the finished rows as local
+// flagged words, exactly as on a single GPU.  No cross-GPU barrier, no system-scope fence, no atomics on the data path;
+// the all-reduce has no kernel of its own.  The LM head scatters its logits rows and arg-max candidates with plain
+// stores; ONE cross-GPU barrier per token (at the very end) makes them visible.
 constexpr int kTpMaxWorld = 8;
 constexpr int kTpCapFloats = 8192;  // largest dim
 constexpr int kTpMaxGrid = 256;     // CTAs per rank (arg-max candidates)
 constexpr int kTpMaxVocab = 1 << 17;
 constexpr size_t kTpOffGen = 0;     // u32: cross-GPU barriers completed by earlier launches (same on every rank)
 constexpr size_t kTpOffBar = 128;   // u32: arrival counter, monotonic (wrap-safe compare)
-constexpr size_t kTpOffSlots = 1024; // float [2 sets][world][kTpCapFloats]
-constexpr size_t kTpOffAmaxV = kTpOffSlots + 2ull * kTpMaxWorld * kTpCapFloats * 4; // float [world][kTpMaxGrid]
+constexpr size_t kTpOffMail = 1024;  // u64 [2 sets][kTpMaxWorld][kTpCapFloats]: flagged partial rows; set 0 behind wo, 1 behind w2
+constexpr size_t kTpOffAmaxV = kTpOffMail + 2ull * kTpMaxWorld * kTpCapFloats * 8; // float [world][kTpMaxGrid]
 constexpr size_t kTpOffAmaxI = kTpOffAmaxV + (size_t)kTpMaxWorld * kTpMaxGrid * 4;   // int   [world][kTpMaxGrid]
 constexpr size_t kTpOffLogits = kTpOffAmaxI + (size_t)kTpMaxWorld * kTpMaxGrid * 4;  // float [vocab], all ranks' rows
 constexpr size_t kTpRegionBytes = kTpOffLogits + (size_t)kTpMaxVocab * 4;

@@ -703,7 +703,10 @@ int Model::launch_mega(InferenceState &s, int token, int pos, int mode, long lon
 	constexpr size_t rep = yalm::mega::kLLRep;
 	a.ll_x = s.mega_ll(), a.ll_hb = a.ll_x + rep * 2 * c.dim, a.ll_att = a.ll_hb + rep * (size_t)a.hb_len;
 	a.ll_acc = a.ll_att + rep * a.q_dim, a.ll_ml = a.ll_acc + (size_t)_mega->plan.grid * a.q_dim;
-	a.seq = s.next_mega_seq();
+	// launch number behind the hand-over flags: per state on one GPU; under tensor parallelism the peers' mailboxes belong
+	// to the process, so the counter does too (every rank issues the same launches in the same order)
+	static unsigned tp_seq = 0;
+	a.seq = c.tp_size > 1 ? ++tp_seq : s.next_mega_seq();
 	a.w2_tmp = s.mega_tmp();
 	a.ctl = s.ctl(), a.tokens_out = s.tokens_dev();
 	a.token = token, a.pos = pos, a.mode = mode;

@@ -248,7 +248,7 @@ def _std_of(name: str, shape, kind: str, lm_scale: float) -> float:
 
 
 def random_tensors(arch: Arch, dtype: str = "fp16", seed: int = 0, lm_scale: float = 4.0,
-                   device: str = "cpu"):
+                   device: str = "cpu", only=None):
     """Yield (name, ndarray, safetensors-dtype) for a seeded random-init model of `arch`.
 
     weights ~ N(0, 1/fan_in); embedding ~ N(0,1); norm weights 1 + 0.1 N(0,1); LM head scaled by
@@ -257,6 +257,8 @@ def random_tensors(arch: Arch, dtype: str = "fp16", seed: int = 0, lm_scale: flo
     device="cuda" draws the large tensors with torch on the GPU (bench-size models)."""
     st = _ST_OF_DTYPE[dtype]
     for idx, (name, shape, kind) in enumerate(tensor_plan(arch)):
+        if only is not None and not only(idx):      # several processes can share the work: tensor idx is independent of the rest
+            continue
         if kind == "norm":
             rng = np.random.default_rng([seed, idx])
             yield name, (1.0 + 0.1 * rng.standard_normal(shape, dtype=np.float32)).astype(np.float32), "F32"
@@ -290,7 +292,8 @@ def random_tensors(arch: Arch, dtype: str = "fp16", seed: int = 0, lm_scale: flo
             codes, scale = quantize_rows_e4m3(w)
             yield name, codes, "F8_E4M3"
             yield name + ".scale", scale, "F32"
-    yield "tokenizer.tokens", synthetic_tokens(arch.vocab_size), "U8"
+    if only is None or only(-1):
+        yield "tokenizer.tokens", synthetic_tokens(arch.vocab_size), "U8"
 
 
 def random_model(arch: Arch, dtype: str = "fp16", seed: int = 0, lm_scale: float = 4.0,
@@ -345,10 +348,13 @@ def kv_bytes_per_token(arch: Arch, kv_len: int) -> int:
 
 
 def random_model_streamed(arch: Arch, dtype: str = "fp16", seed: int = 0, lm_scale: float = 4.0,
-                          device: str = "cpu", pinned: bool = False, path: str | None = None) -> np.ndarray:
+                          device: str = "cpu", pinned: bool = False, path: str | None = None,
+                          part: tuple | None = None, create: bool = True) -> np.ndarray:
     """Same model as random_model() (identical bytes), built straight into one preallocated uint8 array so
     peak host memory is 1x the image (bench-size models: 14 GB Mistral-7B, 93 GB Mixtral, 141 GB Llama-3-70B).
-    `path`: build it in that file instead (np.memmap; e.g. under /dev/shm so that several ranks can map one copy)."""
+    `path`: build it in that file instead (np.memmap; e.g. under /dev/shm so that several ranks can map one copy).
+    `part` = (i, n): draw only tensors i, i + n, ... — n processes fill one file together: process 0 calls with
+    create=True first (sizes the file, writes the header), the others with create=False after it."""
     st = _ST_OF_DTYPE[dtype]
     esz = {"F32": 4, "F16": 2, "F8_E4M3": 1}[st]
     entries = []          # (name, st dtype, shape, nbytes)
@@ -371,16 +377,18 @@ def random_model_streamed(arch: Arch, dtype: str = "fp16", seed: int = 0, lm_sca
     hj += b" " * ((-(8 + len(hj))) % 64)
     total = 8 + len(hj) + off
     if path:
-        img = np.memmap(path, dtype=np.uint8, mode="w+", shape=(total,))
+        img = np.memmap(path, dtype=np.uint8, mode="w+" if create else "r+", shape=(total,))
     elif pinned:
         import torch
         img = torch.empty(total, dtype=torch.uint8, pin_memory=True).numpy()
     else:
         img = np.empty(total, np.uint8)
-    img[:8] = np.frombuffer(struct.pack("<Q", len(hj)), np.uint8)
-    img[8:8 + len(hj)] = np.frombuffer(hj, np.uint8)
+    if create:
+        img[:8] = np.frombuffer(struct.pack("<Q", len(hj)), np.uint8)
+        img[8:8 + len(hj)] = np.frombuffer(hj, np.uint8)
     base = 8 + len(hj)
-    for name, arr, _ in random_tensors(arch, dtype, seed, lm_scale, device):
+    only = None if part is None else (lambda idx: idx % part[1] == part[0] if idx >= 0 else part[0] == 0)
+    for name, arr, _ in random_tensors(arch, dtype, seed, lm_scale, device, only):
         s, e = header[name]["data_offsets"]
         img[base + s: base + e] = np.ascontiguousarray(arr).view(np.uint8).reshape(-1)
     if path:
