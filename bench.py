@@ -133,8 +133,7 @@ def write_model(path, arch, dtype, part=None, create=True):
     part = (rank, world): this process draws every world-th tensor (all ranks of a node fill one file together)."""
     import torch
     dev = "cuda" if torch.cuda.is_available() else "cpu"
-    img = yf.random_model_streamed(arch, dtype, seed=0, device=dev, path=path, part=part, create=create)
-    del img
+    yf.random_model_streamed(arch, dtype, seed=0, device=dev, path=path, part=part, create=create)
 
 
 def run_reference(args, path, context, start=(1, 0), want_logits=False):
