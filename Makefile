@@ -13,7 +13,7 @@ NVFLAGS := -std=c++17 -O3 -lineinfo $(EXTRA) $(ARCH) -ccbin $(HOSTCXX) -Xcompile
 LIB   := yalm_b200/libyalm_b200.so
 
 LIB_SRCS := $(CSRC)/ops_gemv.cu $(CSRC)/ops_attn.cu $(CSRC)/decode_mega.cu $(CSRC)/decode_mega_f32.cu $(CSRC)/decode_mega_f16.cu $(CSRC)/decode_mega_f8.cu $(CSRC)/model.cpp $(CSRC)/codec.cpp $(CSRC)/capi.cpp \
-            $(CSRC)/mem.cpp $(CSRC)/tp.cpp $(CSRC)/loader.cpp $(CSRC)/ops_sample.cu $(CSRC)/sampler.cpp $(CSRC)/tokenizer.cpp
+            $(CSRC)/mem.cpp $(CSRC)/tp.cpp $(CSRC)/loader.cpp $(CSRC)/prefill_gemm.cu $(CSRC)/prefill.cu $(CSRC)/ops_sample.cu $(CSRC)/sampler.cpp $(CSRC)/tokenizer.cpp
 LIB_OBJS := $(patsubst $(CSRC)/%,$(BUILD)/%.o,$(LIB_SRCS))
 HDRS := $(wildcard $(CSRC)/*.h $(CSRC)/*.cuh include/*.h)
 

@@ -44,6 +44,8 @@ WORKLOADS = {
     "llama-3-70b-fp16-4k": ("llama-3-70b", "fp16", 4096, "Llama-3-70B-arch fp16 random-init, 4k context, batch-1 decode"),
     "llama-3.2-1b-fp32": ("llama-3.2-1b", "fp32", 4096, "Llama-3.2-1B fp32 random-init, batch-1 decode"),
     "tiny": ("tiny-moe", "fp16", 64, "tiny MoE test model (debug only)"),
+    # batched prefill: a different metric (prompt tokens hydrated per second), its own line
+    "mistral-7b-fp16-prefill": ("mistral-7b", "fp16", 4096, "Mistral-7B-v0.2 fp16 random-init, 4096-token prompt hydrated in 512-token chunks (tcgen05 GEMMs)"),
 }
 HEADLINE = "mistral-7b-fp16-4k"
 
@@ -212,6 +214,70 @@ def run_gpu_reference(path, context, steps=32, warm=8):
     return {"value": None, "unit": "tok/s", "note": f"reference -d cuda failed (rc {r.returncode}): {(r.stderr or r.stdout)[-300:]}"}
 
 
+def run_prefill(args, arch, dtype, context, desc, base, path):
+    """--workload *-prefill: hydrate a `context`-token prompt in chunks through Model::forward_batch.  One step = one chunk.
+    value = prompt tokens per second (CUDA events around the K timed chunks = the last K chunks of the context, after W
+    untimed ones); roofline bound = tensor: 2 * weight parameters * tokens (+ attention) FLOP against the measured bf16
+    tensor throughput.  The token loop it replaces (the reference's hydrate, src/main.cpp:91-97) is timed beside it."""
+    import torch
+    from yalm_b200 import api
+    write_model(path, arch, dtype)
+    try:
+        model = api.Model(path, context).cuda(0)
+    finally:
+        os.unlink(path)
+    state = api.InferenceState(model)
+    cap, V = model.batch_capacity(), model.vocab_size
+    if not cap:
+        raise SystemExit("bench.py: this model has no batched prefill path")
+    ids = [(i * 7919 + 1) % V for i in range(context)]
+    chunks = [(p, min(cap, context - p)) for p in range(0, context, cap)]
+    K = min(args.steps, len(chunks) - 3)
+    W = len(chunks) - K
+    clocks = ClockSampler(0)
+    clocks.start()
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+    t_host = 0.0
+    for i, (p, n) in enumerate(chunks):
+        if i == W:
+            torch.cuda.synchronize()
+            ev[0].record(torch.cuda.current_stream())   # forward_batch synchronises its own stream before returning
+            t_host = time.perf_counter()
+        state.forward_batch(ids[p:p + n], p)
+    torch.cuda.synchronize()
+    t_host = time.perf_counter() - t_host
+    clk = clocks.stop()
+    toks = sum(n for _, n in chunks[W:])
+    # token-loop hydrate of the same model for comparison (64 positions at the end of the context)
+    st2 = api.InferenceState(model)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for pos in range(context - 64, context):
+        st2.forward(ids[pos], pos, api.MODE_HYDRATE)
+    torch.cuda.synchronize()
+    loop_tok_s = 64 / (time.perf_counter() - t0)
+    a = arch
+    q_dim, kv_dim = a.n_heads * a.head_dim, a.n_kv_heads * a.head_dim
+    params = a.n_layers * (2 * q_dim * a.dim + 2 * kv_dim * a.dim + 3 * a.dim * a.hidden_dim)
+    mean_kv = sum(p + n / 2 for p, n in chunks[W:]) / K
+    flop = 2.0 * params * toks + 4.0 * a.n_layers * q_dim * mean_kv * toks
+    pk = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    peak = float(json.load(open(pk))["bf16_tflops_sustained"]) if os.path.exists(pk) else 1374.5
+    line = dict(base, impl="ours", metric="prefill tok/s (prompt tokens hydrated per second)", value=toks / t_host, steps=K, warmup=W,
+                ms_per_step=1000 * t_host / K, clocks=clk, gpu_launches=K * (2 + 12 * a.n_layers),
+                e2e={"value": toks / t_host, "unit": "tok/s", "h2d_bytes_per_step": 4 * cap, "d2h_bytes_per_step": 4 * V,
+                     "note": "host-timed around Model::forward_batch calls with host token buffers; each call copies the chunk's ids in and the last logits out"},
+                roofline={"bound": "tensor", "kernel": "gemm_f16_kernel (tcgen05.mma kind::f16, TMA operands, TMEM accumulator) + attn_prefill_kernel",
+                          "achieved": flop / t_host / 1e12, "peak": peak, "unit": "TFLOP/s", "frac": flop / t_host / 1e12 / peak,
+                          "traffic": None, "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained"},
+                token_loop_hydrate_tok_s=loop_tok_s, speedup_vs_token_loop=toks / t_host / loop_tok_s,
+                cpu_baseline=None)
+    _emit(line)
+    state.close()
+    st2.close()
+    model.close()
+
+
 def _emit(line):
     """The one JSON line of the contract, on the real stdout (see main: fd 1 is pointed at stderr meanwhile)."""
     os.write(_REAL_STDOUT, (json.dumps(line) + "\n").encode())
@@ -286,6 +352,10 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; yalm_b200 has no CPU fallback (use --impl reference for the CPU arm)")
     torch.cuda.set_device(local_rank)
+    if args.workload.endswith("-prefill"):
+        if world > 1:
+            raise SystemExit("bench.py: the prefill workload is single-GPU")
+        return run_prefill(args, arch, dtype, context, desc, base, path)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
         idt = torch.zeros(128, dtype=torch.uint8, device="cuda")

@@ -133,6 +133,19 @@ int yalm_token_probs(const float *logits, int vocab, int n_rows, const int *targ
 int yalm_gemv(float *xout, const float *x, const void *w, const float *scale, int n, int d, int dtype,
               yalm_stream_t s);
 
+/* ---- (2b) batched prefill ops (net-new, SURVEY.md 8(f).1: the reference hydrates and scores token by token,
+ * src/main.cpp:91-97, 174-184) ---------------------------------------------------------------------------------------
+ * c (M, ldc) fp32 (=|+=) a (M, K) fp16 * w (N, K)^T fp16 on the tcgen05 tensor cores (TMA operand loads, TMEM
+ * accumulator); w is a .yalm weight as stored ((out, in) row-major).  accumulate != 0: c += ... (residual in place). */
+int yalm_gemm_f16(float *c, int ldc, const void *a, const void *w, int M, int N, int K, int accumulate, yalm_stream_t s);
+/* h (M, ldh) fp16 = act(a w1^T) * (a w3^T): fused w1 / w3 projection + GLU (src/infer.cpp:360-375). */
+int yalm_gemm_glu_f16(void *h, int ldh, const void *a, const void *w1, const void *w3, int M, int N, int K, int act,
+                      yalm_stream_t s);
+/* Causal attention of n query rows q16 (n, n_heads * head_dim) fp16 = positions pos0 .. pos0 + n - 1 over the head-major
+ * KV ring (rows 0 .. pos0 + n - 1 valid; no wrap: pos0 + n <= max_seq_len); out16 like q16.  src/infer.cpp:216-248 per row. */
+int yalm_attn_prefill(void *out16, const void *q16, const uint16_t *key_cache, const uint16_t *value_cache, int n, int pos0,
+                      int n_heads, int n_kv_heads, int head_dim, int max_seq_len, yalm_stream_t s);
+
 /* ---- (3a) host-pointer test entry points (src/infer.cu:890-1007 semantics) ------------------- */
 int yalm_matmul_host(float *xout, const float *x, const void *w, const float *scale, int n, int d, int dtype);
 int yalm_mha_host(float *xout, float *att, const uint16_t *kb, const uint16_t *vb, const float *q, int head_dim,
@@ -143,6 +156,9 @@ int yalm_ffn_host(float *xout, const float *x, const void *w1, const void *w2, c
  * std::rand() / RAND_MAX replaced by r), and sample_prob for n_rows rows. */
 int yalm_sample_host(const float *logits, int vocab, float temperature, float r, int *token);
 int yalm_token_probs_host(const float *logits, int vocab, int n_rows, const int *targets, float *probs);
+/* Host-pointer test entry of the prefill GEMM: c (M, N) fp32 = a (M, K) fp16 * w (N, K)^T fp16 [+ c if accumulate];
+ * with w3 != NULL instead h (M, N) fp16 = act(a w^T) * (a w3^T). */
+int yalm_gemm_host(float *c, void *h, const void *a, const void *w, const void *w3, int M, int N, int K, int accumulate, int act);
 /* Same ops timed on the device: `iters` launches after `warmup`, returns mean microseconds per
  * launch (CUDA events) in *usec.  This is what `./build/test -k <name>` prints. */
 int yalm_bench_op(const char *name, int iters, int warmup, double *usec, double *bytes);
@@ -177,6 +193,13 @@ float *yalm_logits(yalm_state *s); /* host, vocab_size fp32 */
  * each step's logits are copied back too (parity mode).  *device_ms (optional) = CUDA-event time. */
 int yalm_generate_greedy(yalm_model *m, yalm_state *s, int token, int pos, int n_gen, int *tokens_out,
                          float *logits_out, float *device_ms);
+/* Batched prefill / perplexity: positions pos0 .. pos0 + n - 1 in one pass (dense tcgen05 GEMMs over the chunk, causal
+ * flash attention, bulk KV append).  Afterwards the KV cache holds the chunk and yalm_logits() the LAST position's
+ * logits; if targets != NULL, probs_out[i] = softmax(logits_i)[targets[i]] (Sampler::sample_prob per position,
+ * src/sampler.cpp:11-25).  n <= yalm_model_batch_capacity() (0: this model / shard has no batched path — fp16 dense
+ * unsharded models have — and the caller walks the tokens with yalm_forward); pos0 + n <= max_seq_len (no ring wrap). */
+int yalm_model_batch_capacity(const yalm_model *m);
+int yalm_forward_batch(yalm_model *m, yalm_state *s, const int *tokens, int n, int pos0, const int *targets, float *probs_out);
 /* The same loop with Sampler::sample on the device: temperature 0 = greedy, > 0 = one draw per step with
  * r = uniform(seed, step).  4 bytes per token come back (the reference moves vocab * 4, src/model.cpp:338). */
 int yalm_generate(yalm_model *m, yalm_state *s, int token, int pos, int n_gen, float temperature,

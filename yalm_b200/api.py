@@ -30,7 +30,8 @@ SYMBOLS = [
     "yalm_model_device_bytes", "yalm_model_load_info", "yalm_state_new", "yalm_state_free", "yalm_forward", "yalm_logits",
     "yalm_generate_greedy", "yalm_state_read", "yalm_forward_launches", "yalm_model_uses_megakernel", "yalm_mega_profile",
     "yalm_profile_ffn", "yalm_sample_advance", "yalm_sample_device1", "yalm_token_probs", "yalm_sample_host",
-    "yalm_token_probs_host", "yalm_generate", "yalm_state_debug_set_launch_seq", "yalm_tokenize", "yalm_detokenize",
+    "yalm_token_probs_host", "yalm_gemm_f16", "yalm_gemm_glu_f16", "yalm_attn_prefill", "yalm_gemm_host",
+    "yalm_model_batch_capacity", "yalm_forward_batch", "yalm_generate", "yalm_state_debug_set_launch_seq", "yalm_tokenize", "yalm_detokenize",
     "yalm_tp_unique_id", "yalm_tp_init", "yalm_tp_finalize", "yalm_tp_shard_plan", "yalm_mega_tile_plan", "yalm_mega_attn_split", "yalm_error_string", "yalm_version",
 ]
 
@@ -83,6 +84,9 @@ def lib():
     L.yalm_state_debug_set_launch_seq.restype = None
     L.yalm_sample_host.argtypes = [vp, i, f, f, C.POINTER(i)]
     L.yalm_token_probs_host.argtypes = [vp, i, i, vp, vp]
+    L.yalm_gemm_host.argtypes = [vp, vp, vp, vp, vp, i, i, i, i, i]
+    L.yalm_model_batch_capacity.argtypes = [vp]
+    L.yalm_forward_batch.argtypes = [vp, vp, vp, i, i, vp, vp]
     L.yalm_tokenize.argtypes = [vp, sz, C.c_char_p, i, vp, i]
     L.yalm_detokenize.argtypes = [vp, sz, vp, i, C.c_char_p, i]
     L.yalm_state_read.argtypes = [vp, vp, i, i, vp, sz]
@@ -160,6 +164,20 @@ def token_probs_cuda(logits: np.ndarray, targets) -> np.ndarray:
     return out
 
 
+def gemm_cuda(a: np.ndarray, w: np.ndarray, c: np.ndarray | None = None, w3: np.ndarray | None = None, act: int = ACT_SILU):
+    """Prefill GEMM test entry: a (M, K) fp16, w (N, K) fp16 -> a w^T as fp32 (+ c), or with w3 the fused GLU as fp16."""
+    a, w = np.ascontiguousarray(a, np.float16), np.ascontiguousarray(w, np.float16)
+    M, K = a.shape
+    N = w.shape[0]
+    if w3 is not None:
+        h = np.zeros((M, N), np.float16)
+        _check(lib().yalm_gemm_host(None, _p(h), _p(a), _p(w), _p(np.ascontiguousarray(w3, np.float16)), M, N, K, 0, act), "gemm_cuda")
+        return h
+    out = np.zeros((M, N), np.float32) if c is None else np.ascontiguousarray(c, np.float32).copy()
+    _check(lib().yalm_gemm_host(_p(out), None, _p(a), _p(w), None, M, N, K, int(c is not None), act), "gemm_cuda")
+    return out
+
+
 def tokenize(image, text: bytes, add_bos: bool = True):
     img = np.frombuffer(image, dtype=np.uint8)
     out = np.zeros(max(16, 2 * len(text) + 2), np.int32)
@@ -222,6 +240,9 @@ class Model:
         lib().yalm_model_load_info(self.h, v)
         return {"device_allocations": v[0], "pinned_staging": bool(v[1])}
 
+    def batch_capacity(self) -> int:
+        return lib().yalm_model_batch_capacity(self.h)
+
     def uses_megakernel(self) -> bool:
         return bool(lib().yalm_model_uses_megakernel(self.h))
 
@@ -265,6 +286,15 @@ class InferenceState:
                "generate_greedy")
         self.device_ms = ms.value
         return (toks.tolist(), lg) if keep_logits else toks.tolist()
+
+    def forward_batch(self, tokens, pos0: int, targets=None):
+        """Positions pos0 .. pos0 + len(tokens) - 1 in one pass (Model::forward_batch); returns the per-position probabilities
+        of `targets` (or None).  logits() afterwards = the last position's."""
+        tokens = np.ascontiguousarray(tokens, np.int32)
+        tg = None if targets is None else np.ascontiguousarray(targets, np.int32)
+        probs = None if targets is None else np.zeros(len(tokens), np.float32)
+        _check(lib().yalm_forward_batch(self.model.h, self.h, _p(tokens), len(tokens), pos0, _p(tg), _p(probs)), "forward_batch")
+        return probs
 
     def generate_sampled(self, token: int, pos: int, n_gen: int, temperature: float, seed: int = 0):
         """n_gen steps with Sampler::sample on the device (temperature 0 = greedy); only token ids come back."""

@@ -357,6 +357,15 @@ extern "C" int yalm_generate_greedy(yalm_model *m, yalm_state *s, int token, int
 	return m->model->generate_greedy(*s->state, token, pos, n_gen, tokens_out, logits_out, device_ms);
 }
 
+extern "C" int yalm_model_batch_capacity(const yalm_model *m) {
+	return m ? m->model->batch_capacity() : 0;
+}
+
+extern "C" int yalm_forward_batch(yalm_model *m, yalm_state *s, const int *tokens, int n, int pos0, const int *targets, float *probs_out) {
+	if (!m || !s) return YALM_EINVAL;
+	return m->model->forward_batch(*s->state, tokens, n, pos0, targets, probs_out);
+}
+
 extern "C" int yalm_generate(yalm_model *m, yalm_state *s, int token, int pos, int n_gen, float temperature,
                              unsigned long long seed, int *tokens_out, float *logits_out, float *device_ms) {
 	if (!m || !s) return YALM_EINVAL;

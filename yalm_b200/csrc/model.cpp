@@ -713,10 +713,6 @@ int Model::launch_mega(InferenceState &s, int token, int pos, int mode, long lon
 	return yalm::mega::launch(_mega->plan, a, s.stream());
 }
 
-bool Model::supports_batch() const { return false; }
-int Model::batch_capacity() const { return 0; }
-int Model::forward_batch(InferenceState &, const int *, int, int, const int *, float *) { return YALM_EINVAL; }
-
 int Model::launches_per_forward(InferenceMode mode) const {
 	if (_mega_ok) return 1;
 	// embed + 5 kernels per block (qkv+rope+append, flash-decode, wo+res, ffn-glu, w2+res) [+ lm head]

@@ -280,6 +280,8 @@ private:
 	long long *_mega_trace = nullptr; // debug: event trace buffer for the next launch
 	struct MegaState;
 	std::shared_ptr<MegaState> _mega;
+	struct PrefillState; // chunk workspace of forward_batch (prefill.cu), created on first use
+	std::shared_ptr<PrefillState> _prefill;
 	Device _device = Device::CPU;
 	bool _tied = false;
 	std::shared_ptr<yalm::DeviceArena> _arena; // ONE device allocation: every weight shard + every KV cache of this rank
