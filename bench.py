@@ -428,13 +428,12 @@ def main():
         want = None
         if rank == 0:
             write_model(spath, sarch, dtype)
+            try:    # the CPU reference first: the other ranks wait at the barrier, not inside a kernel
+                _, _, want, want_last = run_reference(argparse.Namespace(steps=6, warmup=2), spath, context, want_logits=True)
+            except Exception as e:
+                slim_par = {"tokens_identical": None, "note": f"reference failed: {e}"}
         barrier()
         try:
-            if rank == 0:
-                try:
-                    _, _, want, want_last = run_reference(argparse.Namespace(steps=6, warmup=2), spath, context, want_logits=True)
-                except Exception as e:
-                    slim_par = {"tokens_identical": None, "note": f"reference failed: {e}"}
             sm, ss = load(spath, context)
             got, last = greedy_host_loop(ss, 1, 0, 8)
             ss.close()

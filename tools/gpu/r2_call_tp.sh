@@ -7,7 +7,7 @@ cd /root/repo
 mkdir -p gpurun_out
 nvidia-smi -L | head -8; free -g | head -2 | tail -1
 run() { python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port $1 "${@:2}"; }
-for MEGA in 1 0; do
+for MEGA in ${PARITY_PATHS-1 0}; do
   YALM_TP_MEGA=$MEGA OMP_NUM_THREADS=4 timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port $((29700+MEGA)) tests/tp_worker.py > gpurun_out/tp${N}_parity_mega${MEGA}.log 2>&1
   echo "tp$N parity mega=$MEGA rc=$?"; grep -E "PASS|FAIL|skipped|all-reduce over" gpurun_out/tp${N}_parity_mega${MEGA}.log | grep -E "rank 0|FAIL|skipped|all-reduce" | head -12
 done

@@ -32,8 +32,9 @@
 namespace yalm {
 namespace mega {
 
-// A wait longer than this many SM cycles (~4 s) is a bug: trap, never hang.
-constexpr long long kTimeoutCycles = 8000000000ll;
+// A wait longer than this many SM cycles (~60 s) is a bug: trap, never hang.  Long enough for tensor-parallel launches,
+// where every local wait is transitively a wait for the slowest rank (ranks may enter a launch seconds apart).
+constexpr long long kTimeoutCycles = 120000000000ll;
 constexpr int kCT = kConsumerWarps * 32;
 constexpr int kHeadSlots = 1; // a CTA's attention units belong to one KV head (attn_split; needs n_kv_heads <= grid)
 
