@@ -18,7 +18,7 @@ LIB_OBJS := $(patsubst $(CSRC)/%,$(BUILD)/%.o,$(LIB_SRCS))
 HDRS := $(wildcard $(CSRC)/*.h $(CSRC)/*.cuh include/*.h)
 
 all: lib
-cli: $(BUILD)/test $(BUILD)/main
+cli: $(BUILD)/test $(BUILD)/main $(BUILD)/test_kernels
 lib: $(LIB)
 
 $(BUILD)/%.cu.o: $(CSRC)/%.cu $(HDRS)
@@ -39,6 +39,14 @@ $(BUILD)/test: $(CSRC)/test.cpp $(LIB) $(HDRS)
 $(BUILD)/main: $(CSRC)/main.cpp $(LIB) $(HDRS)
 	$(NVCC) $(NVFLAGS) -x cu $(CSRC)/main.cpp -o $@ -Lyalm_b200 -lyalm_b200 \
 	    -Xlinker -rpath,'$$ORIGIN/../yalm_b200'
+
+# test infrastructure: a reference-style C++ caller compiled against csrc/yalm_api.h (tests/cpp), linked with the oracle
+$(BUILD)/test_kernels: tests/cpp/test_kernels.cpp $(LIB) $(HDRS) oracle/liboracle.so
+	$(NVCC) -std=c++17 -O1 $(ARCH) -ccbin $(HOSTCXX) -x cu tests/cpp/test_kernels.cpp -I$(CSRC) -Iinclude -o $@ \
+	    -Lyalm_b200 -lyalm_b200 -Loracle -loracle -Xlinker -rpath,'$$ORIGIN/../yalm_b200' -Xlinker -rpath,'$$ORIGIN/../oracle'
+
+oracle/liboracle.so: oracle/yalm_oracle.c oracle/yalm_oracle.h
+	$(MAKE) -s -C oracle liboracle.so
 
 clean:
 	rm -rf $(BUILD) $(LIB)

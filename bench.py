@@ -313,9 +313,12 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-gpu-reference", action="store_true")
     ap.add_argument("--no-parity", action="store_true", help="skip the parity legs (ncu captures: keeps launch indices simple)")
+    ap.add_argument("--moe-ep", action="store_true", help="MoE: expert parallelism (whole experts per rank) instead of slicing every expert")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
 
+    if args.moe_ep:
+        os.environ["YALM_MOE_EP"] = "1"
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -327,7 +330,7 @@ def main():
             "warmup": args.warmup, "higher_is_better": True, "scaling": "strong" if world > 1 else "weak",
             "vs_baseline": None, "dtype": dtype, "data": "synthetic (seeded random-init weights, synthetic token ids)",
             "config": {"workload": desc, "arch": arch.name, "weights": dtype, "context": context,
-                       "parallelism": f"tp{world}" if world > 1 else "single-gpu",
+                       "parallelism": (f"ep{world} (whole experts per rank) + tp{world} attention / LM head" if args.moe_ep else f"tp{world}") if world > 1 else "single-gpu",
                        "l2": "inputs larger than L2 (weights streamed per token >> 126 MB)"}}
     tag = f"{arch.name}_{dtype}_{os.environ.get('MASTER_PORT', '0')}_{os.getppid() if world > 1 else os.getpid()}"
     path = shm_path(f"yalm_bench_{tag}.yalm")

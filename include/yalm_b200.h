@@ -97,6 +97,18 @@ int yalm_gemv_residual(float *out, const float *residual, const float *v, const 
                        int d, int dtype, int n_active, const int *active_e, const float *active_w,
                        yalm_stream_t s);
 
+/* Expert-parallel variants (the measured alternative to slicing every expert): the rank holds only the
+ * experts e with e % ep_size == ep_rank, stacked in ascending order in w / w1 / w3 (and their scales); the router is
+ * replicated and still selects among all n_experts; rows of experts held elsewhere are skipped here and reach x through
+ * the all-reduce that follows w2.  ep_size == 1 is the plain function. */
+int yalm_gemv_residual_ep(float *out, const float *residual, const float *v, const void *w, const float *scale, int n, int d,
+                          int dtype, int n_active, const int *active_e, const float *active_w, int ep_rank, int ep_size,
+                          yalm_stream_t s);
+int yalm_ffn_glu_ep(float *hb, const float *x, const float *rms_weight, const void *w1, const void *w3, const float *s1,
+                    const float *s3, const void *gate, const float *sgate, int dim, int hidden_dim, int act, float norm_eps,
+                    int dtype, int n_experts, int n_active, int *active_e, float *active_w, float *moe_logits, int ep_rank,
+                    int ep_size, yalm_stream_t s);
+
 /* rmsnorm -> [router GEMV + top-k gate] -> hb[k,i] = act(W1[e_k] xb)[i] * (W3[e_k] xb)[i].
  * Replaces rmsnorm + fused_ffn_w1_w3_glu_act (src/infer.cu:598-620) and, for MoE, the CPU-only
  * router (src/infer.cpp:100-132, 347-349).  Dense: n_experts = 0, gate = NULL; hb is (hidden).

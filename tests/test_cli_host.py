@@ -92,9 +92,6 @@ def test_main_usage_and_flag_parsing(tmp_path):
 def test_cpp_caller_compiles_against_the_cpp_api(tmp_path, oracle):
     """tests/cpp/test_kernels.cpp mirrors src/test.cpp:148-206 + the run_completion call sequence against csrc/yalm_api.h."""
     exe = os.path.join(ROOT, "build", "test_kernels")
-    subprocess.check_call(["nvcc", "-std=c++17", "-O1", "-gencode", "arch=compute_100a,code=sm_100a", "-ccbin", "/usr/bin/g++",
-                           "-x", "cu", os.path.join(ROOT, "tests", "cpp", "test_kernels.cpp"), "-I" + os.path.join(ROOT, "yalm_b200", "csrc"),
-                           "-I" + os.path.join(ROOT, "include"), "-o", exe, "-L" + os.path.join(ROOT, "yalm_b200"), "-lyalm_b200",
-                           "-L" + os.path.join(ROOT, "oracle"), "-loracle", "-Xlinker", "-rpath," + os.path.join(ROOT, "yalm_b200"),
-                           "-Xlinker", "-rpath," + os.path.join(ROOT, "oracle")])
+    subprocess.check_call(["make", "-s", "-C", ROOT, "build/test_kernels"])      # rebuilt whenever a header or the library changed
     assert os.path.exists(exe)
+    assert os.path.getmtime(exe) >= os.path.getmtime(os.path.join(ROOT, "yalm_b200", "csrc", "yalm_api.h"))

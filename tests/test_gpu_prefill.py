@@ -69,8 +69,10 @@ def test_forward_batch_matches_token_loop(oracle, name, chunks):
         pos += c
     got_p = np.array(got_p[:-1])
     np.testing.assert_allclose(got_p, want_p, rtol=2e-2, atol=1e-6)
-    ppl = lambda p: math.exp(-np.log(p.astype(np.float64)).mean())
-    assert abs(ppl(got_p) - ppl(want_p)) / ppl(want_p) < 1e-3
+    ok = want_p > 1e-30            # a random-init model can put a target below fp32's range: no log-probability there
+    if ok.sum() >= 8:
+        ppl = lambda p: math.exp(-np.log(p[ok].astype(np.float64)).mean())
+        assert abs(ppl(got_p) - ppl(want_p)) / ppl(want_p) < 1e-3
     assert np.abs(s.logits() - want_last).max() < LOGIT_TOL
     # the KV rows the chunk appended == the rows the decode path appends (fp16; the GEMM sums in another order: <= 2 ulp)
     L, H, D, T = m.n_layers, m.n_kv_heads, m.head_dim, m.max_seq_len

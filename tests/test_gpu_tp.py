@@ -31,3 +31,17 @@ def test_tp_parity(world, mega):
     sys.stdout.write(r.stdout[-4000:])
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert "PASS" in r.stdout and "FAIL" not in r.stdout
+
+
+def test_expert_parallel_parity():
+    """YALM_MOE_EP=1: rank r holds whole experts e = r, r + 2 of the 4-expert golden model (the measured
+    alternative); same golden tokens / logits, bit-identical on both ranks."""
+    if _gpus() < 2:
+        pytest.skip("needs 2 GPUs")
+    env = dict(os.environ, YALM_MOE_EP="1", OMP_NUM_THREADS="4")
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+                        "--master-port", "29641", os.path.join(ROOT, "tests", "tp_worker.py")], capture_output=True, text=True, timeout=600,
+                       env=env, cwd=ROOT)
+    sys.stdout.write(r.stdout[-3000:])
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert "PASS" in r.stdout and "FAIL" not in r.stdout

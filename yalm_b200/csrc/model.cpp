@@ -362,7 +362,9 @@ static void *upload_strided(yalm::DeviceArena &arena, yalm::Uploader &up, size_t
 // upload pass (cuda), so the arena is exactly as large as what goes into it.
 struct Block::Piece {
 	void **slot;
+	const void *host; // captured before any slot is overwritten with its device address
 	size_t spitch, offset, width, height;
+	bool cont;        // continues the previous piece of the same slot (must land right behind it in the arena)
 };
 
 std::vector<Block::Piece> Block::pieces() {
@@ -373,10 +375,14 @@ std::vector<Block::Piece> Block::pieces() {
 	const size_t E = std::max(1, c.n_experts);
 	const yalm::TpDims td{c.dim, c.hidden_dim, c.head_dim, c.n_heads, c.n_kv_heads, c.vocab_size, (int)B};
 	std::vector<Piece> out;
-	auto whole = [&](void **slot, size_t bytes) { out.push_back({slot, bytes, 0, bytes, 1}); };
+	auto whole = [&](void **slot, size_t bytes) { out.push_back({slot, *slot, bytes, 0, bytes, 1, false}); };
 	auto slice = [&](void **slot, int tensor, size_t repeat) { // `repeat` stacked experts
 		const yalm::TpSlice sl = yalm::tp_slice(td, tensor, c.tp_rank, c.tp_size);
-		out.push_back({slot, sl.spitch, sl.offset, sl.width, sl.height * repeat});
+		out.push_back({slot, *slot, sl.spitch, sl.offset, sl.width, sl.height * repeat, false});
+	};
+	// expert parallelism: whole experts r, r + T, ... of a stacked tensor with `per` bytes per expert, one after the other
+	auto experts = [&](void **slot, size_t per) {
+		for (size_t e = r, j = 0; e < E; e += T, ++j) out.push_back({slot, *slot, per, e * per, per, 1, j > 0});
 	};
 	whole((void **)&_rms_att_weight, dim * 4);
 	whole((void **)&_rms_ffn_weight, dim * 4);
@@ -384,20 +390,26 @@ std::vector<Block::Piece> Block::pieces() {
 	slice(&_wq, yalm::kTpWq, 1);
 	slice(&_wk, yalm::kTpWk, 1);
 	slice(&_wv, yalm::kTpWv, 1);
-	slice(&_w1, yalm::kTpW1, E);
-	slice(&_w3, yalm::kTpW3, E);
+	if (c.moe_ep) experts(&_w1, (size_t)c.hidden_dim * dim * B), experts(&_w3, (size_t)c.hidden_dim * dim * B);
+	else slice(&_w1, yalm::kTpW1, E), slice(&_w3, yalm::kTpW3, E);
 	// row-parallel (columns of W): wo over q_dim, w2 over hidden
 	slice(&_wo, yalm::kTpWo, 1);
-	slice(&_w2, yalm::kTpW2, E);
+	if (c.moe_ep) experts(&_w2, (size_t)c.hidden_dim * dim * B);
+	else slice(&_w2, yalm::kTpW2, E);
 	if (c.n_experts > 0) whole(&_moegate, E * dim * B);
 	if (_sq) {
-		out.push_back({(void **)&_sq, lq * 4, r * lq * 4, lq * 4, 1});
-		out.push_back({(void **)&_sk, lkv * 4, r * lkv * 4, lkv * 4, 1});
-		out.push_back({(void **)&_sv, lkv * 4, r * lkv * 4, lkv * 4, 1});
+		out.push_back({(void **)&_sq, _sq, lq * 4, r * lq * 4, lq * 4, 1, false});
+		out.push_back({(void **)&_sk, _sk, lkv * 4, r * lkv * 4, lkv * 4, 1, false});
+		out.push_back({(void **)&_sv, _sv, lkv * 4, r * lkv * 4, lkv * 4, 1, false});
 		whole((void **)&_so, dim * 4);
-		out.push_back({(void **)&_s1, (size_t)c.hidden_dim * 4, r * lhid * 4, lhid * 4, E});
-		out.push_back({(void **)&_s3, (size_t)c.hidden_dim * 4, r * lhid * 4, lhid * 4, E});
-		whole((void **)&_s2, E * dim * 4);
+		if (c.moe_ep) {
+			experts((void **)&_s1, (size_t)c.hidden_dim * 4), experts((void **)&_s3, (size_t)c.hidden_dim * 4);
+			experts((void **)&_s2, dim * 4);
+		} else {
+			out.push_back({(void **)&_s1, _s1, (size_t)c.hidden_dim * 4, r * lhid * 4, lhid * 4, E, false});
+			out.push_back({(void **)&_s3, _s3, (size_t)c.hidden_dim * 4, r * lhid * 4, lhid * 4, E, false});
+			whole((void **)&_s2, E * dim * 4);
+		}
 		if (_sgate) whole((void **)&_sgate, E * 4);
 	}
 	return out;
@@ -415,7 +427,16 @@ void Block::cuda(yalm::DeviceArena &arena, yalm::Uploader &up) {
 	if (_device != Device::CPU) return;
 	_device = Device::CUDA;
 	const Config &c = *_config;
-	for (const Piece &p : pieces()) *p.slot = upload_strided(arena, up, _device_bytes, *p.slot, p.spitch, p.offset, p.width, p.height);
+	char *prev_end = nullptr;
+	for (const Piece &p : pieces()) {
+		char *dev = static_cast<char *>(upload_strided(arena, up, _device_bytes, p.host, p.spitch, p.offset, p.width, p.height));
+		if (!p.cont) *p.slot = dev;
+		else if (dev != prev_end) { // expert blocks are multiples of 256 bytes for every real shape
+			std::cerr << "FATAL: expert-parallel load: expert size is not a multiple of the arena alignment" << std::endl;
+			abort();
+		}
+		prev_end = dev + p.width * p.height;
+	}
 	const size_t kv_bytes = (size_t)c.max_seq_len * c.local_kv_heads() * c.head_dim * sizeof(f16_t);
 	_key_cache = static_cast<f16_t *>(arena.take(kv_bytes));
 	_value_cache = static_cast<f16_t *>(arena.take(kv_bytes));
@@ -470,9 +491,10 @@ int Block::enqueue(InferenceState &s) const {
 	}
 	const bool moe = c.n_experts > 0;
 	if (s.ffn_timing()) CUDA_CHECK(cudaEventRecordWithFlags(s.ffn_event(_layer_i, 0), s.stream(), cudaEventRecordExternal));
-	rc = yalm_ffn_glu(s.hb(), s.x(), _rms_ffn_weight, _w1, _w3, _s1, _s3, _moegate, _sgate, c.dim, lhid,
-	                  c.act == ActivationType::SILU ? YALM_ACT_SILU : YALM_ACT_GELU, c.norm_eps, dt, c.n_experts,
-	                  c.n_experts_active, s.active_experts(), s.active_experts_weights(), s.moe_weights(), st);
+	const int ep_rank = c.moe_ep ? c.tp_rank : 0, ep_size = c.moe_ep ? c.tp_size : 1;
+	rc = yalm_ffn_glu_ep(s.hb(), s.x(), _rms_ffn_weight, _w1, _w3, _s1, _s3, _moegate, _sgate, c.dim, lhid,
+	                     c.act == ActivationType::SILU ? YALM_ACT_SILU : YALM_ACT_GELU, c.norm_eps, dt, c.n_experts,
+	                     c.n_experts_active, s.active_experts(), s.active_experts_weights(), s.moe_weights(), ep_rank, ep_size, st);
 	if (rc) return rc;
 	if (s.ffn_timing()) CUDA_CHECK(cudaEventRecordWithFlags(s.ffn_event(_layer_i, 1), s.stream(), cudaEventRecordExternal));
 	const int k_act = moe ? c.n_experts_active : 1;
@@ -481,8 +503,8 @@ int Block::enqueue(InferenceState &s) const {
 	if (!tp) {
 		rc = yalm_gemv_residual(s.x(), s.x(), s.hb(), _w2, _s2, lhid, c.dim, dt, k_act, ae, aw, st);
 	} else {
-		rc = yalm_gemv_residual(s.xb(), c.tp_rank == 0 ? s.x() : nullptr, s.hb(), _w2, _s2, lhid, c.dim, dt, k_act, ae,
-		                        aw, st);
+		rc = yalm_gemv_residual_ep(s.xb(), c.tp_rank == 0 ? s.x() : nullptr, s.hb(), _w2, _s2, lhid, c.dim, dt, k_act, ae, aw, ep_rank,
+		                           ep_size, st);
 		if (rc) return rc;
 		rc = yalm::tp_allreduce_sum(s.xb(), s.x(), c.dim, s.stream());
 	}
@@ -563,6 +585,9 @@ void Model::cuda(int device, int tp_rank, int tp_size) {
 		abort();
 	}
 	c.tp_rank = tp_rank, c.tp_size = tp_size;
+	// YALM_MOE_EP=1: whole experts per rank instead of a slice of every expert (per-op kernels; the measured alternative)
+	const char *ep_env = getenv("YALM_MOE_EP");
+	c.moe_ep = ep_env && ep_env[0] == '1' && tp_size > 1 && c.n_experts > 0 && c.n_experts % tp_size == 0;
 	_device = Device::CUDA;
 	set_cuda_device(device);
 	const size_t B = dtype_size(c.weight_dtype), dim = c.dim, V = c.vocab_size, lv = V / tp_size;
@@ -612,6 +637,7 @@ void Model::plan_mega() {
 	// tensor parallel: the in-kernel all-reduce needs the peer-mapped regions (tp.cpp); without them the per-op
 	// kernels + NCCL run instead
 	const bool tp = c.tp_size > 1;
+	if (c.moe_ep) return; // expert parallelism runs on the per-op kernels
 	if (tp) {
 		const yalm::TpPeerView pv = yalm::tp_peer_view();
 		const char *e2 = getenv("YALM_TP_MEGA"); // 0: tensor parallel on the per-op kernels (A/B)

@@ -128,6 +128,7 @@ struct ResidArgs {
 	int n, d, n_active;
 	const int *active_e;
 	const float *active_w;
+	int ep_rank, ep_size; // expert parallelism: this rank holds experts e with e % ep_size == ep_rank, stacked in order (ep_size 1: all)
 };
 
 template <int DT, int R, int U>
@@ -147,8 +148,12 @@ __global__ void __launch_bounds__(kThreads) gemv_residual_kernel(ResidArgs a) {
 #pragma unroll
 		for (int r = 0; r < R; ++r) res[r] = a.residual ? a.residual[row + r] : 0.f;
 		for (int k = 0; k < a.n_active; ++k) {
-			const int e = a.active_e ? a.active_e[k] : 0;
+			int e = a.active_e ? a.active_e[k] : 0;
 			const float ew = a.active_w ? a.active_w[k] : 1.0f;
+			if (a.ep_size > 1) { // another rank's expert: its contribution arrives through the all-reduce
+				if (e % a.ep_size != a.ep_rank) continue;
+				e /= a.ep_size;
+			}
 			const char *base = a.w + ((size_t)e * a.d + row) * row_bytes;
 			const char *rows[R];
 #pragma unroll
@@ -184,6 +189,7 @@ struct FfnArgs {
 	int n_experts, n_active;
 	int *active_e;
 	float *active_w, *moe_logits;
+	int ep_rank, ep_size; // expert parallelism (see ResidArgs)
 };
 
 constexpr int kMaxExperts = 64; // moe_gate's uint64_t mask (src/infer.cpp:111)
@@ -246,7 +252,11 @@ __global__ void __launch_bounds__(kThreads) ffn_glu_kernel(FfnArgs a) {
 	const int ntasks = n_active * per_expert;
 	for (int t = gw; t < ntasks; t += warps) {
 		const int k = t / per_expert, i0 = (t % per_expert) * P;
-		const int e = a.n_experts > 0 ? sel_e[k] : 0;
+		int e = a.n_experts > 0 ? sel_e[k] : 0;
+		if (a.ep_size > 1) { // only the rank that holds expert e computes its hb rows
+			if (e % a.ep_size != a.ep_rank) continue;
+			e /= a.ep_size;
+		}
 		const size_t r0 = (size_t)e * a.hidden + i0;
 		const char *rows[2 * P];
 #pragma unroll
@@ -411,12 +421,19 @@ extern "C" int yalm_qkv_rope_append(float *q_out, uint16_t *key_cache, uint16_t 
 extern "C" int yalm_gemv_residual(float *out, const float *residual, const float *v, const void *w,
                                   const float *scale, int n, int d, int dtype, int n_active, const int *active_e,
                                   const float *active_w, yalm_stream_t s) {
+	return yalm_gemv_residual_ep(out, residual, v, w, scale, n, d, dtype, n_active, active_e, active_w, 0, 1, s);
+}
+
+extern "C" int yalm_gemv_residual_ep(float *out, const float *residual, const float *v, const void *w, const float *scale, int n,
+                                     int d, int dtype, int n_active, const int *active_e, const float *active_w, int ep_rank,
+                                     int ep_size, yalm_stream_t s) {
 	const int ep = ep_of(dtype);
-	if (!ep || !out || !v || !w || n <= 0 || d <= 0 || n_active < 1) return YALM_EINVAL;
+	if (!ep || !out || !v || !w || n <= 0 || d <= 0 || n_active < 1 || ep_size < 1 || ep_rank < 0 || ep_rank >= ep_size) return YALM_EINVAL;
 	if (n % ep || d % 2 || (n_active > 1 && (!active_e || !active_w))) return YALM_EINVAL;
 	ResidArgs a;
 	a.out = out, a.residual = residual, a.v = v, a.w = (const char *)w, a.scale = scale;
 	a.n = n, a.d = d, a.n_active = n_active, a.active_e = active_e, a.active_w = active_w;
+	a.ep_rank = ep_rank, a.ep_size = ep_size;
 	const size_t smem = (size_t)n_active * xs_bytes(dtype, n);
 	YALM_DISPATCH_DT(dtype, return launch_persistent(gemv_residual_kernel<DT, 2, 8>, a, smem, d / 2, (cudaStream_t)s));
 	return 0;
@@ -426,6 +443,15 @@ extern "C" int yalm_ffn_glu(float *hb, const float *x, const float *rms_weight, 
                             const float *s1, const float *s3, const void *gate, const float *sgate, int dim,
                             int hidden_dim, int act, float norm_eps, int dtype, int n_experts, int n_active,
                             int *active_e, float *active_w, float *moe_logits, yalm_stream_t s) {
+	return yalm_ffn_glu_ep(hb, x, rms_weight, w1, w3, s1, s3, gate, sgate, dim, hidden_dim, act, norm_eps, dtype, n_experts, n_active,
+	                       active_e, active_w, moe_logits, 0, 1, s);
+}
+
+extern "C" int yalm_ffn_glu_ep(float *hb, const float *x, const float *rms_weight, const void *w1, const void *w3, const float *s1,
+                               const float *s3, const void *gate, const float *sgate, int dim, int hidden_dim, int act, float norm_eps,
+                               int dtype, int n_experts, int n_active, int *active_e, float *active_w, float *moe_logits, int ep_rank,
+                               int ep_size, yalm_stream_t s) {
+	if (ep_size < 1 || ep_rank < 0 || ep_rank >= ep_size || (ep_size > 1 && (n_experts < 1 || n_experts % ep_size))) return YALM_EINVAL;
 	const int ep = ep_of(dtype);
 	if (!ep || !hb || !x || !w1 || !w3 || dim % ep || dim % 4 || hidden_dim <= 0) return YALM_EINVAL;
 	if (n_experts < 0 || n_experts > kMaxExperts) return YALM_EINVAL;
@@ -437,6 +463,7 @@ extern "C" int yalm_ffn_glu(float *hb, const float *x, const float *rms_weight, 
 	a.dim = dim, a.hidden = hidden_dim, a.act = act, a.eps = norm_eps;
 	a.n_experts = n_experts, a.n_active = n_experts > 0 ? n_active : 1;
 	a.active_e = active_e, a.active_w = active_w, a.moe_logits = moe_logits;
+	a.ep_rank = ep_rank, a.ep_size = ep_size;
 	const size_t smem = (36 + 3 * kMaxExperts) * sizeof(float) + xs_bytes(dtype, dim);
 	const long k = a.n_active;
 	if (hidden_dim % 2 == 0) {

@@ -46,6 +46,9 @@ struct Config {
 	DType weight_dtype = DType::F32;
 	// tensor-parallel shard this process holds (net-new; 0 of 1 = the whole model)
 	int tp_rank = 0, tp_size = 1;
+	// expert parallelism for the MoE FFN (net-new, the measured alternative of SURVEY.md 8(e)): rank r holds whole experts
+	// e with e % tp_size == r instead of a 1 / tp_size slice of every expert; attention and the LM head stay tensor-parallel
+	bool moe_ep = false;
 
 	// If nonzero `context` is supplied, max sequence length is set to `context` (src/model.cpp:31-36).
 	void from_yalm(YALMData &yalm, int context = 0);
@@ -55,7 +58,8 @@ struct Config {
 	// per-shard sizes
 	int local_heads() const { return n_heads / tp_size; }
 	int local_kv_heads() const { return n_kv_heads / tp_size; }
-	int local_hidden() const { return hidden_dim / tp_size; }
+	int local_hidden() const { return moe_ep ? hidden_dim : hidden_dim / tp_size; }
+	int local_experts() const { return moe_ep ? n_experts / tp_size : n_experts; }
 	int local_vocab() const { return vocab_size / tp_size; }
 };
 
