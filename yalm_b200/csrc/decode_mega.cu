@@ -4,6 +4,7 @@
 #include "launch.h"
 
 #include <algorithm>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 
@@ -52,6 +53,34 @@ __global__ void __launch_bounds__(kThreads, 1) stream_probe_kernel(const char *b
 		if (lane == 0) mbar_arrive(empty0 + 8 * s);
 	}
 	if (acc == 0x12345678u) *sink = acc;
+}
+
+// ---- failure record -------------------------------------------------------------------------------------------
+unsigned *fault_record() {
+	static unsigned *rec = nullptr;
+	if (!rec) {
+		if (cudaHostAlloc((void **)&rec, 8 * sizeof(unsigned), cudaHostAllocMapped | cudaHostAllocPortable) != cudaSuccess) {
+			cudaGetLastError();
+			rec = nullptr;
+		} else
+			memset(rec, 0, 8 * sizeof(unsigned));
+	}
+	return rec;
+}
+long long fault_timeout_cycles() {
+	const char *e = getenv("YALM_MEGA_TIMEOUT_S");
+	return e && atof(e) > 0 ? (long long)(atof(e) * 2.0e9) : 0;
+}
+const char *describe_fault() {
+	static char buf[256];
+	const unsigned *r = fault_record();
+	if (!r || !r[0]) return "";
+	static const char *names[] = {"?", "ring stage (mbarrier)", "producer: stage release counter", "consumer: stage release counter",
+	                              "flagged hand-over poll", "grid barrier", "cross-GPU barrier", "tensor-parallel mailbox", "MoE router record",
+	                              "hand-over sample"};
+	snprintf(buf, sizeof(buf), "decode_mega_kernel timed out in: %s (code %u) CTA %u thread %u values 0x%x %u", names[r[0] < 10 ? r[0] : 0], r[0],
+	         r[1], r[2], r[3], r[4]);
+	return buf;
 }
 
 // ---- host side --------------------------------------------------------------------------------------------

@@ -35,6 +35,26 @@ namespace mega {
 // A wait longer than this many SM cycles (~60 s) is a bug: trap, never hang.  Long enough for tensor-parallel launches,
 // where every local wait is transitively a wait for the slowest rank (ranks may enter a launch seconds apart).
 constexpr long long kTimeoutCycles = 120000000000ll;
+// Failure record: the first thread whose wait times out says WHICH wait it was before it traps — into pinned host memory,
+// which survives the dead context (mega.h: fault_record / describe_fault; the host prints it when a launch fails).
+// [0] code (kFault*), [1] CTA, [2] thread, [3] / [4] two wait-specific values.  One pointer per translation unit.
+static __device__ unsigned *g_fault_rec = nullptr;
+static __device__ long long g_timeout_cycles = kTimeoutCycles; // YALM_MEGA_TIMEOUT_S shortens it (debugging)
+enum { kFaultRing = 1, kFaultProducerRel = 2, kFaultConsumerRel = 3, kFaultPoll = 4, kFaultGridBarrier = 5, kFaultTpBarrier = 6,
+       kFaultTpMailbox = 7, kFaultRouter = 8, kFaultSample = 9 };
+static __device__ __noinline__ void die(unsigned code, unsigned x, unsigned y) {
+	unsigned *r = g_fault_rec;
+	if (r && atomicCAS(r, 0u, code) == 0u) {
+		r[1] = blockIdx.x, r[2] = threadIdx.x, r[3] = x, r[4] = y;
+		__threadfence_system();
+	}
+	__trap();
+}
+__device__ __forceinline__ bool timed_out(long long t0) { return clock64() - t0 > g_timeout_cycles; }
+inline void set_fault_pointers(unsigned *rec, long long timeout_cycles) { // host: called once per translation unit
+	cudaMemcpyToSymbol(g_fault_rec, &rec, sizeof(rec));
+	if (timeout_cycles > 0) cudaMemcpyToSymbol(g_timeout_cycles, &timeout_cycles, sizeof(timeout_cycles));
+}
 constexpr int kCT = kConsumerWarps * 32;
 constexpr int kHeadSlots = 1; // a CTA's attention units belong to one KV head (attn_split; needs n_kv_heads <= grid)
 
@@ -63,7 +83,7 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
 	if (mbar_try_wait(bar, parity)) return;
 	const long long t0 = clock64();
 	while (!mbar_try_wait(bar, parity))
-		if (clock64() - t0 > kTimeoutCycles) __trap();
+		if (timed_out(t0)) die(kFaultRing, bar, parity);
 }
 // 1-D bulk copy global -> shared, completion counted in bytes on `bar`; weights/KV are read once per
 // token, so they are tagged evict-first in L2 (activations and partials stay resident).
@@ -195,7 +215,7 @@ __device__ __forceinline__ bool ll_load4(const unsigned long long *p, unsigned f
 // Back-off between polling rounds (keeps the pollers' L2 traffic away from the weight stream); a wait of ~4 s traps.
 __device__ __forceinline__ void ll_backoff(int *round, long long *t0) {
 	if (*round == 0) *t0 = clock64();
-	else if (clock64() - *t0 > kTimeoutCycles) __trap();
+	else if (timed_out(*t0)) die(kFaultPoll, (unsigned)*round, 0);
 	__nanosleep((unsigned)YALM_MEGA_LL_NS << min(*round, 4));
 	++*round;
 }
@@ -530,7 +550,7 @@ struct Producer {
 			const long long t0 = clock64();
 			while (misc[kMiscRouter] != layer + 1) {
 				__nanosleep(32);
-				if (clock64() - t0 > kTimeoutCycles) __trap();
+				if (timed_out(t0)) die(kFaultRouter, (unsigned)layer, (unsigned)slot);
 			}
 		}
 		return misc[kMiscExpert + slot];
@@ -547,7 +567,7 @@ struct Producer {
 				const long long t0 = clock64();
 				while (ld_rel(sm_rel() + s) < r - 1) {
 					__nanosleep(64);
-					if (clock64() - t0 > kTimeoutCycles) __trap();
+					if (timed_out(t0)) die(kFaultProducerRel, s, (unsigned)r);
 				}
 			}
 			mbar_wait(sm_empty0() + 8 * s, (uint32_t)(r - 1) & 1u);
@@ -707,7 +727,7 @@ __device__ __forceinline__ void grid_barrier(Ctx &c, unsigned *sync) {
 			const long long t0 = clock64();
 			do {
 				asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(sync) : "memory");
-				if (clock64() - t0 > kTimeoutCycles) __trap();
+				if (timed_out(t0)) die(kFaultGridBarrier, v, target);
 			} while (v < target);
 		}
 		asm volatile("fence.acq_rel.gpu;" ::: "memory");
@@ -735,7 +755,7 @@ __device__ __forceinline__ void tp_barrier(Ctx &c, const Args &a) {
 			const long long t0 = clock64();
 			do {
 				asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(mine) : "memory");
-				if (clock64() - t0 > kTpTimeoutCycles) __trap();
+				if (timed_out(t0)) die(kFaultTpBarrier, v, target);
 			} while ((int)(v - target) < 0);
 		}
 		asm volatile("fence.acq_rel.sys;" ::: "memory");
@@ -753,7 +773,7 @@ __device__ __forceinline__ const unsigned char *wait_tile(Ctx &c, uint32_t idx, 
 	if (ld_rel(sm_rel() + s) < r) { // an earlier round of this stage is still in use (rare)
 		const long long t0 = clock64();
 		while (ld_rel(sm_rel() + s) < r)
-			if (clock64() - t0 > kTimeoutCycles) __trap();
+			if (timed_out(t0)) die(kFaultConsumerRel, s, (unsigned)r);
 	}
 #ifdef YALM_MEGA_TRACE
 	if (c.prof && c.tid == 0) {
@@ -888,7 +908,7 @@ __device__ __forceinline__ void stage_vec_ll(Ctx &c, const Args &a, const unsign
 			const long long t0 = clock64();
 			do {
 				__nanosleep(40);
-				if (clock64() - t0 > kTimeoutCycles) __trap();
+				if (timed_out(t0)) die(kFaultSample, 0, 0);
 				w = ll_load1(src + at);
 			} while (!ll_ok(w, flag));
 		}
@@ -1187,7 +1207,7 @@ __device__ __forceinline__ void gemv_consume(Ctx &c, const Args &a, Epi &ep, int
 					const long long t0 = clock64();
 					do {
 						__nanosleep(64);
-						if (clock64() - t0 > kTpTimeoutCycles) __trap();
+						if (timed_out(t0)) die(kFaultTpMailbox, (unsigned)(lane / R) | (unsigned)ph << 8 | (unsigned)kind << 24, (unsigned)row);
 						w = ll_load1_sys(p);
 					} while (!ll_ok(w, wflag));
 				}

@@ -4,6 +4,7 @@
 namespace yalm {
 namespace mega {
 const void *kernel_f8(int head_dim, int g, bool tp) {
+	set_fault_pointers(fault_record(), fault_timeout_cycles());
 	return kernel_for<YALM_F8E4M3>(head_dim, g, tp);
 }
 } // namespace mega

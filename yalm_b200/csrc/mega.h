@@ -131,6 +131,11 @@ Plan plan(int dtype, int dim, int q_dim, int kv_dim, int head_dim, int hidden, i
 size_t attn_ws_floats(int grid, int n_heads, int head_dim);
 // One token.  Returns a cudaError_t.
 int launch(const Plan &p, const Args &a, cudaStream_t st);
+// Failure record of the kernel's timeouts (decode_mega.cuh: die): 8 words of pinned, device-mapped host memory, all zero
+// while nothing has gone wrong.  describe_fault() formats it ("" if clean); fault_timeout_cycles(): YALM_MEGA_TIMEOUT_S.
+unsigned *fault_record();
+long long fault_timeout_cycles();
+const char *describe_fault();
 
 } // namespace mega
 } // namespace yalm

@@ -28,6 +28,7 @@ extern "C" int yalm_attn_is_fast_shape(int n_heads, int n_kv_heads, int head_dim
 		if (err__ != cudaSuccess) {                                                                           \
 			fprintf(stderr, "CUDA error in %s at %s:%d: %s (%s=%d)\n", __FUNCTION__, __FILE__, __LINE__,       \
 			        cudaGetErrorString(err__), cudaGetErrorName(err__), (int)err__);                          \
+			if (yalm::mega::describe_fault()[0]) fprintf(stderr, "yalm_b200: %s\n", yalm::mega::describe_fault()); \
 			abort();                                                                                          \
 		}                                                                                                     \
 	} while (0)
