@@ -24,7 +24,7 @@ SYMBOLS = [
     "upload_cuda", "download_cuda_raw", "register_cuda_host", "free_cuda", "unregister_cuda_host",
     "set_cuda_device", "init_cuda_stream",
     "yalm_embed", "yalm_qkv_rope_append", "yalm_attn_workspace_bytes", "yalm_attn_decode", "yalm_gemv_residual",
-    "yalm_ffn_glu", "yalm_lm_head", "yalm_argmax_advance", "yalm_gemv",
+    "yalm_ffn_glu", "yalm_lm_head", "yalm_argmax_advance", "yalm_gemv", "yalm_gemv_residual_ep", "yalm_ffn_glu_ep",
     "yalm_matmul_host", "yalm_mha_host", "yalm_ffn_host", "yalm_bench_op",
     "yalm_model_open_file", "yalm_model_open_memory", "yalm_model_cuda", "yalm_model_close", "yalm_model_config",
     "yalm_model_device_bytes", "yalm_model_load_info", "yalm_state_new", "yalm_state_free", "yalm_forward", "yalm_logits",
