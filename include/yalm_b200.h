@@ -89,6 +89,18 @@ int yalm_attn_decode(float *out, const uint16_t *key_cache, const uint16_t *valu
                      void *workspace, int n_heads, int n_kv_heads, int head_dim, int max_seq_len, const int *ctl,
                      yalm_stream_t s);
 
+/* yalm_attn_decode without a caller workspace and without any allocation (no cudaMalloc / cudaFree / allocating library
+ * call).  This entry point has no counterpart in the reference: it was added for
+ * callers that cannot allocate (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).
+ * The split-K partials live in a file-scope device array of yalm_attn_decode_static_max_bytes() = 2 MiB that every GPU
+ * loading the library holds until exit; shapes whose yalm_attn_workspace_bytes() exceeds it (or with more than 64 KV
+ * heads) are refused with YALM_EINVAL and a message on stderr.  All calls on one device share that array: calls that
+ * overlap on the GPU (different streams or host threads) race — serialise them on one stream.  Same result as
+ * yalm_attn_decode (same kernel, same split count). */
+size_t yalm_attn_decode_static_max_bytes(void);
+int yalm_attn_decode_static(float *out, const uint16_t *key_cache, const uint16_t *value_cache, const float *q, int n_heads,
+                            int n_kv_heads, int head_dim, int max_seq_len, const int *ctl, yalm_stream_t s);
+
 /* out[i] = (residual ? residual[i] : 0) + sum_k aw[k] * (W[e_k] v_k)[i]   (wo and w2 + residual:
  * fused_matmul_add_residuals, src/infer.cu:270-288; MoE mix: src/infer.cpp:377-383).
  * Dense: n_active = 1, active_e = active_w = NULL.  MoE: expert e's matrix starts at

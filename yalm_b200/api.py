@@ -25,6 +25,7 @@ SYMBOLS = [
     "set_cuda_device", "init_cuda_stream",
     "yalm_embed", "yalm_qkv_rope_append", "yalm_attn_workspace_bytes", "yalm_attn_decode", "yalm_gemv_residual",
     "yalm_ffn_glu", "yalm_lm_head", "yalm_argmax_advance", "yalm_gemv", "yalm_gemv_residual_ep", "yalm_ffn_glu_ep",
+    "yalm_attn_decode_static", "yalm_attn_decode_static_max_bytes",
     "yalm_matmul_host", "yalm_mha_host", "yalm_ffn_host", "yalm_bench_op",
     "yalm_model_open_file", "yalm_model_open_memory", "yalm_model_cuda", "yalm_model_close", "yalm_model_config",
     "yalm_model_device_bytes", "yalm_model_load_info", "yalm_state_new", "yalm_state_free", "yalm_forward", "yalm_logits",
@@ -99,6 +100,13 @@ def lib():
     L.yalm_tp_finalize.restype = None
     L.yalm_attn_workspace_bytes.argtypes = [i, i, i]
     L.yalm_attn_workspace_bytes.restype = sz
+    L.yalm_attn_decode.argtypes = [vp, vp, vp, vp, vp, i, i, i, i, vp, vp]
+    L.yalm_attn_decode_static.argtypes = [vp, vp, vp, vp, i, i, i, i, vp, vp]
+    L.yalm_attn_decode_static_max_bytes.restype = sz
+    L.upload_cuda.argtypes = [vp, sz]
+    L.upload_cuda.restype = vp
+    L.free_cuda.argtypes = [vp]
+    L.free_cuda.restype = None
     _lib = L
     return L
 

@@ -17,6 +17,8 @@
 #include "launch.h"
 
 #include <cfloat>
+#include <cstdio>
+#include <mutex>
 
 namespace yalm {
 
@@ -340,6 +342,60 @@ extern "C" int yalm_attn_decode(float *out, const uint16_t *key_cache, const uin
 	YALM_ATTN_CASE(16, 1) YALM_ATTN_CASE(16, 2) YALM_ATTN_CASE(16, 4) YALM_ATTN_CASE(16, 8)
 #undef YALM_ATTN_CASE
 	return YALM_EINVAL;
+}
+
+// ---- yalm_attn_decode with no allocation anywhere (no counterpart in the reference; added
+// for callers that cannot call cudaMalloc: CUDA graph capture, tight serving loops, harnesses that forbid it).
+// The split partials live in ONE file-scope device array per GPU that loads the library (held until exit), so:
+//   * shapes whose workspace exceeds kAttnStaticBytes are refused (YALM_EINVAL + a line on stderr);
+//   * every call on a device shares the array: calls that overlap on the GPU (two streams, or two host threads) race;
+//   * the array keeps the last call's contents; only the arrival counters must start at zero, and they are cleared on the
+//     caller's stream before each launch (a memset node under capture) — the partials are fully rewritten before being read.
+// In host code `g_attn_scratch` is only a stand-in for the symbol: the device address comes from cudaGetSymbolAddress, once
+// per device, with that device current.
+constexpr size_t kAttnStaticBytes = 2u << 20; // 2 MiB: covers every fast shape on a <= 148-SM part (see below)
+constexpr int kAttnStaticMaxDevices = 64;
+static __device__ __align__(256) unsigned char g_attn_scratch[kAttnStaticBytes];
+
+static int attn_static_scratch(void **out) {
+	static std::mutex mu;
+	static void *ptr[kAttnStaticMaxDevices] = {};
+	int dev = -1;
+	YALM_TRY(cudaGetDevice(&dev));
+	if (dev < 0 || dev >= kAttnStaticMaxDevices) return YALM_EINVAL;
+	std::lock_guard<std::mutex> lock(mu);
+	if (!ptr[dev]) {
+		void *p = nullptr;
+		YALM_TRY(cudaGetSymbolAddress(&p, g_attn_scratch)); // device `dev` is current: its copy of the array
+		ptr[dev] = p;
+	}
+	*out = ptr[dev];
+	return 0;
+}
+
+extern "C" size_t yalm_attn_decode_static_max_bytes(void) {
+	return kAttnStaticBytes;
+}
+
+extern "C" int yalm_attn_decode_static(float *out, const uint16_t *key_cache, const uint16_t *value_cache, const float *q,
+                                       int n_heads, int n_kv_heads, int head_dim, int max_seq_len, const int *ctl,
+                                       yalm_stream_t s) {
+	if (!out || !key_cache || !value_cache || !q || !ctl) return YALM_EINVAL;
+	if (n_heads <= 0 || n_kv_heads <= 0 || n_heads % n_kv_heads || max_seq_len <= 0) return YALM_EINVAL;
+	if (!attn_fast_shape(head_dim, n_heads / n_kv_heads)) return YALM_EINVAL;
+	const size_t need = yalm_attn_workspace_bytes(n_heads, n_kv_heads, head_dim);
+	// the counters share the first 256-byte slot of the workspace: 64 KV heads at most
+	if (need > kAttnStaticBytes || (size_t)n_kv_heads * sizeof(unsigned) > 256) {
+		fprintf(stderr,
+		        "yalm_attn_decode_static: n_heads %d, n_kv_heads %d, head_dim %d needs %zu bytes of split-K scratch (and at most "
+		        "64 KV heads); the static scratch holds %zu — use yalm_attn_decode with a caller-owned workspace\n",
+		        n_heads, n_kv_heads, head_dim, need, kAttnStaticBytes);
+		return YALM_EINVAL;
+	}
+	void *scratch = nullptr;
+	if (int rc = attn_static_scratch(&scratch)) return rc;
+	YALM_TRY(cudaMemsetAsync(scratch, 0, 256, (cudaStream_t)s)); // arrival counters (a failed earlier launch may have left them)
+	return yalm_attn_decode(out, key_cache, value_cache, q, scratch, n_heads, n_kv_heads, head_dim, max_seq_len, ctl, s);
 }
 
 // Not in the public header's hot-path list: generic-shape attention with a materialised `att`.
