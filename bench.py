@@ -371,6 +371,11 @@ def main():
         api._check(api.lib().yalm_tp_init(buf.ctypes.data, rank, world), "tp_init")
 
     def barrier():
+        # Drain this rank's own launches BEFORE the collective: hydrate launches are asynchronous, and an NCCL kernel that
+        # slips between two queued whole-token launches on one rank (it waits for its peers) while a peer's NCCL kernel is
+        # still queued behind a whole-token kernel (which waits for this rank's next launch) is a cross-GPU deadlock — the
+        # cooperative launch needs every SM, so it cannot start beside the spinning NCCL kernel.
+        torch.cuda.synchronize()
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
