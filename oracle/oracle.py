@@ -224,7 +224,7 @@ class OracleModel:
         tied = "model.output.weight" not in t
         m.wcls = m.embed if tied else P("model.output.weight")
         m.wcls_scale = m.embed_scale if tied else P("model.output.weight.scale")
-        sizes = dict(x=c.dim, xb=c.dim, xb2=max(c.dim, c.n_heads * c.head_dim), hb=c.hidden_dim, hb2=c.hidden_dim,
+        sizes = dict(x=c.dim, xb=c.dim, xb2=max(c.dim, c.n_heads * c.head_dim), hb=max(c.hidden_dim, c.dim), hb2=c.hidden_dim,  # hb doubles as the wo output (src/infer.cpp:335): dim floats
                      q=c.n_heads * c.head_dim, k=kv_dim, v=kv_dim, att=c.n_heads * c.max_seq_len,
                      logits=c.vocab_size, moe_weights=max(1, c.n_experts), active_w=max(1, c.n_experts_active))
         self.buf = {k: np.zeros(n, np.float32) for k, n in sizes.items()}

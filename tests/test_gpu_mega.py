@@ -14,17 +14,24 @@ from yalm_b200 import yalm_file as yf
 pytestmark = pytest.mark.gpu
 
 
-def run(img, prompt, n_gen, context=0, mega=True, device_loop=False):
-    old = os.environ.get("YALM_B200_MEGA")
-    os.environ["YALM_B200_MEGA"] = "1" if mega else "0"
+def run(img, prompt, n_gen, context=0, mega=True, device_loop=False, pipe=None):
+    """pipe: None = the planner's choice, True / False = YALM_MEGA_W2_PIPE=1 / 0 (pipelined hb slices forced on / off)."""
+    env = {"YALM_B200_MEGA": "1" if mega else "0"}
+    if pipe is not None:
+        env["YALM_MEGA_W2_PIPE"] = "1" if pipe else "0"
+    old = {k: os.environ.get(k) for k in env}
+    os.environ.update(env)
     try:
         m = api.Model(img, context).cuda()
     finally:
-        if old is None:
-            del os.environ["YALM_B200_MEGA"]
-        else:
-            os.environ["YALM_B200_MEGA"] = old
+        for k, v in old.items():
+            if v is None:
+                del os.environ[k]
+            else:
+                os.environ[k] = v
     used = m.uses_megakernel()
+    if pipe is not None and used:
+        assert m.mega_info()["w2_pipe"] == pipe, m.mega_info()
     s = api.InferenceState(m)
     if device_loop:
         for pos, tok in enumerate(prompt[:-1]):
@@ -230,3 +237,50 @@ def test_mega_many_launches_stay_deterministic():
 def test_stream_probe_runs():
     us, by = api.bench_op("stream", iters=3, warmup=0)
     assert by / us / 1e3 > 1000.0        # GB/s: anything on a B200 streams faster than 1 TB/s
+
+
+# Pipelined hb (decode_mega.cuh "pipelined hb"): w2 K-split-major with hb arriving slice by slice through bulk copies.  The
+# planner switches it on only where it buys ring stages (70B-class shapes); here it is forced on (YALM_MEGA_W2_PIPE=1).
+PIPE = {
+    # 3 slices, 1-2 row groups per CTA
+    "fp16-3slices": (yf.Arch(512, 6144, 64, 3, 8, 2, 1000, 256, 500000.0, name="pipe16"), "fp16", 24),
+    # 9 slices of 1024 floats, fewer row groups than CTAs (some CTAs own no w2 rows but walk every slice)
+    "fp32-9slices": (yf.Arch(256, 9216, 32, 2, 8, 2, 512, 64, 10000.0, name="pipe32"), "fp32", 24),
+    # fp8 rows with scales, 2 slices of 4096
+    "fp8-2slices": (yf.Arch(1024, 8192, 128, 2, 8, 2, 512, 128, 1000000.0, name="pipe8"), "fp8", 24),
+    # 70B-like width: 28 row groups per CTA = 3 per warp (the register-rotated group loop), gelu
+    "fp16-wide-3groups": (yf.Arch(8192, 4096, 128, 1, 64, 8, 512, 64, 500000.0, act_type="gelu", name="pipewide"), "fp16", 6),
+    # the headline geometry (7 slices of 2048, 13-14 row groups per CTA = 2 per warp), two layers
+    "mistral-2layers": (yf.slim(yf.ARCHS["mistral-7b"], 2), "fp16", 8),
+}
+
+
+@pytest.mark.parametrize("case", sorted(PIPE))
+def test_mega_pipelined_hb_vs_oracle_and_flagged_path(oracle, case):
+    arch, dt, n = PIPE[case]
+    img = bytes(yf.random_model(arch, dt, seed=11))
+    ref_img = bytes(yf.dequantized_fp32_image(img)) if dt == "fp8" else img
+    prompt = [1, 5, 9, 200, 77]
+    to, lo = oracle.OracleModel(ref_img).generate(prompt, n, keep_logits=True)
+    tp_, lp, used = run(img, prompt, n, pipe=True)
+    assert used
+    assert np.abs(lp - lo).max() < LOGIT_TOL
+    assert tp_ == to
+    tf, lf, _ = run(img, prompt, n, pipe=False)          # same kernel, hb as flagged words: same rows, same order of sums
+    assert tf == tp_
+    assert np.abs(lf - lp).max() < 1e-4
+    td, ld, _ = run(img, prompt, n, pipe=True, device_loop=True)
+    assert td == tp_
+    assert np.abs(ld - lp).max() < 1e-5
+
+
+def test_mega_pipelined_hb_window_wrap_and_many_launches(oracle):
+    """Pipelined hb with a sliding window (-T 32, 150 steps: the slice counters are zeroed by every launch's last CTA and
+    reused by the next) — tokens and logits against the oracle."""
+    arch = yf.Arch(512, 6144, 64, 2, 8, 2, 1000, 256, 500000.0, name="pipewin")
+    img = bytes(yf.random_model(arch, "fp16", seed=12))
+    to, lo = oracle.OracleModel(img, context=32).generate([1, 2, 3], 150, keep_logits=True)
+    tg, lg, used = run(img, [1, 2, 3], 150, context=32, pipe=True)
+    assert used
+    assert np.abs(lg - lo).max() < LOGIT_TOL
+    assert tg == to

@@ -67,8 +67,14 @@ def main():
     # the sampled words were there / when this thread's words were loaded and verified
     if p[:, 1:, 2, 5].max() > 0:
         prev = {0: 4, 2: None, 3: 2, 4: 3}
+        pipe = p[:, 1:, 4, 7].max() > 0 and (p[:, 1:, 4, 6] >= p[:, 1:, 4, 7]).all() and (p[:, 1:, 4, 7] >= p[:, 1:, 4, 2]).all()
         for ph in (0, 3, 4, 2):
             q = p[:, 1:, ph, :]
+            if ph == 4 and pipe:  # pipelined hb: no staging step; slots 7 / 6 = warp 0 reaches the last slice / has it
+                lines.append(f"hand-over into {PH[ph]:10s}: pipelined (hb slices by bulk copy); warp 0 reaches the last slice "
+                             f"{((q[..., 7] - q[..., 2]) * us).mean():5.2f} us into the phase and waits {((q[..., 6] - q[..., 7]) * us).mean():5.2f} us for it "
+                             f"(max over CTAs {((q[..., 6] - q[..., 7]) * us).max(0).mean():5.2f})")
+                continue
             smp = (q[..., 6] - q[..., 1]) * us
             lod = (q[..., 7] - q[..., 6]) * us
             rst = (q[..., 2] - q[..., 7]) * us

@@ -29,7 +29,7 @@ SYMBOLS = [
     "yalm_matmul_host", "yalm_mha_host", "yalm_ffn_host", "yalm_bench_op",
     "yalm_model_open_file", "yalm_model_open_memory", "yalm_model_cuda", "yalm_model_close", "yalm_model_config",
     "yalm_model_device_bytes", "yalm_model_load_info", "yalm_state_new", "yalm_state_free", "yalm_forward", "yalm_logits",
-    "yalm_generate_greedy", "yalm_state_read", "yalm_forward_launches", "yalm_model_uses_megakernel", "yalm_mega_profile",
+    "yalm_generate_greedy", "yalm_state_read", "yalm_forward_launches", "yalm_model_uses_megakernel", "yalm_model_mega_info", "yalm_mega_profile",
     "yalm_profile_ffn", "yalm_sample_advance", "yalm_sample_device1", "yalm_token_probs", "yalm_sample_host",
     "yalm_token_probs_host", "yalm_gemm_f16", "yalm_gemm_glu_f16", "yalm_attn_prefill", "yalm_gemm_host",
     "yalm_model_batch_capacity", "yalm_forward_batch", "yalm_generate", "yalm_state_debug_set_launch_seq", "yalm_tokenize", "yalm_detokenize",
@@ -93,6 +93,7 @@ def lib():
     L.yalm_state_read.argtypes = [vp, vp, i, i, vp, sz]
     L.yalm_forward_launches.argtypes = [vp, i]
     L.yalm_model_uses_megakernel.argtypes = [vp]
+    L.yalm_model_mega_info.argtypes = [vp, C.POINTER(i)]
     L.yalm_mega_profile.argtypes = [vp, vp, i, i, vp, sz, C.POINTER(i)]
     L.yalm_profile_ffn.argtypes = [vp, vp, i, i, i, C.POINTER(C.c_double)]
     L.yalm_tp_unique_id.argtypes = [vp]
@@ -253,6 +254,11 @@ class Model:
 
     def uses_megakernel(self) -> bool:
         return bool(lib().yalm_model_uses_megakernel(self.h))
+
+    def mega_info(self):
+        v = (C.c_int * 4)()
+        _check(lib().yalm_model_mega_info(self.h, v), "mega_info")
+        return {"stages": v[0], "vec_floats": v[1], "w2_pipe": bool(v[2]), "w2_k_splits": v[3]}
 
     def launches(self, mode=MODE_LOGITS) -> int:
         return lib().yalm_forward_launches(self.h, mode)

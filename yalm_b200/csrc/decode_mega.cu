@@ -77,8 +77,8 @@ const char *describe_fault() {
 	if (!r || !r[0]) return "";
 	static const char *names[] = {"?", "ring stage (mbarrier)", "producer: stage release counter", "consumer: stage release counter",
 	                              "flagged hand-over poll", "grid barrier", "cross-GPU barrier", "tensor-parallel mailbox", "MoE router record",
-	                              "hand-over sample"};
-	snprintf(buf, sizeof(buf), "decode_mega_kernel timed out in: %s (code %u) CTA %u thread %u values 0x%x %u", names[r[0] < 10 ? r[0] : 0], r[0],
+	                              "hand-over sample", "hb slice counter"};
+	snprintf(buf, sizeof(buf), "decode_mega_kernel timed out in: %s (code %u) CTA %u thread %u values 0x%x %u", names[r[0] < 11 ? r[0] : 0], r[0],
 	         r[1], r[2], r[3], r[4]);
 	return buf;
 }
@@ -153,19 +153,36 @@ Plan plan(int dtype, int dim, int q_dim, int kv_dim, int head_dim, int hidden, i
 	if (!coop || di.sms < 1) return p;
 	p.grid = di.sms;
 	if (tp && p.grid > kTpMaxGrid) return p;
-	int vf = std::max(padded(dim, ep), std::max(padded(q_dim, ep), padded(hidden, ep)));
 	if (n_kv_heads > p.grid) return p; // a CTA's attention units must span at most kHeadSlots KV heads
 	// the attention unit split runs in 32-bit arithmetic: (units) x (grid + 1) must stay below 2^31
 	const long long units = (long long)n_kv_heads * (max_seq_len / (kStageBytes / (4 * head_dim)) + 1);
 	if (head_dim <= 0 || units * (p.grid + 1) >= (1ll << 31)) return p;
 	// attention: warp records, combine weights, per-warp probability scratch (C rows x G + G)
-	vf = std::max(vf, kHeadSlots * kConsumerWarps * G * (head_dim + 2) + p.grid * G + G +
-	                      kConsumerWarps * (kStageBytes / (4 * head_dim) * G + G) + G * head_dim + 32);
-	p.vec_floats = (vf + 31) / 32 * 32;
+	const int vf_attn = kHeadSlots * kConsumerWarps * G * (head_dim + 2) + p.grid * G + G +
+	                    kConsumerWarps * (kStageBytes / (4 * head_dim) * G + G) + G * head_dim + 32;
 	// header (rope table, scratch, release counters, mbarriers) | ring | vec
+	auto stages_for = [&](int vf) {
+		const long room = (long)di.max_smem_optin - ((long)((std::max(vf, vf_attn) + 31) / 32 * 32) * 4 + kSmemHeader);
+		return (int)std::min<long>(kMaxStages, room / kStageBytes);
+	};
+	int vf = std::max(padded(dim, ep), std::max(padded(q_dim, ep), padded(hidden, ep)));
+	// Pipelined w1/w3 -> w2 hand-over (decode_mega.cuh "pipelined hb"; dense models whose w2 is K-split): hb never sits in
+	// shared memory as a whole — kHbBufs slice buffers behind the other phases' input vector replace it, and the ring gets the
+	// difference (70B-class: 112 KB -> 64 KB, six more stages; measured +6.5 % tok/s on a 16-layer slice).  It is switched
+	// on where it buys at least two ring stages (Mistral-7B: one stage, measured at parity: off); YALM_MEGA_W2_PIPE=1 / 0
+	// force it on (where the shape allows) / off.
+	{
+		const char *e = getenv("YALM_MEGA_W2_PIPE");
+		const int nk = p.shape[kW2][2], groups = (p.shape[kW2][3] + di.sms - 1) / std::max(1, di.sms);
+		const int hb_off = std::max(padded(dim, ep), padded(q_dim, ep)), vf_pipe = hb_off + kHbBufs * p.shape[kW2][1];
+		const bool can = n_experts == 0 && nk >= 2 && nk <= kHbMaxSlices && p.shape[kW2][0] <= 2 &&
+		                 (groups + kConsumerWarps - 1) / kConsumerWarps <= kHbMaxGroups && stages_for(vf_pipe) >= 2;
+		const bool want = e ? atoi(e) != 0 : !tp && stages_for(vf_pipe) >= stages_for(vf) + 2; // tensor parallel: only on request
+		if (can && want) p.w2_pipe = 1, p.hb_slice = p.shape[kW2][1], p.hb_off = hb_off, vf = vf_pipe;
+	}
+	p.vec_floats = (std::max(vf, vf_attn) + 31) / 32 * 32;
 	const size_t fixed = (size_t)p.vec_floats * 4 + kSmemHeader;
-	const long room = (long)di.max_smem_optin - (long)fixed;
-	p.stages = (int)std::min<long>(kMaxStages, room / kStageBytes);
+	p.stages = stages_for(vf);
 	if (p.stages < 2) return p;
 	p.smem = (size_t)p.stages * kStageBytes + fixed;
 	p.dtype = dtype;
@@ -186,6 +203,8 @@ int launch(const Plan &p, const Args &a, cudaStream_t st) {
 	if (!p.ok) return YALM_EINVAL;
 	Args args = a;
 	args.stages = p.stages, args.vec_floats = p.vec_floats;
+	args.w2_pipe = p.w2_pipe, args.hb_slice = p.hb_slice, args.hb_off = p.hb_off;
+	if (p.w2_pipe && (!a.hbp || !a.hb_cnt)) return YALM_EINVAL;
 	memcpy(args.shape, p.shape, sizeof(args.shape));
 	// Timing-experiment knobs.  Read once; with YALM_MEGA_TUNE=1 (tools/mega_sweep.py) they are re-read at every launch.
 	struct Knobs {

@@ -41,7 +41,7 @@ constexpr long long kTimeoutCycles = 120000000000ll;
 static __device__ unsigned *g_fault_rec = nullptr;
 static __device__ long long g_timeout_cycles = kTimeoutCycles; // YALM_MEGA_TIMEOUT_S shortens it (debugging)
 enum { kFaultRing = 1, kFaultProducerRel = 2, kFaultConsumerRel = 3, kFaultPoll = 4, kFaultGridBarrier = 5, kFaultTpBarrier = 6,
-       kFaultTpMailbox = 7, kFaultRouter = 8, kFaultSample = 9 };
+       kFaultTpMailbox = 7, kFaultRouter = 8, kFaultSample = 9, kFaultHb = 10 };
 static __device__ __noinline__ void die(unsigned code, unsigned x, unsigned y) {
 	unsigned *r = g_fault_rec;
 	if (r && atomicCAS(r, 0u, code) == 0u) {
@@ -93,6 +93,12 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void *src, uint32_t
 	    "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;" ::"r"(dst),
 	    "l"(src), "r"(bytes), "r"(bar), "l"(policy)
 	    : "memory");
+}
+// The same without a cache hint (activations: every CTA reads them, they must stay in L2).
+__device__ __forceinline__ void bulk_g2s_plain(uint32_t dst, const void *src, uint32_t bytes, uint32_t bar) {
+	asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst), "l"(src), "r"(bytes),
+	             "r"(bar)
+	             : "memory");
 }
 // Fire-and-forget L2 prefetch of a global range (no completion tracking, never blocks the issuing thread).
 __device__ __forceinline__ void bulk_prefetch_l2(const void *src, uint32_t bytes, bool tma = false) {
@@ -334,7 +340,11 @@ constexpr int kProfSlots = 8, kProfPhases = 6; // phases: qkv, attn, wo, ffn, w2
 // compile-time constants instead of live registers:
 //   rope table (64 float2) | red (16) | misc (32) | release counters (32) | full mbarriers | empty mbarriers | ring | vec
 constexpr int kOffRope = 0, kOffRed = 512, kOffMisc = 576, kOffRel = 704, kOffFull = 832, kOffEmpty = kOffFull + 8 * kMaxStages;
-constexpr int kOffStages = (kOffEmpty + 8 * kMaxStages + 127) / 128 * 128;
+// pipelined hb (below): full / empty mbarriers of the slice buffers | int [2][kHbMaxSlices]: hb elements this CTA still owes
+// each slice, its share | int [kHbMaxSlices]: slice fetched (owned by the slice's duty warp)
+constexpr int kOffHbFull = kOffEmpty + 8 * kMaxStages, kOffHbEmpty = kOffHbFull + 8 * kHbBufs;
+constexpr int kOffHbCnt = (kOffHbEmpty + 8 * kHbBufs + 63) / 64 * 64, kOffHbIssued = kOffHbCnt + 8 * kHbMaxSlices;
+constexpr int kOffStages = (kOffHbIssued + 4 * kHbMaxSlices + 127) / 128 * 128;
 static_assert(kOffStages == kSmemHeader, "mega.h: kSmemHeader must match the kernel's shared-memory header");
 __device__ __forceinline__ unsigned char *sm_base() {
 	extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -352,6 +362,10 @@ static_assert(kMiscExpertW + kMegaMaxActive <= 32 && kMiscPark + 5 <= kMiscRoute
 __device__ __forceinline__ int *sm_rel() { return reinterpret_cast<int *>(sm_base() + kOffRel); } // per-stage release counters
 __device__ __forceinline__ uint32_t sm_full0() { return smem_u32(sm_base() + kOffFull); }
 __device__ __forceinline__ uint32_t sm_empty0() { return smem_u32(sm_base() + kOffEmpty); }
+__device__ __forceinline__ uint32_t sm_hbfull0() { return smem_u32(sm_base() + kOffHbFull); }
+__device__ __forceinline__ uint32_t sm_hbempty0() { return smem_u32(sm_base() + kOffHbEmpty); }
+__device__ __forceinline__ int *sm_hb_cnt() { return reinterpret_cast<int *>(sm_base() + kOffHbCnt); }
+__device__ __forceinline__ volatile int *sm_hb_issued() { return reinterpret_cast<volatile int *>(sm_base() + kOffHbIssued); }
 __device__ __forceinline__ unsigned char *sm_stages() { return sm_base() + kOffStages; }
 __device__ __forceinline__ uint32_t sm_stages_u32() { return smem_u32(sm_base() + kOffStages); }
 
@@ -483,6 +497,7 @@ struct PhaseDesc {
 	// known only once the router of `layer` has run (Producer::expert waits for it).  gpe: row groups per expert (w1/w3).
 	int layer, sub, gpe;
 	size_t estride;
+	bool slice_major; // pipelined hb: w2 tiles in K-split-major order over ALL of the CTA's row groups
 };
 
 struct Producer {
@@ -499,7 +514,7 @@ struct Producer {
 		d.m0 = d.m1 = d.m2 = nullptr, d.rows0 = d.rows1 = d.K = 0, d.g_first = d.full_groups = d.full_tiles = d.nb_last = 0;
 		d.kc = d.vc = nullptr, d.nch = 1, d.u0 = 0;
 		d.sh.R = d.sh.KT = d.sh.nk = d.sh.G = 1;
-		d.layer = 0, d.sub = 0, d.gpe = 0, d.estride = 0;
+		d.layer = 0, d.sub = 0, d.gpe = 0, d.estride = 0, d.slice_major = false;
 		const int n_phases = a.n_layers * ppl_of(a) + (a.mode != kHydrate ? 1 : 0);
 		if (ph >= n_phases) return d;
 		int l, k, sub;
@@ -521,7 +536,7 @@ struct Producer {
 		switch (k) {
 		case 2: d.kind = kWO, d.m0 = L.wo, d.rows0 = a.dim, d.K = a.q_dim; break;
 		case 3: d.kind = kFFN, d.m0 = L.w1, d.m1 = L.w3, d.rows0 = a.hidden; break;
-		case 4: d.kind = kW2, d.m0 = L.w2, d.rows0 = a.dim, d.K = a.hidden; break;
+		case 4: d.kind = kW2, d.m0 = L.w2, d.rows0 = a.dim, d.K = a.hidden, d.slice_major = a.w2_pipe != 0; break;
 		case 5: d.kind = kLM, d.m0 = a.wcls, d.rows0 = a.vocab; break;
 		default: break;
 		}
@@ -612,7 +627,9 @@ struct Producer {
 			return i;
 		}
 		int gl, kc;
-		if (i < d.full_tiles) {
+		if (d.slice_major) {
+			kc = i / d.nunits, gl = i - kc * d.nunits;
+		} else if (i < d.full_tiles) {
 			const int r = i % (kConsumerWarps * d.sh.nk);
 			gl = i / (kConsumerWarps * d.sh.nk) * kConsumerWarps + r % kConsumerWarps, kc = r / kConsumerWarps;
 		} else {
@@ -980,6 +997,86 @@ __device__ __forceinline__ void stage_vec_ll(Ctx &c, const Args &a, const unsign
 	cbar();
 }
 
+// ---- pipelined hb (w1/w3 -> w2, dense models; Args::w2_pipe) ---------------------------------------------------------
+// hb is the largest vector that changes hands (hidden floats) and the phase that produces it is the longest of the layer:
+// most of its rows are finished long before the phase is.  w2's K splits make natural slices — a w2 tile of K split kc needs
+// hb[kc*KT, (kc+1)*KT) only.  So instead of staging all of hb behind the slowest CTA of w1/w3:
+//   * the w1/w3 epilogue stores hb as plain fp32 in the permuted layout the w2 tile loop reads (hbp[xs_slot(row)]) and counts
+//     the element down in a shared-memory counter of its slice (acq_rel at CTA scope); the thread that stores the CTA's LAST
+//     element of a slice publishes the CTA's whole share with ONE GPU-scope fence + red on the slice's global completion
+//     counter (a fence per element, even deferred to the thread's next epilogue, cost ~1.5 us each with the memory system
+//     saturated: measured, the w1/w3 phase went from 31 to 45 us per layer);
+//   * w2 walks its tiles K-split-major over ALL of the CTA's row groups (Producer::tile, slice_major), every warp carrying
+//     the partial sums of its (at most kHbMaxGroups) groups across the slices, so a slice is used once and kHbBufs buffers of
+//     one slice each replace the whole-hb buffer — shared memory that goes to the ring instead;
+//   * slice s is pulled into buffer s % kHbBufs with one bulk copy by lane 0 of its duty warp (s % kConsumerWarps) as soon as
+//     its counter is full and the buffer's previous slice has been released by all warps (acquire load, proxy fence,
+//     cp.async.bulk completing on the buffer's mbarrier): the first kHbBufs slices while the CTA is still in the w1/w3 tile
+//     loop, the others one slice ahead of their use;
+//   * every warp waits for slice kc on the buffer's full mbarrier in front of its tiles of K split kc and arrives on the empty
+//     mbarrier behind them (all warps, with or without tiles: every layer walks every slice, so use counts stay uniform).
+// The w1/w3 -> w2 boundary has no staging step, no polling by 352 threads and no CTA barrier; only the LAST slice waits for
+// the slowest CTA of w1/w3, and by then w2 has been streaming for microseconds.
+__device__ __forceinline__ uint32_t hb_buf_u32(const Ctx &c, const Args &a, int b) {
+	return sm_stages_u32() + (uint32_t)c.S * kStageBytes + (uint32_t)(a.hb_off + b * a.hb_slice) * 4;
+}
+// w1/w3 epilogue, after the thread's stores of one hb element of `slice`.
+__device__ __forceinline__ void hb_count(const Args &a, int layer, int slice) {
+	int *cnt = sm_hb_cnt() + slice;
+	int old;
+	if (a.debug & 32) asm volatile("atom.relaxed.cta.shared::cta.add.s32 %0, [%1], -1;" : "=r"(old) : "r"(smem_u32(cnt)) : "memory"); // timing experiment only
+	else asm volatile("atom.acq_rel.cta.shared::cta.add.s32 %0, [%1], -1;" : "=r"(old) : "r"(smem_u32(cnt)) : "memory");
+	if (old == 1) { // the CTA's share of the slice is complete, and every store to it happens-before this point
+		asm volatile("fence.acq_rel.gpu;" ::: "memory");
+		asm volatile("red.relaxed.gpu.global.add.u32 [%0], %1;" ::"l"(a.hb_cnt + (size_t)layer * kHbMaxSlices + slice), "r"(cnt[kHbMaxSlices]) : "memory");
+	}
+}
+// Start of the w1/w3 phase (in front of its staging step's CTA barriers): thread s < slices sets up slice s — how many hb
+// elements this CTA's row groups g_first, g_first + ncta, ... (NL of them, RH rows each) contribute to it.
+__device__ __forceinline__ void hb_setup(const Args &a, const Ctx &c) {
+	const int s = c.tid;
+	if (s >= a.shape[kW2][2]) return;
+	const int RH = max(1, a.shape[kFFN][0] / 2);
+	int g_first, NL;
+	my_groups(c, a.shape[kFFN][3], &g_first, &NL);
+	const int gps = a.hb_slice / RH; // row groups per slice
+	auto below = [&](int x) { return x <= g_first ? 0 : min(NL, (x - g_first + c.ncta - 1) / c.ncta); }; // this CTA's groups below group x
+	const int n = (below((s + 1) * gps) - below(s * gps)) * RH;
+	sm_hb_cnt()[s] = n, sm_hb_cnt()[kHbMaxSlices + s] = n;
+	sm_hb_issued()[s] = 0;
+}
+// Lane 0 of slice s's duty warp: pull the slice into its buffer once it is complete and the buffer is free (`blocking`: wait
+// for both).  `own`: called from the w1/w3 tile loop — do not even ask before this CTA's own share is in.
+__device__ __forceinline__ void hb_fetch(const Ctx &c, const Args &a, int layer, int s, bool blocking, bool own) {
+	if (own && *reinterpret_cast<volatile int *>(sm_hb_cnt() + s) != 0) return;
+	const int idx = layer * a.shape[kW2][2] + s, b = idx % kHbBufs, r = idx / kHbBufs; // r-th use of buffer b in this launch
+	if (r > 0) { // all warps have released the slice that used the buffer before
+		const uint32_t eb = sm_hbempty0() + 8 * b, par = (uint32_t)(r - 1) & 1u;
+		if (!mbar_try_wait(eb, par)) {
+			if (!blocking) return;
+			mbar_wait(eb, par);
+		}
+	}
+	const unsigned *cn = a.hb_cnt + (size_t)layer * kHbMaxSlices + s;
+	unsigned v = ld_acquire(cn);
+	if (v != (unsigned)a.hb_slice) {
+		if (!blocking) return;
+		const long long t0 = clock64();
+		do {
+			__nanosleep(64);
+			if (timed_out(t0)) die(kFaultHb, (unsigned)layer << 8 | (unsigned)s, v);
+			v = ld_acquire(cn);
+		} while (v != (unsigned)a.hb_slice);
+	}
+	// the bulk copy (async proxy) is ordered behind the acquire, and its shared-memory writes behind the warps' generic reads of
+	// the buffer's previous slice (observed through the empty mbarrier)
+	asm volatile("fence.proxy.async;" ::: "memory");
+	const uint32_t bar = sm_hbfull0() + 8 * b, bytes = (uint32_t)a.hb_slice * 4;
+	mbar_expect_tx(bar, bytes);
+	bulk_g2s_plain(hb_buf_u32(c, a, b), a.hbp + (size_t)s * a.hb_slice, bytes, bar);
+	sm_hb_issued()[s] = 1;
+}
+
 // Per-phase epilogue state.
 struct Epi {
 	int kind;
@@ -989,9 +1086,241 @@ struct Epi {
 	int sub, n_sub;                        // w2 sub-phase (MoE: one per selected expert; dense: 0 of 1)
 	float ew;                              // MoE: gate weight of this sub-phase's expert (1 for dense models)
 	int gpe;                               // MoE w1/w3: row groups per expert (0: dense)
+	int layer;
 	float best_v;                          // LM head: running arg-max of this lane's rows
 	int best_i;
 };
+
+// acc2[r] += dot(row r of the tile at shared address `wa0` (R rows of KT columns), the input slice at `xa0`); both addresses
+// already include the lane's 16-byte offset.
+template <int DT, int R>
+__device__ __forceinline__ void tile_fma(uint32_t wa, uint32_t xa, int KT, int lane, float2 (&acc2)[R]) {
+	using T = WTraits<DT>;
+	constexpr int EP = T::EP, CH = 32 * EP, Q = EP / 4;
+	const int chunks = (KT + CH - 1) / CH, nfull = KT / CH;
+	const int row_stride = KT * T::BYTES;
+	int cc = 0;
+	for (; cc + 2 <= nfull; cc += 2, wa += 1024, xa += 2 * CH * 4) { // all loads of two chunks, then the math
+		uint4 w[2][R];
+		float4 xv[2][Q];
+#pragma unroll
+		for (int u = 0; u < 2; ++u)
+#pragma unroll
+			for (int r = 0; r < R; ++r) w[u][r] = lds128(wa + r * row_stride + u * 512);
+#pragma unroll
+		for (int u = 0; u < 2; ++u)
+#pragma unroll
+			for (int q = 0; q < Q; ++q) xv[u][q] = lds128f(xa + (u * CH + q * 128) * 4);
+#pragma unroll
+		for (int u = 0; u < 2; ++u)
+#pragma unroll
+			for (int r = 0; r < R; ++r) acc2[r] = fma16x2<DT>(w[u][r], xv[u], acc2[r]);
+	}
+	for (; cc < chunks; ++cc, wa += 512, xa += CH * 4) { // odd full chunk and / or the ragged last one
+		if (cc * CH + lane * EP < KT) {
+			uint4 w[R];
+			float4 xv[Q];
+#pragma unroll
+			for (int r = 0; r < R; ++r) w[r] = lds128(wa + r * row_stride);
+#pragma unroll
+			for (int q = 0; q < Q; ++q) xv[q] = lds128f(xa + q * 128 * 4);
+#pragma unroll
+			for (int r = 0; r < R; ++r) acc2[r] = fma16x2<DT>(w[r], xv, acc2[r]);
+		}
+	}
+}
+
+// Residual operand of the wo / w2 epilogue of row group g (lane = replica * R + row; tensor parallel: tp_collect adds it).
+template <int R, bool TP>
+__device__ __forceinline__ float load_resid(const Ctx &c, const Args &a, const Epi &ep, int g) {
+	constexpr int NREP = YALM_MEGA_LL ? kLLRep : 1;
+	const int kind = ep.kind, lane = c.lane;
+	float resid = 0.f;
+	if (!TP && (kind == kWO || kind == kW2) && lane < R * NREP) {
+		// flagged hand-over: x after wo lives in ll_x[0] (complete: this CTA polled all of it when it staged w1/w3);
+		// x before wo is the plain copy written behind w2 of the layer before, on the far side of a grid barrier
+		if (kind == kW2 && ep.sub > 0) resid = __ldcg(a.w2_tmp + (long)g * R + lane % R); // x + the earlier experts' contributions
+		else if (YALM_MEGA_LL && kind == kW2) resid = ll_val(ll_load1(a.ll_x + (size_t)(c.cta % kLLRep) * a.dim + (long)g * R + lane % R)); // the replica this CTA polled and verified
+		else resid = __ldcg(a.x + (long)g * R + lane % R);
+	}
+	return resid;
+}
+
+// Epilogue of row group g: acc[r] = finished dot products of its R rows (valid in every lane); lane t handles output item t.
+template <int DT, int R, bool TP>
+__device__ __forceinline__ void gemv_epilogue(Ctx &c, const Args &a, Epi &ep, int g, const float (&acc)[R], float resid, unsigned wflag) {
+	constexpr bool LL = YALM_MEGA_LL;  // x: flagged words (tensor parallel: the finished rows, after the exchange at the end of the phase)
+	constexpr bool LLH = YALM_MEGA_LL; // hb (and att_out): flagged too
+	constexpr int NREP = LL ? kLLRep : 1;    // flagged vectors are written kLLRep times (lane -> replica): see kLLRep
+	constexpr int NREPH = LLH ? kLLRep : 1;
+	using T = WTraits<DT>;
+	constexpr int EP = T::EP;
+	const int kind = ep.kind, lane = c.lane;
+	const int t = lane;
+	if (kind == kQKV) {
+		if (t < R / 2) {
+			float v0 = acc[0], v1 = acc[R > 1 ? 1 : 0];
+#pragma unroll
+			for (int r = 2; r + 1 < R; r += 2)
+				if (t == r / 2) v0 = acc[r], v1 = acc[r + 1];
+			long row = (long)g * R + 2 * t;
+			int which = 0;
+			const float *sc = ep.scale0;
+			if (row >= ep.rows0 + ep.rows1) which = 2, row -= ep.rows0 + ep.rows1, sc = ep.scale2;
+			else if (row >= ep.rows0) which = 1, row -= ep.rows0, sc = ep.scale1;
+			if (DT == YALM_F8E4M3 && sc) v0 *= sc[row], v1 *= sc[row + 1];
+			v0 = clipf(v0, a.clip), v1 = clipf(v1, a.clip);
+			const int hd = a.head_dim, j = (int)(row % hd);
+			if (which < 2) { // interleaved-pair RoPE (src/infer.cpp:200-213), cos/sin from the per-token table
+				const float2 cs = sm_rope()[j >> 1];
+				const float r0 = v0 * cs.x - v1 * cs.y, r1 = v0 * cs.y + v1 * cs.x;
+				v0 = r0, v1 = r1;
+			}
+			if (which == 0) {
+				*reinterpret_cast<float2 *>(a.q + row) = make_float2(v0, v1);
+			} else {
+				__half *cache = reinterpret_cast<__half *>(which == 1 ? ep.L->kc : ep.L->vc);
+				__half *dst = cache + ((size_t)(row / hd) * a.max_seq_len + c.kv_pos) * hd + j;
+				*reinterpret_cast<__half2 *>(dst) = __floats2half2_rn(v0, v1);
+			}
+		}
+	} else if (kind == kFFN) {
+		constexpr int RH = R > 1 ? R / 2 : 1;
+		if (t < RH * NREPH) { // every lane holds all sums: lane = replica * RH + row
+			const int tr = t % RH;
+			float gt = acc[0], up = acc[RH < R ? RH : 0];
+#pragma unroll
+			for (int r = 1; r < RH; ++r)
+				if (tr == r) gt = acc[r], up = acc[RH + r < R ? RH + r : 0];
+			const long row = (long)g * RH + tr; // MoE: row of hb = slot * hidden + i
+			if (DT == YALM_F8E4M3 && ep.scale0) {
+				long srow = row;
+				if (ep.gpe) { // scales are stacked per expert like the weights
+					const int slot = g / ep.gpe;
+					srow = (long)sm_misc()[kMiscExpert + slot] * a.hidden + (row - (long)slot * a.hidden);
+				}
+				gt *= ep.scale0[srow], up *= ep.scale1[srow];
+			}
+			gt = a.act == YALM_ACT_GELU ? act_gelu(gt) : act_silu(gt);
+			if (a.w2_pipe) { // pipelined hb: plain fp32 in the w2 tile loop's layout + the slice's completion count
+				if (t < RH) {
+					a.hb[row] = gt * up;
+					a.hbp[xs_slot<EP>((int)row)] = gt * up;
+					hb_count(a, ep.layer, (int)row / a.hb_slice);
+				}
+			} else {
+				if (t < RH) a.hb[row] = gt * up;
+				if (LLH) ll_store(a.ll_hb + (size_t)(t / RH) * a.hb_len + row, gt * up, wflag);
+			}
+		}
+	} else if (TP) {
+		// tensor parallel: the rows are partial sums (wo / w2: this rank's slice of the input dimension) or this
+		// rank's slice of the vocabulary.  Every lane holds all R sums, so lane r hands the group's R values to
+		// rank r over NVLink: flagged words into mailbox [set][this rank] (collected by the warp that owns the same
+		// rows there: tp_collect below), or plain stores into the gathered logits.
+		const long row0 = (long)g * R;
+		float vv[R];
+#pragma unroll
+		for (int r = 0; r < R; ++r) {
+			vv[r] = acc[r];
+			if (DT == YALM_F8E4M3 && ep.scale0) vv[r] *= ep.scale0[row0 + r];
+		}
+		if (kind == kLM && t < R) {
+			float v = vv[0];
+#pragma unroll
+			for (int r = 1; r < R; ++r)
+				if (t == r) v = vv[r];
+			const int row = a.vocab_base + (int)row0 + t;
+			if (v > ep.best_v) ep.best_v = v, ep.best_i = row;
+		}
+		if (kind == kW2 && ep.n_sub > 1) { // MoE: gate weight, then on top of the earlier experts' sums (same lanes, earlier sub-phase)
+#pragma unroll
+			for (int r = 0; r < R; ++r) vv[r] = ep.sub > 0 ? fmaf(ep.ew, vv[r], __ldcg(a.w2_tmp + row0 + r)) : ep.ew * vv[r];
+		}
+		if (kind == kW2 && ep.sub + 1 < ep.n_sub) { // not the last expert: park the sums, nothing crosses the GPUs yet
+			float v = vv[0];
+#pragma unroll
+			for (int r = 1; r < R; ++r)
+				if (t == r) v = vv[r];
+			if (t < R) a.w2_tmp[row0 + t] = v;
+		} else if (lane < a.tp_world && kind == kLM) {
+			float *dst = reinterpret_cast<float *>(a.tp_peer[lane] + kTpOffLogits) + a.vocab_base + row0;
+			if (R == 4) *reinterpret_cast<float4 *>(dst) = make_float4(vv[0], vv[R > 1 ? 1 : 0], vv[R > 2 ? 2 : 0], vv[R > 3 ? 3 : 0]);
+			else if (R == 2) *reinterpret_cast<float2 *>(dst) = make_float2(vv[0], vv[R > 1 ? 1 : 0]);
+			else dst[0] = vv[0];
+		} else if (lane < a.tp_world) {
+			unsigned long long *dst = reinterpret_cast<unsigned long long *>(a.tp_peer[lane] + kTpOffMail) +
+			                          (size_t)((kind == kW2 ? kTpMaxWorld : 0) + a.tp_rank) * kTpCapFloats + row0;
+			if (R == 4) ll_store2_sys(dst, vv[0], vv[R > 1 ? 1 : 0], wflag), ll_store2_sys(dst + 2, vv[R > 2 ? 2 : 0], vv[R > 3 ? 3 : 0], wflag);
+			else if (R == 2) ll_store2_sys(dst, vv[0], vv[R > 1 ? 1 : 0], wflag);
+			else ll_store_sys(dst, vv[0], wflag);
+		}
+	} else if (t < (kind == kLM ? R : R * NREP)) { // wo / w2: lane = replica * R + row
+		const int tr = t % R;
+		float v = acc[0];
+#pragma unroll
+		for (int r = 1; r < R; ++r)
+			if (tr == r) v = acc[r];
+		const long row = (long)g * R + tr;
+		if (DT == YALM_F8E4M3 && ep.scale0) v *= ep.scale0[row];
+		if (kind == kLM) {
+			a.logits[row] = v;
+			if (v > ep.best_v) ep.best_v = v, ep.best_i = (int)row; // a lane's rows ascend: first maximum wins
+		} else {
+			// x += W v (src/infer.cpp:335-337); MoE: x += weight * (W2[e] hb_e), expert after expert (:377-383)
+			const float xn = kind == kW2 && ep.n_sub > 1 ? fmaf(ep.ew, v, resid) : resid + v;
+			if (kind == kW2 && ep.sub + 1 < ep.n_sub) {
+				if (t < R) a.w2_tmp[row] = xn; // the next expert's sub-phase continues the row (same lane)
+			} else {
+				if (LL) ll_store(a.ll_x + (size_t)((kind == kW2 ? kLLRep : 0) + t / R) * a.dim + row, xn, wflag);
+				if ((!LL || kind == kW2) && t < R) a.x[row] = xn;
+			}
+		}
+	}
+}
+
+// Tensor parallel, behind wo and behind (the last sub-phase of) w2: finish this warp's rows.  Every rank's partial of group g
+// has been (or is being) pushed into this rank's mailbox by the warp that owns g there; lane = rank * R + row polls its word,
+// the sums run in rank order on top of the residual (the same bits on every rank), and the finished rows go out as local
+// flagged words.
+template <int R>
+__device__ __forceinline__ void tp_collect(Ctx &c, const Args &a, int kind, int g_first, int NL, unsigned wflag, int ph) {
+	constexpr int NREP = YALM_MEGA_LL ? kLLRep : 1;
+	const int lane = c.lane, warp = c.warp;
+	const unsigned long long *mail = reinterpret_cast<const unsigned long long *>(a.tp_peer[a.tp_rank] + kTpOffMail) +
+	                                 (size_t)(kind == kW2 ? kTpMaxWorld : 0) * kTpCapFloats;
+	const int W = a.tp_world;
+	for (int b8 = 0; b8 < NL; b8 += kConsumerWarps) {
+		if (warp >= min(kConsumerWarps, NL - b8)) break;
+		const int g = g_first + (b8 + warp) * c.ncta;
+		const int tr = lane % R;
+		const long row = (long)g * R + tr;
+		float part = 0.f;
+		if (lane < W * R) {
+			const unsigned long long *p = mail + (size_t)(lane / R) * kTpCapFloats + row;
+			unsigned long long w = ll_load1_sys(p);
+			if (!ll_ok(w, wflag)) {
+				const long long t0 = clock64();
+				do {
+					__nanosleep(64);
+					if (timed_out(t0)) die(kFaultTpMailbox, (unsigned)(lane / R) | (unsigned)ph << 8 | (unsigned)kind << 24, (unsigned)row);
+					w = ll_load1_sys(p);
+				} while (!ll_ok(w, wflag));
+			}
+			part = ll_val(w);
+		}
+		// residual: x before wo is the plain copy behind w2 of the layer before (far side of the attention grid barrier);
+		// x before w2 is ll_x[0], complete in the replica this CTA verified when it staged w1/w3
+		float xn = 0.f;
+		if (lane < R * NREP)
+			xn = kind == kW2 ? ll_val(ll_load1(a.ll_x + (size_t)(c.cta % kLLRep) * a.dim + row)) : __ldcg(a.x + row);
+		for (int r = 0; r < W; ++r) xn += __shfl_sync(kFull, part, r * R + tr);
+		if (lane < R * NREP) {
+			ll_store(a.ll_x + (size_t)((kind == kW2 ? kLLRep : 0) + lane / R) * a.dim + row, xn, wflag);
+			if (kind == kW2 && lane < R) a.x[row] = xn;
+		}
+	}
+}
 
 // All row groups of one GEMV phase owned by this CTA; the input vector is already staged in c.vec.
 // Warp w owns groups w, w+8, ... of the CTA's list: it adds up all K-split tiles of the group, shuffle-reduces,
@@ -999,240 +1328,136 @@ struct Epi {
 template <int DT, int R, bool TP>
 __device__ __forceinline__ void gemv_consume(Ctx &c, const Args &a, Epi &ep, int ph) {
 	static_assert(YALM_MEGA_LL || !TP, "tensor parallelism rides on the flagged hand-over");
-	constexpr bool LL = YALM_MEGA_LL;  // x: flagged words (tensor parallel: the finished rows, after the exchange at the end of the phase)
-	constexpr bool LLH = YALM_MEGA_LL; // hb (and att_out): flagged too
-	constexpr int NREP = LL ? kLLRep : 1;    // flagged vectors are written kLLRep times (lane -> replica): see kLLRep
-	constexpr int NREPH = LLH ? kLLRep : 1;
 	const unsigned wflag = ll_flag(a.seq, ph + 1); // flagged hand-over: the next phase polls for this
 	using T = WTraits<DT>;
-	constexpr int EP = T::EP, CH = 32 * EP, Q = EP / 4;
+	constexpr int EP = T::EP, CH = 32 * EP;
 	const Shape sh = shape_of(a, ep.kind);
 	const int kind = ep.kind;
-	const int chunks = (sh.KT + CH - 1) / CH, nfull = sh.KT / CH;
-	const int row_stride = sh.KT * T::BYTES;
+	const int chunks = (sh.KT + CH - 1) / CH;
 	const int lane = c.lane, warp = c.warp;
 	int g_first, NL;
 	my_groups(c, sh.G, &g_first, &NL);
 	const uint32_t base = c.it;
+	const bool pipe_ffn = a.w2_pipe && kind == kFFN; // pipelined hb: this phase produces the slices
 	for (int b8 = 0; b8 < NL; b8 += kConsumerWarps) {
 		const int nb = min(kConsumerWarps, NL - b8);
 		if (warp >= nb) break;
 		const int g = g_first + (b8 + warp) * c.ncta;
-		// residual operand of the wo / w2 epilogue: issue the L2 read now, it is consumed after the tiles
-		float resid = 0.f;
-		if (!TP && (kind == kWO || kind == kW2) && lane < R * NREP) { // lane = replica * R + row of the group (epilogue below; tensor parallel: tp_collect)
-			// flagged hand-over: x after wo lives in ll_x[0] (complete: this CTA polled all of it when it staged w1/w3);
-			// x before wo is the plain copy written behind w2 of the layer before, on the far side of a grid barrier
-			if (kind == kW2 && ep.sub > 0) resid = __ldcg(a.w2_tmp + (long)g * R + lane % R); // x + the earlier experts' contributions
-			else if (LL && kind == kW2) resid = ll_val(ll_load1(a.ll_x + (size_t)(c.cta % kLLRep) * a.dim + (long)g * R + lane % R)); // the replica this CTA polled and verified
-			else resid = __ldcg(a.x + (long)g * R + lane % R);
+		if (pipe_ffn && warp < kHbBufs && warp < a.shape[kW2][2] && !(a.debug & 64)) { // duty warp of one of the first slices: fetch it once it is complete (never waits)
+			if (lane == 0 && !sm_hb_issued()[warp]) hb_fetch(c, a, ep.layer, warp, false, true);
+			__syncwarp();
 		}
+		// residual operand of the wo / w2 epilogue: issue the L2 read now, it is consumed after the tiles
+		const float resid = load_resid<R, TP>(c, a, ep, g);
 		float2 acc2[R];
 #pragma unroll
 		for (int r = 0; r < R; ++r) acc2[r] = make_float2(0.f, 0.f);
 		for (int kc = 0; kc < sh.nk; ++kc) {
 			uint32_t slot;
 			const unsigned char *tile = wait_tile(c, base + (uint32_t)(b8 * sh.nk + kc * nb + warp), &slot);
-			if (!(a.debug & 1)) {
-				// shared-space addresses: this lane's 16 bytes of chunk 0 of row 0, and its x quarter 0
-				uint32_t wa = tile_u32(c, tile) + lane * 16;
-				uint32_t xa = c.vec_u32 + (uint32_t)(kc * chunks * CH) * 4 + lane * 16;
-				int cc = 0;
-				for (; cc + 2 <= nfull; cc += 2, wa += 1024, xa += 2 * CH * 4) { // all loads of two chunks, then the math
-					uint4 w[2][R];
-					float4 xv[2][Q];
-#pragma unroll
-					for (int u = 0; u < 2; ++u)
-#pragma unroll
-						for (int r = 0; r < R; ++r) w[u][r] = lds128(wa + r * row_stride + u * 512);
-#pragma unroll
-					for (int u = 0; u < 2; ++u)
-#pragma unroll
-						for (int q = 0; q < Q; ++q) xv[u][q] = lds128f(xa + (u * CH + q * 128) * 4);
-#pragma unroll
-					for (int u = 0; u < 2; ++u)
-#pragma unroll
-						for (int r = 0; r < R; ++r) acc2[r] = fma16x2<DT>(w[u][r], xv[u], acc2[r]);
-				}
-				for (; cc < chunks; ++cc, wa += 512, xa += CH * 4) { // odd full chunk and / or the ragged last one
-					if (cc * CH + lane * EP < sh.KT) {
-						uint4 w[R];
-						float4 xv[Q];
-#pragma unroll
-						for (int r = 0; r < R; ++r) w[r] = lds128(wa + r * row_stride);
-#pragma unroll
-						for (int q = 0; q < Q; ++q) xv[q] = lds128f(xa + q * 128 * 4);
-#pragma unroll
-						for (int r = 0; r < R; ++r) acc2[r] = fma16x2<DT>(w[r], xv, acc2[r]);
-					}
-				}
-			}
+			if (!(a.debug & 1))
+				tile_fma<DT, R>(tile_u32(c, tile) + lane * 16, c.vec_u32 + (uint32_t)(kc * chunks * CH) * 4 + lane * 16, sh.KT, lane, acc2);
 			release(c, slot);
 		}
 		float acc[R];
 #pragma unroll
 		for (int r = 0; r < R; ++r) acc[r] = warp_sum(acc2[r].x + acc2[r].y);
-		// ---- epilogue: lane t handles output item t of the group -----------------------------------------
-		const int t = lane;
-		if (kind == kQKV) {
-			if (t < R / 2) {
-				float v0 = acc[0], v1 = acc[R > 1 ? 1 : 0];
-#pragma unroll
-				for (int r = 2; r + 1 < R; r += 2)
-					if (t == r / 2) v0 = acc[r], v1 = acc[r + 1];
-				long row = (long)g * R + 2 * t;
-				int which = 0;
-				const float *sc = ep.scale0;
-				if (row >= ep.rows0 + ep.rows1) which = 2, row -= ep.rows0 + ep.rows1, sc = ep.scale2;
-				else if (row >= ep.rows0) which = 1, row -= ep.rows0, sc = ep.scale1;
-				if (DT == YALM_F8E4M3 && sc) v0 *= sc[row], v1 *= sc[row + 1];
-				v0 = clipf(v0, a.clip), v1 = clipf(v1, a.clip);
-				const int hd = a.head_dim, j = (int)(row % hd);
-				if (which < 2) { // interleaved-pair RoPE (src/infer.cpp:200-213), cos/sin from the per-token table
-					const float2 cs = sm_rope()[j >> 1];
-					const float r0 = v0 * cs.x - v1 * cs.y, r1 = v0 * cs.y + v1 * cs.x;
-					v0 = r0, v1 = r1;
-				}
-				if (which == 0) {
-					*reinterpret_cast<float2 *>(a.q + row) = make_float2(v0, v1);
-				} else {
-					__half *cache = reinterpret_cast<__half *>(which == 1 ? ep.L->kc : ep.L->vc);
-					__half *dst = cache + ((size_t)(row / hd) * a.max_seq_len + c.kv_pos) * hd + j;
-					*reinterpret_cast<__half2 *>(dst) = __floats2half2_rn(v0, v1);
-				}
-			}
-		} else if (kind == kFFN) {
-			constexpr int RH = R > 1 ? R / 2 : 1;
-			if (t < RH * NREPH) { // every lane holds all sums: lane = replica * RH + row
-				const int tr = t % RH;
-				float gt = acc[0], up = acc[RH < R ? RH : 0];
-#pragma unroll
-				for (int r = 1; r < RH; ++r)
-					if (tr == r) gt = acc[r], up = acc[RH + r < R ? RH + r : 0];
-				const long row = (long)g * RH + tr; // MoE: row of hb = slot * hidden + i
-				if (DT == YALM_F8E4M3 && ep.scale0) {
-					long srow = row;
-					if (ep.gpe) { // scales are stacked per expert like the weights
-						const int slot = g / ep.gpe;
-						srow = (long)sm_misc()[kMiscExpert + slot] * a.hidden + (row - (long)slot * a.hidden);
-					}
-					gt *= ep.scale0[srow], up *= ep.scale1[srow];
-				}
-				gt = a.act == YALM_ACT_GELU ? act_gelu(gt) : act_silu(gt);
-				if (t < RH) a.hb[row] = gt * up;
-				if (LLH) ll_store(a.ll_hb + (size_t)(t / RH) * a.hb_len + row, gt * up, wflag);
-			}
-		} else if (TP) {
-			// tensor parallel: the rows are partial sums (wo / w2: this rank's slice of the input dimension) or this
-			// rank's slice of the vocabulary.  Every lane holds all R sums, so lane r hands the group's R values to
-			// rank r over NVLink: flagged words into mailbox [set][this rank] (collected by the warp that owns the same
-			// rows there: tp_collect below), or plain stores into the gathered logits.
-			const long row0 = (long)g * R;
-			float vv[R];
-#pragma unroll
-			for (int r = 0; r < R; ++r) {
-				vv[r] = acc[r];
-				if (DT == YALM_F8E4M3 && ep.scale0) vv[r] *= ep.scale0[row0 + r];
-			}
-			if (kind == kLM && t < R) {
-				float v = vv[0];
-#pragma unroll
-				for (int r = 1; r < R; ++r)
-					if (t == r) v = vv[r];
-				const int row = a.vocab_base + (int)row0 + t;
-				if (v > ep.best_v) ep.best_v = v, ep.best_i = row;
-			}
-			if (kind == kW2 && ep.n_sub > 1) { // MoE: gate weight, then on top of the earlier experts' sums (same lanes, earlier sub-phase)
-#pragma unroll
-				for (int r = 0; r < R; ++r) vv[r] = ep.sub > 0 ? fmaf(ep.ew, vv[r], __ldcg(a.w2_tmp + row0 + r)) : ep.ew * vv[r];
-			}
-			if (kind == kW2 && ep.sub + 1 < ep.n_sub) { // not the last expert: park the sums, nothing crosses the GPUs yet
-				float v = vv[0];
-#pragma unroll
-				for (int r = 1; r < R; ++r)
-					if (t == r) v = vv[r];
-				if (t < R) a.w2_tmp[row0 + t] = v;
-			} else if (lane < a.tp_world && kind == kLM) {
-				float *dst = reinterpret_cast<float *>(a.tp_peer[lane] + kTpOffLogits) + a.vocab_base + row0;
-				if (R == 4) *reinterpret_cast<float4 *>(dst) = make_float4(vv[0], vv[R > 1 ? 1 : 0], vv[R > 2 ? 2 : 0], vv[R > 3 ? 3 : 0]);
-				else if (R == 2) *reinterpret_cast<float2 *>(dst) = make_float2(vv[0], vv[R > 1 ? 1 : 0]);
-				else dst[0] = vv[0];
-			} else if (lane < a.tp_world) {
-				unsigned long long *dst = reinterpret_cast<unsigned long long *>(a.tp_peer[lane] + kTpOffMail) +
-				                          (size_t)((kind == kW2 ? kTpMaxWorld : 0) + a.tp_rank) * kTpCapFloats + row0;
-				if (R == 4) ll_store2_sys(dst, vv[0], vv[R > 1 ? 1 : 0], wflag), ll_store2_sys(dst + 2, vv[R > 2 ? 2 : 0], vv[R > 3 ? 3 : 0], wflag);
-				else if (R == 2) ll_store2_sys(dst, vv[0], vv[R > 1 ? 1 : 0], wflag);
-				else ll_store_sys(dst, vv[0], wflag);
-			}
-		} else if (t < (kind == kLM ? R : R * NREP)) { // wo / w2: lane = replica * R + row
-			const int tr = t % R;
-			float v = acc[0];
-#pragma unroll
-			for (int r = 1; r < R; ++r)
-				if (tr == r) v = acc[r];
-			const long row = (long)g * R + tr;
-			if (DT == YALM_F8E4M3 && ep.scale0) v *= ep.scale0[row];
-			if (kind == kLM) {
-				a.logits[row] = v;
-				if (v > ep.best_v) ep.best_v = v, ep.best_i = (int)row; // a lane's rows ascend: first maximum wins
-			} else {
-				// x += W v (src/infer.cpp:335-337); MoE: x += weight * (W2[e] hb_e), expert after expert (:377-383)
-				const float xn = kind == kW2 && ep.n_sub > 1 ? fmaf(ep.ew, v, resid) : resid + v;
-				if (kind == kW2 && ep.sub + 1 < ep.n_sub) {
-					if (t < R) a.w2_tmp[row] = xn; // the next expert's sub-phase continues the row (same lane)
-				} else {
-					if (LL) ll_store(a.ll_x + (size_t)((kind == kW2 ? kLLRep : 0) + t / R) * a.dim + row, xn, wflag);
-					if ((!LL || kind == kW2) && t < R) a.x[row] = xn;
-				}
-			}
-		}
+		gemv_epilogue<DT, R, TP>(c, a, ep, g, acc, resid, wflag);
 	}
-	if (TP && (kind == kWO || (kind == kW2 && ep.sub + 1 == ep.n_sub))) {
-		// ---- tensor parallel: finish this warp's rows.  Every rank's partial of group g has been (or is being) pushed into
-		// this rank's mailbox by the warp that owns g there; lane = rank * R + row polls its word, the sums run in rank
-		// order on top of the residual (the same bits on every rank), and the finished rows go out as local flagged words.
-		const unsigned long long *mail = reinterpret_cast<const unsigned long long *>(a.tp_peer[a.tp_rank] + kTpOffMail) +
-		                                 (size_t)(kind == kW2 ? kTpMaxWorld : 0) * kTpCapFloats;
-		const int W = a.tp_world;
-		for (int b8 = 0; b8 < NL; b8 += kConsumerWarps) {
-			if (warp >= min(kConsumerWarps, NL - b8)) break;
-			const int g = g_first + (b8 + warp) * c.ncta;
-			const int tr = lane % R;
-			const long row = (long)g * R + tr;
-			float part = 0.f;
-			if (lane < W * R) {
-				const unsigned long long *p = mail + (size_t)(lane / R) * kTpCapFloats + row;
-				unsigned long long w = ll_load1_sys(p);
-				if (!ll_ok(w, wflag)) {
-					const long long t0 = clock64();
-					do {
-						__nanosleep(64);
-						if (timed_out(t0)) die(kFaultTpMailbox, (unsigned)(lane / R) | (unsigned)ph << 8 | (unsigned)kind << 24, (unsigned)row);
-						w = ll_load1_sys(p);
-					} while (!ll_ok(w, wflag));
-				}
-				part = ll_val(w);
-			}
-			// residual: x before wo is the plain copy behind w2 of the layer before (far side of the attention grid barrier);
-			// x before w2 is ll_x[0], complete in the replica this CTA verified when it staged w1/w3
-			float xn = 0.f;
-			if (lane < R * NREP)
-				xn = kind == kW2 ? ll_val(ll_load1(a.ll_x + (size_t)(c.cta % kLLRep) * a.dim + row)) : __ldcg(a.x + row);
-			for (int r = 0; r < W; ++r) xn += __shfl_sync(kFull, part, r * R + tr);
-			if (lane < R * NREP) {
-				ll_store(a.ll_x + (size_t)((kind == kW2 ? kLLRep : 0) + lane / R) * a.dim + row, xn, wflag);
-				if (kind == kW2 && lane < R) a.x[row] = xn;
-			}
-		}
-	}
+	if (TP && (kind == kWO || (kind == kW2 && ep.sub + 1 == ep.n_sub))) tp_collect<R>(c, a, kind, g_first, NL, wflag, ph);
 	c.it = base + (uint32_t)(NL * sh.nk);
 	if (!(kind == kW2 && ep.sub + 1 < ep.n_sub)) c.rot = (c.rot + sh.G) % c.ncta; // w2 sub-phases share one row -> CTA map
+}
+
+// w2 with pipelined hb (see "pipelined hb"): K-split-major over all of this CTA's row groups.  Warp w owns groups w, w + W, ...
+// (J <= kHbMaxGroups of them) and keeps their partial sums in registers across the slices; ring tile of (K split kc, group gl)
+// = base + kc * NL + gl.  The group loop is a run-time loop over ONE copy of the tile code: the register arrays rotate by one
+// group per iteration (plain moves), so the current group is always index 0.
+template <int DT, int R, bool TP>
+__device__ __forceinline__ void w2_pipe_consume(Ctx &c, const Args &a, Epi &ep, int ph) {
+	constexpr int W = kConsumerWarps, JM = kHbMaxGroups;
+	const unsigned wflag = ll_flag(a.seq, ph + 1);
+	const Shape sh = shape_of(a, kW2);
+	const int lane = c.lane, warp = c.warp;
+	int g_first, NL;
+	my_groups(c, sh.G, &g_first, &NL);
+	const uint32_t base = c.it;
+	const int J = warp < NL ? (NL - warp + W - 1) / W : 0;
+	float2 acc2[JM][R];
+	float resid[JM];
+#pragma unroll
+	for (int j = 0; j < JM; ++j) {
+		resid[j] = j < J ? load_resid<R, TP>(c, a, ep, g_first + (warp + W * j) * c.ncta) : 0.f;
+#pragma unroll
+		for (int r = 0; r < R; ++r) acc2[j][r] = make_float2(0.f, 0.f);
+	}
+	auto rotate = [&]() {
+#pragma unroll
+		for (int r = 0; r < R; ++r) {
+			const float2 t = acc2[0][r];
+#pragma unroll
+			for (int j = 0; j + 1 < JM; ++j) acc2[j][r] = acc2[j + 1][r];
+			acc2[JM - 1][r] = t;
+		}
+		const float t = resid[0];
+#pragma unroll
+		for (int j = 0; j + 1 < JM; ++j) resid[j] = resid[j + 1];
+		resid[JM - 1] = t;
+	};
+	// lane 0: fetch slice s if this warp is its duty warp and it has not been fetched yet
+	auto duty = [&](int s, bool blocking) {
+		if (s < sh.nk && s % W == warp) {
+			if (lane == 0 && !sm_hb_issued()[s]) hb_fetch(c, a, ep.layer, s, blocking, false);
+			__syncwarp();
+		}
+	};
+	for (int kc = 0; kc < sh.nk; ++kc) {
+		const int idx = ep.layer * sh.nk + kc, b = idx % kHbBufs;
+		duty(kc, true);
+#pragma unroll 1
+		for (int s = kc + 1; s < kc + kHbBufs; ++s) duty(s, false); // ahead: slice s's buffer is free once every warp has left slice s - kHbBufs
+		const bool probe = c.prof && c.tid == 0 && kc == sh.nk - 1; // profile: how long the LAST slice keeps warp 0 waiting
+		if (probe) c.prof[((size_t)ep.layer * kProfPhases + 4) * kProfSlots + 7] = clock64();
+		mbar_wait(sm_hbfull0() + 8 * b, (uint32_t)(idx / kHbBufs) & 1u);
+		if (probe) c.prof[((size_t)ep.layer * kProfPhases + 4) * kProfSlots + 6] = clock64();
+		const uint32_t xa = hb_buf_u32(c, a, b) + lane * 16;
+#pragma unroll 1
+		for (int j = 0; j < JM; ++j) {
+			if (j < J) {
+				uint32_t slot;
+				const unsigned char *tile = wait_tile(c, base + (uint32_t)(kc * NL + warp + W * j), &slot);
+				if (!(a.debug & 1)) tile_fma<DT, R>(tile_u32(c, tile) + lane * 16, xa, sh.KT, lane, acc2[0]);
+				release(c, slot);
+			}
+			rotate();
+		}
+#pragma unroll 1
+		for (int s = kc + 1; s < kc + kHbBufs; ++s) duty(s, false); // second chance: the slower warps have moved on meanwhile
+		__syncwarp();
+		if (lane == 0) mbar_arrive(sm_hbempty0() + 8 * b);
+	}
+#pragma unroll 1
+	for (int j = 0; j < JM; ++j) {
+		if (j < J) {
+			float acc[R];
+#pragma unroll
+			for (int r = 0; r < R; ++r) acc[r] = warp_sum(acc2[0][r].x + acc2[0][r].y);
+			gemv_epilogue<DT, R, TP>(c, a, ep, g_first + (warp + W * j) * c.ncta, acc, resid[0], wflag);
+		}
+		rotate();
+	}
+	if (TP) tp_collect<R>(c, a, kW2, g_first, NL, wflag, ph);
+	c.it = base + (uint32_t)(NL * sh.nk);
+	c.rot = (c.rot + sh.G) % c.ncta;
 }
 
 template <int DT, bool TP>
 __device__ __forceinline__ void gemv_phase(Ctx &c, const Args &a, Epi &ep, int ph) {
 	const int R = a.shape[ep.kind][0];
-	if (R == 4) gemv_consume<DT, 4, TP>(c, a, ep, ph);
+	if (a.w2_pipe && ep.kind == kW2) { // plan(): R <= 2
+		if (R == 2) w2_pipe_consume<DT, 2, TP>(c, a, ep, ph);
+		else w2_pipe_consume<DT, 1, TP>(c, a, ep, ph);
+	} else if (R == 4) gemv_consume<DT, 4, TP>(c, a, ep, ph);
 	else if (R == 2) gemv_consume<DT, 2, TP>(c, a, ep, ph);
 	else gemv_consume<DT, 1, TP>(c, a, ep, ph);
 }
@@ -1753,6 +1978,10 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_c
 			mbar_init(sm_empty0() + 8 * i, 1);
 			sm_rel()[i] = 0;
 		}
+		for (int i = 0; i < kHbBufs; ++i) {
+			mbar_init(sm_hbfull0() + 8 * i, 1);
+			mbar_init(sm_hbempty0() + 8 * i, kConsumerWarps);
+		}
 		asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
 	}
 	// RoPE table of this token: cos/sin(pos * theta^(-j/rotary_dim)) with the reference's fp32 formula
@@ -1782,7 +2011,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_c
 		phase_of(ph, a, &l, &k, &sub);
 		ep.sub = k == 4 ? sub : 0, ep.n_sub = k == 4 ? a.n_sub : 1, ep.ew = 1.0f, ep.gpe = 0;
 		const Layer &L = a.layers[l];
-		ep.L = &L;
+		ep.L = &L, ep.layer = l;
 		stamp(c, l, k, 0);
 		const float *rms = k == 0 ? L.rms_att : k == 3 ? L.rms_ffn : k == 5 ? a.rms_final : nullptr;
 		float4 wv[kNormCache];
@@ -1816,7 +2045,10 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_c
 			break;
 		default: ep.kind = kLM, ep.scale0 = a.wcls_scale, ep.best_v = -FLT_MAX, ep.best_i = 0x7fffffff; break;
 		}
-		if (flagged) {
+		if (a.w2_pipe && k == 3) hb_setup(a, c); // pipelined hb: ordered before the tile loop by the staging step's CTA barriers
+		if (a.w2_pipe && k == 4) {
+			// pipelined hb: nothing to stage — the slices of hb arrive by bulk copy, each awaited where it is needed
+		} else if (flagged) {
 			if (YALM_MEGA_LL_ATTN && k == 2) { // distributed attention combine of this CTA's head slice (flags of phase ph - 1)
 				const int C = kStageBytes / (4 * HD), nch = (c.kv_len + C - 1) / C;
 				const AttnSplit sp = attn_split(c.cta, c.ncta, a.n_kv_heads, nch);
@@ -1921,12 +2153,19 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_c
 	if (c.tid == 0) {
 		__threadfence();
 		const unsigned prev = atomicAdd(a.sync + 1, 1u);
-		if (prev + 1 == (unsigned)c.ncta) {
+		const bool last = prev + 1 == (unsigned)c.ncta;
+		if (last) {
 			a.sync[0] = 0;
 			a.sync[1] = 0;
 			if (TP) *reinterpret_cast<unsigned *>(a.tp_peer[a.tp_rank] + kTpOffGen) = c.xgen;
 			__threadfence();
 		}
+		sm_misc()[0] = last ? 1 : 0;
+	}
+	if (a.w2_pipe) { // the last CTA out zeroes the hb slice counters for the next launch
+		cbar();
+		if (sm_misc()[0])
+			for (int i = c.tid; i < a.n_layers * kHbMaxSlices; i += kCT) a.hb_cnt[i] = 0;
 	}
 }
 

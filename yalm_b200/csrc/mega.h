@@ -19,7 +19,12 @@ constexpr int kConsumerWarps = 11;
 constexpr int kProducerWarps = 1; // all 32 lanes issue: lane l takes tile l of each batch of min(stages, 32) tiles
 constexpr int kThreads = (kConsumerWarps + kProducerWarps) * 32;
 constexpr int kMaxStages = 24;
-constexpr int kSmemHeader = 1280; // rope table, reduction scratch, release counters, mbarriers in front of the ring
+constexpr int kSmemHeader = 1536; // rope table, reduction scratch, release counters, mbarriers in front of the ring
+// Pipelined w1/w3 -> w2 hand-over (dense models, Args::w2_pipe; decode_mega.cuh "pipelined hb"): hb travels as plain fp32
+// in the permuted shared-memory layout, sliced by the K splits of w2; each slice has a completion counter and is pulled
+// into one of kHbBufs shared-memory buffers by a bulk copy; w2 walks its tiles K-split-major, so a warp carries the
+// partial sums of all its row groups (at most kHbMaxGroups) across the slices.
+constexpr int kHbMaxSlices = 16, kHbBufs = 4, kHbMaxGroups = 3;
 constexpr int kTraceEvents = 1 << 16;
 // Mixture of experts (Mixtral: 8 experts, 2 active; the reference has MoE on the CPU only, src/infer.cpp:100-132, 347-384;
 // its CUDA path asserts, src/infer.cu:865-867).  The router runs in the staging step of the w1/w3 phase (every CTA
@@ -111,6 +116,12 @@ struct Args {
 	unsigned long long *ll_ml;  // (n_kv, grid, G, 2): {max, flag}, {sum, flag}
 	unsigned seq;               // launch number of this inference state, starts at 1
 	float *w2_tmp;              // [dim]: MoE, x + the earlier experts' contributions, private to the lane that wrote it
+	// pipelined hb (w2_pipe != 0): hbp = hb in the permuted layout (xs_slot) the w2 tile loop reads; hb_cnt = completion
+	// counters [n_layers][kHbMaxSlices] (zero between launches); hb_slice = floats per slice (= columns per w2 tile);
+	// hb_off = float offset of the slice buffers inside the vec region (behind the phases' own input vector)
+	float *hbp;
+	unsigned *hb_cnt;
+	int w2_pipe, hb_slice, hb_off;
 	char *tp_peer[kTpMaxWorld]; // every rank's region (kTpOff*), [tp_rank] = this rank's own
 };
 
@@ -118,6 +129,7 @@ struct Plan {
 	bool ok = false;
 	int dtype = 0, grid = 0, stages = 0, vec_floats = 0;
 	bool tp = false;
+	int w2_pipe = 0, hb_slice = 0, hb_off = 0; // pipelined hb (Args)
 	size_t smem = 0;
 	const void *kernel = nullptr;
 	int shape[5][4] = {};

@@ -235,6 +235,8 @@ void InferenceState::cuda() {
 	    {(void **)&_mega_amax_val, sizeof(float) * (size_t)sms},
 	    {(void **)&_mega_amax_idx, sizeof(int) * (size_t)sms},
 	    {(void **)&_mega_tmp, sizeof(float) * c.dim},
+	    {(void **)&_mega_hbp, sizeof(float) * ((size_t)k_act * lhid + 512)}, // hb in the w2 tile loop's permuted layout (padded to a chunk)
+	    {(void **)&_mega_hb_cnt, sizeof(unsigned) * (size_t)c.n_layers * yalm::mega::kHbMaxSlices},
 	    {(void **)&_mega_ll, 8 * (yalm::mega::kLLRep * ((size_t)2 * c.dim + (size_t)k_act * lhid + (size_t)lh * c.head_dim) +
 	                              (size_t)sms * lh * c.head_dim + (size_t)sms * lh * 2)},
 	};
@@ -665,6 +667,13 @@ void Model::plan_mega() {
 	_mega_ok = true;
 }
 
+int Model::mega_info(int *out4) const {
+	if (!_mega_ok) return YALM_EINVAL;
+	const yalm::mega::Plan &p = _mega->plan;
+	out4[0] = p.stages, out4[1] = p.vec_floats, out4[2] = p.w2_pipe, out4[3] = p.shape[3][2];
+	return 0;
+}
+
 int Model::mega_profile(InferenceState &s, int token, int pos, long long *out, size_t count, int *grid) {
 	if (!_mega_ok) return YALM_EINVAL;
 	const Config &c = *config;
@@ -735,6 +744,7 @@ int Model::launch_mega(InferenceState &s, int token, int pos, int mode, long lon
 	static unsigned tp_seq = 0;
 	a.seq = c.tp_size > 1 ? ++tp_seq : s.next_mega_seq();
 	a.w2_tmp = s.mega_tmp();
+	a.hbp = s.mega_hbp(), a.hb_cnt = s.mega_hb_cnt();
 	a.ctl = s.ctl(), a.tokens_out = s.tokens_dev();
 	a.token = token, a.pos = pos, a.mode = mode;
 	return yalm::mega::launch(_mega->plan, a, s.stream());

@@ -136,6 +136,8 @@ struct InferenceState {
 	int *mega_amax_idx() const { return _mega_amax_idx; }
 	unsigned long long *mega_ll() const { return _mega_ll; }
 	float *mega_tmp() const { return _mega_tmp; }
+	float *mega_hbp() const { return _mega_hbp; }
+	unsigned *mega_hb_cnt() const { return _mega_hb_cnt; }
 	unsigned next_mega_seq() { return ++_mega_seq; }
 	void set_mega_seq(unsigned v) { _mega_seq = v; } // tests: start the hand-over flags' launch counter near its wrap
 
@@ -163,6 +165,8 @@ private:
 	unsigned *_mega_counters = nullptr, *_mega_sync = nullptr;
 	int *_mega_amax_idx = nullptr;
 	float *_mega_tmp = nullptr; // x + first column half of w2 (YALM_MEGA_W2_SPLIT)
+	float *_mega_hbp = nullptr;        // pipelined hb (mega.h: Args::hbp, hb_cnt)
+	unsigned *_mega_hb_cnt = nullptr;
 	unsigned long long *_mega_ll = nullptr; // flagged hand-over buffers: x[2][dim] | hb | att | acc | ml (mega.h: Args::ll_*)
 	unsigned _mega_seq = 0;
 	void *_arena = nullptr; // one device allocation behind all of the above
@@ -271,6 +275,7 @@ struct Model {
 	// the per-op kernel graph: unsharded dense models whose shapes the tile planner accepts.  Set
 	// YALM_B200_MEGA=0 in the environment before cuda() to force the per-op path.
 	bool uses_megakernel() const { return _mega_ok; }
+	int mega_info(int *out4) const; // {ring stages, vec floats, pipelined hb, K splits of w2}; YALM_EINVAL without the megakernel
 	// One forward pass with the kernel's phase profile on: clock64 stamps per (CTA, layer, phase, slot), see
 	// decode_mega.cuh.  out == null: only *grid is returned.
 	int mega_profile(InferenceState &s, int token, int pos, long long *out, size_t count, int *grid);
