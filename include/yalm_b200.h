@@ -244,9 +244,10 @@ int yalm_forward_launches(const yalm_model *m, int mode);
  * (tensor-parallel shards, MoE, shapes the tile planner rejects, or YALM_B200_MEGA=0 in the environment). */
 int yalm_model_uses_megakernel(const yalm_model *m);
 /* Plan of the whole-token kernel for this model (no reference counterpart: the reference has no such kernel):
- * out4 = {ring stages, floats of the shared-memory vector region, 1 if hb travels w1/w3 -> w2 as pipelined slices
- * (decode_mega.cuh "pipelined hb") else 0, K splits of w2}.  Returns YALM_EINVAL when the model does not run on it. */
-int yalm_model_mega_info(const yalm_model *m, int *out4);
+ * out8 = {ring stages, floats of the shared-memory vector region, 1 if hb travels w1/w3 -> w2 as pipelined slices
+ * (decode_mega.cuh "pipelined hb") else 0, K splits of w2, 1 if the GEMV phases run on the tensor cores (decode_mega.cuh
+ * "tensor-core GEMV") else 0, 0, 0, 0}.  Returns YALM_EINVAL when the model does not run on it. */
+int yalm_model_mega_info(const yalm_model *m, int *out8);
 /* One forward pass (logits mode) with the megakernel's phase profile on.  out receives grid * n_layers * 48
  * clock64 values: per CTA, per layer, 6 phases (qkv, attention, wo, w1/w3, w2, lm head) x 8 slots
  * ([0] phase entered [1] grid barrier passed [2] input vector staged [3] tiles + epilogue done

@@ -14,11 +14,14 @@ from yalm_b200 import yalm_file as yf
 pytestmark = pytest.mark.gpu
 
 
-def run(img, prompt, n_gen, context=0, mega=True, device_loop=False, pipe=None):
-    """pipe: None = the planner's choice, True / False = YALM_MEGA_W2_PIPE=1 / 0 (pipelined hb slices forced on / off)."""
+def run(img, prompt, n_gen, context=0, mega=True, device_loop=False, pipe=None, mma=None):
+    """pipe: None = the planner's choice, True / False = YALM_MEGA_W2_PIPE=1 / 0 (pipelined hb slices forced on / off);
+    mma likewise for YALM_MEGA_MMA (GEMV phases on the tensor cores)."""
     env = {"YALM_B200_MEGA": "1" if mega else "0"}
     if pipe is not None:
         env["YALM_MEGA_W2_PIPE"] = "1" if pipe else "0"
+    if mma is not None:
+        env["YALM_MEGA_MMA"] = "1" if mma else "0"
     old = {k: os.environ.get(k) for k in env}
     os.environ.update(env)
     try:
@@ -32,6 +35,8 @@ def run(img, prompt, n_gen, context=0, mega=True, device_loop=False, pipe=None):
     used = m.uses_megakernel()
     if pipe is not None and used:
         assert m.mega_info()["w2_pipe"] == pipe, m.mega_info()
+    if mma is not None and used:
+        assert m.mega_info()["mma"] == mma, m.mega_info()
     s = api.InferenceState(m)
     if device_loop:
         for pos, tok in enumerate(prompt[:-1]):
@@ -284,3 +289,49 @@ def test_mega_pipelined_hb_window_wrap_and_many_launches(oracle):
     assert used
     assert np.abs(lg - lo).max() < LOGIT_TOL
     assert tg == to
+
+
+# Tensor-core GEMV (decode_mega.cuh "tensor-core GEMV"): 16-row weight tiles through 3-D tensor copies, mma.sync against x as
+# an fp16 hi + lo pair.  Forced on (YALM_MEGA_MMA=1) and off on the same image.
+MMA = {
+    # 2 K stages per tile (fewer than warps: most warps park zero partials), head_dim 64
+    "small-k512": (yf.Arch(512, 1024, 64, 3, 8, 2, 1000, 256, 500000.0, name="mma512"), 24),
+    # gelu + clip, head_dim 128, 4 K stages
+    "gelu-clip-k1024": (yf.Arch(1024, 2048, 128, 2, 8, 2, 512, 128, 1000000.0, act_type="gelu", qkv_clip=1.5, name="mma1024"), 24),
+    # 70B-like width: 56 rows per CTA in w2 / wo (4 tiles of 14), 32 K stages, head group 8
+    "wide-8192": (yf.Arch(8192, 4096, 128, 1, 64, 8, 512, 64, 500000.0, name="mmawide"), 6),
+    # the headline geometry, two layers
+    "mistral-2layers": (yf.slim(yf.ARCHS["mistral-7b"], 2), 8),
+}
+
+
+@pytest.mark.parametrize("case", sorted(MMA))
+def test_mega_tensor_core_gemv_vs_oracle_and_simt_path(oracle, case):
+    arch, n = MMA[case]
+    img = bytes(yf.random_model(arch, "fp16", seed=13))
+    prompt = [1, 5, 9, 200, 77]
+    to, lo = oracle.OracleModel(img).generate(prompt, n, keep_logits=True)
+    tm, lm, used = run(img, prompt, n, mma=True)
+    assert used
+    assert np.abs(lm - lo).max() < LOGIT_TOL
+    assert tm == to
+    ts, ls, _ = run(img, prompt, n, mma=False)
+    assert ts == tm
+    assert np.abs(ls - lm).max() < 2e-3                   # x = hi + lo to 2^-22, sums in another order
+    td, ld, _ = run(img, prompt, n, mma=True, device_loop=True)
+    assert td == tm
+    assert np.abs(ld - lm).max() < 1e-5
+
+
+def test_mega_tensor_core_gemv_window_wrap(oracle):
+    """Tensor-core GEMV with a sliding window (-T 32, 150 steps, sinks re-rotated) — tokens and logits against the oracle,
+    and bit-identical logits on a second state (the partial sums are added in warp order)."""
+    arch = yf.Arch(512, 1024, 64, 2, 8, 2, 1000, 256, 500000.0, name="mmawin")
+    img = bytes(yf.random_model(arch, "fp16", seed=15))
+    to, lo = oracle.OracleModel(img, context=32).generate([1, 2, 3], 150, keep_logits=True)
+    tg, lg, used = run(img, [1, 2, 3], 150, context=32, mma=True)
+    assert used
+    assert np.abs(lg - lo).max() < LOGIT_TOL
+    assert tg == to
+    tg2, lg2, _ = run(img, [1, 2, 3], 150, context=32, mma=True)
+    assert (lg2 == lg).all()

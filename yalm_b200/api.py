@@ -256,9 +256,9 @@ class Model:
         return bool(lib().yalm_model_uses_megakernel(self.h))
 
     def mega_info(self):
-        v = (C.c_int * 4)()
+        v = (C.c_int * 8)()
         _check(lib().yalm_model_mega_info(self.h, v), "mega_info")
-        return {"stages": v[0], "vec_floats": v[1], "w2_pipe": bool(v[2]), "w2_k_splits": v[3]}
+        return {"stages": v[0], "vec_floats": v[1], "w2_pipe": bool(v[2]), "w2_k_splits": v[3], "mma": bool(v[4])}
 
     def launches(self, mode=MODE_LOGITS) -> int:
         return lib().yalm_forward_launches(self.h, mode)

@@ -423,9 +423,9 @@ extern "C" int yalm_model_uses_megakernel(const yalm_model *m) {
 	return m && m->model->uses_megakernel() ? 1 : 0;
 }
 
-extern "C" int yalm_model_mega_info(const yalm_model *m, int *out4) {
-	if (!m || !out4) return YALM_EINVAL;
-	return m->model->mega_info(out4);
+extern "C" int yalm_model_mega_info(const yalm_model *m, int *out8) {
+	if (!m || !out8) return YALM_EINVAL;
+	return m->model->mega_info(out8);
 }
 
 extern "C" int yalm_mega_profile(yalm_model *m, yalm_state *s, int token, int pos, long long *out, size_t count, int *grid) {

@@ -3,6 +3,8 @@
 #include "decode_mega.cuh"
 #include "launch.h"
 
+#include <cuda.h> // CUtensorMap + enums only: cuTensorMapEncodeTiled is resolved at run time (cudaGetDriverEntryPoint)
+
 #include <algorithm>
 #include <cstdio>
 #include <cstdlib>
@@ -84,6 +86,30 @@ const char *describe_fault() {
 }
 
 // ---- host side --------------------------------------------------------------------------------------------
+int make_weight_map(void *map128, const void *dev_ptr, int rows, int K, int box_rows) {
+	typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
+	                                  const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+	                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+	static EncodeTiledFn fn = [] {
+		void *p = nullptr;
+		cudaDriverEntryPointQueryResult q;
+		if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess) p = nullptr;
+		return reinterpret_cast<EncodeTiledFn>(p);
+	}();
+	static_assert(sizeof(CUtensorMap) == 128, "tensor map records are 128 bytes");
+	if (!fn || K % 64 || box_rows < 1 || box_rows > 256) return YALM_EINVAL;
+	// (column within a 64-column block, row, column block): a box = 64 x box_rows x 4 lands as [block][row][128 bytes]
+	// (tried: (column, column block, row) boxes, which the copy engine walks row by row — 512 contiguous bytes at a time — and
+	// which land as [row][block][128 bytes]: the same streaming rate, 4-way bank conflicts in ldmatrix)
+	const cuuint64_t dims[3] = {64, (cuuint64_t)rows, (cuuint64_t)(K / 64)};
+	const cuuint64_t strides[2] = {(cuuint64_t)K * 2, 128};
+	const cuuint32_t box[3] = {64, (cuuint32_t)box_rows, kMmaKCols / 64}, estr[3] = {1, 1, 1};
+	const CUresult r = fn(reinterpret_cast<CUtensorMap *>(map128), CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 3, const_cast<void *>(dev_ptr), dims, strides,
+	                      box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+	                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+	return r == CUDA_SUCCESS ? 0 : YALM_EINVAL;
+}
+
 static inline int ep_of(int dtype) {
 	return dtype == YALM_F32 ? 4 : dtype == YALM_F16 ? 8 : dtype == YALM_F8E4M3 ? 16 : 0;
 }
@@ -152,6 +178,8 @@ Plan plan(int dtype, int dim, int q_dim, int kv_dim, int head_dim, int hidden, i
 	cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
 	if (!coop || di.sms < 1) return p;
 	p.grid = di.sms;
+	if (const char *e = getenv("YALM_MEGA_GRID")) // experiment: fewer CTAs than SMs (row blocks that fill whole 16-row tiles)
+		if (atoi(e) >= 8 && atoi(e) < p.grid) p.grid = atoi(e);
 	if (tp && p.grid > kTpMaxGrid) return p;
 	if (n_kv_heads > p.grid) return p; // a CTA's attention units must span at most kHeadSlots KV heads
 	// the attention unit split runs in 32-bit arithmetic: (units) x (grid + 1) must stay below 2^31
@@ -166,6 +194,28 @@ Plan plan(int dtype, int dim, int q_dim, int kv_dim, int head_dim, int hidden, i
 		return (int)std::min<long>(kMaxStages, room / kStageBytes);
 	};
 	int vf = std::max(padded(dim, ep), std::max(padded(q_dim, ep), padded(hidden, ep)));
+	// Tensor-core GEMV (decode_mega.cuh "tensor-core GEMV"): fp16 dense models, every K a multiple of 256 columns.
+	// YALM_MEGA_MMA=1 / 0 force it on (where the shape allows) / off.
+	{
+		const char *e = getenv("YALM_MEGA_MMA");
+		const bool can = dtype == YALM_F16 && !tp && n_experts == 0 && dim % kMmaKCols == 0 && q_dim % kMmaKCols == 0 &&
+		                 hidden % kMmaKCols == 0 && q_dim % 2 == 0 && kv_dim % 2 == 0 && dim % 2 == 0 && vocab % 2 == 0;
+		if (can && (e ? atoi(e) != 0 : false)) {
+			p.mma = 1;
+			auto box_rows = [&](int rows, int unit, int cap) { // largest block of one matrix's rows per CTA -> rows per tile
+				const int per = ((rows / unit + p.grid - 1) / p.grid) * unit; // (in `unit`s: row pairs, or rows of w1 AND w3)
+				int best = std::min(cap, per), waste = 1 << 30;
+				for (int mt = std::min(cap, per); mt >= std::max(unit, cap / 2); mt -= unit) { // least over-fetch, larger tiles on ties
+					const int w = (per + mt - 1) / mt * mt - per;
+					if (w < waste) waste = w, best = mt;
+				}
+				return best;
+			};
+			p.mma_mt[0] = box_rows(q_dim, 2, 16), p.mma_mt[1] = box_rows(kv_dim, 2, 16), p.mma_mt[2] = box_rows(dim, 2, 16);
+			p.mma_mt[3] = box_rows(hidden, 1, 8), p.mma_mt[4] = box_rows(dim, 2, 16), p.mma_mt[5] = box_rows(vocab, 2, 16);
+			vf += kMmaSlots * kConsumerWarps * 16; // the tiles' per-warp partial sums live behind the input vector
+		}
+	}
 	// Pipelined w1/w3 -> w2 hand-over (decode_mega.cuh "pipelined hb"; dense models whose w2 is K-split): hb never sits in
 	// shared memory as a whole — kHbBufs slice buffers behind the other phases' input vector replace it, and the ring gets the
 	// difference (70B-class: 112 KB -> 64 KB, six more stages; measured +6.5 % tok/s on a 16-layer slice).  It is switched
@@ -175,7 +225,7 @@ Plan plan(int dtype, int dim, int q_dim, int kv_dim, int head_dim, int hidden, i
 		const char *e = getenv("YALM_MEGA_W2_PIPE");
 		const int nk = p.shape[kW2][2], groups = (p.shape[kW2][3] + di.sms - 1) / std::max(1, di.sms);
 		const int hb_off = std::max(padded(dim, ep), padded(q_dim, ep)), vf_pipe = hb_off + kHbBufs * p.shape[kW2][1];
-		const bool can = n_experts == 0 && nk >= 2 && nk <= kHbMaxSlices && p.shape[kW2][0] <= 2 &&
+		const bool can = !p.mma && n_experts == 0 && nk >= 2 && nk <= kHbMaxSlices && p.shape[kW2][0] <= 2 &&
 		                 (groups + kConsumerWarps - 1) / kConsumerWarps <= kHbMaxGroups && stages_for(vf_pipe) >= 2;
 		const bool want = e ? atoi(e) != 0 : !tp && stages_for(vf_pipe) >= stages_for(vf) + 2; // tensor parallel: only on request
 		if (can && want) p.w2_pipe = 1, p.hb_slice = p.shape[kW2][1], p.hb_off = hb_off, vf = vf_pipe;
@@ -204,6 +254,9 @@ int launch(const Plan &p, const Args &a, cudaStream_t st) {
 	Args args = a;
 	args.stages = p.stages, args.vec_floats = p.vec_floats;
 	args.w2_pipe = p.w2_pipe, args.hb_slice = p.hb_slice, args.hb_off = p.hb_off;
+	args.mma = p.mma;
+	memcpy(args.mma_mt, p.mma_mt, sizeof(args.mma_mt));
+	if (p.mma && !a.tmaps) return YALM_EINVAL;
 	if (p.w2_pipe && (!a.hbp || !a.hb_cnt)) return YALM_EINVAL;
 	memcpy(args.shape, p.shape, sizeof(args.shape));
 	// Timing-experiment knobs.  Read once; with YALM_MEGA_TUNE=1 (tools/mega_sweep.py) they are re-read at every launch.

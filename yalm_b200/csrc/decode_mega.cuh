@@ -100,6 +100,28 @@ __device__ __forceinline__ void bulk_g2s_plain(uint32_t dst, const void *src, ui
 	             "r"(bar)
 	             : "memory");
 }
+// 3-D tensor copy global -> shared (tensor-core GEMV: 64 columns x rows x column blocks of a weight matrix, SWIZZLE_128B)
+__device__ __forceinline__ void tma_load_3d(uint32_t dst, const void *map, int c0, int c1, int c2, uint32_t bar, uint64_t policy) {
+	if (policy == 0) return; // debug: no copies
+	asm volatile(
+	    "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1, {%2, %3, %4}], [%5], %6;" ::"r"(dst),
+	    "l"(map), "r"(c0), "r"(c1), "r"(c2), "r"(bar), "l"(policy)
+	    : "memory");
+}
+__device__ __forceinline__ void ldmatrix_x4(uint32_t (&r)[4], uint32_t addr) {
+	asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0, %1, %2, %3}, [%4];" : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
+}
+__device__ __forceinline__ uint2 lds64(uint32_t addr) {
+	uint2 v;
+	asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(addr));
+	return v;
+}
+// D (16 x 8, fp32) += A (16 x 16 fp16, row) * B (16 x 8 fp16, col)
+__device__ __forceinline__ void mma16816(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+	asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%0, %1, %2, %3};"
+	             : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+	             : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
 // Fire-and-forget L2 prefetch of a global range (no completion tracking, never blocks the issuing thread).
 __device__ __forceinline__ void bulk_prefetch_l2(const void *src, uint32_t bytes, bool tma = false) {
 	if (tma) { // one request to the copy engine (debug & 16)
@@ -344,10 +366,13 @@ constexpr int kOffRope = 0, kOffRed = 512, kOffMisc = 576, kOffRel = 704, kOffFu
 // each slice, its share | int [kHbMaxSlices]: slice fetched (owned by the slice's duty warp)
 constexpr int kOffHbFull = kOffEmpty + 8 * kMaxStages, kOffHbEmpty = kOffHbFull + 8 * kHbBufs;
 constexpr int kOffHbCnt = (kOffHbEmpty + 8 * kHbBufs + 63) / 64 * 64, kOffHbIssued = kOffHbCnt + 8 * kHbMaxSlices;
-constexpr int kOffStages = (kOffHbIssued + 4 * kHbMaxSlices + 127) / 128 * 128;
+// tensor-core GEMV (below): done / free mbarriers of the tiles' partial-sum slots
+constexpr int kOffMmaDone = (kOffHbIssued + 4 * kHbMaxSlices + 63) / 64 * 64, kOffMmaFree = kOffMmaDone + 8 * kMmaSlots;
+static_assert(kOffMmaFree + 8 * kMmaSlots <= kSmemHeader, "shared-memory header overflow");
+constexpr int kOffStages = kSmemHeader; // 1024-byte aligned: swizzled tensor copies land in the stages
 static_assert(kOffStages == kSmemHeader, "mega.h: kSmemHeader must match the kernel's shared-memory header");
 __device__ __forceinline__ unsigned char *sm_base() {
-	extern __shared__ __align__(128) unsigned char smem_raw[];
+	extern __shared__ __align__(1024) unsigned char smem_raw[];
 	return smem_raw;
 }
 __device__ __forceinline__ float2 *sm_rope() { return reinterpret_cast<float2 *>(sm_base() + kOffRope); } // cos/sin of pos * freq_j
@@ -355,6 +380,7 @@ __device__ __forceinline__ float *sm_red() { return reinterpret_cast<float *>(sm
 __device__ __forceinline__ int *sm_misc() { return reinterpret_cast<int *>(sm_base() + kOffMisc); }
 // sm_misc slots: [0] combine flag, [4, 4 + consumer warps) arg-max indices, [16..] parked context
 constexpr int kMiscToken = 16, kMiscPos = 17, kMiscPark = 18;
+constexpr int kMiscMmaTiles = 2; // tensor-core GEMV: the tile counter, parked across the attention unit loop
 // MoE router record (written by consumer thread 0 in the w1/w3 staging step, polled by the producer warp):
 // [kMiscRouter] = layer + 1 once [kMiscExpert + k] (ids) and [kMiscExpertW + k] (weights, as float bits) are set
 constexpr int kMiscRouter = 23, kMiscExpert = 24, kMiscExpertW = 28;
@@ -366,6 +392,8 @@ __device__ __forceinline__ uint32_t sm_hbfull0() { return smem_u32(sm_base() + k
 __device__ __forceinline__ uint32_t sm_hbempty0() { return smem_u32(sm_base() + kOffHbEmpty); }
 __device__ __forceinline__ int *sm_hb_cnt() { return reinterpret_cast<int *>(sm_base() + kOffHbCnt); }
 __device__ __forceinline__ volatile int *sm_hb_issued() { return reinterpret_cast<volatile int *>(sm_base() + kOffHbIssued); }
+__device__ __forceinline__ uint32_t sm_mma_done0() { return smem_u32(sm_base() + kOffMmaDone); }
+__device__ __forceinline__ uint32_t sm_mma_free0() { return smem_u32(sm_base() + kOffMmaFree); }
 __device__ __forceinline__ unsigned char *sm_stages() { return sm_base() + kOffStages; }
 __device__ __forceinline__ uint32_t sm_stages_u32() { return smem_u32(sm_base() + kOffStages); }
 
@@ -385,6 +413,7 @@ struct Ctx {
 	int rot;     // CTA rotation of the current GEMV phase
 	unsigned bar_gen;
 	unsigned xgen; // cross-GPU barriers passed, earlier launches included (tensor parallelism)
+	unsigned mt;   // tensor-core GEMV: tiles of this launch so far (same in every warp): slot and use count of a tile's partial sums
 	int kv_sink, kv_pos, kv_len; // token and pos: sm_misc()[kMiscToken], [kMiscPos]
 };
 
@@ -464,6 +493,49 @@ __device__ __forceinline__ bool attn_has_unit(int r, int nc, int nch) {
 	return nch >= nc || (unsigned)(r + 1) * nch / nc > (unsigned)r * nch / nc;
 }
 
+// ---- tensor-core GEMV: geometry (shared by the producer and the consumers) ---------------------------------------------
+// A phase multiplies up to three matrices (QKV) by the staged vector.  CTA c owns a contiguous block of each matrix's rows
+// (in units of 2 rows — RoPE and store pairs — or of 1 row of w1 AND of w3), cut into tiles of at most MT rows (MT = the
+// tensor map's box rows, planned so that the largest block splits evenly: 28 rows -> 2 x 14); a tile's K is walked in
+// stages of kMmaKCols columns.  Ring order: tile after tile, K stages inside; stage s of the phase belongs to warp s % W.
+struct MmaSub {
+	int map;        // tensor map record
+	int row0, nrows; // this CTA's rows of the matrix
+	int MT, nt;     // rows per tile, tiles
+	int goff;       // row offset of the matrix in the phase's output (q | k | v)
+};
+struct MmaPhase {
+	MmaSub sub[3];
+	int nsub, nkb, ntiles;
+	bool ffn; // w1 rows -> tile rows 0-7, the same rows of w3 -> tile rows 8-15 (second box at +4096 bytes)
+};
+__device__ __forceinline__ MmaPhase mma_phase(const Args &a, int kind, int layer, int cta, int ncta) {
+	MmaPhase p;
+	p.nsub = 1, p.ffn = false, p.nkb = a.dim / kMmaKCols;
+	const int mb = layer * kMmPerLayer;
+	auto set = [&](int i, int map, int rows, int unit, int MT, int goff) {
+		const int n = rows / unit;
+		const int u0 = (int)((long long)cta * n / ncta), u1 = (int)((long long)(cta + 1) * n / ncta);
+		p.sub[i].map = map, p.sub[i].row0 = u0 * unit, p.sub[i].nrows = (u1 - u0) * unit;
+		p.sub[i].MT = MT, p.sub[i].nt = (p.sub[i].nrows + MT - 1) / MT, p.sub[i].goff = goff;
+	};
+	p.sub[1].nt = p.sub[2].nt = 0;
+	switch (kind) {
+	case kQKV:
+		p.nsub = 3;
+		set(0, mb + kMmWq, a.q_dim, 2, a.mma_mt[0], 0);
+		set(1, mb + kMmWk, a.kv_dim, 2, a.mma_mt[1], a.q_dim);
+		set(2, mb + kMmWv, a.kv_dim, 2, a.mma_mt[1], a.q_dim + a.kv_dim);
+		break;
+	case kWO: set(0, mb + kMmWo, a.dim, 2, a.mma_mt[2], 0), p.nkb = a.q_dim / kMmaKCols; break;
+	case kFFN: set(0, mb + kMmW1, a.hidden, 1, a.mma_mt[3], 0), p.ffn = true; break;
+	case kW2: set(0, mb + kMmW2, a.dim, 2, a.mma_mt[4], 0), p.nkb = a.hidden / kMmaKCols; break;
+	default: set(0, a.n_layers * kMmPerLayer, a.vocab, 2, a.mma_mt[5], 0); break;
+	}
+	p.ntiles = p.sub[0].nt + p.sub[1].nt + p.sub[2].nt;
+	return p;
+}
+
 // ---- producer ---------------------------------------------------------------------------------------------
 // Ring order inside a GEMV phase: this CTA's groups in blocks of kConsumerWarps; inside a block the K-split index
 // is the slow axis and the group the fast one, so every consumer warp (one group each) has a tile in flight.
@@ -498,6 +570,9 @@ struct PhaseDesc {
 	int layer, sub, gpe;
 	size_t estride;
 	bool slice_major; // pipelined hb: w2 tiles in K-split-major order over ALL of the CTA's row groups
+	bool mma;         // tensor-core GEMV: tiles = (tile, K stage) of mp, one 3-D tensor copy each
+	MmaPhase mp;
+	const char *tmaps;
 };
 
 struct Producer {
@@ -514,7 +589,7 @@ struct Producer {
 		d.m0 = d.m1 = d.m2 = nullptr, d.rows0 = d.rows1 = d.K = 0, d.g_first = d.full_groups = d.full_tiles = d.nb_last = 0;
 		d.kc = d.vc = nullptr, d.nch = 1, d.u0 = 0;
 		d.sh.R = d.sh.KT = d.sh.nk = d.sh.G = 1;
-		d.layer = 0, d.sub = 0, d.gpe = 0, d.estride = 0, d.slice_major = false;
+		d.layer = 0, d.sub = 0, d.gpe = 0, d.estride = 0, d.slice_major = false, d.mma = false;
 		const int n_phases = a.n_layers * ppl_of(a) + (a.mode != kHydrate ? 1 : 0);
 		if (ph >= n_phases) return d;
 		int l, k, sub;
@@ -539,6 +614,11 @@ struct Producer {
 		case 4: d.kind = kW2, d.m0 = L.w2, d.rows0 = a.dim, d.K = a.hidden, d.slice_major = a.w2_pipe != 0; break;
 		case 5: d.kind = kLM, d.m0 = a.wcls, d.rows0 = a.vocab; break;
 		default: break;
+		}
+		if (a.mma) { // tensor-core GEMV: the phase's stages follow from its geometry
+			d.mma = true, d.mp = mma_phase(a, d.kind, l, c.cta, c.ncta), d.tmaps = static_cast<const char *>(a.tmaps);
+			d.ntiles = d.nunits = d.mp.ntiles * d.mp.nkb;
+			return d;
 		}
 		d.sh = shape_of(a, d.kind);
 		if (a.n_experts > 0 && (k == 3 || k == 4)) {
@@ -625,6 +705,21 @@ struct Producer {
 			bulk_g2s(dst, d.kc + off, bytes, bar, policy);
 			bulk_g2s(dst + kStageBytes / 2, d.vc + off, bytes, bar, policy);
 			return i;
+		}
+		if (d.mma) {
+			int T = i / d.mp.nkb;
+			const int kb = i - T * d.mp.nkb;
+			int m = 0;
+			if (T >= d.mp.sub[0].nt) T -= d.mp.sub[0].nt, m = 1;
+			if (m == 1 && T >= d.mp.sub[1].nt) T -= d.mp.sub[1].nt, m = 2;
+			const MmaSub sb = m == 0 ? d.mp.sub[0] : m == 1 ? d.mp.sub[1] : d.mp.sub[2];
+			const uint32_t box = 4u * (uint32_t)sb.MT * 128u;
+			uint32_t bar;
+			const uint32_t dst = acquire(ring_idx, d.mp.ffn ? 2 * box : box, &bar);
+			const int row = sb.row0 + T * sb.MT;
+			tma_load_3d(dst, d.tmaps + (size_t)sb.map * 128, 0, row, kb * (kMmaKCols / 64), bar, policy);
+			if (d.mp.ffn) tma_load_3d(dst + 4096, d.tmaps + (size_t)(sb.map + (kMmW3 - kMmW1)) * 128, 0, row, kb * (kMmaKCols / 64), bar, policy);
+			return -1;
 		}
 		int gl, kc;
 		if (d.slice_major) {
@@ -820,6 +915,28 @@ __device__ __forceinline__ void release(Ctx &c, uint32_t idx) {
 	}
 }
 
+// Four consecutive elements e .. e+3 (e % 4 == 0) of a phase's input vector -> shared memory.  SIMT path: fp32 in the
+// permuted layout of xs_slot.  Tensor-core GEMV: an fp16 hi + lo pair (x = hi + lo to 2^-22) in the order of the mma B
+// fragment: 16 bytes per (16-column k step, t) = [hi(2t, 2t+1) | hi(2t+8, 2t+9) | lo(2t, 2t+1) | lo(2t+8, 2t+9)], so that
+// thread (g, t) of a warp fetches its fragment of column g & 1 (hi or lo) with one 8-byte load.
+template <int EP>
+__device__ __forceinline__ void stage_store4(const Ctx &c, const Args &a, int e, float4 v) {
+	if (a.mma) {
+		const int ks = e >> 4, kk = e & 15; // kk in {0, 4, 8, 12}: elements kk, kk+1 -> t = (kk & 7) / 2, kk+2, kk+3 -> t + 1; same half
+		char *base = reinterpret_cast<char *>(c.vec) + (size_t)(ks * 4 + ((kk & 7) >> 1)) * 16 + (kk >> 3) * 4;
+		// hi is clamped to the fp16 range (lo then carries up to another 65504: |x| < 1.3e5 stays exact to 2^-22, beyond saturates)
+		const __half2 h01 = __floats2half2_rn(fminf(fmaxf(v.x, -65504.f), 65504.f), fminf(fmaxf(v.y, -65504.f), 65504.f));
+		const __half2 h23 = __floats2half2_rn(fminf(fmaxf(v.z, -65504.f), 65504.f), fminf(fmaxf(v.w, -65504.f), 65504.f));
+		const float2 f01 = __half22float2(h01), f23 = __half22float2(h23);
+		*reinterpret_cast<__half2 *>(base) = h01;
+		*reinterpret_cast<__half2 *>(base + 8) = __floats2half2_rn(v.x - f01.x, v.y - f01.y);
+		*reinterpret_cast<__half2 *>(base + 16) = h23;
+		*reinterpret_cast<__half2 *>(base + 24) = __floats2half2_rn(v.z - f23.x, v.w - f23.y);
+	} else {
+		*reinterpret_cast<float4 *>(c.vec + xs_slot<EP>(e)) = v;
+	}
+}
+
 // Input vector -> permuted shared layout (xs_slot).  embed_token < 0: fp32 vector in global memory (read through
 // L2: other CTAs wrote it during this launch); >= 0: that row of the weight-typed embedding table (layer 0).
 template <int DT>
@@ -876,16 +993,14 @@ __device__ __forceinline__ void stage_vec(Ctx &c, const Args &a, const float *sr
 			const int e = (c.tid + i * kCT) * 4;
 			if (e < n) {
 				const float4 v = cache[i], w = wv[i];
-				*reinterpret_cast<float4 *>(c.vec + xs_slot<EP>(e)) =
-				    make_float4(v.x * scale * w.x, v.y * scale * w.y, v.z * scale * w.z, v.w * scale * w.w);
+				stage_store4<EP>(c, a, e, make_float4(v.x * scale * w.x, v.y * scale * w.y, v.z * scale * w.z, v.w * scale * w.w));
 				if (seed_x) *reinterpret_cast<float4 *>(x_out + e) = v;
 			}
 		}
 		for (int e = (c.tid + NC * kCT) * 4; e < n; e += kCT * 4) {
 			const float4 v = load_in4<DT>(a, src, embed_token, e);
 			const float4 w = *reinterpret_cast<const float4 *>(rms_w + e);
-			*reinterpret_cast<float4 *>(c.vec + xs_slot<EP>(e)) =
-			    make_float4(v.x * scale * w.x, v.y * scale * w.y, v.z * scale * w.z, v.w * scale * w.w);
+			stage_store4<EP>(c, a, e, make_float4(v.x * scale * w.x, v.y * scale * w.y, v.z * scale * w.z, v.w * scale * w.w));
 			if (seed_x) *reinterpret_cast<float4 *>(x_out + e) = v;
 		}
 	} else {
@@ -895,10 +1010,10 @@ __device__ __forceinline__ void stage_vec(Ctx &c, const Args &a, const float *sr
 #pragma unroll
 			for (int i = 0; i < 4; ++i) v[i] = __ldcg(reinterpret_cast<const float4 *>(src + e + i * kCT * 4));
 #pragma unroll
-			for (int i = 0; i < 4; ++i) *reinterpret_cast<float4 *>(c.vec + xs_slot<EP>(e + i * kCT * 4)) = v[i];
+			for (int i = 0; i < 4; ++i) stage_store4<EP>(c, a, e + i * kCT * 4, v[i]);
 		}
 		for (; e < n; e += kCT * 4)
-			*reinterpret_cast<float4 *>(c.vec + xs_slot<EP>(e)) = __ldcg(reinterpret_cast<const float4 *>(src + e));
+			stage_store4<EP>(c, a, e, __ldcg(reinterpret_cast<const float4 *>(src + e)));
 	}
 	cbar();
 }
@@ -968,7 +1083,7 @@ __device__ __forceinline__ void stage_vec_ll(Ctx &c, const Args &a, const unsign
 #pragma unroll
 			for (int i = 0; i < NC; ++i) {
 				const int e = e0 + i * kCT * 4;
-				if (e < n) *reinterpret_cast<float4 *>(c.vec + xs_slot<EP>(e)) = cache[i];
+				if (e < n) stage_store4<EP>(c, a, e, cache[i]);
 			}
 		}
 	}
@@ -988,8 +1103,7 @@ __device__ __forceinline__ void stage_vec_ll(Ctx &c, const Args &a, const unsign
 						ll_load4(src + e, flag, &v); // validated in the first pass
 						w = *reinterpret_cast<const float4 *>(rms_w + e);
 					}
-					*reinterpret_cast<float4 *>(c.vec + xs_slot<EP>(e)) =
-					    make_float4(v.x * scale * w.x, v.y * scale * w.y, v.z * scale * w.z, v.w * scale * w.w);
+					stage_store4<EP>(c, a, e, make_float4(v.x * scale * w.x, v.y * scale * w.y, v.z * scale * w.z, v.w * scale * w.w));
 				}
 			}
 		}
@@ -1451,8 +1565,164 @@ __device__ __forceinline__ void w2_pipe_consume(Ctx &c, const Args &a, Epi &ep, 
 	c.rot = (c.rot + sh.G) % c.ncta;
 }
 
+// ---- tensor-core GEMV (fp16 dense models; Args::mma) -------------------------------------------------------------------
+// The SIMT tile loop above is at its floor — 63 instructions per 2 KB of fp16 weights, half of them fp16 -> fp32
+// conversions — and with three resident warps per scheduler it runs at 1.5x the rate HBM delivers, so every stall of a
+// phase boundary is paid in full.  Here the multiply-accumulate goes to the tensor cores:
+//   * a ring stage is a 16-row x 256-column tile of the row-major weight matrix, fetched by ONE 3-D tensor copy (64 columns
+//     x MT rows x 4 column blocks, SWIZZLE_128B): it lands as [column block][row][128 bytes] with the 16-byte chunks of every
+//     row XOR-ed with address bits 7-9, which makes the eight row addresses of an ldmatrix conflict-free;
+//   * x sits in shared memory as an fp16 hi + lo pair in B-fragment order (stage_store4): B column 0 = hi, column 1 = lo, so
+//     D[row][0] + D[row][1] = W x to 2^-22 relative, fp32 accumulation in the tensor core; the other six columns are ignored;
+//   * per 16-column k step: one ldmatrix.x4 (A), one 8-byte load (B), one mma.sync.m16n8k16 — 48 + addressing instructions per
+//     8 KB stage instead of 252;
+//   * the K stages of a tile go round the consumer warps (stage s -> warp s % W), every warp keeps its partial D in four
+//     registers while it stays on the tile, then parks the 16 row sums in slot (tile % kMmaSlots) and arrives on the slot's
+//     `done` mbarrier; the tile's owner warp (tile % W) adds the W partials in warp order — deterministic — and runs the same
+//     pair-wise epilogue as the SIMT path (gemv_epilogue<2>), then frees the slot.
+// Measured (Mistral-7B fp16, 4k context, one B200): tokens identical to the SIMT path and the reference; without
+// any copies a token takes 2.21 ms instead of 2.29 (452 vs 436 tok/s) — but the stream of 3-D tensor copies (7 KB in an 8 KB
+// stage, 512 contiguous bytes per row) runs 7 % below the 1-D row pieces (340 vs 367 tok/s with the arithmetic skipped on
+// both), so the whole token is 311 vs 326 tok/s: the path is opt-in (YALM_MEGA_MMA=1), not the default.
+// Rows past the CTA's block inside its last tile belong to the next CTA, which computes them itself: they are fetched twice
+// (+1 % of the bytes at MT = 14) and masked here.  w1/w3: tile rows 0-7 are rows of w1, rows 8-15 the same rows of w3, so the
+// gate and the up value of an hb element meet in one thread.
+// Epilogue of one tile, lane-parallel (fp16 dense models on one GPU: no row scales, no experts, no mailboxes): y = the row
+// sums in lanes 0-15 (w1/w3: gate rows in lanes 0-7, up rows in lanes 8-15), vr valid rows from row `row_t` of matrix m.
+// Same arithmetic as gemv_epilogue, one item per lane instead of one call per row pair.  `resid`: see the call site.
+__device__ __forceinline__ void mma_epilogue(Ctx &c, const Args &a, Epi &ep, int m, int row_t, int vr, float y, float resid, unsigned wflag) {
+	const int lane = c.lane, kind = ep.kind;
+	if (kind == kFFN) { // lane = replica * 8 + element
+		const int p = lane & 7, rp = lane >> 3;
+		const float gate = __shfl_sync(kFull, y, p), up = __shfl_sync(kFull, y, 8 + p);
+		if (p < vr && rp < kLLRep) {
+			const float gt = a.act == YALM_ACT_GELU ? act_gelu(gate) : act_silu(gate);
+			const long row = row_t + p;
+			if (rp == 0) a.hb[row] = gt * up;
+			ll_store(a.ll_hb + (size_t)rp * a.hb_len + row, gt * up, wflag);
+		}
+	} else if (kind == kQKV) { // lane = row pair
+		float v0 = __shfl_sync(kFull, y, (2 * lane) & 31), v1 = __shfl_sync(kFull, y, (2 * lane + 1) & 31);
+		if (2 * lane < vr) {
+			const int row = row_t + 2 * lane, hd = a.head_dim, j = row % hd; // row inside wq (m 0) / wk (1) / wv (2)
+			v0 = clipf(v0, a.clip), v1 = clipf(v1, a.clip);
+			if (m < 2) { // interleaved-pair RoPE (src/infer.cpp:200-213), cos/sin from the per-token table
+				const float2 cs = sm_rope()[j >> 1];
+				const float r0 = v0 * cs.x - v1 * cs.y, r1 = v0 * cs.y + v1 * cs.x;
+				v0 = r0, v1 = r1;
+			}
+			if (m == 0) {
+				*reinterpret_cast<float2 *>(a.q + row) = make_float2(v0, v1);
+			} else {
+				__half *cache = reinterpret_cast<__half *>(m == 1 ? ep.L->kc : ep.L->vc);
+				*reinterpret_cast<__half2 *>(cache + ((size_t)(row / hd) * a.max_seq_len + c.kv_pos) * hd + j) = __floats2half2_rn(v0, v1);
+			}
+		}
+	} else if (kind == kLM) { // lane = row
+		if (lane < vr) {
+			const int row = row_t + lane;
+			a.logits[row] = y;
+			if (y > ep.best_v) ep.best_v = y, ep.best_i = row; // a lane's rows ascend: first maximum wins
+		}
+	} else { // wo / w2: x += W v (src/infer.cpp:335-337); lane = (replica & 1) * 16 + row, two passes over the replicas
+		const int r = lane & 15;
+		const float xn = resid + __shfl_sync(kFull, y, r);
+		if (r < vr) {
+			const long row = row_t + r;
+			unsigned long long *dst = a.ll_x + (size_t)(kind == kW2 ? kLLRep : 0) * a.dim + row;
+#pragma unroll
+			for (int rp = lane >> 4; rp < kLLRep; rp += 2) ll_store(dst + (size_t)rp * a.dim, xn, wflag);
+			if (kind == kW2 && lane < 16) a.x[row] = xn;
+		}
+	}
+}
+
+template <int DT, bool TP>
+__device__ __forceinline__ void mma_consume(Ctx &c, const Args &a, Epi &ep, int ph) {
+	constexpr int W = kConsumerWarps;
+	const unsigned wflag = ll_flag(a.seq, ph + 1);
+	const int lane = c.lane, warp = c.warp, g8 = lane >> 2, t4 = lane & 3;
+	const MmaPhase mp = mma_phase(a, ep.kind, ep.layer, c.cta, c.ncta);
+	const uint32_t base = c.it;
+	float *part = c.vec + (a.vec_floats - kMmaSlots * W * 16); // [slot][warp][16 rows]
+	// ldmatrix geometry of this lane: matrix lane / 8 = a0..a3 = (rows 0-7 | 8-15) x (k 0-7 | 8-15); it supplies one row address
+	const int mi = lane >> 3, arow = (lane & 7) + ((mi & 1) << 3), kch = mi >> 1;
+	const uint32_t xb = c.vec_u32 + (uint32_t)t4 * 16 + (uint32_t)(g8 & 1) * 8; // B fragment of column g8 & 1 (hi | lo)
+	int T = 0;
+	for (int m = 0; m < mp.nsub; ++m) {
+		const MmaSub sb = m == 0 ? mp.sub[0] : m == 1 ? mp.sub[1] : mp.sub[2];
+		const uint32_t rstride = (uint32_t)sb.MT * 128; // one column block of the box
+		const uint32_t roff = mp.ffn ? (arow < 8 ? 0u : 4096u) + (uint32_t)(arow & 7) * 128 : (uint32_t)arow * 128;
+		for (int t = 0; t < sb.nt; ++t, ++T) {
+			float acc[4][4]; // four independent accumulator sets (k step % 4): a single set is one dependent chain of 16 mma per stage
+#pragma unroll
+			for (int q = 0; q < 4; ++q)
+#pragma unroll
+				for (int i = 0; i < 4; ++i) acc[q][i] = 0.f;
+			const int s0 = T * mp.nkb;
+			for (int kb = (warp - s0 % W + W) % W; kb < mp.nkb; kb += W) {
+				uint32_t slot;
+				const unsigned char *tile = wait_tile(c, base + (uint32_t)(s0 + kb), &slot);
+				if (!(a.debug & 1)) {
+					const uint32_t tb = tile_u32(c, tile) + roff, xk = xb + (uint32_t)kb * (kMmaKCols / 16 * 64);
+#pragma unroll
+					for (int j = 0; j < 4; ++j) {
+						const uint32_t ra = tb + j * rstride, sw = (ra >> 7) & 7u;
+#pragma unroll
+						for (int q = 0; q < 4; ++q) { // k step 4 j + q: 16-byte chunks 2 q (k 0-7) and 2 q + 1 (k 8-15) of column block j
+							uint32_t A[4];
+							ldmatrix_x4(A, ra + ((((uint32_t)(2 * q + kch)) ^ sw) << 4));
+							const uint2 B = lds64(xk + (uint32_t)(4 * j + q) * 64);
+							mma16816(acc[q], A, B.x, B.y);
+						}
+					}
+				}
+				release(c, slot);
+			}
+			// park this warp's 16 row sums (zero if it had no stage of the tile) and report
+			const unsigned Tg = c.mt + (unsigned)T, ps = Tg % kMmaSlots, use = Tg / kMmaSlots;
+			if (use > 0) mbar_wait(sm_mma_free0() + 8 * ps, (use - 1) & 1u); // the slot's previous tile has been summed
+			float *pp = part + (ps * W + warp) * 16;
+			if (t4 == 0) { // columns 0 (W hi) + 1 (W lo) of rows g8 and g8 + 8
+				pp[g8] = ((acc[0][0] + acc[0][1]) + (acc[1][0] + acc[1][1])) + ((acc[2][0] + acc[2][1]) + (acc[3][0] + acc[3][1]));
+				pp[g8 + 8] = ((acc[0][2] + acc[0][3]) + (acc[1][2] + acc[1][3])) + ((acc[2][2] + acc[2][3]) + (acc[3][2] + acc[3][3]));
+			}
+			__syncwarp();
+			if (lane == 0) mbar_arrive(sm_mma_done0() + 8 * ps);
+			if (Tg % W != (unsigned)warp) continue;
+			// ---- owner of the tile: sum the partials in warp order, then the lane-parallel epilogue ----------------------
+			const int row_t = sb.row0 + t * sb.MT, vr = min(sb.MT, sb.nrows - t * sb.MT);
+			// residual operand of wo / w2 (lane & 15 = row), in flight across the wait: x after wo lives in ll_x[0] (the replica
+			// this CTA verified when it staged w1/w3), x before wo is the plain copy written behind w2 of the layer before
+			float resid = 0.f;
+			if ((ep.kind == kWO || ep.kind == kW2) && (lane & 15) < vr) {
+				const long row = row_t + (lane & 15);
+				resid = ep.kind == kW2 ? ll_val(ll_load1(a.ll_x + (size_t)(c.cta % kLLRep) * a.dim + row)) : __ldcg(a.x + row);
+			}
+			mbar_wait(sm_mma_done0() + 8 * ps, use & 1u);
+			float y = 0.f;
+			if (lane < 16) {
+				const float *q = part + ps * W * 16 + lane;
+#pragma unroll
+				for (int w = 0; w < W; ++w) y += q[w * 16];
+			}
+			__syncwarp();
+			if (lane == 0) mbar_arrive(sm_mma_free0() + 8 * ps);
+			mma_epilogue(c, a, ep, m, row_t, vr, y, resid, wflag);
+		}
+	}
+	c.mt += (unsigned)mp.ntiles;
+	c.it = base + (uint32_t)(mp.ntiles * mp.nkb);
+}
+
 template <int DT, bool TP>
 __device__ __forceinline__ void gemv_phase(Ctx &c, const Args &a, Epi &ep, int ph) {
+	if constexpr (DT == YALM_F16 && !TP) {
+		if (a.mma) {
+			mma_consume<DT, TP>(c, a, ep, ph);
+			return;
+		}
+	}
 	const int R = a.shape[ep.kind][0];
 	if (a.w2_pipe && ep.kind == kW2) { // plan(): R <= 2
 		if (R == 2) w2_pipe_consume<DT, 2, TP>(c, a, ep, ph);
@@ -1701,7 +1971,7 @@ __device__ __forceinline__ void attention_consume(Ctx &c, const Args &a, const L
 	// (the alternative is the compiler spilling inside the loop, and local memory is an L2 round trip here).
 	volatile int *pk = sm_misc() + kMiscPark;
 	if (c.tid == 0) {
-		pk[0] = c.rot, pk[1] = (int)c.bar_gen, pk[2] = (int)c.xgen;
+		pk[0] = c.rot, pk[1] = (int)c.bar_gen, pk[2] = (int)c.xgen, sm_misc()[kMiscMmaTiles] = (int)c.mt;
 		pk[3] = (int)(unsigned)((unsigned long long)c.prof), pk[4] = (int)(unsigned)((unsigned long long)c.prof >> 32);
 	}
 	for (int i = warp; i < NU; i += W) {
@@ -1816,7 +2086,7 @@ __device__ __forceinline__ void attention_consume(Ctx &c, const Args &a, const L
 	}
 	if (warp < NU) park();
 	cbar();
-	c.rot = pk[0], c.bar_gen = (unsigned)pk[1], c.xgen = (unsigned)pk[2];
+	c.rot = pk[0], c.bar_gen = (unsigned)pk[1], c.xgen = (unsigned)pk[2], c.mt = (unsigned)sm_misc()[kMiscMmaTiles];
 	c.prof = reinterpret_cast<long long *>((unsigned long long)(unsigned)pk[3] | (unsigned long long)(unsigned)pk[4] << 32);
 	stamp(c, layer, 1, 5);
 
@@ -1959,7 +2229,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_c
 	c.cta = blockIdx.x, c.ncta = gridDim.x;
 	c.tid = threadIdx.x, c.warp = threadIdx.x >> 5, c.lane = threadIdx.x & 31;
 	c.it = 0, c.rot = 0, c.bar_gen = 0;
-	c.xgen = 0;
+	c.xgen = 0, c.mt = 0;
 	if (TP) c.xgen = *reinterpret_cast<const volatile unsigned *>(a.tp_peer[a.tp_rank] + kTpOffGen); // written by the previous launch
 	c.prof = a.prof ? a.prof + (size_t)blockIdx.x * a.n_layers * kProfPhases * kProfSlots : nullptr;
 #ifdef YALM_MEGA_TRACE
@@ -1981,6 +2251,10 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_c
 		for (int i = 0; i < kHbBufs; ++i) {
 			mbar_init(sm_hbfull0() + 8 * i, 1);
 			mbar_init(sm_hbempty0() + 8 * i, kConsumerWarps);
+		}
+		for (int i = 0; i < kMmaSlots; ++i) {
+			mbar_init(sm_mma_done0() + 8 * i, kConsumerWarps);
+			mbar_init(sm_mma_free0() + 8 * i, 1);
 		}
 		asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
 	}

@@ -19,12 +19,18 @@ constexpr int kConsumerWarps = 11;
 constexpr int kProducerWarps = 1; // all 32 lanes issue: lane l takes tile l of each batch of min(stages, 32) tiles
 constexpr int kThreads = (kConsumerWarps + kProducerWarps) * 32;
 constexpr int kMaxStages = 24;
-constexpr int kSmemHeader = 1536; // rope table, reduction scratch, release counters, mbarriers in front of the ring
+constexpr int kSmemHeader = 2048; // (a multiple of 1024: the ring stages are 1024-byte aligned for swizzled tensor copies) // rope table, reduction scratch, release counters, mbarriers in front of the ring
 // Pipelined w1/w3 -> w2 hand-over (dense models, Args::w2_pipe; decode_mega.cuh "pipelined hb"): hb travels as plain fp32
 // in the permuted shared-memory layout, sliced by the K splits of w2; each slice has a completion counter and is pulled
 // into one of kHbBufs shared-memory buffers by a bulk copy; w2 walks its tiles K-split-major, so a warp carries the
 // partial sums of all its row groups (at most kHbMaxGroups) across the slices.
 constexpr int kHbMaxSlices = 16, kHbBufs = 4, kHbMaxGroups = 3;
+// Tensor-core GEMV (fp16 dense models, Args::mma; decode_mega.cuh "tensor-core GEMV"): a ring stage holds 16-row tiles of
+// 256 columns fetched with ONE 3-D tensor copy (64 columns x MT rows x 4 column blocks, SWIZZLE_128B) and is multiplied
+// with mma.sync.m16n8k16 against x kept as an fp16 hi + lo pair; the K stages of a tile are spread over the consumer warps
+// and summed in warp order through kMmaSlots partial slots in shared memory.
+constexpr int kMmaKCols = 256, kMmaSlots = 8;
+enum MmaMat { kMmWq = 0, kMmWk, kMmWv, kMmWo, kMmW1, kMmW2, kMmW3, kMmPerLayer }; // tensor map l * kMmPerLayer + i; the LM head's is last
 constexpr int kTraceEvents = 1 << 16;
 // Mixture of experts (Mixtral: 8 experts, 2 active; the reference has MoE on the CPU only, src/infer.cpp:100-132, 347-384;
 // its CUDA path asserts, src/infer.cu:865-867).  The router runs in the staging step of the w1/w3 phase (every CTA
@@ -122,6 +128,10 @@ struct Args {
 	float *hbp;
 	unsigned *hb_cnt;
 	int w2_pipe, hb_slice, hb_off;
+	// tensor-core GEMV (mma != 0): 128-byte CUtensorMap records (MmaMat order per layer, LM head last); box rows per matrix
+	// class: [0] wq [1] wk / wv [2] wo [3] w1 / w3 (rows of each) [4] w2 [5] LM head
+	const void *tmaps;
+	int mma, mma_mt[6];
 	char *tp_peer[kTpMaxWorld]; // every rank's region (kTpOff*), [tp_rank] = this rank's own
 };
 
@@ -130,6 +140,7 @@ struct Plan {
 	int dtype = 0, grid = 0, stages = 0, vec_floats = 0;
 	bool tp = false;
 	int w2_pipe = 0, hb_slice = 0, hb_off = 0; // pipelined hb (Args)
+	int mma = 0, mma_mt[6] = {}; // tensor-core GEMV (Args)
 	size_t smem = 0;
 	const void *kernel = nullptr;
 	int shape[5][4] = {};
@@ -143,6 +154,9 @@ Plan plan(int dtype, int dim, int q_dim, int kv_dim, int head_dim, int hidden, i
 size_t attn_ws_floats(int grid, int n_heads, int head_dim);
 // One token.  Returns a cudaError_t.
 int launch(const Plan &p, const Args &a, cudaStream_t st);
+// Tensor-core GEMV: tensor map (128 bytes at `map128`) of a (rows, K) row-major fp16 matrix on the device for boxes of
+// 64 columns x box_rows rows x 4 column blocks, 128-byte swizzle, zero fill past the last row.  Returns 0 or YALM_EINVAL.
+int make_weight_map(void *map128, const void *dev_ptr, int rows, int K, int box_rows);
 // Failure record of the kernel's timeouts (decode_mega.cuh: die): 8 words of pinned, device-mapped host memory, all zero
 // while nothing has gone wrong.  describe_fault() formats it ("" if clean); fault_timeout_cycles(): YALM_MEGA_TIMEOUT_S.
 unsigned *fault_record();

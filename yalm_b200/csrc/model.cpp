@@ -630,7 +630,11 @@ void Model::cuda(int device, int tp_rank, int tp_size) {
 struct Model::MegaState {
 	yalm::mega::Plan plan;
 	yalm::mega::Layer *layers = nullptr; // device
-	~MegaState() { cudaFree(layers); }
+	void *tmaps = nullptr;               // device: tensor maps of the weight matrices (tensor-core GEMV)
+	~MegaState() {
+		cudaFree(layers);
+		cudaFree(tmaps);
+	}
 };
 
 void Model::plan_mega() {
@@ -663,14 +667,37 @@ void Model::plan_mega() {
 	}
 	CUDA_CHECK(cudaMalloc((void **)&ms->layers, sizeof(yalm::mega::Layer) * host.size()));
 	CUDA_CHECK(cudaMemcpy(ms->layers, host.data(), sizeof(yalm::mega::Layer) * host.size(), cudaMemcpyHostToDevice));
+	if (ms->plan.mma) { // tensor-core GEMV: one tensor map per weight matrix (mega.h: MmaMat order per layer, LM head last)
+		using namespace yalm::mega;
+		const int q_dim = c.local_heads() * c.head_dim, kv_dim = c.local_kv_heads() * c.head_dim, hid = c.local_hidden();
+		std::vector<unsigned char> maps((host.size() * kMmPerLayer + 1) * 128);
+		bool ok = true;
+		for (size_t i = 0; i < host.size(); ++i) {
+			const Layer &L = host[i];
+			unsigned char *m = maps.data() + i * kMmPerLayer * 128;
+			const int *mt = ms->plan.mma_mt;
+			ok = ok && make_weight_map(m + kMmWq * 128, L.wq, q_dim, c.dim, mt[0]) == 0 && make_weight_map(m + kMmWk * 128, L.wk, kv_dim, c.dim, mt[1]) == 0 &&
+			     make_weight_map(m + kMmWv * 128, L.wv, kv_dim, c.dim, mt[1]) == 0 && make_weight_map(m + kMmWo * 128, L.wo, c.dim, q_dim, mt[2]) == 0 &&
+			     make_weight_map(m + kMmW1 * 128, L.w1, hid, c.dim, mt[3]) == 0 && make_weight_map(m + kMmW3 * 128, L.w3, hid, c.dim, mt[3]) == 0 &&
+			     make_weight_map(m + kMmW2 * 128, L.w2, c.dim, hid, mt[4]) == 0;
+		}
+		ok = ok && make_weight_map(maps.data() + host.size() * kMmPerLayer * 128, wcls, c.local_vocab(), c.dim, ms->plan.mma_mt[5]) == 0;
+		if (!ok) {
+			std::cerr << "FATAL: tensor maps for the tensor-core GEMV could not be encoded" << std::endl;
+			abort();
+		}
+		CUDA_CHECK(cudaMalloc((void **)&ms->tmaps, maps.size()));
+		CUDA_CHECK(cudaMemcpy(ms->tmaps, maps.data(), maps.size(), cudaMemcpyHostToDevice));
+	}
 	_mega = ms;
 	_mega_ok = true;
 }
 
-int Model::mega_info(int *out4) const {
+int Model::mega_info(int *out8) const {
 	if (!_mega_ok) return YALM_EINVAL;
 	const yalm::mega::Plan &p = _mega->plan;
-	out4[0] = p.stages, out4[1] = p.vec_floats, out4[2] = p.w2_pipe, out4[3] = p.shape[3][2];
+	out8[0] = p.stages, out8[1] = p.vec_floats, out8[2] = p.w2_pipe, out8[3] = p.shape[3][2], out8[4] = p.mma;
+	out8[5] = out8[6] = out8[7] = 0;
 	return 0;
 }
 
@@ -745,6 +772,7 @@ int Model::launch_mega(InferenceState &s, int token, int pos, int mode, long lon
 	a.seq = c.tp_size > 1 ? ++tp_seq : s.next_mega_seq();
 	a.w2_tmp = s.mega_tmp();
 	a.hbp = s.mega_hbp(), a.hb_cnt = s.mega_hb_cnt();
+	a.tmaps = _mega->tmaps;
 	a.ctl = s.ctl(), a.tokens_out = s.tokens_dev();
 	a.token = token, a.pos = pos, a.mode = mode;
 	return yalm::mega::launch(_mega->plan, a, s.stream());

@@ -275,7 +275,7 @@ struct Model {
 	// the per-op kernel graph: unsharded dense models whose shapes the tile planner accepts.  Set
 	// YALM_B200_MEGA=0 in the environment before cuda() to force the per-op path.
 	bool uses_megakernel() const { return _mega_ok; }
-	int mega_info(int *out4) const; // {ring stages, vec floats, pipelined hb, K splits of w2}; YALM_EINVAL without the megakernel
+	int mega_info(int *out8) const; // {ring stages, vec floats, pipelined hb, K splits of w2, tensor-core GEMV, 0, 0, 0}; YALM_EINVAL without the megakernel
 	// One forward pass with the kernel's phase profile on: clock64 stamps per (CTA, layer, phase, slot), see
 	// decode_mega.cuh.  out == null: only *grid is returned.
 	int mega_profile(InferenceState &s, int token, int pos, long long *out, size_t count, int *grid);
