@@ -12,7 +12,7 @@ EXTRA ?=
 NVFLAGS := -std=c++17 -O3 -lineinfo $(EXTRA) $(ARCH) -ccbin $(HOSTCXX) -Xcompiler -fPIC,-Wall,-fopenmp -Iinclude
 LIB   := yalm_b200/libyalm_b200.so
 
-LIB_SRCS := $(CSRC)/ops_gemv.cu $(CSRC)/ops_attn.cu $(CSRC)/decode_mega.cu $(CSRC)/decode_mega_f32.cu $(CSRC)/decode_mega_f16.cu $(CSRC)/decode_mega_f8.cu $(CSRC)/model.cpp $(CSRC)/codec.cpp $(CSRC)/capi.cpp \
+LIB_SRCS := $(CSRC)/ops_gemv.cu $(CSRC)/ops_attn.cu $(CSRC)/decode_mega.cu $(CSRC)/decode_mega_f32.cu $(CSRC)/decode_mega_f16.cu $(CSRC)/decode_mega_f8.cu $(CSRC)/decode_mega_f32_pipe.cu $(CSRC)/decode_mega_f16_pipe.cu $(CSRC)/decode_mega_f8_pipe.cu $(CSRC)/decode_mega_f16_mma.cu $(CSRC)/model.cpp $(CSRC)/codec.cpp $(CSRC)/capi.cpp \
             $(CSRC)/mem.cpp $(CSRC)/tp.cpp $(CSRC)/loader.cpp $(CSRC)/prefill_gemm.cu $(CSRC)/prefill.cu $(CSRC)/ops_sample.cu $(CSRC)/sampler.cpp $(CSRC)/tokenizer.cpp
 LIB_OBJS := $(patsubst $(CSRC)/%,$(BUILD)/%.o,$(LIB_SRCS))
 HDRS := $(wildcard $(CSRC)/*.h $(CSRC)/*.cuh include/*.h)

@@ -128,12 +128,18 @@ size_t attn_ws_floats(int grid, int n_heads, int head_dim) {
 const void *kernel_f32(int head_dim, int g, bool tp);
 const void *kernel_f16(int head_dim, int g, bool tp);
 const void *kernel_f8(int head_dim, int g, bool tp);
+const void *kernel_f32_pipe(int head_dim, int g, bool tp);
+const void *kernel_f16_pipe(int head_dim, int g, bool tp);
+const void *kernel_f8_pipe(int head_dim, int g, bool tp);
+const void *kernel_f16_mma(int head_dim, int g, bool tp);
 
-static const void *kernel_of(int dtype, int head_dim, int g, bool tp) {
+// variant: 0 default, 1 pipelined hb, 2 tensor-core GEMV (decode_mega.cuh: gemv_phase); null if not compiled
+static const void *kernel_of(int dtype, int head_dim, int g, bool tp, int variant) {
 	switch (dtype) {
-	case YALM_F32: return kernel_f32(head_dim, g, tp);
-	case YALM_F16: return kernel_f16(head_dim, g, tp);
-	case YALM_F8E4M3: return kernel_f8(head_dim, g, tp);
+	case YALM_F32: return variant == 0 ? kernel_f32(head_dim, g, tp) : variant == 1 ? kernel_f32_pipe(head_dim, g, tp) : nullptr;
+	case YALM_F16:
+		return variant == 0 ? kernel_f16(head_dim, g, tp) : variant == 1 ? kernel_f16_pipe(head_dim, g, tp) : kernel_f16_mma(head_dim, g, tp);
+	case YALM_F8E4M3: return variant == 0 ? kernel_f8(head_dim, g, tp) : variant == 1 ? kernel_f8_pipe(head_dim, g, tp) : nullptr;
 	}
 	return nullptr;
 }
@@ -168,8 +174,7 @@ Plan plan(int dtype, int dim, int q_dim, int kv_dim, int head_dim, int hidden, i
 	if (!ep) return p;
 	if (n_kv_heads <= 0 || n_heads % n_kv_heads) return p;
 	const int G = n_heads / n_kv_heads;
-	p.kernel = kernel_of(dtype, head_dim, G, tp);
-	if (!p.kernel) return p;
+	if (!kernel_of(dtype, head_dim, G, tp, 0)) return p;
 	if (dim % ep || q_dim % ep || hidden % ep || dim % 4 || q_dim % 4 || hidden % 4) return p;
 	if (!plan_shapes(dtype, dim, q_dim, kv_dim, hidden, vocab, n_sub, p.shape)) return p;
 	const DeviceInfo &di = device_info();
@@ -225,11 +230,13 @@ Plan plan(int dtype, int dim, int q_dim, int kv_dim, int head_dim, int hidden, i
 		const char *e = getenv("YALM_MEGA_W2_PIPE");
 		const int nk = p.shape[kW2][2], groups = (p.shape[kW2][3] + di.sms - 1) / std::max(1, di.sms);
 		const int hb_off = std::max(padded(dim, ep), padded(q_dim, ep)), vf_pipe = hb_off + kHbBufs * p.shape[kW2][1];
-		const bool can = !p.mma && n_experts == 0 && nk >= 2 && nk <= kHbMaxSlices && p.shape[kW2][0] <= 2 &&
+		const bool can = !p.mma && !tp && n_experts == 0 && nk >= 2 && nk <= kHbMaxSlices && p.shape[kW2][0] <= 2 &&
 		                 (groups + kConsumerWarps - 1) / kConsumerWarps <= kHbMaxGroups && stages_for(vf_pipe) >= 2;
-		const bool want = e ? atoi(e) != 0 : !tp && stages_for(vf_pipe) >= stages_for(vf) + 2; // tensor parallel: only on request
+		const bool want = e ? atoi(e) != 0 : stages_for(vf_pipe) >= stages_for(vf) + 2;
 		if (can && want) p.w2_pipe = 1, p.hb_slice = p.shape[kW2][1], p.hb_off = hb_off, vf = vf_pipe;
 	}
+	p.kernel = kernel_of(dtype, head_dim, G, tp, p.mma ? 2 : p.w2_pipe ? 1 : 0);
+	if (!p.kernel) return p;
 	p.vec_floats = (std::max(vf, vf_attn) + 31) / 32 * 32;
 	const size_t fixed = (size_t)p.vec_floats * 4 + kSmemHeader;
 	p.stages = stages_for(vf);

@@ -583,6 +583,7 @@ struct Producer {
 	bool steady; // false: only the next phase's prefix is fetched (during the phase-boundary bubble), nothing in-phase
 	bool pf_tma; // L2 look-ahead through cp.async.bulk.prefetch.L2 (one request per range) instead of per-line prefetches
 
+	template <int V>
 	__device__ __forceinline__ PhaseDesc describe(const Args &a, int ph, int rot, int HD, int B) {
 		PhaseDesc d;
 		d.kind = kNone, d.ntiles = 0, d.nunits = 0, d.unit_bytes = kStageBytes, d.rot_next = rot, d.tile_bytes = 0;
@@ -611,11 +612,11 @@ struct Producer {
 		switch (k) {
 		case 2: d.kind = kWO, d.m0 = L.wo, d.rows0 = a.dim, d.K = a.q_dim; break;
 		case 3: d.kind = kFFN, d.m0 = L.w1, d.m1 = L.w3, d.rows0 = a.hidden; break;
-		case 4: d.kind = kW2, d.m0 = L.w2, d.rows0 = a.dim, d.K = a.hidden, d.slice_major = a.w2_pipe != 0; break;
+		case 4: d.kind = kW2, d.m0 = L.w2, d.rows0 = a.dim, d.K = a.hidden, d.slice_major = V == 1; break;
 		case 5: d.kind = kLM, d.m0 = a.wcls, d.rows0 = a.vocab; break;
 		default: break;
 		}
-		if (a.mma) { // tensor-core GEMV: the phase's stages follow from its geometry
+		if (V == 2) { // tensor-core GEMV: the phase's stages follow from its geometry
 			d.mma = true, d.mp = mma_phase(a, d.kind, l, c.cta, c.ncta), d.tmaps = static_cast<const char *>(a.tmaps);
 			d.ntiles = d.nunits = d.mp.ntiles * d.mp.nkb;
 			return d;
@@ -694,6 +695,7 @@ struct Producer {
 	}
 	// Tile i of phase d -> ring index ring_idx (waits for its stage).  Returns the tile's look-ahead unit, or -1 if
 	// the tile is not the first of its unit.
+	template <int V>
 	__device__ __forceinline__ int tile(const PhaseDesc &d, int i, uint32_t ring_idx, int HD, int max_seq, int B) {
 		if (d.kind == kAttn) {
 			const int u = d.u0 + i, kvh = u / d.nch, r0 = (u % d.nch) * (kStageBytes / (4 * HD));
@@ -706,7 +708,7 @@ struct Producer {
 			bulk_g2s(dst + kStageBytes / 2, d.vc + off, bytes, bar, policy);
 			return i;
 		}
-		if (d.mma) {
+		if (V == 2 && d.mma) {
 			int T = i / d.mp.nkb;
 			const int kb = i - T * d.mp.nkb;
 			int m = 0;
@@ -722,7 +724,7 @@ struct Producer {
 			return -1;
 		}
 		int gl, kc;
-		if (d.slice_major) {
+		if (V == 1 && d.slice_major) {
 			kc = i / d.nunits, gl = i - kc * d.nunits;
 		} else if (i < d.full_tiles) {
 			const int r = i % (kConsumerWarps * d.sh.nk);
@@ -784,12 +786,13 @@ struct Producer {
 	}
 	// Every phase of the token, in order (phase -1 is empty: it only fetches the prefix of phase 0).
 	// `ahead` is in ring stages (kStageBytes); per phase it becomes a whole number of look-ahead units.
+	template <int V>
 	__device__ __forceinline__ void run(const Args &a, int HD, int B) {
 		const int n_phases = a.n_layers * ppl_of(a) + (a.mode != kHydrate ? 1 : 0);
 		const uint32_t ahead_bytes = (uint32_t)ahead * kStageBytes;
-		PhaseDesc cur = describe(a, n_phases, 0, HD, B); // kNone
+		PhaseDesc cur = describe<V>(a, n_phases, 0, HD, B); // kNone
 		for (int ph = -1; ph < n_phases; ++ph) {
-			const PhaseDesc nxt = describe(a, ph + 1, cur.rot_next, HD, B);
+			const PhaseDesc nxt = describe<V>(a, ph + 1, cur.rot_next, HD, B);
 			const int n = cur.ntiles, nu = cur.nunits;
 			const int dist = (int)max(1u, ahead_bytes / cur.unit_bytes);                         // look-ahead of this phase, in its units
 			const int npre = ahead > 0 ? min((int)max(1u, ahead_bytes / nxt.unit_bytes), nxt.nunits) : 0; // prefix of the next phase fetched here
@@ -799,7 +802,7 @@ struct Producer {
 			for (int t0 = 0; t0 < n_eff; t0 += nb) {
 				const int i = t0 + c.lane;
 				if (c.lane < nb && i < n_eff) {
-					const int unit = n > 0 ? tile(cur, i, c.it + (uint32_t)i, HD, a.max_seq_len, B) : i;
+					const int unit = n > 0 ? tile<V>(cur, i, c.it + (uint32_t)i, HD, a.max_seq_len, B) : i;
 					if (ahead > 0 && unit >= 0) {
 						if (unit + dist < nu) {
 							if (steady) prefetch_unit(cur, unit + dist, HD, a.max_seq_len, B);
@@ -919,9 +922,9 @@ __device__ __forceinline__ void release(Ctx &c, uint32_t idx) {
 // permuted layout of xs_slot.  Tensor-core GEMV: an fp16 hi + lo pair (x = hi + lo to 2^-22) in the order of the mma B
 // fragment: 16 bytes per (16-column k step, t) = [hi(2t, 2t+1) | hi(2t+8, 2t+9) | lo(2t, 2t+1) | lo(2t+8, 2t+9)], so that
 // thread (g, t) of a warp fetches its fragment of column g & 1 (hi or lo) with one 8-byte load.
-template <int EP>
+template <int EP, int V>
 __device__ __forceinline__ void stage_store4(const Ctx &c, const Args &a, int e, float4 v) {
-	if (a.mma) {
+	if (V == 2) {
 		const int ks = e >> 4, kk = e & 15; // kk in {0, 4, 8, 12}: elements kk, kk+1 -> t = (kk & 7) / 2, kk+2, kk+3 -> t + 1; same half
 		char *base = reinterpret_cast<char *>(c.vec) + (size_t)(ks * 4 + ((kk & 7) >> 1)) * 16 + (kk >> 3) * 4;
 		// hi is clamped to the fp16 range (lo then carries up to another 65504: |x| < 1.3e5 stays exact to 2^-22, beyond saturates)
@@ -961,7 +964,7 @@ __device__ __forceinline__ void load_norm_weights(const Ctx &c, const float *rms
 }
 
 // `wv`: this thread's norm weights (load_norm_weights), fetched before the grid barrier.
-template <int DT>
+template <int DT, int V>
 __device__ __forceinline__ void stage_vec(Ctx &c, const Args &a, const float *src, int n, const float *rms_w, int embed_token,
                                           const float4 (&wv)[kNormCache]) {
 	constexpr int EP = WTraits<DT>::EP;
@@ -993,14 +996,14 @@ __device__ __forceinline__ void stage_vec(Ctx &c, const Args &a, const float *sr
 			const int e = (c.tid + i * kCT) * 4;
 			if (e < n) {
 				const float4 v = cache[i], w = wv[i];
-				stage_store4<EP>(c, a, e, make_float4(v.x * scale * w.x, v.y * scale * w.y, v.z * scale * w.z, v.w * scale * w.w));
+				stage_store4<EP, V>(c, a, e, make_float4(v.x * scale * w.x, v.y * scale * w.y, v.z * scale * w.z, v.w * scale * w.w));
 				if (seed_x) *reinterpret_cast<float4 *>(x_out + e) = v;
 			}
 		}
 		for (int e = (c.tid + NC * kCT) * 4; e < n; e += kCT * 4) {
 			const float4 v = load_in4<DT>(a, src, embed_token, e);
 			const float4 w = *reinterpret_cast<const float4 *>(rms_w + e);
-			stage_store4<EP>(c, a, e, make_float4(v.x * scale * w.x, v.y * scale * w.y, v.z * scale * w.z, v.w * scale * w.w));
+			stage_store4<EP, V>(c, a, e, make_float4(v.x * scale * w.x, v.y * scale * w.y, v.z * scale * w.z, v.w * scale * w.w));
 			if (seed_x) *reinterpret_cast<float4 *>(x_out + e) = v;
 		}
 	} else {
@@ -1010,10 +1013,10 @@ __device__ __forceinline__ void stage_vec(Ctx &c, const Args &a, const float *sr
 #pragma unroll
 			for (int i = 0; i < 4; ++i) v[i] = __ldcg(reinterpret_cast<const float4 *>(src + e + i * kCT * 4));
 #pragma unroll
-			for (int i = 0; i < 4; ++i) stage_store4<EP>(c, a, e + i * kCT * 4, v[i]);
+			for (int i = 0; i < 4; ++i) stage_store4<EP, V>(c, a, e + i * kCT * 4, v[i]);
 		}
 		for (; e < n; e += kCT * 4)
-			stage_store4<EP>(c, a, e, __ldcg(reinterpret_cast<const float4 *>(src + e)));
+			stage_store4<EP, V>(c, a, e, __ldcg(reinterpret_cast<const float4 *>(src + e)));
 	}
 	cbar();
 }
@@ -1022,7 +1025,7 @@ __device__ __forceinline__ void stage_vec(Ctx &c, const Args &a, const float *sr
 // own elements; round 0 issues all of a batch's loads back to back, later rounds only re-read what is still missing.
 // The CTA barrier in front of the first shared-memory store also ends the previous phase for this CTA (its warps may
 // still be reading c.vec in their tile loops).
-template <int DT>
+template <int DT, int V>
 __device__ __forceinline__ void stage_vec_ll(Ctx &c, const Args &a, const unsigned long long *src, int n, const float *rms_w,
                                              unsigned flag, const float4 (&wv)[kNormCache], long long *probe) {
 	constexpr int EP = WTraits<DT>::EP;
@@ -1083,7 +1086,7 @@ __device__ __forceinline__ void stage_vec_ll(Ctx &c, const Args &a, const unsign
 #pragma unroll
 			for (int i = 0; i < NC; ++i) {
 				const int e = e0 + i * kCT * 4;
-				if (e < n) stage_store4<EP>(c, a, e, cache[i]);
+				if (e < n) stage_store4<EP, V>(c, a, e, cache[i]);
 			}
 		}
 	}
@@ -1103,7 +1106,7 @@ __device__ __forceinline__ void stage_vec_ll(Ctx &c, const Args &a, const unsign
 						ll_load4(src + e, flag, &v); // validated in the first pass
 						w = *reinterpret_cast<const float4 *>(rms_w + e);
 					}
-					stage_store4<EP>(c, a, e, make_float4(v.x * scale * w.x, v.y * scale * w.y, v.z * scale * w.z, v.w * scale * w.w));
+					stage_store4<EP, V>(c, a, e, make_float4(v.x * scale * w.x, v.y * scale * w.y, v.z * scale * w.z, v.w * scale * w.w));
 				}
 			}
 		}
@@ -1261,7 +1264,7 @@ __device__ __forceinline__ float load_resid(const Ctx &c, const Args &a, const E
 }
 
 // Epilogue of row group g: acc[r] = finished dot products of its R rows (valid in every lane); lane t handles output item t.
-template <int DT, int R, bool TP>
+template <int DT, int R, bool TP, int V>
 __device__ __forceinline__ void gemv_epilogue(Ctx &c, const Args &a, Epi &ep, int g, const float (&acc)[R], float resid, unsigned wflag) {
 	constexpr bool LL = YALM_MEGA_LL;  // x: flagged words (tensor parallel: the finished rows, after the exchange at the end of the phase)
 	constexpr bool LLH = YALM_MEGA_LL; // hb (and att_out): flagged too
@@ -1316,7 +1319,7 @@ __device__ __forceinline__ void gemv_epilogue(Ctx &c, const Args &a, Epi &ep, in
 				gt *= ep.scale0[srow], up *= ep.scale1[srow];
 			}
 			gt = a.act == YALM_ACT_GELU ? act_gelu(gt) : act_silu(gt);
-			if (a.w2_pipe) { // pipelined hb: plain fp32 in the w2 tile loop's layout + the slice's completion count
+			if (V == 1) { // pipelined hb: plain fp32 in the w2 tile loop's layout + the slice's completion count
 				if (t < RH) {
 					a.hb[row] = gt * up;
 					a.hbp[xs_slot<EP>((int)row)] = gt * up;
@@ -1439,7 +1442,7 @@ __device__ __forceinline__ void tp_collect(Ctx &c, const Args &a, int kind, int 
 // All row groups of one GEMV phase owned by this CTA; the input vector is already staged in c.vec.
 // Warp w owns groups w, w+8, ... of the CTA's list: it adds up all K-split tiles of the group, shuffle-reduces,
 // and its first lanes run the epilogue.  Nothing here synchronises with the other warps.
-template <int DT, int R, bool TP>
+template <int DT, int R, bool TP, int V>
 __device__ __forceinline__ void gemv_consume(Ctx &c, const Args &a, Epi &ep, int ph) {
 	static_assert(YALM_MEGA_LL || !TP, "tensor parallelism rides on the flagged hand-over");
 	const unsigned wflag = ll_flag(a.seq, ph + 1); // flagged hand-over: the next phase polls for this
@@ -1452,7 +1455,7 @@ __device__ __forceinline__ void gemv_consume(Ctx &c, const Args &a, Epi &ep, int
 	int g_first, NL;
 	my_groups(c, sh.G, &g_first, &NL);
 	const uint32_t base = c.it;
-	const bool pipe_ffn = a.w2_pipe && kind == kFFN; // pipelined hb: this phase produces the slices
+	const bool pipe_ffn = V == 1 && kind == kFFN; // pipelined hb: this phase produces the slices
 	for (int b8 = 0; b8 < NL; b8 += kConsumerWarps) {
 		const int nb = min(kConsumerWarps, NL - b8);
 		if (warp >= nb) break;
@@ -1476,7 +1479,7 @@ __device__ __forceinline__ void gemv_consume(Ctx &c, const Args &a, Epi &ep, int
 		float acc[R];
 #pragma unroll
 		for (int r = 0; r < R; ++r) acc[r] = warp_sum(acc2[r].x + acc2[r].y);
-		gemv_epilogue<DT, R, TP>(c, a, ep, g, acc, resid, wflag);
+		gemv_epilogue<DT, R, TP, V>(c, a, ep, g, acc, resid, wflag);
 	}
 	if (TP && (kind == kWO || (kind == kW2 && ep.sub + 1 == ep.n_sub))) tp_collect<R>(c, a, kind, g_first, NL, wflag, ph);
 	c.it = base + (uint32_t)(NL * sh.nk);
@@ -1556,7 +1559,7 @@ __device__ __forceinline__ void w2_pipe_consume(Ctx &c, const Args &a, Epi &ep, 
 			float acc[R];
 #pragma unroll
 			for (int r = 0; r < R; ++r) acc[r] = warp_sum(acc2[0][r].x + acc2[0][r].y);
-			gemv_epilogue<DT, R, TP>(c, a, ep, g_first + (warp + W * j) * c.ncta, acc, resid[0], wflag);
+			gemv_epilogue<DT, R, TP, 1>(c, a, ep, g_first + (warp + W * j) * c.ncta, acc, resid[0], wflag);
 		}
 		rotate();
 	}
@@ -1715,21 +1718,23 @@ __device__ __forceinline__ void mma_consume(Ctx &c, const Args &a, Epi &ep, int 
 	c.it = base + (uint32_t)(mp.ntiles * mp.nkb);
 }
 
-template <int DT, bool TP>
+// Kernel variant V (compile time: the default kernel carries none of the optional paths — with all of them in one kernel it
+// had 60 % more code and its instruction-cache hit rate fell from 94 to 91 %): 0 = flagged hand-over everywhere, SIMT tile
+// loops; 1 = pipelined hb; 2 = tensor-core GEMV.  Same-box A/B of variant 0 against the kernel before these paths existed:
+// 329.3 / 329.8 vs 329.4 / 328.7 tok/s.
+template <int DT, bool TP, int V>
 __device__ __forceinline__ void gemv_phase(Ctx &c, const Args &a, Epi &ep, int ph) {
-	if constexpr (DT == YALM_F16 && !TP) {
-		if (a.mma) {
-			mma_consume<DT, TP>(c, a, ep, ph);
-			return;
-		}
+	if constexpr (V == 2) {
+		mma_consume<DT, TP>(c, a, ep, ph);
+	} else {
+		const int R = a.shape[ep.kind][0];
+		if (V == 1 && ep.kind == kW2) { // plan(): R <= 2
+			if (R == 2) w2_pipe_consume<DT, 2, TP>(c, a, ep, ph);
+			else w2_pipe_consume<DT, 1, TP>(c, a, ep, ph);
+		} else if (R == 4) gemv_consume<DT, 4, TP, V>(c, a, ep, ph);
+		else if (R == 2) gemv_consume<DT, 2, TP, V>(c, a, ep, ph);
+		else gemv_consume<DT, 1, TP, V>(c, a, ep, ph);
 	}
-	const int R = a.shape[ep.kind][0];
-	if (a.w2_pipe && ep.kind == kW2) { // plan(): R <= 2
-		if (R == 2) w2_pipe_consume<DT, 2, TP>(c, a, ep, ph);
-		else w2_pipe_consume<DT, 1, TP>(c, a, ep, ph);
-	} else if (R == 4) gemv_consume<DT, 4, TP>(c, a, ep, ph);
-	else if (R == 2) gemv_consume<DT, 2, TP>(c, a, ep, ph);
-	else gemv_consume<DT, 1, TP>(c, a, ep, ph);
 }
 
 // ---- attention --------------------------------------------------------------------------------------------
@@ -2217,7 +2222,7 @@ __device__ __forceinline__ void derive_ring(int pos, int max_seq_len, int *kv_si
 }
 
 // ---- the kernel -----------------------------------------------------------------------------------------
-template <int DT, int HD, int G, bool TP>
+template <int DT, int HD, int G, bool TP, int V>
 __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_constant__ Args a) {
 	using T = WTraits<DT>;
 	constexpr int B = T::BYTES;
@@ -2248,11 +2253,11 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_c
 			mbar_init(sm_empty0() + 8 * i, 1);
 			sm_rel()[i] = 0;
 		}
-		for (int i = 0; i < kHbBufs; ++i) {
+		for (int i = 0; V == 1 && i < kHbBufs; ++i) {
 			mbar_init(sm_hbfull0() + 8 * i, 1);
 			mbar_init(sm_hbempty0() + 8 * i, kConsumerWarps);
 		}
-		for (int i = 0; i < kMmaSlots; ++i) {
+		for (int i = 0; V == 2 && i < kMmaSlots; ++i) {
 			mbar_init(sm_mma_done0() + 8 * i, kConsumerWarps);
 			mbar_init(sm_mma_free0() + 8 * i, 1);
 		}
@@ -2272,7 +2277,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_c
 		// ================================ producers ================================
 		// (the L2 look-ahead experiment does not know about expert-indirect rows: off for MoE)
 		Producer p{c, (a.debug & 8) ? 0ull : policy_evict_first(), min(c.S, 32), (a.debug & 8) || a.n_experts > 0 ? 0 : abs(a.l2_ahead), a.l2_ahead > 0, (a.debug & 16) != 0};
-		p.run(a, HD, B);
+		p.template run<V>(a, HD, B);
 		return;
 	}
 
@@ -2319,8 +2324,8 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_c
 			break;
 		default: ep.kind = kLM, ep.scale0 = a.wcls_scale, ep.best_v = -FLT_MAX, ep.best_i = 0x7fffffff; break;
 		}
-		if (a.w2_pipe && k == 3) hb_setup(a, c); // pipelined hb: ordered before the tile loop by the staging step's CTA barriers
-		if (a.w2_pipe && k == 4) {
+		if (V == 1 && k == 3) hb_setup(a, c); // pipelined hb: ordered before the tile loop by the staging step's CTA barriers
+		if (V == 1 && k == 4) {
 			// pipelined hb: nothing to stage — the slices of hb arrive by bulk copy, each awaited where it is needed
 		} else if (flagged) {
 			if (YALM_MEGA_LL_ATTN && k == 2) { // distributed attention combine of this CTA's head slice (flags of phase ph - 1)
@@ -2333,9 +2338,9 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_c
 			const unsigned long long *lsrc = k == 2 ? a.ll_att : k == 3 ? a.ll_x : k == 4 ? a.ll_hb : a.ll_x + (size_t)kLLRep * a.dim;
 			lsrc += (size_t)(c.cta % kLLRep) * (k == 4 ? a.hb_len : n); // this CTA's replica
 			if (k == 4) lsrc += (size_t)sub * n;
-			stage_vec_ll<DT>(c, a, lsrc, n, rms, rflag, wv, c.prof ? c.prof + ((size_t)l * kProfPhases + k) * kProfSlots : nullptr);
+			stage_vec_ll<DT, V>(c, a, lsrc, n, rms, rflag, wv, c.prof ? c.prof + ((size_t)l * kProfPhases + k) * kProfSlots : nullptr);
 		} else {
-			stage_vec<DT>(c, a, src, n, rms, ph == 0 ? sm_misc()[kMiscToken] : -1, wv);
+			stage_vec<DT, V>(c, a, src, n, rms, ph == 0 ? sm_misc()[kMiscToken] : -1, wv);
 		}
 		if (moe && k == 3) moe_router<DT>(c, a, L, l); // on the vector just staged; releases the producer's w1/w3 and w2 tiles
 		stamp(c, l, k, 2);
@@ -2350,7 +2355,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_c
 				*ptr = __floats2half2_rn(v.x, v.y);
 			}
 		}
-		gemv_phase<DT, TP>(c, a, ep, ph);
+		gemv_phase<DT, TP, V>(c, a, ep, ph);
 		stamp(c, l, k, 3);
 	}
 	if (a.mode == kGreedy) {
@@ -2436,19 +2441,25 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_c
 		}
 		sm_misc()[0] = last ? 1 : 0;
 	}
-	if (a.w2_pipe) { // the last CTA out zeroes the hb slice counters for the next launch
+	if (V == 1) { // the last CTA out zeroes the hb slice counters for the next launch
 		cbar();
 		if (sm_misc()[0])
 			for (int i = c.tid; i < a.n_layers * kHbMaxSlices; i += kCT) a.hb_cnt[i] = 0;
 	}
 }
 
-// (head_dim, q heads per kv head) combinations compiled; others use the per-op kernel path.
-template <int DT>
+// (head_dim, q heads per kv head) combinations compiled; others use the per-op kernel path.  V: kernel variant (gemv_phase);
+// the optional variants exist for one GPU only.
+template <int DT, int V>
 inline const void *kernel_for(int head_dim, int g, bool tp) {
+	if (V != 0 && tp) return nullptr;
 #define YALM_MEGA_CASE(HD, GG)                                                                                \
-	if (head_dim == HD && g == GG)                                                                            \
-		return tp ? (const void *)decode_mega_kernel<DT, HD, GG, true> : (const void *)decode_mega_kernel<DT, HD, GG, false>;
+	if (head_dim == HD && g == GG) {                                                                          \
+		if constexpr (V == 0) {                                                                               \
+			if (tp) return (const void *)decode_mega_kernel<DT, HD, GG, true, 0>;                             \
+		}                                                                                                     \
+		return (const void *)decode_mega_kernel<DT, HD, GG, false, V>;                                        \
+	}
 	YALM_MEGA_CASE(128, 4) YALM_MEGA_CASE(128, 8) YALM_MEGA_CASE(64, 4) YALM_MEGA_CASE(32, 4) YALM_MEGA_CASE(32, 2)
 #undef YALM_MEGA_CASE
 	return nullptr;

@@ -1,0 +1,11 @@
+// decode_mega_kernel instantiations for YALM_F32 weights, variant 1: pipelined hb (decode_mega.cuh "pipelined hb").
+#include "decode_mega.cuh"
+
+namespace yalm {
+namespace mega {
+const void *kernel_f32_pipe(int head_dim, int g, bool tp) {
+	set_fault_pointers(fault_record(), fault_timeout_cycles());
+	return kernel_for<YALM_F32, 1>(head_dim, g, tp);
+}
+} // namespace mega
+} // namespace yalm
