@@ -273,6 +273,13 @@ int yalm_tp_shard_plan(const int *dims, int tensor, int rank, int size, long lon
  * yalm_mega_attn_split: out5 = {kv head, first CTA of the head, CTAs of the head, first chunk, chunks} of CTA `cta` for a
  * context of `n_chunks` KV row chunks per head.  Both return YALM_EINVAL for shapes the kernel does not take. */
 int yalm_mega_tile_plan(int dtype, int dim, int q_dim, int kv_dim, int hidden, int vocab, int *out20);
+/* Tensor-core GEMV geometry (decode_mega.cuh "tensor-core GEMV"): out4 = {rows per tile, first row, rows, tiles} of CTA `cta`
+ * of `grid` for a matrix of `rows` rows partitioned in units of `unit` rows with tiles of at most `cap` rows.
+ * yalm_mega_hb_share (pipelined hb): the number of hb elements of slice `slice` (slice_elems elements each) that CTA `cta`
+ * produces when the w1/w3 phase has `groups` row groups of rows_per_group rows, group g on CTA (rotation + g) % grid;
+ * negative = YALM_EINVAL. */
+int yalm_mega_mma_plan(int rows, int unit, int cap, int grid, int cta, int *out4);
+int yalm_mega_hb_share(int groups, int rows_per_group, int slice_elems, int grid, int cta, int rotation, int slice);
 int yalm_mega_attn_split(int cta, int ncta, int n_kv_heads, int n_chunks, int *out5);
 
 /* The CLI's tokenizer (greedy longest-prefix match + byte fallback, src/tokenizer.cpp:57-94; decode_one :44-55) over an

@@ -98,3 +98,53 @@ def test_attention_split_rejects_bad_arguments():
     assert f(148, 148, 8, 4, out) != 0
     assert f(0, 148, 8, 0, out) != 0
     assert f(0, 148, 8, 4, None) != 0
+
+
+# ---- tensor-core GEMV geometry and pipelined-hb shares (decode_mega.cuh: mma_block / mma_box_rows / hb_share) -----------------
+def mma_plan(rows, unit, cap, grid, cta):
+    out = (C.c_int * 4)()
+    rc = api.lib().yalm_mega_mma_plan(rows, unit, cap, grid, cta, out)
+    return rc, tuple(out[:])
+
+
+@pytest.mark.parametrize("name,grid", [("mistral-7b", 148), ("mistral-7b", 128), ("llama-3-70b", 148), ("llama-3.2-1b", 148)])
+def test_tensor_core_tiles_cover_every_row_once_and_fit_a_stage(name, grid):
+    arch = yf.ARCHS[name]
+    q, kv = arch.n_heads * arch.head_dim, arch.n_kv_heads * arch.head_dim
+    # (rows, unit, cap): pairs of rows in tiles of <= 16; w1 / w3: single rows of each in tiles of <= 8 + 8
+    for rows, unit, cap in [(q, 2, 16), (kv, 2, 16), (arch.dim, 2, 16), (arch.hidden_dim, 1, 8), (arch.vocab_size, 2, 16)]:
+        nxt, mts, over = 0, set(), 0
+        for cta in range(grid):
+            rc, (mt, row0, nrows, nt) = mma_plan(rows, unit, cap, grid, cta)
+            assert rc == 0
+            assert row0 == nxt and nrows % unit == 0          # contiguous blocks, whole units
+            assert nt == -(-nrows // mt) and (nt - 1) * mt < nrows <= nt * mt or nrows == 0
+            nxt += nrows
+            mts.add(mt)
+            over += nt * mt - nrows                           # rows fetched twice (they belong to the next CTA)
+        assert nxt == rows and len(mts) == 1
+        mt = mts.pop()
+        assert cap // 2 <= mt <= cap or mt == min(cap, -(-rows // unit // grid) * unit)
+        stage = 4 * mt * 128 * (2 if unit == 1 else 1)        # 4 column blocks of 128 bytes per row; w1 / w3: two boxes, second at +4096
+        assert stage <= STAGE_BYTES and (unit != 1 or 4 * mt * 128 <= 4096)
+        if rows // grid >= cap:                               # blocks of at least one full tile: over-fetch stays small
+            assert over <= 0.08 * rows, (rows, mt, over)      # (Mistral-7B on 148 CTAs: ~1 %; wk / wv blocks of 6-8 rows: 16 %)
+    assert mma_plan(4096, 2, 16, 148, 148)[0] != 0 and mma_plan(4095, 2, 16, 148, 0)[0] != 0
+
+
+@pytest.mark.parametrize("name,dt,tp", [("mistral-7b", "fp16", 1), ("llama-3-70b", "fp16", 1), ("mistral-7b", "fp8", 1)])
+def test_pipelined_hb_shares_add_up_to_the_slices(name, dt, tp):
+    """Every slice of hb (one K split of w2) is complete when the per-CTA shares the w1/w3 epilogues count down add up to the
+    slice: for every rotation of the row-group -> CTA map."""
+    arch, dtype = yf.ARCHS[name], api.DTYPE_OF[dt]
+    rc, sh = tile_plan(dtype, *local_dims(arch, tp))
+    assert rc == 0
+    rh, groups = max(1, int(sh[2][0]) // 2), int(sh[2][3])     # w1/w3: rows of hb per group, row groups
+    kt, nk = int(sh[3][1]), int(sh[3][2])                      # w2: columns per tile = slice, K splits
+    assert nk >= 2 and kt * nk == arch.hidden_dim // tp and groups * rh == arch.hidden_dim // tp
+    grid = 148
+    for rot in (0, 1, 57, 147):
+        for s in range(nk):
+            total = sum(api.lib().yalm_mega_hb_share(groups, rh, kt, grid, cta, rot, s) for cta in range(grid))
+            assert total == kt, (rot, s, total)
+    assert api.lib().yalm_mega_hb_share(groups, rh, kt, grid, grid, 0, 0) < 0

@@ -33,7 +33,7 @@ SYMBOLS = [
     "yalm_profile_ffn", "yalm_sample_advance", "yalm_sample_device1", "yalm_token_probs", "yalm_sample_host",
     "yalm_token_probs_host", "yalm_gemm_f16", "yalm_gemm_glu_f16", "yalm_attn_prefill", "yalm_gemm_host",
     "yalm_model_batch_capacity", "yalm_forward_batch", "yalm_generate", "yalm_state_debug_set_launch_seq", "yalm_tokenize", "yalm_detokenize",
-    "yalm_tp_unique_id", "yalm_tp_init", "yalm_tp_finalize", "yalm_tp_shard_plan", "yalm_mega_tile_plan", "yalm_mega_attn_split", "yalm_error_string", "yalm_version",
+    "yalm_tp_unique_id", "yalm_tp_init", "yalm_tp_finalize", "yalm_tp_shard_plan", "yalm_mega_tile_plan", "yalm_mega_attn_split", "yalm_mega_mma_plan", "yalm_mega_hb_share", "yalm_error_string", "yalm_version",
 ]
 
 

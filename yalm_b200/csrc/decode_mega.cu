@@ -207,15 +207,7 @@ Plan plan(int dtype, int dim, int q_dim, int kv_dim, int head_dim, int hidden, i
 		                 hidden % kMmaKCols == 0 && q_dim % 2 == 0 && kv_dim % 2 == 0 && dim % 2 == 0 && vocab % 2 == 0;
 		if (can && (e ? atoi(e) != 0 : false)) {
 			p.mma = 1;
-			auto box_rows = [&](int rows, int unit, int cap) { // largest block of one matrix's rows per CTA -> rows per tile
-				const int per = ((rows / unit + p.grid - 1) / p.grid) * unit; // (in `unit`s: row pairs, or rows of w1 AND w3)
-				int best = std::min(cap, per), waste = 1 << 30;
-				for (int mt = std::min(cap, per); mt >= std::max(unit, cap / 2); mt -= unit) { // least over-fetch, larger tiles on ties
-					const int w = (per + mt - 1) / mt * mt - per;
-					if (w < waste) waste = w, best = mt;
-				}
-				return best;
-			};
+			auto box_rows = [&](int rows, int unit, int cap) { return mma_box_rows(rows, unit, cap, p.grid); };
 			p.mma_mt[0] = box_rows(q_dim, 2, 16), p.mma_mt[1] = box_rows(kv_dim, 2, 16), p.mma_mt[2] = box_rows(dim, 2, 16);
 			p.mma_mt[3] = box_rows(hidden, 1, 8), p.mma_mt[4] = box_rows(dim, 2, 16), p.mma_mt[5] = box_rows(vocab, 2, 16);
 			vf += kMmaSlots * kConsumerWarps * 16; // the tiles' per-warp partial sums live behind the input vector
@@ -228,7 +220,7 @@ Plan plan(int dtype, int dim, int q_dim, int kv_dim, int head_dim, int hidden, i
 	// force it on (where the shape allows) / off.
 	{
 		const char *e = getenv("YALM_MEGA_W2_PIPE");
-		const int nk = p.shape[kW2][2], groups = (p.shape[kW2][3] + di.sms - 1) / std::max(1, di.sms);
+		const int nk = p.shape[kW2][2], groups = (p.shape[kW2][3] + p.grid - 1) / std::max(1, p.grid); // row groups of w2 per CTA
 		const int hb_off = std::max(padded(dim, ep), padded(q_dim, ep)), vf_pipe = hb_off + kHbBufs * p.shape[kW2][1];
 		const bool can = !p.mma && !tp && n_experts == 0 && nk >= 2 && nk <= kHbMaxSlices && p.shape[kW2][0] <= 2 &&
 		                 (groups + kConsumerWarps - 1) / kConsumerWarps <= kHbMaxGroups && stages_for(vf_pipe) >= 2;
@@ -297,6 +289,21 @@ extern "C" int yalm_mega_tile_plan(int dtype, int dim, int q_dim, int kv_dim, in
 	for (int k = 0; k < 5; ++k)
 		for (int j = 0; j < 4; ++j) out20[4 * k + j] = shape[k][j];
 	return 0;
+}
+extern "C" int yalm_mega_mma_plan(int rows, int unit, int cap, int grid, int cta, int *out4) {
+	if (!out4 || rows < 1 || unit < 1 || cap < unit || rows % unit || grid < 1 || cta < 0 || cta >= grid) return YALM_EINVAL;
+	int row0, nrows;
+	yalm::mega::mma_block(cta, grid, rows, unit, &row0, &nrows);
+	const int mt = yalm::mega::mma_box_rows(rows, unit, cap, grid);
+	out4[0] = mt, out4[1] = row0, out4[2] = nrows, out4[3] = (nrows + mt - 1) / mt;
+	return 0;
+}
+extern "C" int yalm_mega_hb_share(int groups, int rows_per_group, int slice_elems, int grid, int cta, int rotation, int slice) {
+	if (groups < 1 || rows_per_group < 1 || slice_elems < rows_per_group || slice_elems % rows_per_group || grid < 1 || cta < 0 || cta >= grid ||
+	    rotation < 0 || rotation >= grid || slice < 0)
+		return YALM_EINVAL;
+	const int g_first = (cta - rotation + grid) % grid, NL = g_first < groups ? (groups - g_first + grid - 1) / grid : 0;
+	return yalm::mega::hb_share(g_first, NL, grid, slice_elems / rows_per_group, rows_per_group, slice);
 }
 extern "C" int yalm_mega_attn_split(int cta, int ncta, int n_kv_heads, int n_chunks, int *out5) {
 	if (!out5 || ncta < 1 || cta < 0 || cta >= ncta || n_kv_heads < 1 || n_kv_heads > ncta || n_chunks < 1) return YALM_EINVAL;

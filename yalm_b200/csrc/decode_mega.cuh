@@ -498,6 +498,24 @@ __device__ __forceinline__ bool attn_has_unit(int r, int nc, int nch) {
 // (in units of 2 rows — RoPE and store pairs — or of 1 row of w1 AND of w3), cut into tiles of at most MT rows (MT = the
 // tensor map's box rows, planned so that the largest block splits evenly: 28 rows -> 2 x 14); a tile's K is walked in
 // stages of kMmaKCols columns.  Ring order: tile after tile, K stages inside; stage s of the phase belongs to warp s % W.
+// Block of a matrix's rows owned by CTA `cta`: units of `unit` rows, split as evenly as integer division allows.
+__host__ __device__ inline void mma_block(int cta, int ncta, int rows, int unit, int *row0, int *nrows) {
+	const int n = rows / unit;
+	const int u0 = (int)((long long)cta * n / ncta), u1 = (int)((long long)(cta + 1) * n / ncta);
+	*row0 = u0 * unit, *nrows = (u1 - u0) * unit;
+}
+// Rows per tile (= box rows of the matrix's tensor map) for the largest block of `rows` rows over `grid` CTAs: at most `cap`,
+// at least cap / 2, the value with the least over-fetch in a CTA's last tile (larger tiles on ties).
+__host__ __device__ inline int mma_box_rows(int rows, int unit, int cap, int grid) {
+	const int per = ((rows / unit + grid - 1) / grid) * unit;
+	const int hi = cap < per ? cap : per, lo = unit > cap / 2 ? unit : cap / 2;
+	int best = hi, waste = 1 << 30;
+	for (int mt = hi; mt >= lo; mt -= unit) {
+		const int w = (per + mt - 1) / mt * mt - per;
+		if (w < waste) waste = w, best = mt;
+	}
+	return best;
+}
 struct MmaSub {
 	int map;        // tensor map record
 	int row0, nrows; // this CTA's rows of the matrix
@@ -514,9 +532,8 @@ __device__ __forceinline__ MmaPhase mma_phase(const Args &a, int kind, int layer
 	p.nsub = 1, p.ffn = false, p.nkb = a.dim / kMmaKCols;
 	const int mb = layer * kMmPerLayer;
 	auto set = [&](int i, int map, int rows, int unit, int MT, int goff) {
-		const int n = rows / unit;
-		const int u0 = (int)((long long)cta * n / ncta), u1 = (int)((long long)(cta + 1) * n / ncta);
-		p.sub[i].map = map, p.sub[i].row0 = u0 * unit, p.sub[i].nrows = (u1 - u0) * unit;
+		mma_block(cta, ncta, rows, unit, &p.sub[i].row0, &p.sub[i].nrows);
+		p.sub[i].map = map;
 		p.sub[i].MT = MT, p.sub[i].nt = (p.sub[i].nrows + MT - 1) / MT, p.sub[i].goff = goff;
 	};
 	p.sub[1].nt = p.sub[2].nt = 0;
@@ -1148,6 +1165,14 @@ __device__ __forceinline__ void hb_count(const Args &a, int layer, int slice) {
 		asm volatile("red.relaxed.gpu.global.add.u32 [%0], %1;" ::"l"(a.hb_cnt + (size_t)layer * kHbMaxSlices + slice), "r"(cnt[kHbMaxSlices]) : "memory");
 	}
 }
+// hb elements of slice s that come from a CTA whose row groups are g_first, g_first + ncta, ... (NL of them, RH rows each);
+// gps = row groups per slice.
+__host__ __device__ inline int hb_share(int g_first, int NL, int ncta, int gps, int RH, int s) {
+	const int lo = s * gps, hi = (s + 1) * gps; // groups below x owned by the CTA: 0 if x <= g_first, else ceil((x - g_first) / ncta) capped at NL
+	int b_lo = lo <= g_first ? 0 : (lo - g_first + ncta - 1) / ncta, b_hi = hi <= g_first ? 0 : (hi - g_first + ncta - 1) / ncta;
+	b_lo = b_lo < NL ? b_lo : NL, b_hi = b_hi < NL ? b_hi : NL;
+	return (b_hi - b_lo) * RH;
+}
 // Start of the w1/w3 phase (in front of its staging step's CTA barriers): thread s < slices sets up slice s — how many hb
 // elements this CTA's row groups g_first, g_first + ncta, ... (NL of them, RH rows each) contribute to it.
 __device__ __forceinline__ void hb_setup(const Args &a, const Ctx &c) {
@@ -1156,9 +1181,7 @@ __device__ __forceinline__ void hb_setup(const Args &a, const Ctx &c) {
 	const int RH = max(1, a.shape[kFFN][0] / 2);
 	int g_first, NL;
 	my_groups(c, a.shape[kFFN][3], &g_first, &NL);
-	const int gps = a.hb_slice / RH; // row groups per slice
-	auto below = [&](int x) { return x <= g_first ? 0 : min(NL, (x - g_first + c.ncta - 1) / c.ncta); }; // this CTA's groups below group x
-	const int n = (below((s + 1) * gps) - below(s * gps)) * RH;
+	const int n = hb_share(g_first, NL, c.ncta, a.hb_slice / RH, RH, s);
 	sm_hb_cnt()[s] = n, sm_hb_cnt()[kHbMaxSlices + s] = n;
 	sm_hb_issued()[s] = 0;
 }
