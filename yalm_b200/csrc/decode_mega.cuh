@@ -18,6 +18,10 @@
 // 699-888): ~323 kernel nodes -> 1 launch.  Arithmetic (fp32 accumulate, formulas, clip/rope/softmax
 // definitions) follows the CPU reference exactly as the per-op kernels do (gemv.cuh, ops_attn.cu).
 //
+// Kernel variants (template parameter V, one translation unit each, chosen by mega::plan): 0 = as described above; 1 = hb
+// travels w1/w3 -> w2 slice by slice through bulk copies ("pipelined hb" below: shared memory for ring stages on wide models);
+// 2 = the GEMV phases on the tensor cores ("tensor-core GEMV" below: an experiment, opt-in).
+//
 // Code size matters here: the per-layer instruction footprint has to stay inside the SM's instruction cache
 // (every phase body runs once per layer), so every phase body has exactly ONE call site (the phase loops below).
 // They are force-inlined all the same: a __noinline__ callee taking Ctx& forces the whole context struct into
